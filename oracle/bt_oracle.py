@@ -1,0 +1,146 @@
+"""Torch-CPU restatement of the reference's variational-layer arithmetic.
+
+TEST INFRASTRUCTURE ONLY (see oracle/__init__.py).  Every function cites the
+reference lines (relative to /root/reference/bayesian_torch/) it follows.  All
+functions are pure: eps / sign tensors are inputs, never drawn here, so the
+same tensors can be fed to the CUDA path.  ``dtype=torch.float64`` gives a
+higher-precision answer for tolerance studies; the reference computes in fp32.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional, Sequence, Tuple
+
+import torch
+import torch.nn.functional as F
+
+__all__ = [
+    "softplus_ref", "kl_normal", "kl_normal_from_rho", "sample_weight",
+    "linear_reparam", "conv_reparam", "linear_flipout", "conv_flipout",
+    "get_rho", "mc_moments", "predictive_entropy", "mutual_information",
+]
+
+
+def _c(t, dtype):
+    return None if t is None else t.to("cpu", dtype)
+
+
+def softplus_ref(rho: torch.Tensor) -> torch.Tensor:
+    """sigma = log1p(exp(rho)), un-stabilised exactly as the reference writes it
+    (layers/variational_layers/linear_variational.py:163)."""
+    return torch.log1p(torch.exp(rho))
+
+
+def kl_normal(mu_q, sigma_q, mu_p, sigma_p) -> torch.Tensor:
+    """Element-wise KL(N(mu_q,sigma_q) || N(mu_p,sigma_p)) then .mean()
+    (layers/base_variational_layer.py:70-72).  mu_p / sigma_p may be python
+    scalars or tensors broadcastable to mu_q."""
+    mu_p = torch.as_tensor(mu_p, dtype=mu_q.dtype)
+    sigma_p = torch.as_tensor(sigma_p, dtype=mu_q.dtype)
+    kl = (torch.log(sigma_p) - torch.log(sigma_q)
+          + (sigma_q ** 2 + (mu_q - mu_p) ** 2) / (2 * (sigma_p ** 2)) - 0.5)
+    return kl.mean()
+
+
+def kl_normal_from_rho(mu, rho, mu_b=None, rho_b=None, prior_mu=0.0,
+                       prior_sigma=1.0, dtype=torch.float32) -> torch.Tensor:
+    """kl_loss() of a layer: weight mean + bias mean
+    (linear_variational.py:146-158, conv_variational.py:353-360)."""
+    mu, rho, mu_b, rho_b = (_c(t, dtype) for t in (mu, rho, mu_b, rho_b))
+    kl = kl_normal(mu, softplus_ref(rho), prior_mu, prior_sigma)
+    if mu_b is not None:
+        kl = kl + kl_normal(mu_b, softplus_ref(rho_b), prior_mu, prior_sigma)
+    return kl
+
+
+def sample_weight(mu, rho, eps):
+    """w = mu + log1p(exp(rho)) * eps (linear_variational.py:163-166)."""
+    return mu + softplus_ref(rho) * eps
+
+
+def _conv(rank: int):
+    return {1: F.conv1d, 2: F.conv2d, 3: F.conv3d}[rank]
+
+
+def linear_reparam(x, mu_w, rho_w, mu_b, rho_b, eps_w, eps_b, prior_mu=0.0,
+                   prior_sigma=1.0, dtype=torch.float32
+                   ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """LinearReparameterization.forward (linear_variational.py:160-204)."""
+    x, mu_w, rho_w, mu_b, rho_b, eps_w, eps_b = (
+        _c(t, dtype) for t in (x, mu_w, rho_w, mu_b, rho_b, eps_w, eps_b))
+    w = sample_weight(mu_w, rho_w, eps_w)
+    b = None if mu_b is None else sample_weight(mu_b, rho_b, eps_b)
+    out = F.linear(x, w, b)
+    return out, kl_normal_from_rho(mu_w, rho_w, mu_b, rho_b, prior_mu, prior_sigma, dtype)
+
+
+def conv_reparam(x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b, stride=1, padding=0,
+                 dilation=1, groups=1, prior_mu=0.0, prior_sigma=1.0,
+                 dtype=torch.float32) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Conv{1,2,3}dReparameterization.forward (conv_variational.py:197-231,
+    362-407, 785-819); the rank comes from the kernel tensor."""
+    x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b = (
+        _c(t, dtype) for t in (x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b))
+    w = sample_weight(mu_k, rho_k, eps_k)
+    b = None if mu_b is None else sample_weight(mu_b, rho_b, eps_b)
+    out = _conv(mu_k.dim() - 2)(x, w, b, stride, padding, dilation, groups)
+    return out, kl_normal_from_rho(mu_k, rho_k, mu_b, rho_b, prior_mu, prior_sigma, dtype)
+
+
+def linear_flipout(x, mu_w, rho_w, mu_b, rho_b, eps_w, eps_b, sign_in, sign_out,
+                   prior_mu=0.0, prior_sigma=1.0, dtype=torch.float32):
+    """LinearFlipout.forward (flipout_layers/linear_flipout.py:145-197):
+    out = x.mu^T + mu_b + ((x*s_in).(sigma*eps)^T + sigma_b*eps_b) * s_out."""
+    x, mu_w, rho_w, mu_b, rho_b, eps_w, eps_b, sign_in, sign_out = (
+        _c(t, dtype) for t in (x, mu_w, rho_w, mu_b, rho_b, eps_w, eps_b, sign_in, sign_out))
+    delta_w = softplus_ref(rho_w) * eps_w
+    delta_b = None if mu_b is None else softplus_ref(rho_b) * eps_b
+    mean_path = F.linear(x, mu_w, mu_b)
+    pert = F.linear(x * sign_in, delta_w, delta_b)
+    out = mean_path + pert * sign_out
+    return out, kl_normal_from_rho(mu_w, rho_w, mu_b, rho_b, prior_mu, prior_sigma, dtype)
+
+
+def conv_flipout(x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b, sign_in, sign_out,
+                 stride=1, padding=0, dilation=1, groups=1, prior_mu=0.0,
+                 prior_sigma=1.0, dtype=torch.float32):
+    """Conv2dFlipout.forward (flipout_layers/conv_flipout.py:370-439)."""
+    x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b, sign_in, sign_out = (
+        _c(t, dtype) for t in (x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b, sign_in, sign_out))
+    conv = _conv(mu_k.dim() - 2)
+    delta_k = softplus_ref(rho_k) * eps_k
+    delta_b = None if mu_b is None else softplus_ref(rho_b) * eps_b
+    mean_path = conv(x, mu_k, mu_b, stride, padding, dilation, groups)
+    pert = conv(x * sign_in, delta_k, delta_b, stride, padding, dilation, groups)
+    out = mean_path + pert * sign_out
+    return out, kl_normal_from_rho(mu_k, rho_k, mu_b, rho_b, prior_mu, prior_sigma, dtype)
+
+
+def get_rho(w: torch.Tensor, delta: float) -> torch.Tensor:
+    """MOPED rho init: log(expm1(delta*|w|) + 1e-20) (utils/util.py:63-69)."""
+    return torch.log(torch.expm1(delta * torch.abs(w)) + 1e-20)
+
+
+def mc_moments(logits: torch.Tensor, softmax: bool = True):
+    """Predictive mean / variance over the S axis of [S,B,C] logits.  The mean
+    of softmax is what evaluate() forms
+    (examples/main_bayesian_cifar_dnn2bnn.py:545,554-556); variance is
+    E[p^2]-E[p]^2 (population), the quantity the multi-GPU path all-reduces."""
+    p = torch.softmax(logits.double(), dim=-1) if softmax else logits.double()
+    mean = p.mean(0)
+    var = (p * p).mean(0) - mean * mean
+    return mean, var
+
+
+def predictive_entropy(probs: torch.Tensor) -> torch.Tensor:
+    """Entropy of the mean predictive distribution (utils/util.py:41-52);
+    probs is [S,B,C]."""
+    m = probs.double().mean(0)
+    return -(m * torch.log(m + 1e-15)).sum(-1)
+
+
+def mutual_information(probs: torch.Tensor) -> torch.Tensor:
+    """H[mean p] - mean H[p] (utils/util.py:55-60)."""
+    p = probs.double()
+    per_sample = -(p * torch.log(p + 1e-15)).sum(-1)
+    return predictive_entropy(p) - per_sample.mean(0)

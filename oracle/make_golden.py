@@ -1,0 +1,188 @@
+"""Generate tests/golden/*.npz by RUNNING THE REFERENCE ITSELF on CPU.
+
+Run in the build container only (needs /root/reference, read-only):
+    python oracle/make_golden.py
+The GPU box has no /root/reference; tests read the committed .npz files.
+
+Harness-side shims, no edits to the reference:
+  * `termcolor` is imported by conv_variational.py:55 but not installed -> stub;
+  * the fork made `prior_type` a required kl_div argument and only wired it for
+    Linear/Conv2d Reparameterization; for the other layers the forward is run
+    with return_kl=False and KL is computed with the reference's own
+    kl_div(..., 'normal') on the same tensors (= upstream behaviour).
+Each fixture stores inputs (x, mu/rho, eps, signs), outputs (out, kl) and the
+autograd gradients of  L = sum(out*g) + c*kl  w.r.t. x and every parameter.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, "tests", "golden")
+KL_COEF = 0.37
+
+
+def import_reference():
+    stub = types.ModuleType("termcolor")
+    stub.colored = lambda s, *a, **k: s
+    sys.modules.setdefault("termcolor", stub)
+    if "/root/reference" not in sys.path:
+        sys.path.insert(0, "/root/reference")
+    import bayesian_torch.layers as L  # noqa
+    from bayesian_torch.models import dnn_to_bnn as D  # noqa
+    from bayesian_torch.utils import util as U  # noqa
+    return L, D, U
+
+
+def ref_kl(layer):
+    """kl_loss() with 'normal' semantics for every layer class."""
+    w = "mu_weight" if hasattr(layer, "mu_weight") else "mu_kernel"
+    r = w.replace("mu", "rho")
+    kl = layer.kl_div(getattr(layer, w), torch.log1p(torch.exp(getattr(layer, r))),
+                      layer.prior_weight_mu, layer.prior_weight_sigma, "normal")
+    if layer.mu_bias is not None:
+        kl = kl + layer.kl_div(layer.mu_bias, torch.log1p(torch.exp(layer.rho_bias)),
+                               layer.prior_bias_mu, layer.prior_bias_sigma, "normal")
+    return kl
+
+
+def run_case(name, layer, x, flipout=False, seed=0, extra=None):
+    torch.manual_seed(1000 + seed)
+    x = x.clone().requires_grad_(True)
+    torch.manual_seed(2000 + seed)
+    out = layer(x, return_kl=False)
+    kl = ref_kl(layer)
+    g = torch.randn(out.shape, generator=torch.Generator().manual_seed(3000 + seed))
+    loss = (out * g).sum() + KL_COEF * kl
+    params = [p for p in layer.parameters()]
+    grads = torch.autograd.grad(loss, [x] + params)
+    wn = "weight" if hasattr(layer, "mu_weight") else "kernel"
+    d = {
+        "x": x.detach(), "g": g, "out": out.detach(), "kl": kl.detach(),
+        "mu_w": getattr(layer, "mu_" + wn).detach(), "rho_w": getattr(layer, "rho_" + wn).detach(),
+        "eps_w": getattr(layer, "eps_" + wn).detach().clone(),
+        "dx": grads[0],
+    }
+    names = [n for n, _ in layer.named_parameters()]
+    for n, gr in zip(names, grads[1:]):
+        d["d_" + n] = gr
+    if layer.mu_bias is not None:
+        d.update(mu_b=layer.mu_bias.detach(), rho_b=layer.rho_bias.detach(),
+                 eps_b=layer.eps_bias.detach().clone())
+    if flipout:
+        # replay the reference's draw order to recover the sign tensors
+        torch.manual_seed(2000 + seed)
+        if x.dim() == 2 or hasattr(layer, "mu_weight"):
+            # linear_flipout.py:150,162 then :169-170
+            layer.eps_weight.clone().normal_()
+            if layer.mu_bias is not None:
+                layer.eps_bias.clone().normal_()
+            s_in = x.detach().clone().uniform_(-1, 1).sign()
+            s_out = out.detach().clone().uniform_(-1, 1).sign()
+        else:
+            # conv_flipout.py:385-386 then :390,401
+            s_in = x.detach().clone().uniform_(-1, 1).sign()
+            s_out = out.detach().clone().uniform_(-1, 1).sign()
+        d.update(sign_in=s_in, sign_out=s_out)
+    if extra:
+        d.update(extra)
+    np.savez_compressed(os.path.join(OUT, name + ".npz"),
+                        **{k: (v.numpy() if torch.is_tensor(v) else np.asarray(v)) for k, v in d.items()})
+    print(f"{name:34s} out{tuple(out.shape)} kl={float(kl):.6f}")
+
+
+def cfg(**kw):
+    return {"cfg_" + k: np.asarray(v) for k, v in kw.items()}
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    L, D, U = import_reference()
+    torch.manual_seed(0)
+    R = torch.randn
+
+    # ---- LinearReparameterization (linear_variational.py:54) ----
+    run_case("linear_rp_8x5x7_bias", L.LinearReparameterization(5, 7), R(8, 5), seed=1)
+    run_case("linear_rp_33x70x37_nobias", L.LinearReparameterization(70, 37, bias=False), R(33, 70), seed=2)
+    run_case("linear_rp_lead_2x3x16x24", L.LinearReparameterization(16, 24), R(2, 3, 16), seed=3)
+    run_case("linear_rp_128x256x192_prior", L.LinearReparameterization(
+        256, 192, prior_mean=0.3, prior_variance=0.5, posterior_rho_init=-2.0), R(128, 256), seed=4,
+        extra=cfg(prior_mean=0.3, prior_variance=0.5))
+
+    # ---- Conv2dReparameterization (conv_variational.py:234) ----
+    def c2(name, x, seed, **kw):
+        layer = L.Conv2dReparameterization(prior_type="normal", **kw)
+        ex = cfg(stride=kw.get("stride", 1), padding=kw.get("padding", 0), dilation=kw.get("dilation", 1),
+                 groups=kw.get("groups", 1), prior_mean=kw.get("prior_mean", 0), prior_variance=kw.get("prior_variance", 1))
+        run_case(name, layer, x, seed=seed, extra=ex)
+    c2("conv2d_rp_1x1", R(2, 16, 9, 9), 10, in_channels=16, out_channels=24, kernel_size=1)
+    c2("conv2d_rp_3x3_p1", R(3, 8, 12, 12), 11, in_channels=8, out_channels=16, kernel_size=3, padding=1)
+    c2("conv2d_rp_3x3_s2_p1", R(2, 8, 13, 11), 12, in_channels=8, out_channels=12, kernel_size=3, stride=2, padding=1)
+    c2("conv2d_rp_7x7_s2_p3_c3", R(2, 3, 32, 32), 13, in_channels=3, out_channels=16, kernel_size=7, stride=2, padding=3, bias=False)
+    c2("conv2d_rp_groups2", R(2, 8, 10, 10), 14, in_channels=8, out_channels=12, kernel_size=3, padding=1, groups=2)
+    c2("conv2d_rp_dil2", R(2, 4, 14, 14), 15, in_channels=4, out_channels=6, kernel_size=3, padding=2, dilation=2)
+    c2("conv2d_rp_prior", R(2, 4, 8, 8), 16, in_channels=4, out_channels=8, kernel_size=(3, 2), padding=(1, 0),
+       stride=(1, 2), prior_mean=-0.2, prior_variance=2.0)
+    c2("conv2d_rp_64ch", R(2, 64, 14, 14), 17, in_channels=64, out_channels=64, kernel_size=3, padding=1, bias=False)
+
+    # ---- Conv1d / Conv3d Reparameterization (conv_variational.py:68, :650) ----
+    run_case("conv1d_rp_k3", L.Conv1dReparameterization(6, 10, 3, stride=2, padding=1), R(3, 6, 25), seed=20,
+             extra=cfg(stride=2, padding=1, dilation=1, groups=1))
+    run_case("conv3d_rp_k3", L.Conv3dReparameterization(4, 6, 3, 0, 1, 0, -3.0, stride=1, padding=1), R(2, 4, 6, 7, 5),
+             seed=21, extra=cfg(stride=1, padding=1, dilation=1, groups=1))
+
+    # ---- Flipout (linear_flipout.py:49, conv_flipout.py:247) ----
+    run_case("linear_fo_16x20x12", L.LinearFlipout(20, 12), R(16, 20), flipout=True, seed=30)
+    run_case("linear_fo_nobias", L.LinearFlipout(33, 9, bias=False), R(5, 33), flipout=True, seed=31)
+    run_case("conv2d_fo_3x3", L.Conv2dFlipout(8, 12, 3, padding=1), R(2, 8, 10, 10), flipout=True, seed=32,
+             extra=cfg(stride=1, padding=1, dilation=1, groups=1))
+    run_case("conv2d_fo_s2_nobias", L.Conv2dFlipout(6, 8, 3, stride=2, padding=1, bias=False), R(2, 6, 11, 11),
+             flipout=True, seed=33, extra=cfg(stride=2, padding=1, dilation=1, groups=1))
+
+    # ---- MOPED rho (utils/util.py:63-69) and tensor-valued priors (utils/util.py:101-104) ----
+    w = R(40, 30) * 0.05
+    lay = L.LinearReparameterization(30, 40)
+    lay.mu_weight.data.copy_(w)
+    lay.rho_weight.data.copy_(U.get_rho(w, 0.5))
+    lay.prior_weight_mu = w.clone() * 0.9
+    lay.prior_weight_sigma = torch.rand(40, 30) + 0.5
+    run_case("linear_rp_moped_tensorprior", lay, R(4, 30), seed=40,
+             extra={"moped_w": w, "moped_delta": np.asarray(0.5), "moped_rho": U.get_rho(w, 0.5),
+                    "prior_w_mu": lay.prior_weight_mu, "prior_w_sigma": lay.prior_weight_sigma})
+
+    # ---- dnn_to_bnn + get_kl_loss on a small torch model (models/dnn_to_bnn.py:127-165) ----
+    torch.manual_seed(50)
+    net = torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3, padding=1), torch.nn.ReLU(), torch.nn.Conv2d(8, 8, 3, stride=2, bias=False),
+                              torch.nn.Flatten(), torch.nn.Linear(8 * 3 * 3, 10))
+    dnn_state = {k: v.clone() for k, v in net.state_dict().items()}
+    params = {"prior_mu": 0.0, "prior_sigma": 1.0, "posterior_mu_init": 0.0, "posterior_rho_init": -3.0,
+              "type": "Reparameterization", "moped_enable": True, "moped_delta": 0.5}
+    D.dnn_to_bnn(net, params)
+    for m in net.modules():
+        if hasattr(m, "prior_type"):
+            m.prior_type = "normal"
+    x = R(4, 3, 8, 8)
+    torch.manual_seed(51)
+    y = net(x)
+    kl = D.get_kl_loss(net)
+    d = {"x": x, "out": y.detach(), "kl": kl.detach()}
+    d.update({"dnn_" + k: v for k, v in dnn_state.items()})
+    d.update({"bnn_" + k: v.detach() for k, v in net.state_dict().items()})
+    for i, m in enumerate(net):
+        if hasattr(m, "eps_kernel"):
+            d[f"eps_{i}_w"] = m.eps_kernel.clone()
+        if hasattr(m, "eps_weight"):
+            d[f"eps_{i}_w"] = m.eps_weight.clone()
+        if getattr(m, "eps_bias", None) is not None:
+            d[f"eps_{i}_b"] = m.eps_bias.clone()
+    np.savez_compressed(os.path.join(OUT, "dnn_to_bnn_small.npz"), **{k: v.numpy() for k, v in d.items()})
+    print("dnn_to_bnn_small", tuple(y.shape), float(kl), sorted(net.state_dict().keys()))
+
+
+if __name__ == "__main__":
+    main()

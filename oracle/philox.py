@@ -1,0 +1,85 @@
+"""Numpy restatement of the in-kernel counter-based RNG contract.
+
+TEST INFRASTRUCTURE ONLY (see oracle/__init__.py).  This is not reference
+arithmetic -- the reference draws eps with torch's own generator
+(linear_variational.py:164) -- it is the specification of the stream the CUDA
+kernels generate in registers (csrc/bt_rng.cuh), restated so tests can
+predict it:
+
+  Philox4x32-10, key = (seed_lo, seed_hi),
+  counter = (block_lo, block_hi, sample_id, stream_id)
+  normals : block = elem_idx // 4; Box-Muller on (r0,r1) -> z0,z1 and (r2,r3) -> z2,z3
+            with u = ((r >> 8) + 0.5) * 2^-24
+  signs   : block = elem_idx // 128; bit (elem_idx % 128) of r0|r1<<32|..., 1 -> -1
+  stream_id = layer_id << 4 | kind, kind: 0 eps_weight, 1 eps_bias, 2 sign_in, 3 sign_out
+"""
+from __future__ import annotations
+
+import numpy as np
+
+M0 = np.uint64(0xD2511F53)
+M1 = np.uint64(0xCD9E8D57)
+W0 = 0x9E3779B9
+W1 = 0xBB67AE85
+MASK = np.uint64(0xFFFFFFFF)
+
+KIND_EPS_W, KIND_EPS_B, KIND_SIGN_IN, KIND_SIGN_OUT = 0, 1, 2, 3
+
+
+def stream_id(layer_id: int, kind: int) -> int:
+    return ((layer_id << 4) | kind) & 0xFFFFFFFF
+
+
+def philox4x32_10(c0, c1, c2, c3, k0: int, k1: int):
+    """Vectorised Philox4x32-10; c* are uint32 arrays (broadcastable)."""
+    c0, c1, c2, c3 = (np.asarray(c, dtype=np.uint64) & MASK for c in np.broadcast_arrays(c0, c1, c2, c3))
+    k0 &= 0xFFFFFFFF
+    k1 &= 0xFFFFFFFF
+    for _ in range(10):
+        p0 = M0 * c0
+        p1 = M1 * c2
+        hi0, lo0 = p0 >> np.uint64(32), p0 & MASK
+        hi1, lo1 = p1 >> np.uint64(32), p1 & MASK
+        c0, c1, c2, c3 = (hi1 ^ c1 ^ np.uint64(k0)) & MASK, lo1, (hi0 ^ c3 ^ np.uint64(k1)) & MASK, lo0
+        k0 = (k0 + W0) & 0xFFFFFFFF
+        k1 = (k1 + W1) & 0xFFFFFFFF
+    return tuple(c.astype(np.uint32) for c in (c0, c1, c2, c3))
+
+
+def _split_seed(seed: int):
+    return seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF
+
+
+def normal(n: int, seed: int, sample_id: int, stream: int, start: int = 0) -> np.ndarray:
+    """eps[start:start+n] of the (seed, sample_id, stream) normal stream, float64."""
+    idx = np.arange(start, start + n, dtype=np.uint64)
+    first, last = int(idx[0] // 4) if n else 0, int((start + n + 3) // 4)
+    blocks = np.arange(first, last, dtype=np.uint64)
+    k0, k1 = _split_seed(seed)
+    r = philox4x32_10(blocks & MASK, blocks >> np.uint64(32), np.uint64(sample_id & 0xFFFFFFFF),
+                      np.uint64(stream & 0xFFFFFFFF), k0, k1)
+    u = [((x >> np.uint32(8)).astype(np.float64) + 0.5) * 2.0 ** -24 for x in r]
+    z = np.empty((len(blocks), 4), dtype=np.float64)
+    for j in (0, 2):
+        rad = np.sqrt(-2.0 * np.log(u[j]))
+        ang = 2.0 * np.pi * u[j + 1]
+        z[:, j] = rad * np.cos(ang)
+        z[:, j + 1] = rad * np.sin(ang)
+    z = z.reshape(-1)
+    off = start - first * 4
+    return z[off:off + n]
+
+
+def sign(n: int, seed: int, sample_id: int, stream: int, start: int = 0) -> np.ndarray:
+    """Rademacher +-1 for elements [start, start+n) of the sign stream, float32."""
+    idx = np.arange(start, start + n, dtype=np.uint64)
+    blocks = idx // np.uint64(128)
+    ub, inv = np.unique(blocks, return_inverse=True)
+    k0, k1 = _split_seed(seed)
+    r = philox4x32_10(ub & MASK, ub >> np.uint64(32), np.uint64(sample_id & 0xFFFFFFFF),
+                      np.uint64(stream & 0xFFFFFFFF), k0, k1)
+    words = np.stack(r, axis=1)  # [nblocks, 4]
+    within = (idx % np.uint64(128)).astype(np.int64)
+    w = words[inv, within // 32]
+    bit = (w >> (within % 32).astype(np.uint32)) & np.uint32(1)
+    return np.where(bit == 1, -1.0, 1.0).astype(np.float32)
