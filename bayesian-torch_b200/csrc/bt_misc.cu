@@ -1,0 +1,184 @@
+// Small element-wise / reduction kernels around the layer path: RNG stream export,
+// MOPED rho init, Monte-Carlo predictive reduction.
+#include "bt_common.cuh"
+
+namespace {
+
+__global__ void philox_normal_fill_kernel(float* __restrict__ out, int64_t n, BtRngKey key) {
+  const int64_t nblk = (n + 3) >> 2;
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < nblk; b += (int64_t)gridDim.x * blockDim.x) {
+    const float4 z = bt_normal4((uint64_t)b, key);
+    const int64_t i = b << 2;
+    if (i + 3 < n && ((uintptr_t)out & 15) == 0) {
+      *reinterpret_cast<float4*>(out + i) = z;
+    } else {
+      const float v[4] = {z.x, z.y, z.z, z.w};
+      for (int j = 0; j < 4 && i + j < n; ++j) out[i + j] = v[j];
+    }
+  }
+}
+
+__global__ void philox_sign_fill_kernel(float* __restrict__ out, int64_t n, BtRngKey key) {
+  // one Philox call covers 128 elements; a thread writes the 32 elements of one word
+  const int64_t nwords = (n + 31) >> 5;
+  for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 r = bt_philox((uint64_t)(w >> 2), key);
+    const int q = (int)(w & 3);
+    const uint32_t word = q == 0 ? r.x : (q == 1 ? r.y : (q == 2 ? r.z : r.w));
+    const int64_t i0 = w << 5;
+    for (int j = 0; j < 32 && i0 + j < n; ++j) out[i0 + j] = ((word >> j) & 1u) ? -1.f : 1.f;
+  }
+}
+
+// rho = log(expm1(delta*|w|) + 1e-20)   (utils/util.py:63-69)
+__global__ void moped_rho_kernel(const float* __restrict__ w, float* __restrict__ rho, int64_t n, float delta) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    rho[i] = logf(expm1f(delta * fabsf(w[i])) + 1e-20f);
+}
+
+// One warp per (s, b) row of logits[S,B,C]: softmax in registers/strided passes, then
+// atomically accumulate p, p^2 into [B,C] and sum_c p log p into [B].
+template <typename T>
+__global__ void mc_accumulate_kernel(const T* __restrict__ logits, int64_t S, int64_t B, int64_t C, int softmax,
+                                     float* __restrict__ sum_p, float* __restrict__ sum_p2,
+                                     float* __restrict__ sum_plogp) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  // a warp owns batch row b and loops over s, so the [B,C] accumulators need no atomics
+  for (int64_t b = warp; b < B; b += nwarps) {
+    for (int64_t c0 = 0; c0 < C; c0 += 32 * 8) {  // register tile of 8 columns per lane
+      float ap[8], ap2[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { ap[j] = 0.f; ap2[j] = 0.f; }
+      for (int64_t s = 0; s < S; ++s) {
+        const T* row = logits + (s * B + b) * C;
+        float mx = -INFINITY, den = 1.f;
+        if (softmax) {
+          for (int64_t c = lane; c < C; c += 32) mx = fmaxf(mx, bt_to_float<T>(row[c]));
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+          float d = 0.f;
+          for (int64_t c = lane; c < C; c += 32) d += expf(bt_to_float<T>(row[c]) - mx);
+          den = bt_warp_sum(d);
+        }
+        float plogp = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int64_t c = c0 + lane + 32 * j;
+          if (c < C) {
+            const float v = bt_to_float<T>(row[c]);
+            const float pr = softmax ? expf(v - mx) / den : v;
+            ap[j] += pr;
+            ap2[j] += pr * pr;
+          }
+        }
+        if (sum_plogp && c0 == 0) {  // entropy term needs the whole row: separate strided pass
+          for (int64_t c = lane; c < C; c += 32) {
+            const float v = bt_to_float<T>(row[c]);
+            const float pr = softmax ? expf(v - mx) / den : v;
+            plogp += pr * logf(pr + 1e-15f);
+          }
+          plogp = bt_warp_sum(plogp);
+          if (lane == 0) sum_plogp[b] += plogp;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int64_t c = c0 + lane + 32 * j;
+        if (c < C) {
+          if (sum_p) sum_p[b * C + c] += ap[j];
+          if (sum_p2) sum_p2[b * C + c] += ap2[j];
+        }
+      }
+    }
+  }
+}
+
+__global__ void mc_finalize_kernel(const float* __restrict__ sum_p, const float* __restrict__ sum_p2,
+                                   const float* __restrict__ sum_plogp, float inv_s, int64_t B, int64_t C,
+                                   float* __restrict__ mean, float* __restrict__ var, float* __restrict__ entropy,
+                                   float* __restrict__ mi) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t b = warp; b < B; b += nwarps) {
+    float h = 0.f;
+    for (int64_t c = lane; c < C; c += 32) {
+      const float m = sum_p[b * C + c] * inv_s;
+      if (mean) mean[b * C + c] = m;
+      if (var && sum_p2) var[b * C + c] = fmaxf(sum_p2[b * C + c] * inv_s - m * m, 0.f);
+      h -= m * logf(m + 1e-15f);
+    }
+    h = bt_warp_sum(h);
+    if (lane == 0) {
+      if (entropy) entropy[b] = h;
+      if (mi && sum_plogp) mi[b] = h + sum_plogp[b] * inv_s;
+    }
+  }
+}
+
+int grid_for(int64_t work_items, int threads) {
+  int64_t blocks = (work_items + threads - 1) / threads;
+  const int64_t cap = (int64_t)bt_num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  return blocks < 1 ? 1 : (int)blocks;
+}
+
+}  // namespace
+
+extern "C" int bt_philox_normal_fill(float* out, int64_t n, uint64_t seed, uint32_t sample_id, uint32_t layer_id,
+                                     int kind, bt_stream_t stream) {
+  BT_REQUIRE(out && n >= 0 && kind >= 0 && kind < 16, BT_ERR_INVALID, "bt_philox_normal_fill: bad argument");
+  if (n == 0) return BT_OK;
+  philox_normal_fill_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, (cudaStream_t)stream>>>(
+      out, n, bt_rng_key(seed, sample_id, layer_id, kind));
+  BT_LAUNCH_OK("philox_normal_fill_kernel");
+  return BT_OK;
+}
+
+extern "C" int bt_philox_sign_fill(float* out, int64_t n, uint64_t seed, uint32_t sample_id, uint32_t layer_id,
+                                   int kind, bt_stream_t stream) {
+  BT_REQUIRE(out && n >= 0 && kind >= 0 && kind < 16, BT_ERR_INVALID, "bt_philox_sign_fill: bad argument");
+  if (n == 0) return BT_OK;
+  philox_sign_fill_kernel<<<grid_for((n + 31) / 32, 256), 256, 0, (cudaStream_t)stream>>>(
+      out, n, bt_rng_key(seed, sample_id, layer_id, kind));
+  BT_LAUNCH_OK("philox_sign_fill_kernel");
+  return BT_OK;
+}
+
+extern "C" int bt_moped_rho(const float* w, float* rho, int64_t n, float delta, bt_stream_t stream) {
+  BT_REQUIRE(w && rho && n >= 0, BT_ERR_INVALID, "bt_moped_rho: bad argument");
+  if (n == 0) return BT_OK;
+  moped_rho_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(w, rho, n, delta);
+  BT_LAUNCH_OK("moped_rho_kernel");
+  return BT_OK;
+}
+
+extern "C" int bt_mc_accumulate(const void* logits, int dtype, int64_t S, int64_t B, int64_t C, int apply_softmax,
+                                float* sum_p, float* sum_p2, float* sum_plogp, bt_stream_t stream) {
+  BT_REQUIRE(logits && S >= 0 && B >= 0 && C > 0, BT_ERR_INVALID, "bt_mc_accumulate: bad argument");
+  if (S == 0 || B == 0) return BT_OK;
+  const int grid = grid_for(B * 32, 256);
+  if (dtype == BT_F32)
+    mc_accumulate_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)logits, S, B, C, apply_softmax,
+                                                                         sum_p, sum_p2, sum_plogp);
+  else if (dtype == BT_BF16)
+    mc_accumulate_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)logits, S, B, C, apply_softmax, sum_p, sum_p2, sum_plogp);
+  else
+    BT_REQUIRE(false, BT_ERR_UNSUPPORTED, "bt_mc_accumulate: dtype %d", dtype);
+  BT_LAUNCH_OK("mc_accumulate_kernel");
+  return BT_OK;
+}
+
+extern "C" int bt_mc_finalize(const float* sum_p, const float* sum_p2, const float* sum_plogp, int64_t S_total,
+                              int64_t B, int64_t C, float* mean, float* var, float* entropy, float* mutual_info,
+                              bt_stream_t stream) {
+  BT_REQUIRE(sum_p && S_total > 0 && B >= 0 && C > 0, BT_ERR_INVALID, "bt_mc_finalize: bad argument");
+  if (B == 0) return BT_OK;
+  mc_finalize_kernel<<<grid_for(B * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+      sum_p, sum_p2, sum_plogp, 1.f / (float)S_total, B, C, mean, var, entropy, mutual_info);
+  BT_LAUNCH_OK("mc_finalize_kernel");
+  return BT_OK;
+}

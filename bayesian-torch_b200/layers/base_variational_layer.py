@@ -1,0 +1,244 @@
+"""Base class of the B200-native Bayesian layers.
+
+Mirrors the interface of the reference's BaseVariationalLayer_
+(bayesian_torch/layers/base_variational_layer.py:42-100): the ``dnn_to_bnn_flag``
+property, ``kl_div`` and ``get_kernel_size``.  The arithmetic runs in
+libbt_b200.so; one generic implementation serves every Reparameterization /
+Flipout class, the public classes only pin the reference's constructor
+signatures and attribute names.
+"""
+from __future__ import annotations
+
+import collections.abc
+from itertools import repeat
+from typing import Optional
+
+import torch
+import torch.nn as nn
+from torch.nn import Parameter
+
+from .. import _lib, ops
+
+
+def get_kernel_size(x, n):
+    """int -> n-tuple, iterable -> tuple (base_variational_layer.py:37-40)."""
+    if isinstance(x, collections.abc.Iterable):
+        return tuple(x)
+    return tuple(repeat(x, n))
+
+
+def _ntuple(v, n):
+    t = get_kernel_size(v, n)
+    if len(t) != n:
+        raise ValueError(f"expected {n} values, got {t}")
+    return tuple(int(i) for i in t)
+
+
+class BaseVariationalLayer_(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self._dnn_to_bnn_flag = False
+
+    @property
+    def dnn_to_bnn_flag(self):
+        return self._dnn_to_bnn_flag
+
+    @dnn_to_bnn_flag.setter
+    def dnn_to_bnn_flag(self, value):
+        self._dnn_to_bnn_flag = value
+
+    def kl_div(self, mu_q, sigma_q, mu_p, sigma_p, prior_type="normal"):
+        """mean over elements of KL(N(mu_q, sigma_q) || N(mu_p, sigma_p))
+        (base_variational_layer.py:55-72).  mu_p / sigma_p: python scalars or tensors shaped
+        like mu_q.  prior_type None is read as 'normal' (upstream behaviour; the fork's
+        Conv2d default of None raises there)."""
+        if prior_type is None:
+            prior_type = "normal"
+        if prior_type == "laplace":
+            raise NotImplementedError("the fork's 'laplace' prior is outside this build's hot path (SURVEY.md 8f)")
+        if prior_type != "normal":
+            raise ValueError(f"Unknown prior_type: {prior_type}")
+
+        def split(p):
+            if torch.is_tensor(p) and p.numel() > 1:
+                return 0.0 if p is mu_p else 1.0, p.expand_as(mu_q)
+            return float(p), None
+        pm, pm_t = split(mu_p)
+        ps, ps_t = split(sigma_p)
+        return ops.kl_normal_multi([mu_q], [sigma_q], pm, ps, [pm_t], [ps_t], q_is_sigma=True)
+
+
+class _BayesLayer(BaseVariationalLayer_):
+    """Generic variational layer: rank 0 = Linear, 1..3 = ConvNd; Reparameterization or Flipout."""
+
+    _rank = 0
+    _flipout = False
+    _wname = "weight"  # parameter suffix: mu_weight / mu_kernel
+
+    # per-layer overrides of the process-wide settings in ops (None = follow the global)
+    sample_mode: Optional[str] = None
+    path: Optional[str] = None
+
+    def _setup(self, w_shape, bias: bool, prior_mean, prior_variance, mu_init, rho_init):
+        w = self._wname
+        self.register_parameter("mu_" + w, Parameter(torch.empty(w_shape)))
+        self.register_parameter("rho_" + w, Parameter(torch.empty(w_shape)))
+        self.register_buffer("eps_" + w, torch.empty(w_shape), persistent=False)
+        self.register_buffer("prior_weight_mu", torch.empty(w_shape), persistent=False)
+        self.register_buffer("prior_weight_sigma", torch.empty(w_shape), persistent=False)
+        n = w_shape[0]
+        if bias:
+            self.mu_bias = Parameter(torch.empty(n))
+            self.rho_bias = Parameter(torch.empty(n))
+            self.register_buffer("eps_bias", torch.empty(n), persistent=False)
+            self.register_buffer("prior_bias_mu", torch.empty(n), persistent=False)
+            self.register_buffer("prior_bias_sigma", torch.empty(n), persistent=False)
+        else:
+            self.register_parameter("mu_bias", None)
+            self.register_parameter("rho_bias", None)
+            self.register_buffer("eps_bias", None, persistent=False)
+            self.register_buffer("prior_bias_mu", None, persistent=False)
+            self.register_buffer("prior_bias_sigma", None, persistent=False)
+        self._mu0, self._rho0 = float(mu_init), float(rho_init)
+        self._layer_id = ops.next_layer_id()
+        self._calls = 0
+        self.sign_input = None   # 'buffer' mode: Flipout sign tensors supplied by the caller
+        self.sign_output = None
+        self.quant_prepare = False
+        self.init_parameters()
+
+    # -- reference API ---------------------------------------------------------------------
+    def init_parameters(self):
+        """Constant priors, mu ~ N(mu_init, 0.1), rho ~ N(rho_init, 0.1)
+        (linear_variational.py:133-144)."""
+        w = self._wname
+        self.prior_weight_mu.fill_(self.prior_mean)
+        self.prior_weight_sigma.fill_(self.prior_variance)
+        getattr(self, "mu_" + w).data.normal_(mean=self._mu0, std=0.1)
+        getattr(self, "rho_" + w).data.normal_(mean=self._rho0, std=0.1)
+        if self.mu_bias is not None:
+            self.prior_bias_mu.fill_(self.prior_mean)
+            self.prior_bias_sigma.fill_(self.prior_variance)
+            self.mu_bias.data.normal_(mean=self._mu0, std=0.1)
+            self.rho_bias.data.normal_(mean=self._rho0, std=0.1)
+        self._mark_constant_priors()
+
+    def prepare(self):
+        raise NotImplementedError("INT8 post-training quantisation stubs are outside this build's scope (SURVEY.md row 9)")
+
+    def _mark_constant_priors(self):
+        self._prior_marks = {n: (id(b), b._version) for n, b in self._prior_buffers().items() if b is not None}
+
+    def _prior_buffers(self):
+        return {n: getattr(self, n) for n in ("prior_weight_mu", "prior_weight_sigma", "prior_bias_mu", "prior_bias_sigma")}
+
+    def _prior_tensors(self):
+        """(w_mu, w_sigma, b_mu, b_sigma): a buffer is passed to the kernel only if someone
+        replaced or modified it after init (utils/util.py:MOPED assigns tensor priors,
+        :101-104); untouched constant buffers are folded into the two scalars."""
+        out = []
+        for n, b in self._prior_buffers().items():
+            mark = self._prior_marks.get(n)
+            changed = b is not None and (mark is None or mark != (id(b), b._version))
+            out.append(b if changed else None)
+        return tuple(out)
+
+    def _apply(self, fn, *args, **kwargs):
+        # .half()/.bfloat16()/.to(dtype) keep mu/rho/eps/prior in fp32: the kernels read fp32
+        # masters and round the SAMPLED weight once (bf16 operands, fp32 accumulate).
+        def keep_fp32(t):
+            r = fn(t)
+            if t.dtype == torch.float32 and r.is_floating_point() and r.dtype != torch.float32:
+                r = r.to(torch.float32)
+            return r
+        const = {n: b is not None and self._prior_marks.get(n) == (id(b), b._version)
+                 for n, b in self._prior_buffers().items()} if hasattr(self, "_prior_marks") else {}
+        super()._apply(keep_fp32, *args, **kwargs)
+        for n, was_const in const.items():  # moving devices re-creates buffers; constants stay constants
+            if was_const:
+                b = getattr(self, n)
+                self._prior_marks[n] = (id(b), b._version)
+        return self
+
+    def _w(self):
+        w = self._wname
+        return getattr(self, "mu_" + w), getattr(self, "rho_" + w)
+
+    def kl_loss(self):
+        """kl(weight) + kl(bias), each a mean over elements (linear_variational.py:146-158)."""
+        mu_w, rho_w = self._w()
+        pt = self._prior_tensors()
+        mus, rhos, pm, ps = [mu_w], [rho_w], [pt[0]], [pt[1]]
+        if self.mu_bias is not None:
+            mus.append(self.mu_bias); rhos.append(self.rho_bias); pm.append(pt[2]); ps.append(pt[3])
+        return ops.kl_normal_multi(mus, rhos, float(self.prior_mean), float(self.prior_variance), pm, ps)
+
+    # -- forward ----------------------------------------------------------------------------
+    def _conv_args(self):
+        r = self._rank
+        return (_ntuple(self.stride, r), _ntuple(self.padding, r), _ntuple(self.dilation, r), int(self.groups))
+
+    def forward(self, input, return_kl=True):
+        if self.dnn_to_bnn_flag:
+            return_kl = False
+        mu_w, rho_w = self._w()
+        r = self._rank
+        mode = self.sample_mode or ops.get_sample_mode()
+        x = input
+        lead = None
+        if r == 0:
+            lead = x.shape[:-1]
+            x = x.reshape(-1, x.shape[-1])
+        elif x.dim() != r + 2:
+            raise RuntimeError(f"{type(self).__name__} expects a {r + 2}-d input, got {tuple(x.shape)}")
+        call = ops.LayerCall(rank=r, flipout=self._flipout)
+        if r > 0:
+            call.stride, call.padding, call.dilation, call.groups = self._conv_args()
+        call.prior_mu, call.prior_sigma = float(self.prior_mean), float(self.prior_variance)
+        call.prior_t = self._prior_tensors()
+        call.seed, call.layer_id = ops.get_seed(), self._layer_id
+        call.n_samples = ops.current_n_samples()
+        call.x_shared = call.n_samples > 1 and ops._STATE.shared_batch is not None and x.shape[0] == ops._STATE.shared_batch
+        call.want_kl = bool(return_kl)
+        call.path = ops._PATHS[self.path or ops.get_path()]
+        if ops._STATE.sample_override is not None:
+            call.sample_id = ops._STATE.sample_override
+        else:
+            call.sample_id = self._calls & 0xFFFFFFFF
+            self._calls += call.n_samples
+        eps_w = getattr(self, "eps_" + self._wname)
+        if mode == "torch":
+            ops._require_cuda(x)
+            if self._flipout and r > 0:   # conv_flipout.py:385-386,390,401 draw order
+                call.sign_in, call.sign_out = self._draw_signs(x, mu_w)
+            call.eps_w = eps_w.normal_()   # linear_variational.py:164
+            if self.mu_bias is not None:
+                call.eps_b = self.eps_bias.normal_()
+            if self._flipout and r == 0:  # linear_flipout.py:150,162 then :169-170
+                call.sign_in, call.sign_out = self._draw_signs(x, mu_w)
+        elif mode == "buffer":
+            call.eps_w = eps_w
+            call.eps_b = self.eps_bias
+            if self._flipout:
+                if self.sign_input is None or self.sign_output is None:
+                    raise RuntimeError("sample mode 'buffer' on a Flipout layer needs layer.sign_input / layer.sign_output")
+                call.sign_in, call.sign_out = self.sign_input, self.sign_output
+        out, kl = ops.bayes_layer(call, x, mu_w, rho_w, self.mu_bias, self.rho_bias)
+        if lead is not None:
+            out = out.reshape(*lead, out.shape[-1])
+        if return_kl:
+            return out, kl
+        return out
+
+    def _draw_signs(self, x, mu_w):
+        """sign(U(-1,1)) per element of x and of the output, drawn with torch's generator in
+        the reference's order so a seeded run replays the reference's stream."""
+        s_in = torch.empty_like(x, dtype=torch.float32, memory_format=torch.contiguous_format).uniform_(-1, 1).sign()
+        if self._rank == 0:
+            oshape = (x.shape[0], mu_w.shape[0])
+        else:
+            st, pd, dl, _ = self._conv_args()
+            sp = [ops._conv_out_size(x.shape[2 + i], mu_w.shape[2 + i], st[i], pd[i], dl[i]) for i in range(self._rank)]
+            oshape = (x.shape[0], mu_w.shape[0], *sp)
+        s_out = torch.empty(oshape, dtype=torch.float32, device=x.device).uniform_(-1, 1).sign()
+        return s_in, s_out

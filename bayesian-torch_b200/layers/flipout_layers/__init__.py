@@ -1,0 +1,2 @@
+from .linear_flipout import *  # noqa: F401,F403
+from .conv_flipout import *  # noqa: F401,F403

@@ -1,0 +1,2 @@
+from .linear_variational import *  # noqa: F401,F403
+from .conv_variational import *  # noqa: F401,F403

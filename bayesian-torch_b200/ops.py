@@ -1,0 +1,499 @@
+"""Host-side operator layer: torch tensors in, C-ABI calls out.
+
+PyTorch is plumbing here (device memory, streams, autograd bookkeeping); all
+arithmetic of the hot path runs in libbt_b200.so.  CPU tensors raise -- there
+is no CPU / eager fallback (BASELINE.json north_star).
+"""
+from __future__ import annotations
+
+import contextlib
+import ctypes as C
+import threading
+from dataclasses import dataclass, field
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import Geom, LayerGrads, LayerParams
+
+# --------------------------------------------------------------------------- RNG / mode state
+
+
+class _State(threading.local):
+    def __init__(self):
+        self.seed = 0x5EEDB200
+        self.sample_override: Optional[int] = None  # set by mc_sample()
+        self.sample_mode = "philox"                  # "philox" | "torch" | "buffer"
+        self.path = "auto"                           # "auto" | "simt" | "tc"
+        self.n_samples = 1                           # >1 inside mc_batched()
+        self.shared_batch: Optional[int] = None      # batch of the un-folded model input
+
+
+_STATE = _State()
+_layer_counter = [0]
+_counter_lock = threading.Lock()
+
+_PATHS = {"auto": _lib.PATH_AUTO, "simt": _lib.PATH_SIMT_F32, "tc": _lib.PATH_TC_BF16}
+
+
+def next_layer_id() -> int:
+    with _counter_lock:
+        _layer_counter[0] += 1
+        return _layer_counter[0] & 0x0FFFFFFF
+
+
+def manual_seed(seed: int) -> None:
+    """Seed of the in-kernel Philox streams (independent of torch's generator)."""
+    _STATE.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+
+
+def get_seed() -> int:
+    return _STATE.seed
+
+
+def set_sample_mode(mode: str) -> None:
+    """'philox': eps/signs generated in registers (default, nothing materialised);
+    'torch' : eps drawn with torch's generator into the layer's eps_* buffers exactly
+              like the reference (linear_variational.py:164), then fed to the kernel;
+    'buffer': use whatever the eps_* buffers / sign tensors hold (parity tests)."""
+    if mode not in ("philox", "torch", "buffer"):
+        raise ValueError(f"unknown sample mode {mode!r}")
+    _STATE.sample_mode = mode
+
+
+def get_sample_mode() -> str:
+    return _STATE.sample_mode
+
+
+def set_path(path: str) -> None:
+    """'auto' (tensor cores when the problem qualifies), 'simt' (fp32 parity path), 'tc'."""
+    if path not in _PATHS:
+        raise ValueError(f"unknown path {path!r}")
+    _STATE.path = path
+
+
+def get_path() -> str:
+    return _STATE.path
+
+
+@contextlib.contextmanager
+def sample_mode(mode: str):
+    old = _STATE.sample_mode
+    set_sample_mode(mode)
+    try:
+        yield
+    finally:
+        _STATE.sample_mode = old
+
+
+@contextlib.contextmanager
+def path(p: str):
+    old = _STATE.path
+    set_path(p)
+    try:
+        yield
+    finally:
+        _STATE.path = old
+
+
+@contextlib.contextmanager
+def mc_sample(sample_id: int):
+    """Pin the Monte-Carlo sample index used by every layer inside the block: sample s
+    of a model is the same weight draw on any rank / any GPU count."""
+    old = _STATE.sample_override
+    _STATE.sample_override = int(sample_id) & 0xFFFFFFFF
+    try:
+        yield
+    finally:
+        _STATE.sample_override = old
+
+
+@contextlib.contextmanager
+def mc_batched(n_samples: int, first_sample: int = 0, shared_batch: Optional[int] = None):
+    """Run S weight samples in ONE pass: inside the block the leading batch axis of every
+    Bayesian layer input is read as [S*B, ...] (sample-major) and sample s of the batch
+    uses weight draw first_sample + s.  Deterministic torch layers (BN, ReLU, pooling)
+    work unchanged on the folded batch.  shared_batch=B: a layer input whose batch is B
+    (the model input) is shared by all samples and only its OUTPUT is folded to [S*B, ...]."""
+    old = (_STATE.n_samples, _STATE.sample_override, _STATE.shared_batch)
+    _STATE.n_samples = int(n_samples)
+    _STATE.sample_override = int(first_sample) & 0xFFFFFFFF
+    _STATE.shared_batch = shared_batch
+    try:
+        yield
+    finally:
+        _STATE.n_samples, _STATE.sample_override, _STATE.shared_batch = old
+
+
+def current_n_samples() -> int:
+    return _STATE.n_samples
+
+
+# --------------------------------------------------------------------------- helpers
+
+_DT = {torch.float32: _lib.BT_F32, torch.bfloat16: _lib.BT_BF16}
+
+
+def _require_cuda(*tensors) -> torch.device:
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError(
+                "bayesian_torch_b200 runs on CUDA (sm_100a) only: got a CPU tensor; there is no CPU fallback")
+        dev = dev or t.device
+        if t.device != dev:
+            raise RuntimeError(f"tensors on different devices: {t.device} vs {dev}")
+    return dev
+
+
+def _f32c(t: Optional[torch.Tensor], name: str) -> Optional[torch.Tensor]:
+    if t is None:
+        return None
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32 (got {t.dtype}); variational parameters stay fp32 masters")
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr_array(tensors: Sequence[Optional[torch.Tensor]]):
+    arr = (C.c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        arr[i] = _ptr(t)
+    return arr
+
+
+# --------------------------------------------------------------------------- KL
+
+
+def kl_workspace(n: int, device) -> torch.Tensor:
+    nbytes = _lib.lib().bt_workspace_bytes(b"kl", None, n)
+    return torch.empty(nbytes, dtype=torch.uint8, device=device)
+
+
+def _kl_call(mus, rhos, q_is_sigma, prior_mu, prior_sigma, pmu_t, psig_t, want_each, d_mu=None, d_rho=None,
+             grad_scale=None):
+    dev = _require_cuda(*mus, *rhos)
+    n = len(mus)
+    numel = (C.c_int64 * n)(*[m.numel() for m in mus])
+    each = torch.empty(n, dtype=torch.float32, device=dev) if want_each else None
+    total = torch.empty((), dtype=torch.float32, device=dev)
+    ws = kl_workspace(n, dev)
+    any_pt = any(t is not None for t in pmu_t) or any(t is not None for t in psig_t)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().bt_kl_normal_multi(
+            n, _ptr_array(mus), _ptr_array(rhos), numel, int(q_is_sigma), float(prior_mu), float(prior_sigma),
+            _ptr_array(pmu_t) if any_pt else None, _ptr_array(psig_t) if any_pt else None,
+            _ptr(each), _ptr(total), _ptr_array(d_mu) if d_mu is not None else None,
+            _ptr_array(d_rho) if d_rho is not None else None, _ptr(grad_scale), _ptr(ws), _stream())
+    _lib.check(rc, "bt_kl_normal_multi")
+    return total, each
+
+
+class _KLMulti(torch.autograd.Function):
+    """sum_i mean(KL(N(mu_i, softplus(rho_i)) || prior_i)) in one launch, with analytic gradients."""
+
+    @staticmethod
+    def forward(ctx, cfg, *params):
+        n = len(params) // 2
+        mus = [_f32c(p.detach(), "mu") for p in params[:n]]
+        rhos = [_f32c(p.detach(), "rho") for p in params[n:]]
+        total, _ = _kl_call(mus, rhos, cfg["q_is_sigma"], cfg["prior_mu"], cfg["prior_sigma"], cfg["pmu_t"],
+                            cfg["psig_t"], False)
+        ctx.cfg = cfg
+        ctx.save_for_backward(*params)
+        return total
+
+    @staticmethod
+    def backward(ctx, g):
+        params = ctx.saved_tensors
+        cfg = ctx.cfg
+        n = len(params) // 2
+        mus = [_f32c(p.detach(), "mu") for p in params[:n]]
+        rhos = [_f32c(p.detach(), "rho") for p in params[n:]]
+        d_mu = [torch.empty_like(m) for m in mus]
+        d_rho = [torch.empty_like(r) for r in rhos]
+        gs = g.detach().to(torch.float32).contiguous()
+        _kl_call(mus, rhos, cfg["q_is_sigma"], cfg["prior_mu"], cfg["prior_sigma"], cfg["pmu_t"], cfg["psig_t"], False,
+                 d_mu, d_rho, gs)
+        grads = [d.view_as(p) for d, p in zip(d_mu + d_rho, params)]
+        return (None, *grads)
+
+
+def kl_normal_multi(mus: Sequence[torch.Tensor], rhos: Sequence[torch.Tensor], prior_mu: float = 0.0,
+                    prior_sigma: float = 1.0, prior_mu_t: Optional[Sequence] = None,
+                    prior_sigma_t: Optional[Sequence] = None, q_is_sigma: bool = False) -> torch.Tensor:
+    """Sum over tensors of the mean element-wise Gaussian KL (base_variational_layer.py:70-72).
+    One kernel launch for the whole table; differentiable w.r.t. every mu and rho."""
+    n = len(mus)
+    if n == 0:
+        raise ValueError("kl_normal_multi: empty tensor list")
+    cfg = {
+        "q_is_sigma": bool(q_is_sigma), "prior_mu": float(prior_mu), "prior_sigma": float(prior_sigma),
+        "pmu_t": [None if t is None else _f32c(t.detach(), "prior_mu") for t in (prior_mu_t or [None] * n)],
+        "psig_t": [None if t is None else _f32c(t.detach(), "prior_sigma") for t in (prior_sigma_t or [None] * n)],
+    }
+    out = None
+    for i in range(0, n, 192):  # KL_MAX_TENSORS per launch
+        sub = dict(cfg, pmu_t=cfg["pmu_t"][i:i + 192], psig_t=cfg["psig_t"][i:i + 192])
+        part = _KLMulti.apply(sub, *mus[i:i + 192], *rhos[i:i + 192])
+        out = part if out is None else out + part
+    return out
+
+
+# --------------------------------------------------------------------------- layer op
+
+
+@dataclass
+class LayerCall:
+    """Everything one forward/backward of a Bayesian layer needs besides x and the parameters."""
+    rank: int                                   # 0 linear, 1..3 conv
+    flipout: bool
+    stride: Tuple[int, ...] = ()
+    padding: Tuple[int, ...] = ()
+    dilation: Tuple[int, ...] = ()
+    groups: int = 1
+    prior_mu: float = 0.0
+    prior_sigma: float = 1.0
+    prior_t: Tuple[Optional[torch.Tensor], ...] = (None, None, None, None)  # w_mu, w_sigma, b_mu, b_sigma
+    eps_w: Optional[torch.Tensor] = None        # None -> Philox
+    eps_b: Optional[torch.Tensor] = None
+    sign_in: Optional[torch.Tensor] = None
+    sign_out: Optional[torch.Tensor] = None
+    seed: int = 0
+    sample_id: int = 0
+    layer_id: int = 0
+    n_samples: int = 1
+    x_shared: bool = False                      # mc_batched: x is the un-folded model input
+    want_kl: bool = True
+    path: int = _lib.PATH_AUTO
+
+
+def _conv_out_size(i, k, s, p, d):
+    return (i + 2 * p - d * (k - 1) - 1) // s + 1
+
+
+def _fill3(dst, vals):
+    for i, v in enumerate(vals):
+        dst[i] = int(v)
+
+
+def _build_geom(call: LayerCall, x: torch.Tensor, w_shape, out: torch.Tensor) -> Geom:
+    """x: [rows, c_in] (linear) or [B*, C, *spatial]; out likewise. Strides in elements."""
+    g = Geom()
+    g.rank = call.rank
+    g.groups = call.groups
+    g.n_samples = call.n_samples
+    g.x_dtype = _DT[x.dtype]
+    g.out_dtype = _DT[out.dtype]
+    S = call.n_samples
+    if call.x_shared:
+        g.batch = x.shape[0]
+    else:
+        if x.shape[0] % S != 0:
+            raise RuntimeError(f"mc_batched({S}): leading batch {x.shape[0]} is not a multiple of the sample count")
+        g.batch = x.shape[0] // S
+    g.c_in = x.shape[1]
+    g.c_out = w_shape[0]
+    xs, os_ = x.stride(), out.stride()
+    g.x_batch_stride, g.x_chan_stride = xs[0], xs[1]
+    g.out_batch_stride, g.out_chan_stride = os_[0], os_[1]
+    g.x_sample_stride = xs[0] * g.batch if (S > 1 and not call.x_shared) else 0
+    g.out_sample_stride = os_[0] * g.batch if S > 1 else 0
+    r = call.rank
+    _fill3(g.in_size, x.shape[2:2 + r]); _fill3(g.out_size, out.shape[2:2 + r]); _fill3(g.k_size, w_shape[2:2 + r])
+    _fill3(g.stride, call.stride); _fill3(g.pad, call.padding); _fill3(g.dil, call.dilation)
+    _fill3(g.x_sp_stride, xs[2:2 + r]); _fill3(g.out_sp_stride, os_[2:2 + r])
+    return g
+
+
+def _build_params(call: LayerCall, mu_w, rho_w, mu_b, rho_b) -> Tuple[LayerParams, list]:
+    p = LayerParams()
+    keep = [mu_w, rho_w, mu_b, rho_b]
+    p.mu_w, p.rho_w, p.mu_b, p.rho_b = _ptr(mu_w), _ptr(rho_w), _ptr(mu_b), _ptr(rho_b)
+    eps_w, eps_b = _f32c(call.eps_w, "eps_w"), _f32c(call.eps_b, "eps_b")
+    keep += [eps_w, eps_b]
+    p.eps_w, p.eps_b = _ptr(eps_w), _ptr(eps_b)
+    p.sign_in, p.sign_out = _ptr(call.sign_in), _ptr(call.sign_out)
+    pts = [None if t is None else _f32c(t, "prior") for t in call.prior_t]
+    keep += pts
+    p.prior_mu_w_t, p.prior_sigma_w_t, p.prior_mu_b_t, p.prior_sigma_b_t = (_ptr(t) for t in pts)
+    p.prior_mu, p.prior_sigma = float(call.prior_mu), float(call.prior_sigma)
+    p.seed, p.sample_id, p.layer_id = call.seed, call.sample_id, call.layer_id
+    return p, keep
+
+
+def _entry(call: LayerCall, bwd: bool):
+    L = _lib.lib()
+    if call.flipout:
+        return (L.bt_linear_flipout_bwd if bwd else L.bt_linear_flipout_fwd) if call.rank == 0 else \
+               (L.bt_conv2d_flipout_bwd if bwd else L.bt_conv2d_flipout_fwd)
+    return (L.bt_linear_reparam_bwd if bwd else L.bt_linear_reparam_fwd) if call.rank == 0 else \
+           (L.bt_conv_reparam_bwd if bwd else L.bt_conv_reparam_fwd)
+
+
+def _like_x_format(x: torch.Tensor, shape) -> torch.Tensor:
+    """Output allocated in x's memory format (channels-last stays channels-last)."""
+    if x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last) and not x.is_contiguous():
+        return torch.empty(shape, dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    if x.dim() == 5 and x.is_contiguous(memory_format=torch.channels_last_3d) and not x.is_contiguous():
+        return torch.empty(shape, dtype=x.dtype, device=x.device, memory_format=torch.channels_last_3d)
+    return torch.empty(shape, dtype=x.dtype, device=x.device)
+
+
+def _dense(x: torch.Tensor) -> torch.Tensor:
+    """Any dense layout is consumed through strides; only overlapping / exotic views are copied."""
+    if x.is_contiguous():
+        return x
+    if x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last):
+        return x
+    if x.dim() == 5 and x.is_contiguous(memory_format=torch.channels_last_3d):
+        return x
+    return x.contiguous()
+
+
+def _match_strides(t: torch.Tensor, ref: torch.Tensor) -> torch.Tensor:
+    """fp32 copy of t laid out exactly like ref (the kernels index signs with x's / out's offsets)."""
+    t = t.detach().reshape(ref.shape)
+    if t.dtype == torch.float32 and t.stride() == ref.stride():
+        return t
+    return torch.empty_like(ref, dtype=torch.float32).copy_(t)
+
+
+class _BayesLayerFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, call: LayerCall, x, mu_w, rho_w, mu_b, rho_b):
+        dev = _require_cuda(x, mu_w, rho_w, mu_b, rho_b)
+        if x.dtype not in _DT:
+            raise RuntimeError(f"activations must be float32 or bfloat16, got {x.dtype}")
+        mu_wc, rho_wc = _f32c(mu_w.detach(), "mu"), _f32c(rho_w.detach(), "rho")
+        mu_bc = None if mu_b is None else _f32c(mu_b.detach(), "mu_bias")
+        rho_bc = None if rho_b is None else _f32c(rho_b.detach(), "rho_bias")
+        xd = _dense(x.detach())
+        r = call.rank
+        nb = xd.shape[0] * (call.n_samples if call.x_shared else 1)
+        if r == 0:
+            out_shape = (nb, mu_wc.shape[0])
+        else:
+            sp = [_conv_out_size(xd.shape[2 + i], mu_wc.shape[2 + i], call.stride[i], call.padding[i], call.dilation[i])
+                  for i in range(r)]
+            if min(sp) <= 0:
+                raise RuntimeError(f"conv output size {sp} is not positive for input {tuple(xd.shape)}")
+            out_shape = (nb, mu_wc.shape[0], *sp)
+        if xd.shape[1] != mu_wc.shape[1] * call.groups:
+            raise RuntimeError(f"input has {xd.shape[1]} channels/features, layer expects {mu_wc.shape[1] * call.groups}")
+        out = _like_x_format(xd, out_shape)
+        if call.sign_in is not None:
+            call.sign_in = _match_strides(call.sign_in, xd)
+        if call.sign_out is not None:
+            call.sign_out = _match_strides(call.sign_out, out)
+        g = _build_geom(call, xd, mu_wc.shape, out)
+        p, keep = _build_params(call, mu_wc, rho_wc, mu_bc, rho_bc)
+        L = _lib.lib()
+        op = b"flipout_fwd" if call.flipout else b"reparam_fwd"
+        ws = torch.empty(max(int(L.bt_workspace_bytes(op, C.byref(g), 2)), 256), dtype=torch.uint8, device=dev)
+        kl = torch.empty((), dtype=torch.float32, device=dev) if call.want_kl else None
+        with torch.cuda.device(dev):
+            rc = _entry(call, False)(C.byref(g), C.byref(p), _ptr(xd), _ptr(out), _ptr(kl), _ptr(ws), call.path, _stream())
+        _lib.check(rc, "layer forward")
+        ctx.call = call
+        ctx.out_meta = (tuple(out.shape), tuple(out.stride()))
+        ctx.save_for_backward(x, mu_w, rho_w, mu_b, rho_b)
+        if kl is None:
+            kl = torch.zeros((), dtype=torch.float32, device=dev)
+            ctx.mark_non_differentiable(kl)
+        return out, kl
+
+    @staticmethod
+    def backward(ctx, g_out, g_kl):
+        call: LayerCall = ctx.call
+        x, mu_w, rho_w, mu_b, rho_b = ctx.saved_tensors
+        dev = x.device
+        mu_wc, rho_wc = _f32c(mu_w.detach(), "mu"), _f32c(rho_w.detach(), "rho")
+        mu_bc = None if mu_b is None else _f32c(mu_b.detach(), "mu_bias")
+        rho_bc = None if rho_b is None else _f32c(rho_b.detach(), "rho_bias")
+        xd = _dense(x.detach())
+        if g_out is None:  # only kl was used downstream
+            g_out = torch.empty_strided(ctx.out_meta[0], ctx.out_meta[1], dtype=x.dtype, device=dev).zero_()
+        S = call.n_samples
+        if S != 1:
+            raise RuntimeError("backward through mc_batched() is not supported; loop over mc_sample(s) for training")
+        # grad_out must share dtype with x and have a dense layout
+        go = _dense(g_out.detach().to(x.dtype))
+        geom = _build_geom(call, xd, mu_wc.shape, go)
+        p, keep = _build_params(call, mu_wc, rho_wc, mu_bc, rho_bc)
+        grads = LayerGrads()
+        gx = torch.empty_like(xd) if ctx.needs_input_grad[1] else None
+        need_w = ctx.needs_input_grad[2] or ctx.needs_input_grad[3]
+        gmu = torch.empty_like(mu_wc) if need_w else None
+        grho = torch.empty_like(rho_wc) if need_w else None
+        need_b = mu_b is not None and (ctx.needs_input_grad[4] or ctx.needs_input_grad[5])
+        gmb = torch.empty_like(mu_bc) if need_b else None
+        grb = torch.empty_like(rho_bc) if need_b else None
+        grads.grad_x, grads.grad_mu_w, grads.grad_rho_w = _ptr(gx), _ptr(gmu), _ptr(grho)
+        grads.grad_mu_b, grads.grad_rho_b = _ptr(gmb), _ptr(grb)
+        gk = None
+        if call.want_kl and g_kl is not None:
+            gk = g_kl.detach().to(torch.float32).contiguous()
+        ws = torch.empty(256, dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = _entry(call, True)(C.byref(geom), C.byref(p), _ptr(xd), _ptr(go), _ptr(gk), C.byref(grads), _ptr(ws),
+                                    _lib.PATH_AUTO, _stream())
+        _lib.check(rc, "layer backward")
+        if gx is not None and gx.shape != x.shape:
+            gx = gx.view_as(x)
+        return None, gx, gmu, grho, gmb, grb
+
+
+def bayes_layer(call: LayerCall, x, mu_w, rho_w, mu_b, rho_b):
+    """(out, kl) of one Bayesian layer call; kl is a zero constant when call.want_kl is False."""
+    return _BayesLayerFn.apply(call, x, mu_w, rho_w, mu_b, rho_b)
+
+
+# --------------------------------------------------------------------------- misc exports
+
+
+def philox_normal(n: int, seed: int, sample_id: int, layer_id: int, kind: int, device="cuda") -> torch.Tensor:
+    """The exact N(0,1) stream the fused kernels generate in registers (bt_philox_normal_fill)."""
+    out = torch.empty(n, dtype=torch.float32, device=device)
+    with torch.cuda.device(out.device):
+        _lib.check(_lib.lib().bt_philox_normal_fill(_ptr(out), n, seed, sample_id, layer_id, kind, _stream()), "philox_normal")
+    return out
+
+
+def philox_sign(n: int, seed: int, sample_id: int, layer_id: int, kind: int, device="cuda") -> torch.Tensor:
+    out = torch.empty(n, dtype=torch.float32, device=device)
+    with torch.cuda.device(out.device):
+        _lib.check(_lib.lib().bt_philox_sign_fill(_ptr(out), n, seed, sample_id, layer_id, kind, _stream()), "philox_sign")
+    return out
+
+
+def philox_eps_weight(w_shape, seed: int, sample_id: int, layer_id: int, device="cuda") -> torch.Tensor:
+    """eps tensor in the weight's logical layout [c_out, c_in/g, *k] holding the values the
+    kernels use: the stream is indexed in packed (n, tap, channel) order (shared with the
+    tensor-core path, which stages weights channel-fastest)."""
+    n, c = int(w_shape[0]), int(w_shape[1])
+    taps = 1
+    for k in w_shape[2:]:
+        taps *= int(k)
+    flat = philox_normal(n * c * taps, seed, sample_id, layer_id, _lib.KIND_EPS_W, device)
+    return flat.view(n, taps, c).permute(0, 2, 1).reshape(tuple(w_shape)).contiguous()
+
+
+def moped_rho(w: torch.Tensor, delta: float) -> torch.Tensor:
+    """rho = log(expm1(delta*|w|) + 1e-20)  (utils/util.py:63-69) as one kernel."""
+    _require_cuda(w)
+    wc = _f32c(w.detach(), "w")
+    rho = torch.empty_like(wc)
+    with torch.cuda.device(wc.device):
+        _lib.check(_lib.lib().bt_moped_rho(_ptr(wc), _ptr(rho), wc.numel(), float(delta), _stream()), "moped_rho")
+    return rho

@@ -48,3 +48,16 @@ def cuda_device():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="session", autouse=True)
+def _built_library():
+    """The shared library is a build artefact (git-ignored); build it on first use."""
+    import importlib.util
+    lib = os.path.join(ROOT, "bayesian-torch_b200", "csrc", "libbt_b200.so")
+    if not os.path.exists(lib):
+        spec = importlib.util.spec_from_file_location("bt_build", os.path.join(ROOT, "bayesian-torch_b200", "csrc", "build.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        mod.build()
+    return lib

@@ -1,0 +1,55 @@
+"""world_size-2 gloo test of the N>1 path's host logic: sample sharding + the single
+all-reduce of the packed moment buffer reproduce the one-rank result."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, S, B, Cc, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import bayesian_torch_b200 as bt
+    torch.manual_seed(0)
+    logits = torch.randn(S, B, Cc)           # every rank can form any sample (counter-based RNG in the product)
+    first, last = bt.shard_samples(S, rank, world)
+    p = torch.softmax(logits[first:last].double(), -1)
+    buf = torch.cat([p.sum(0).flatten(), (p * p).sum(0).flatten(), (p * torch.log(p + 1e-15)).sum(-1).sum(0)]).float()
+    bt.allreduce_moments(buf)
+    if rank == 0:
+        ret.put(buf.clone())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_moment_allreduce_matches_single_rank():
+    S, B, Cc = 7, 5, 11
+    ctx = mp.get_context("spawn")
+    ret = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, S, B, Cc, ret)) for r in range(2)]
+    [p.start() for p in procs]
+    buf = ret.get(timeout=120)
+    [p.join(timeout=120) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    torch.manual_seed(0)
+    logits = torch.randn(S, B, Cc)
+    mean, var = oracle.mc_moments(logits)
+    bc = B * Cc
+    got_mean = buf[:bc].view(B, Cc).double() / S
+    got_var = buf[bc:2 * bc].view(B, Cc).double() / S - got_mean ** 2
+    torch.testing.assert_close(got_mean, mean, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(got_var, var, rtol=1e-4, atol=1e-6)
+    p = torch.softmax(logits.double(), -1)
+    mi = oracle.predictive_entropy(p) + buf[2 * bc:].double() / S
+    torch.testing.assert_close(mi, oracle.mutual_information(p), rtol=1e-4, atol=1e-5)
