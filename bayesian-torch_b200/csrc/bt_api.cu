@@ -50,7 +50,8 @@ extern "C" int64_t bt_workspace_bytes(const char* op, const bt_geom* g, int n_te
 }
 
 static int check_common(const bt_geom* g, const bt_layer_params* p, const void* x, const void* out, const char* who) {
-  BT_REQUIRE(g && p && x && out, BT_ERR_INVALID, "%s: null argument", who);
+  BT_REQUIRE(g && p, BT_ERR_INVALID, "%s: null argument", who);
+  BT_REQUIRE((x && out) || g->batch == 0, BT_ERR_INVALID, "%s: null tensor pointer", who);
   BT_REQUIRE(p->mu_w && p->rho_w, BT_ERR_INVALID, "%s: mu_w / rho_w are required", who);
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {

@@ -235,7 +235,8 @@ int bt_simt_forward(const bt_geom* geom, const bt_layer_params* lp, const void* 
   SGeo g;
   int rc = bt_sgeo_from(geom, &g, "simt forward");
   if (rc != BT_OK) return rc;
-  BT_REQUIRE(lp && lp->mu_w && lp->rho_w && x && out, BT_ERR_INVALID, "simt forward: null tensor pointer");
+  BT_REQUIRE(lp && lp->mu_w && lp->rho_w && ((x && out) || g.M == 0), BT_ERR_INVALID,
+             "simt forward: null tensor pointer");
   BT_REQUIRE((lp->mu_b == nullptr) == (lp->rho_b == nullptr), BT_ERR_INVALID,
              "simt forward: mu_b and rho_b must both be given or both be null");
   BT_REQUIRE(!(flipout && geom->n_samples > 1 && (lp->sign_in || lp->sign_out)), BT_ERR_UNSUPPORTED,
