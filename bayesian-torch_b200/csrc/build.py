@@ -24,6 +24,9 @@ def _mtime(p):
 
 def build(force: bool = False, verbose: bool = False) -> str:
     newest_hdr = max(_mtime(os.path.join(HERE, h)) for h in HEADERS)
+    newest_src = max(_mtime(os.path.join(HERE, s)) for s in SOURCES)
+    if not force and _mtime(LIB) >= max(newest_hdr, newest_src):
+        return LIB  # prebuilt library is current (the case on the GPU box)
     objs, jobs = [], []
     for src in SOURCES:
         s = os.path.join(HERE, src)

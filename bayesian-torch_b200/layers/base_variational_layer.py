@@ -225,7 +225,7 @@ class _BayesLayer(BaseVariationalLayer_):
                 call.sign_in, call.sign_out = self.sign_input, self.sign_output
         out, kl = ops.bayes_layer(call, x, mu_w, rho_w, self.mu_bias, self.rho_bias)
         if lead is not None:
-            out = out.reshape(*lead, out.shape[-1])
+            out = out.reshape(-1, *lead[1:], out.shape[-1])   # leading axis may be folded S*B
         if return_kl:
             return out, kl
         return out
