@@ -1,0 +1,135 @@
+"""tcgen05 / TMEM path (bf16 operands, fp32 accumulate, weight sampled in shared memory)
+against the CPU oracle.  The oracle is evaluated on the SAME rounded operands the kernel
+multiplies -- x in bf16 and W = bf16(mu + softplus(rho)*eps) -- so the only differences
+left are fp32 accumulation order and the bf16 rounding of the output: documented bound
+|err| <= 2^-8 * max|out| for bf16 outputs (observed ~2e-3)."""
+import pytest
+import torch
+
+import bayesian_torch_b200 as bt
+import oracle
+from bayesian_torch_b200 import _lib, ops
+from bayesian_torch_b200 import layers as L
+
+pytestmark = pytest.mark.gpu
+BF16_OUT_TOL = 2.0 ** -8
+
+
+def bf16_round(t):
+    return t.to(torch.bfloat16).to(torch.float32)
+
+
+def oracle_bf16(layer, x, conv_kw=None):
+    mu, rho = layer._w()
+    eps = getattr(layer, "eps_" + layer._wname)
+    w = bf16_round(oracle.sample_weight(mu.detach().cpu(), rho.detach().cpu(), eps.cpu()))
+    b = None
+    if layer.mu_bias is not None:
+        b = oracle.sample_weight(layer.mu_bias.detach().cpu(), layer.rho_bias.detach().cpu(), layer.eps_bias.cpu())
+    xr = bf16_round(x.cpu().float())
+    if conv_kw is None:
+        return torch.nn.functional.linear(xr.double(), w.double(), None if b is None else b.double())
+    return torch.nn.functional.conv2d(xr.double(), w.double(), None if b is None else b.double(), **conv_kw)
+
+
+def run_tc(layer, x):
+    layer.sample_mode, layer.path = "buffer", "tc"
+    out, kl = layer(x)
+    torch.cuda.synchronize()
+    return out, kl
+
+
+CONV_CASES = [
+    # cin, cout, k, stride, pad, batch, hw, bias          what it exercises
+    (64, 64, 1, 1, 0, 2, 14, True),     # 1x1, BN=64, stationary
+    (64, 64, 3, 1, 1, 3, 17, False),    # 3x3 stationary panel (K=576), ragged M
+    (64, 128, 1, 2, 0, 2, 16, True),    # strided 1x1 downsample, BN=128
+    (128, 128, 3, 1, 1, 2, 14, True),   # K=1152 > smem panel -> streaming, multi-accumulator
+    (256, 136, 3, 2, 1, 2, 15, True),   # N tail (136 = 128 + 8), stride 2, K=2304
+    (16, 32, 3, 1, 1, 2, 9, True),      # C_in < 64: several taps per k-block, K tail (144 = 2*64 + 16)
+    (8, 8, 5, 1, 2, 1, 11, False),      # 25 taps of 8 channels
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,stride,pad,batch,hw,bias", CONV_CASES)
+def test_conv2d_tc_matches_oracle(cin, cout, k, stride, pad, batch, hw, bias, cuda_device):
+    torch.manual_seed(cin * 1000 + cout + k)
+    layer = L.Conv2dReparameterization(cin, cout, k, stride=stride, padding=pad, bias=bias, prior_type="normal").to(cuda_device)
+    layer.eps_kernel.normal_()
+    if bias:
+        layer.eps_bias.normal_()
+    x = torch.randn(batch, cin, hw, hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    out, kl = run_tc(layer, x)
+    assert out.dtype == torch.bfloat16 and out.is_contiguous(memory_format=torch.channels_last)
+    want = oracle_bf16(layer, x, dict(stride=stride, padding=pad))
+    err = float((out.cpu().double() - want).abs().max() / want.abs().max())
+    assert err <= BF16_OUT_TOL, f"rel err {err}"
+    wkl = oracle.kl_normal_from_rho(layer.mu_kernel.detach(), layer.rho_kernel.detach(),
+                                    None if not bias else layer.mu_bias.detach(), None if not bias else layer.rho_bias.detach())
+    assert float(kl) == pytest.approx(float(wkl), rel=1e-5)     # KL stays fp32 whatever the GEMM precision
+
+
+@pytest.mark.parametrize("rows,k,n", [(300, 256, 192), (128, 2048, 1000), (4096, 1024, 1024), (5, 64, 8)])
+def test_linear_tc_matches_oracle(rows, k, n, cuda_device):
+    torch.manual_seed(rows + k + n)
+    layer = L.LinearReparameterization(k, n).to(cuda_device)
+    layer.eps_weight.normal_(); layer.eps_bias.normal_()
+    x = torch.randn(rows, k, device=cuda_device).bfloat16()
+    out, _ = run_tc(layer, x)
+    want = oracle_bf16(layer, x)
+    err = float((out.cpu().double() - want).abs().max() / want.abs().max())
+    assert err <= BF16_OUT_TOL, f"rel err {err}"
+
+
+def test_tc_philox_equals_exported_stream_and_simt(cuda_device):
+    """In-kernel Philox on the tensor-core path == the exported stream fed through the
+    deterministic mode == the same draw on the fp32 SIMT path (one RNG contract)."""
+    torch.manual_seed(3)
+    bt.manual_seed(99)
+    layer = L.Conv2dReparameterization(64, 128, 3, padding=1, prior_type="normal").to(cuda_device)
+    x = torch.randn(2, 64, 12, 12, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    layer.sample_mode, layer.path = "philox", "tc"
+    with bt.mc_sample(5):
+        out_p, _ = layer(x)
+    layer.eps_kernel.copy_(ops.philox_eps_weight(layer.mu_kernel.shape, ops.get_seed(), 5, layer._layer_id, cuda_device))
+    layer.eps_bias.copy_(ops.philox_normal(128, ops.get_seed(), 5, layer._layer_id, _lib.KIND_EPS_B, cuda_device))
+    out_b, _ = run_tc(layer, x)
+    assert float((out_p.float() - out_b.float()).abs().max()) <= 2.0 ** -7 * float(out_b.float().abs().max())
+    layer.sample_mode, layer.path = "philox", "simt"
+    with bt.mc_sample(5):
+        out_s, _ = layer(x)
+    err = float((out_p.float() - out_s.float()).abs().max() / out_s.float().abs().max())
+    assert err < 2e-2          # bf16 weight rounding vs fp32 weights
+    with bt.mc_sample(6):
+        layer.path = "tc"
+        other, _ = layer(x)
+    assert not torch.allclose(other.float(), out_p.float(), atol=1e-2)
+
+
+def test_tc_mc_batched_equals_sample_loop(cuda_device):
+    torch.manual_seed(4)
+    layer = L.Conv2dReparameterization(64, 64, 3, padding=1, bias=False, prior_type="normal").to(cuda_device)
+    layer.path = "tc"
+    layer.dnn_to_bnn_flag = True
+    x = torch.randn(3, 64, 10, 10, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    loop = []
+    for s in range(4):
+        with bt.mc_sample(40 + s):
+            loop.append(layer(x))
+    with bt.mc_batched(4, 40, shared_batch=3):
+        folded = layer(x)
+    torch.cuda.synchronize()
+    assert torch.equal(folded, torch.cat(loop))
+    with bt.mc_batched(4, 40):                 # per-sample inputs, as deeper layers see them
+        again = layer(torch.cat([x] * 4).contiguous(memory_format=torch.channels_last))
+    assert torch.equal(again, folded)
+
+
+def test_tc_rejects_what_it_cannot_run(cuda_device):
+    layer = L.Conv2dReparameterization(3, 16, 7, stride=2, padding=3, prior_type="normal").to(cuda_device)
+    layer.path = "tc"
+    with pytest.raises(RuntimeError, match="tensor-core path unavailable"):
+        layer(torch.randn(1, 3, 32, 32, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last))
+    layer.path = "auto"                        # auto falls back to the fp32 kernel, loudly documented in DESIGN.md
+    out, _ = layer(torch.randn(1, 3, 32, 32, device=cuda_device))
+    assert out.shape == (1, 16, 16, 16)
