@@ -61,6 +61,19 @@ static int check_common(const bt_geom* g, const bt_layer_params* p, const void* 
   return BT_OK;
 }
 
+extern "C" int bt_select_path(const bt_geom* g, const bt_layer_params* p, int flipout, int path) {
+  BT_REQUIRE(g && p, BT_ERR_INVALID, "bt_select_path: null argument");
+  const char* why = "";
+  const bool tc = bt_tc_supported(g, p, flipout != 0, &why);
+  if (path == BT_PATH_TC_BF16) {
+    BT_REQUIRE(tc, BT_ERR_UNSUPPORTED, "tensor-core path unavailable: %s", why);
+    return BT_PATH_TC_BF16;
+  }
+  if (path == BT_PATH_AUTO) return tc ? BT_PATH_TC_BF16 : BT_PATH_SIMT_F32;
+  BT_REQUIRE(path == BT_PATH_SIMT_F32, BT_ERR_INVALID, "bt_select_path: unknown path %d", path);
+  return BT_PATH_SIMT_F32;
+}
+
 static int forward_common(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, float* kl_out,
                           void* workspace, int path, bool flipout, const char* who, bt_stream_t stream) {
   int rc = check_common(g, p, x, out, who);

@@ -31,6 +31,22 @@ class _State(threading.local):
 
 
 _STATE = _State()
+
+
+class _Profile:
+    """Launch counter + optional CUDA-event timing of every layer call (bench.py roofline)."""
+
+    def __init__(self):
+        self.launches = 0        # kernels of libbt_b200.so launched (always counted)
+        self.timing = False      # record (path, flops, bytes, start, end) per layer call
+        self.records = []
+
+    def reset(self):
+        self.launches = 0
+        self.records = []
+
+
+PROFILE = _Profile()
 _layer_counter = [0]
 _counter_lock = threading.Lock()
 
@@ -403,8 +419,20 @@ class _BayesLayerFn(torch.autograd.Function):
         ws = torch.empty(max(int(L.bt_workspace_bytes(op, C.byref(g), 2)), 256), dtype=torch.uint8, device=dev)
         kl = torch.empty((), dtype=torch.float32, device=dev) if call.want_kl else None
         with torch.cuda.device(dev):
+            used = L.bt_select_path(C.byref(g), C.byref(p), int(call.flipout), call.path)
+            if PROFILE.timing:
+                ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                ev0.record()
             rc = _entry(call, False)(C.byref(g), C.byref(p), _ptr(xd), _ptr(out), _ptr(kl), _ptr(ws), call.path, _stream())
+            if PROFILE.timing:
+                ev1.record()
+                m = out.numel() // out.shape[1]
+                kred = mu_wc.numel() // mu_wc.shape[0]
+                flops = 2.0 * m * out.shape[1] * kred * (2 if call.flipout else 1)
+                nbytes = xd.numel() * xd.element_size() + out.numel() * out.element_size() + 8 * mu_wc.numel()
+                PROFILE.records.append((used, flops, nbytes, ev0, ev1))
         _lib.check(rc, "layer forward")
+        PROFILE.launches += (2 if used == _lib.PATH_TC_BF16 else 1) + (1 if call.want_kl else 0)
         ctx.call = call
         ctx.out_meta = (tuple(out.shape), tuple(out.stride()))
         ctx.save_for_backward(x, mu_w, rho_w, mu_b, rho_b)

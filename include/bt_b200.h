@@ -118,6 +118,10 @@ int bt_shutdown(void);
  * geometry; 0 when none is needed. */
 int64_t bt_workspace_bytes(const char* op, const bt_geom* g, int n_tensors);
 
+/* Which kernel family a forward call with these arguments will run on (BT_PATH_SIMT_F32 or
+ * BT_PATH_TC_BF16) given the requested `path`; negative bt_status if it cannot run at all. */
+int bt_select_path(const bt_geom* g, const bt_layer_params* p, int flipout, int path);
+
 /* ---- KL: replaces BaseVariationalLayer_.kl_div(..., 'normal') + .mean()
  *      (layers/base_variational_layer.py:55-72), every layer's kl_loss()
  *      (linear_variational.py:146-158, conv_variational.py:353-360) and the Python
