@@ -43,8 +43,10 @@ def test_oracle_forward_matches_reference(name):
     d = load_golden(name)
     out, kl, _ = run_oracle(name, d)
     # same ATen ops in the same order => bit-exact on the machine that made the
-    # fixtures; allow fp32 round-off for other CPUs / torch builds.
-    torch.testing.assert_close(out.detach(), d["out"], rtol=1e-5, atol=1e-6)
+    # fixtures; other CPUs / thread counts reorder the fp32 GEMM sums, so allow
+    # round-off proportional to the output scale (cancelling sums land near 0).
+    scale = max(float(d["out"].abs().max()), 1.0)
+    torch.testing.assert_close(out.detach(), d["out"], rtol=1e-5, atol=4e-6 * scale)
     torch.testing.assert_close(kl.detach(), d["kl"], rtol=1e-6, atol=1e-7)
 
 
