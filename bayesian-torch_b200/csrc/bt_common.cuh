@@ -88,29 +88,47 @@ __device__ __forceinline__ uint4 bt_philox(uint64_t block, const BtRngKey& key) 
   return make_uint4(c0, c1, c2, c3);
 }
 
-// Box-Muller on two 32-bit words: u = ((r >> 8) + 0.5) * 2^-24 in (0,1).
-__device__ __forceinline__ float2 bt_box_muller(uint32_t r0, uint32_t r1) {
-  const float u0 = ((float)(r0 >> 8) + 0.5f) * 5.9604644775390625e-08f;
-  const float u1 = ((float)(r1 >> 8) + 0.5f) * 5.9604644775390625e-08f;
-  const float rad = sqrtf(-2.f * __logf(u0));
+// Box-Muller on ONE 32-bit word: u0 from the high 16 bits sets the radius, u1 from the low
+// 16 bits the angle; u = (h + 0.5) * 2^-16 in (0,1), built without an int->float conversion
+// as 1.m - 1.  Radius tops out at sqrt(2 ln 2^17) = 4.85 sigma, ample for bf16 weights, and
+// one Philox4x32 call now yields EIGHT normals (the sampling cost bounds the fused GEMM).
+//   z0 = r cos(2 pi (u1 - 1/2)),  z1 = r sin(2 pi (u1 - 1/2)),  r = sqrt(-2 ln u0)
+__device__ __forceinline__ float bt_sqrt_approx(float x) {
+  float y;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float2 bt_box_muller16(uint32_t w) {
+  const float x0 = __uint_as_float(0x3F800040u | ((w >> 9) & 0x007FFF80u));  // 1 + u0
+  const float x1 = __uint_as_float(0x3F800040u | ((w << 7) & 0x007FFF80u));  // 1 + u1
+  const float rad = bt_sqrt_approx(-1.3862943611198906f * __log2f(x0 - 1.0f));
   float s, c;
-  __sincosf(6.2831853071795864f * u1, &s, &c);
+  __sincosf(6.2831853071795864f * (x1 - 1.5f), &s, &c);
   return make_float2(rad * c, rad * s);
 }
 
-// Four N(0,1) values for elements 4*block .. 4*block+3 of the stream.
-__device__ __forceinline__ float4 bt_normal4(uint64_t block, const BtRngKey& key) {
+// Eight N(0,1) values for elements 8*block .. 8*block+7 of the stream.
+__device__ __forceinline__ void bt_normal8(uint64_t block, const BtRngKey& key, float (&z)[8]) {
   const uint4 r = bt_philox(block, key);
-  const float2 a = bt_box_muller(r.x, r.y);
-  const float2 b = bt_box_muller(r.z, r.w);
+  const float2 a = bt_box_muller16(r.x), b = bt_box_muller16(r.y), c = bt_box_muller16(r.z), d = bt_box_muller16(r.w);
+  z[0] = a.x; z[1] = a.y; z[2] = b.x; z[3] = b.y; z[4] = c.x; z[5] = c.y; z[6] = d.x; z[7] = d.y;
+}
+
+// Four N(0,1) values for elements 4*quad .. 4*quad+3 (half a Philox block; the generic
+// tensor-core kernel stages float4 groups).
+__device__ __forceinline__ float4 bt_normal4(uint64_t quad, const BtRngKey& key) {
+  const uint4 r = bt_philox(quad >> 1, key);
+  const float2 a = bt_box_muller16((quad & 1) ? r.z : r.x), b = bt_box_muller16((quad & 1) ? r.w : r.y);
   return make_float4(a.x, a.y, b.x, b.y);
 }
 
-// One N(0,1) value for stream element idx (wasteful: 1 of 4 lanes used; SIMT path only).
+// One N(0,1) value for stream element idx (wasteful: 1 of 8 lanes used; SIMT path only).
 __device__ __forceinline__ float bt_normal1(uint64_t idx, const BtRngKey& key) {
-  const float4 z = bt_normal4(idx >> 2, key);
-  const int l = (int)(idx & 3);
-  return l == 0 ? z.x : (l == 1 ? z.y : (l == 2 ? z.z : z.w));
+  const uint4 r = bt_philox(idx >> 3, key);
+  const int wsel = (int)((idx >> 1) & 3);
+  const uint32_t w = wsel == 0 ? r.x : (wsel == 1 ? r.y : (wsel == 2 ? r.z : r.w));
+  const float2 z = bt_box_muller16(w);
+  return (idx & 1) ? z.y : z.x;
 }
 
 // Rademacher sign of stream element idx: bit (idx % 128) of the 128-bit block idx / 128; 1 -> -1.
@@ -156,6 +174,9 @@ int bt_simt_backward(const bt_geom* g, const bt_layer_params* p, const void* x, 
                      const float* grad_kl, const bt_layer_grads* grads, void* workspace, bool flipout,
                      cudaStream_t stream);
 bool bt_tc_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why);
+bool bt_tc2_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why);
+int bt_tc2_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
+                   bool flipout, cudaStream_t stream);
 int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
                   bool flipout, cudaStream_t stream);
 int64_t bt_tc_workspace_bytes(const bt_geom* g);

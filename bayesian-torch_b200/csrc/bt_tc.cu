@@ -20,6 +20,8 @@
 //   streaming : MT (<= 512/BN) accumulators stay resident in TMEM so each generated W k-block
 //               feeds MT m-tiles before it is overwritten.
 // Work item = (sample s, n-block, group of MT m-tiles); CTAs take contiguous item ranges.
+#include <stdlib.h>
+
 #include "bt_common.cuh"
 #include "bt_tc.cuh"
 
@@ -368,7 +370,18 @@ static int64_t weight_elems(const bt_geom* g) {
   return g->c_out * (g->c_in / g->groups) * t;
 }
 
-bool bt_tc_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why) {
+// (mu, softplus(rho), eps) -> packed [N][tap][Cin] fp32 arrays shared by both tensor-core kernels.
+int bt_tc_pack(const bt_layer_params* p, int64_t wn, int Cin, int T, float* mu_p, float* sig_p, float* eps_p,
+               cudaStream_t stream) {
+  int64_t blocks = (wn + 255) / 256;
+  const int64_t cap = (int64_t)bt_num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  tc_pack_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, wn, Cin, T);
+  BT_LAUNCH_OK("tc_pack_kernel");
+  return BT_OK;
+}
+
+bool bt_tc1_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why) {
 #define TC_NO(cond, msg) if (cond) { *why = msg; return false; }
   TC_NO(flipout, "Flipout runs on the fp32 path in this build");
   TC_NO(g->groups != 1, "groups != 1");
@@ -402,10 +415,10 @@ static int tc_launch(const TcArgs& a, int grid, int smem_bytes, cudaStream_t str
   return BT_OK;
 }
 
-int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
-                  bool flipout, cudaStream_t stream) {
+int bt_tc1_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
+                   bool flipout, cudaStream_t stream) {
   const char* why = "";
-  BT_REQUIRE(bt_tc_supported(g, p, flipout, &why), BT_ERR_UNSUPPORTED, "tensor-core forward: %s", why);
+  BT_REQUIRE(bt_tc1_supported(g, p, flipout, &why), BT_ERR_UNSUPPORTED, "tensor-core forward: %s", why);
   BT_REQUIRE(workspace, BT_ERR_INVALID, "tensor-core forward: workspace required (bt_workspace_bytes)");
   BT_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 15) == 0 && ((uintptr_t)workspace & 15) == 0, BT_ERR_ALIGN,
              "tensor-core forward: x / out / workspace must be 16-byte aligned");
@@ -444,11 +457,8 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   float* sig_p = mu_p + wn;
   float* eps_p = p->eps_w ? sig_p + wn : nullptr;
   {
-    int64_t blocks = (wn + 255) / 256;
-    const int64_t cap = (int64_t)bt_num_sms() * 8;
-    if (blocks > cap) blocks = cap;
-    tc_pack_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, wn, a.Cin, a.T);
-    BT_LAUNCH_OK("tc_pack_kernel");
+    const int rc = bt_tc_pack(p, wn, a.Cin, a.T, mu_p, sig_p, eps_p, stream);
+    if (rc != BT_OK) return rc;
   }
   a.mu_p = mu_p; a.sig_p = sig_p; a.eps_p = eps_p;
 
@@ -485,4 +495,26 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   const bool o32 = g->out_dtype == BT_F32;
   if (BN == 64) return o32 ? tc_launch<64, float>(a, grid, smem_bytes, stream) : tc_launch<64, __nv_bfloat16>(a, grid, smem_bytes, stream);
   return o32 ? tc_launch<128, float>(a, grid, smem_bytes, stream) : tc_launch<128, __nv_bfloat16>(a, grid, smem_bytes, stream);
+}
+
+// ---- dispatch between the two tensor-core kernels: the TMA-fed one (bt_tc2.cu) when the
+// tensors are dense channels-last with c_in % 64 == 0 (or Linear), else the cp.async one above.
+// BT_TC_IMPL=1|2 pins one of them (tests / profiling).
+static int tc_impl_env() {
+  const char* v = getenv("BT_TC_IMPL");
+  return v && *v ? atoi(v) : 0;
+}
+
+bool bt_tc_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why) {
+  const int pin = tc_impl_env();
+  if (pin != 1 && bt_tc2_supported(g, p, flipout, why)) return true;
+  if (pin == 2) return false;
+  return bt_tc1_supported(g, p, flipout, why);
+}
+
+int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
+                  bool flipout, cudaStream_t stream) {
+  const char* why = "";
+  if (tc_impl_env() != 1 && bt_tc2_supported(g, p, flipout, &why)) return bt_tc2_forward(g, p, x, out, workspace, flipout, stream);
+  return bt_tc1_forward(g, p, x, out, workspace, flipout, stream);
 }

@@ -27,21 +27,24 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-__device__ __forceinline__ uint64_t globaltimer_ns() {
-  uint64_t t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
 // Bounded wait: a protocol bug must surface as a trapped kernel (CUDA error on the host),
-// never as a hung GPU.  try_wait suspends in hardware, so polling the timer is cheap.
+// never as a hung GPU.  try_wait suspends the thread in hardware until the phase completes or
+// a short system time limit passes, so the loop is not a busy spin; the hang guard reads the
+// cheap SM-local clock, and only once every 4096 failed probes (%globaltimer costs about a
+// microsecond per read and used to dominate every wait that did not succeed at once).
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  const uint64_t t0 = globaltimer_ns();
+  uint32_t spins = 0;
+  long long t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (globaltimer_ns() - t0 > 4000000000ull) {  // 4 s
-      printf("bt_b200: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n", (int)blockIdx.x,
-             (int)threadIdx.x, bar, parity);
-      __trap();
+    if ((++spins & 0xFFFu) == 0) {
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > 8000000000ll) {  // ~4 s at 2 GHz
+        printf("bt_b200: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n", (int)blockIdx.x,
+               (int)threadIdx.x, bar, parity);
+        __trap();
+      }
     }
   }
 }

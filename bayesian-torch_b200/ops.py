@@ -363,6 +363,8 @@ def _like_x_format(x: torch.Tensor, shape) -> torch.Tensor:
         return torch.empty(shape, dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
     if x.dim() == 5 and x.is_contiguous(memory_format=torch.channels_last_3d) and not x.is_contiguous():
         return torch.empty(shape, dtype=x.dtype, device=x.device, memory_format=torch.channels_last_3d)
+    if x.dim() == 3 and not x.is_contiguous() and x.stride(1) == 1:
+        return torch.empty((shape[0], shape[2], shape[1]), dtype=x.dtype, device=x.device).permute(0, 2, 1)
     return torch.empty(shape, dtype=x.dtype, device=x.device)
 
 
@@ -374,6 +376,8 @@ def _dense(x: torch.Tensor) -> torch.Tensor:
         return x
     if x.dim() == 5 and x.is_contiguous(memory_format=torch.channels_last_3d):
         return x
+    if x.dim() == 3 and x.stride(1) == 1 and x.stride(2) == x.shape[1] and x.stride(0) == x.shape[1] * x.shape[2]:
+        return x   # [B, C, L] view of a dense [B, L, C] buffer: channels-last for Conv1d
     return x.contiguous()
 
 

@@ -8,8 +8,9 @@ predict it:
 
   Philox4x32-10, key = (seed_lo, seed_hi),
   counter = (block_lo, block_hi, sample_id, stream_id)
-  normals : block = elem_idx // 4; Box-Muller on (r0,r1) -> z0,z1 and (r2,r3) -> z2,z3
-            with u = ((r >> 8) + 0.5) * 2^-24
+  normals : block = elem_idx // 8; word r_i -> (z_2i, z_2i+1) by Box-Muller with
+            u0 = ((r_i >> 16) + 0.5) * 2^-16 (radius), u1 = ((r_i & 0xFFFF) + 0.5) * 2^-16 (angle):
+            z_2i = sqrt(-2 ln u0) cos(2 pi (u1 - 1/2)), z_2i+1 = sqrt(-2 ln u0) sin(2 pi (u1 - 1/2))
   signs   : block = elem_idx // 128; bit (elem_idx % 128) of r0|r1<<32|..., 1 -> -1
   stream_id = layer_id << 4 | kind, kind: 0 eps_weight, 1 eps_bias, 2 sign_in, 3 sign_out
 """
@@ -52,21 +53,21 @@ def _split_seed(seed: int):
 
 def normal(n: int, seed: int, sample_id: int, stream: int, start: int = 0) -> np.ndarray:
     """eps[start:start+n] of the (seed, sample_id, stream) normal stream, float64."""
-    idx = np.arange(start, start + n, dtype=np.uint64)
-    first, last = int(idx[0] // 4) if n else 0, int((start + n + 3) // 4)
+    first, last = (start // 8) if n else 0, (start + n + 7) // 8
     blocks = np.arange(first, last, dtype=np.uint64)
     k0, k1 = _split_seed(seed)
     r = philox4x32_10(blocks & MASK, blocks >> np.uint64(32), np.uint64(sample_id & 0xFFFFFFFF),
                       np.uint64(stream & 0xFFFFFFFF), k0, k1)
-    u = [((x >> np.uint32(8)).astype(np.float64) + 0.5) * 2.0 ** -24 for x in r]
-    z = np.empty((len(blocks), 4), dtype=np.float64)
-    for j in (0, 2):
-        rad = np.sqrt(-2.0 * np.log(u[j]))
-        ang = 2.0 * np.pi * u[j + 1]
-        z[:, j] = rad * np.cos(ang)
-        z[:, j + 1] = rad * np.sin(ang)
+    z = np.empty((len(blocks), 8), dtype=np.float64)
+    for j, w in enumerate(r):
+        u0 = ((w >> np.uint32(16)).astype(np.float64) + 0.5) * 2.0 ** -16
+        u1 = ((w & np.uint32(0xFFFF)).astype(np.float64) + 0.5) * 2.0 ** -16
+        rad = np.sqrt(-2.0 * np.log(u0))
+        ang = 2.0 * np.pi * (u1 - 0.5)
+        z[:, 2 * j] = rad * np.cos(ang)
+        z[:, 2 * j + 1] = rad * np.sin(ang)
     z = z.reshape(-1)
-    off = start - first * 4
+    off = start - first * 8
     return z[off:off + n]
 
 

@@ -48,6 +48,9 @@ CONV_CASES = [
     (256, 136, 3, 2, 1, 2, 15, True),   # N tail (136 = 128 + 8), stride 2, K=2304
     (16, 32, 3, 1, 1, 2, 9, True),      # C_in < 64: several taps per k-block, K tail (144 = 2*64 + 16)
     (8, 8, 5, 1, 2, 1, 11, False),      # 25 taps of 8 channels
+    (128, 256, 1, 1, 0, 4, 28, True),   # 1x1, two n-blocks, several m-tiles per CTA (TMA path)
+    (512, 64, 3, 1, 1, 1, 7, False),    # deep K (72 k-blocks) streaming, tiny M
+    (64, 72, 3, 1, 1, 2, 20, True),     # N = 72: second n-block has 8 live columns
 ]
 
 
@@ -69,7 +72,43 @@ def test_conv2d_tc_matches_oracle(cin, cout, k, stride, pad, batch, hw, bias, cu
     assert float(kl) == pytest.approx(float(wkl), rel=1e-5)     # KL stays fp32 whatever the GEMM precision
 
 
-@pytest.mark.parametrize("rows,k,n", [(300, 256, 192), (128, 2048, 1000), (4096, 1024, 1024), (5, 64, 8)])
+def _conv_generic(cuda_device, cin, cout, ksz, stride, pad, dil, batch, hw, out_f32=False):
+    torch.manual_seed(cin + cout)
+    layer = L.Conv2dReparameterization(cin, cout, ksz, stride=stride, padding=pad, dilation=dil, bias=True,
+                                       prior_type="normal").to(cuda_device)
+    layer.eps_kernel.normal_(); layer.eps_bias.normal_()
+    x = torch.randn(batch, cin, *hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    out, _ = run_tc(layer, x)
+    want = oracle_bf16(layer, x, dict(stride=stride, padding=pad, dilation=dil))
+    err = float((out.cpu().double() - want).abs().max() / want.abs().max())
+    assert err <= BF16_OUT_TOL, f"rel err {err}"
+
+
+@pytest.mark.parametrize("ksz,stride,pad,dil,hw", [
+    ((3, 1), (1, 1), (1, 0), (1, 1), (13, 10)),   # H-only filter: catches a swapped (W,H) corner / offset order
+    ((1, 5), (1, 2), (0, 2), (1, 1), (9, 21)),    # W-only filter, W stride 2
+    ((3, 3), (2, 1), (1, 1), (1, 1), (16, 11)),   # anisotropic stride
+    ((3, 3), (1, 1), (2, 2), (2, 2), (12, 12)),   # dilation 2
+    ((3, 2), (1, 1), (0, 1), (1, 2), (8, 9)),     # even filter width, mixed padding / dilation
+])
+def test_conv2d_tma_im2col_geometry(ksz, stride, pad, dil, hw, cuda_device):
+    _conv_generic(cuda_device, 64, 64, ksz, stride, pad, dil, 3, hw)
+
+
+def test_conv1d_tc_matches_oracle(cuda_device):
+    torch.manual_seed(11)
+    layer = L.Conv1dReparameterization(64, 128, 3, stride=2, padding=1).to(cuda_device)
+    layer.eps_kernel.normal_(); layer.eps_bias.normal_()
+    x = torch.randn(4, 37, 64, device=cuda_device).bfloat16().permute(0, 2, 1)   # [B, C, L] with channels fastest
+    out, _ = run_tc(layer, x)
+    w = bf16_round(oracle.sample_weight(layer.mu_kernel.detach().cpu(), layer.rho_kernel.detach().cpu(), layer.eps_kernel.cpu()))
+    b = oracle.sample_weight(layer.mu_bias.detach().cpu(), layer.rho_bias.detach().cpu(), layer.eps_bias.cpu())
+    want = torch.nn.functional.conv1d(bf16_round(x.cpu().float()).double(), w.double(), b.double(), stride=2, padding=1)
+    err = float((out.cpu().double() - want).abs().max() / want.abs().max())
+    assert err <= BF16_OUT_TOL, f"rel err {err}"
+
+
+@pytest.mark.parametrize("rows,k,n", [(300, 256, 192), (128, 2048, 1000), (4096, 1024, 1024), (5, 64, 8), (77, 72, 40)])
 def test_linear_tc_matches_oracle(rows, k, n, cuda_device):
     torch.manual_seed(rows + k + n)
     layer = L.LinearReparameterization(k, n).to(cuda_device)
