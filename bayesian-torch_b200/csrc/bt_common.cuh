@@ -174,9 +174,7 @@ int bt_simt_backward(const bt_geom* g, const bt_layer_params* p, const void* x, 
                      const float* grad_kl, const bt_layer_grads* grads, void* workspace, bool flipout,
                      cudaStream_t stream);
 bool bt_tc_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why);
-bool bt_tc2_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why);
-int bt_tc2_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
-                   bool flipout, cudaStream_t stream);
+
 int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
                   bool flipout, cudaStream_t stream);
 int64_t bt_tc_workspace_bytes(const bt_geom* g);

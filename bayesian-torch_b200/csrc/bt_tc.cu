@@ -1,26 +1,34 @@
-// tcgen05 / TMEM implicit GEMM with the weight tile SAMPLED IN SHARED MEMORY (sm_100a).
+// TMA-fed tcgen05 / TMEM implicit GEMM with the weight tile SAMPLED IN SHARED MEMORY (sm_100a).
 //
 //   out[s][m][n] = sum_k A(x_s)[m][k] * bf16(mu[n][k] + sigma[n][k] * eps_s[n][k]) + (mu_b + sigma_b * eps_b)[n]
 //
-// replaces, for bf16 activations, the reference's per-call sequence  log1p(exp(rho)) ->
-// normal_() -> sigma*eps -> mu+tmp -> F.linear / F.conv2d  (linear_variational.py:163-181,
-// conv_variational.py:366-385).  The sampled weight never exists in global memory: producer
-// warps turn (mu, sigma, Philox eps) into bf16 tiles written straight into the 128B-swizzled
-// shared-memory layout tcgen05.mma consumes.
+// replaces, for bf16 channels-last activations, the reference's per-call sequence
+// log1p(exp(rho)) -> normal_() -> sigma*eps -> mu+tmp -> F.linear / F.conv2d
+// (linear_variational.py:163-181, conv_variational.py:366-385).  The sampled weight never
+// exists in global memory.
 //
-// Persistent, warp-specialised CTA (1 per SM, 544 threads):
-//   warps  0-3  epilogue   : TMEM -> registers (tcgen05.ld) -> +sampled bias -> global
-//   warps  4-7  A loaders  : im2col rows of x (NHWC, bf16) by 16-byte cp.async into swizzled smem
-//   warps  8-15 W producers: mu + sigma*eps -> bf16 -> swizzled smem (in-register Philox4x32-10)
-//   warp   16   MMA issuer : one thread issues tcgen05.mma (M=128, N=BN, K=16), accumulators in TMEM
-// Pipelines (all mbarrier based): A ring (a_full/a_empty), W ring (w_full/w_empty), accumulator
-// sets in TMEM (acc_full/acc_empty).  Two ways to amortise the sampling cost over the batch:
-//   stationary: the whole [BN x K] sampled panel fits in shared memory -> generated once per
-//               (sample, n-block) and reused for every m-tile the CTA owns;
-//   streaming : MT (<= 512/BN) accumulators stay resident in TMEM so each generated W k-block
-//               feeds MT m-tiles before it is overwritten.
-// Work item = (sample s, n-block, group of MT m-tiles); CTAs take contiguous item ranges.
+// Persistent warp-specialised CTA, one per SM:
+//   warps 0-3   epilogue : tcgen05.ld -> +sampled bias -> bf16/f32 -> swizzled smem -> TMA store
+//   warp  4     A loader : ONE thread issues TMA loads; convolutions use the im2col tensor-map
+//                          mode (cuTensorMapEncodeIm2col), so the 128-pixel x 64-channel tile of one
+//                          filter tap lands in the 128B-swizzled K-major layout tcgen05.mma reads,
+//                          padding zero-filled by the hardware; Linear uses a tiled 2-d map
+//   warps 5-6   MMA      : two issuer warps (tile t of an m-group -> issuer t % 2), each a
+//                          warp-uniform loop whose elected lane issues tcgen05.mma (M=128, N=BN,
+//                          K=16) into TMEM accumulators.  Measured on B200 (tools/ubench/pipe2.cu):
+//                          one issuing thread costs ~340 cycles per 4-MMA ring slot against 256
+//                          cycles of tensor work at N=128, two issuers overlap completely
+//   warps 7-14  W producers: mu + sigma * eps -> bf16 -> swizzled smem, eps from in-register
+//                          Philox4x32-10 (8 normals per call) or the caller's tensor
+// mbarrier pipelines: A ring (TMA complete_tx / tcgen05.commit), W ring or stationary panel,
+// accumulator sets in TMEM.  The sampling cost is amortised over the batch either by keeping
+// the whole [BN x K] sampled panel in shared memory (stationary) or by keeping MT accumulators
+// resident in TMEM so one generated k-block feeds MT m-tiles (streaming).
+#include <cuda.h>
 #include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
 
 #include "bt_common.cuh"
 #include "bt_tc.cuh"
@@ -29,492 +37,829 @@ using namespace btc;
 
 namespace {
 
-constexpr int BM = 128;          // UMMA M
-constexpr int BK = 64;           // k-block: 64 bf16 = one 128-byte swizzle row
+constexpr int BM = 128;
+constexpr int BK = 64;
 constexpr int A_SLOT = BM * BK * 2;  // 16 KB
-constexpr int CTRL_BYTES = 3072;
-constexpr int MAX_NA = 12, MAX_RW = 24, MAX_SETS = 8, MAX_MT = 4, MAX_TAPS = 64;
-constexpr int NUM_THREADS = 17 * 32;
-constexpr int A_LAG = 2;         // cp.async groups in flight per loader thread
+constexpr int CTRL_BYTES = 2048;
+constexpr int STAGE_BYTES = 4 * 2 * 4096;  // per epilogue warp: 2 buffers of 32 rows x 128 B (1 when smem is tight)
+constexpr int N_PROD_WARPS = 8;
+constexpr int N_MMA_WARPS = 2;  // issuer warps: tile t of an m-group belongs to issuer t % 2
+constexpr int WARP_TMA = 4, WARP_MMA = 5, WARP_PROD0 = WARP_MMA + N_MMA_WARPS;
+constexpr int NUM_THREADS = (WARP_PROD0 + N_PROD_WARPS) * 32;  // 480
+constexpr int PROD_THREADS = N_PROD_WARPS * 32;
+constexpr int MAX_NA = 8, MAX_RW = 24, MAX_SETS = 8, MAX_MT = 4;
 constexpr int SMEM_LIMIT = 232448;
+constexpr int RING_BYTES = SMEM_LIMIT - 1024 - CTRL_BYTES - STAGE_BYTES;  // A ring + W ring / panel
 
-struct TcArgs {
-  const __nv_bfloat16* x;
-  void* out;
-  const float *mu_p, *sig_p, *eps_p;   // packed [N][K], k = tap*Cin + c
+struct Tc2Args {
+  const float *mu_p, *sig_p, *eps_p;  // packed [N][K], k = tap*Cin + c
   const float *mu_b, *rho_b, *eps_b;
-  int64_t M, total_items;
-  int64_t xss, xbs, xs0, xs1, xs2, oss, obs, os0, os1, os2;
-  int N, K, Cin, C8, T, S, NB;
-  int ID, IH, IW, OD, OH, OW, KH, KW;
-  int sd, sh, sw, pd, ph, pw, dd, dh, dw;
+  int64_t total_items;
+  int N, K, S, NB;   // K: GEMM reduction length = row pitch of the packed parameter arrays
+  int Kt;            // true reduction length (pitch of the RNG stream); < K when the patch matrix pads K up to 8
+  int Ms;            // GEMM rows per sample: batch * OH * OW
+  int x_rows_per_s;  // images (conv) / rows (linear) per sample in x; 0 when all samples share x
+  int conv;          // 1: im2col map, 0: tiled 2-d map
+  int OH, OW, KW, CB;  // CB = Cin / 64: k-blocks per filter tap
+  int sh, sw, ph, pw, dh, dw;
   int num_mt, num_mg, MT, NSETS, nkb, NA, RW, stationary;
+  int NR, NAr;       // A rings (one per active MMA issuer) and slots per ring; NA = NR * NAr
+  int stage_bufs;    // epilogue staging buffers per warp (2, or 1 when shared memory is tight)
+  int debug;         // BT_TC2_DEBUG bits (timing experiments only): 1 = skip the output stores
   uint64_t seed;
   uint32_t sample_id, layer_id;
 };
 
-struct Ctrl {  // lives in the first CTRL_BYTES of dynamic shared memory
+struct Ctrl {
   uint64_t a_full[MAX_NA], a_empty[MAX_NA];
   uint64_t w_full[MAX_RW], w_empty[MAX_RW];
   uint64_t acc_full[MAX_SETS], acc_empty[MAX_SETS];
   uint32_t tmem_base;
   uint32_t pad[3];
   float bias[256];
-  int4 taps[MAX_TAPS];
 };
 static_assert(sizeof(Ctrl) <= CTRL_BYTES, "control block too large");
 
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c, int w, int h,
+                                                   int n, uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], "
+      "[%2], {%7, %8};"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+__device__ __forceinline__ bool elect_one() {  // one lane of the (converged) warp
+  uint32_t is_leader;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(is_leader));
+  return is_leader != 0;
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+
 // ---------------------------------------------------------------- parameter packing ----
-// mu[n][c][tap] -> mu_p[n][tap*Cin + c], sigma_p = softplus(rho) likewise (sigma does not depend on
-// the sample, so it is hoisted out of the per-sample loop), optional eps likewise.
-__global__ void tc_pack_kernel(const float* __restrict__ mu, const float* __restrict__ rho,
-                               const float* __restrict__ eps, float* __restrict__ mu_p, float* __restrict__ sig_p,
-                               float* __restrict__ eps_p, int64_t total, int Cin, int T) {
+// mu[n][c][tap] -> mu_p[n][tap*Cin + c] with row pitch Kp (zero beyond K), sigma_p = softplus(rho)
+// likewise (sigma does not depend on the sample: hoisted out of the per-sample work), eps likewise.
+__global__ void tc2_pack_kernel(const float* __restrict__ mu, const float* __restrict__ rho,
+                                const float* __restrict__ eps, float* __restrict__ mu_p, float* __restrict__ sig_p,
+                                float* __restrict__ eps_p, int64_t total, int Cin, int T, int Kp) {
+  const int K = Cin * T;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    // i indexes the packed layout: (n, tap, c)
-    const int64_t K = (int64_t)Cin * T;
-    const int64_t n = i / K;
-    const int64_t r = i - n * K;
-    const int64_t tap = r / Cin, c = r - tap * Cin;
-    const int64_t src = n * K + c * T + tap;
-    mu_p[i] = mu[src];
-    sig_p[i] = bt_softplus(rho[src]);
-    if (eps_p) eps_p[i] = eps[src];
+    const int64_t n = i / Kp;
+    const int k = (int)(i - n * Kp);
+    float m = 0.f, sg = 0.f, e = 0.f;
+    if (k < K) {
+      const int tap = k / Cin, c = k - tap * Cin;
+      const int64_t src = n * K + (int64_t)c * T + tap;
+      m = mu[src];
+      sg = bt_softplus(rho[src]);
+      if (eps_p) e = eps[src];
+    }
+    mu_p[i] = m;
+    sig_p[i] = sg;
+    if (eps_p) eps_p[i] = e;
+  }
+}
+
+// ---------------------------------------------------------------- patch matrix ----
+// Explicit im2col of x into a dense bf16 matrix A[row][k], k = tap*Cin + c, row pitch Kp, for
+// convolutions the im2col tensor map cannot describe (C_in not a multiple of 64 -- the RGB stem --
+// rank 3, or x not channels-last).  Costs rows*Kp*2 bytes of extra traffic, paid once per call
+// and shared by every Monte-Carlo sample of the call when x is shared.
+struct PatchGeo {
+  int64_t rows, xbs, xcs, xs0, xs1, xs2;
+  int Kp, K, Cin, KH, KW;
+  int OD, OH, OW, ID, IH, IW;
+  int sd, sh, sw, pd, ph, pw, dd, dh, dw;
+};
+
+template <typename TX>
+__global__ void tc2_patch_kernel(const TX* __restrict__ x, __nv_bfloat16* __restrict__ A, const PatchGeo g) {
+  const int C8 = g.Kp >> 3;
+  const int64_t total = g.rows * C8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = i / C8;
+    const int chunk = (int)(i - row * C8);
+    int64_t r = row;
+    const int ow = (int)(r % g.OW); r /= g.OW;
+    const int oh = (int)(r % g.OH); r /= g.OH;
+    const int od = (int)(r % g.OD); r /= g.OD;
+    const TX* xi = x + r * g.xbs;
+    const int id0 = od * g.sd - g.pd, ih0 = oh * g.sh - g.ph, iw0 = ow * g.sw - g.pw;
+    int k = chunk * 8;
+    int tap = k / g.Cin, c = k - tap * g.Cin;
+    int kw = tap % g.KW, kh = (tap / g.KW) % g.KH, kd = tap / (g.KW * g.KH);
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e, ++k) {
+      v[e] = 0.f;
+      if (k < g.K) {
+        const int id = id0 + kd * g.dd, ih = ih0 + kh * g.dh, iw = iw0 + kw * g.dw;
+        if ((unsigned)id < (unsigned)g.ID && (unsigned)ih < (unsigned)g.IH && (unsigned)iw < (unsigned)g.IW)
+          v[e] = bt_to_float<TX>(xi[(int64_t)c * g.xcs + (int64_t)id * g.xs0 + (int64_t)ih * g.xs1 + (int64_t)iw * g.xs2]);
+      }
+      if (++c == g.Cin) { c = 0; if (++kw == g.KW) { kw = 0; if (++kh == g.KH) { kh = 0; ++kd; } } }
+    }
+    uint4 pk;
+    pk.x = pack_bf16(v[0], v[1]); pk.y = pack_bf16(v[2], v[3]); pk.z = pack_bf16(v[4], v[5]); pk.w = pack_bf16(v[6], v[7]);
+    *reinterpret_cast<uint4*>(A + row * g.Kp + chunk * 8) = pk;
   }
 }
 
 template <int BN, typename TO>
-__global__ void __launch_bounds__(NUM_THREADS, 1) tc_fwd_kernel(const __grid_constant__ TcArgs a) {
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_out,
+               const __grid_constant__ Tc2Args a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
-  uint8_t* smem = smem_raw + (base - raw);
-  Ctrl* ctrl = reinterpret_cast<Ctrl*>(smem);
+  Ctrl* ctrl = reinterpret_cast<Ctrl*>(smem_raw + (base - raw));
   constexpr int W_SLOT = BN * BK * 2;
-  const uint32_t a_base = base + CTRL_BYTES;
+  constexpr int SUBN = 128 / (int)sizeof(TO);  // output columns per 128-byte staging row
+  const uint32_t stage_base = base + CTRL_BYTES;
+  const uint32_t a_base = stage_base + (uint32_t)a.stage_bufs * 16384u;
   const uint32_t w_base = a_base + a.NA * A_SLOT;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  // ---- one-time setup
   if (threadIdx.x == 0) {
-    for (int i = 0; i < a.NA; ++i) { mbar_init(smem_u32(&ctrl->a_full[i]), 128); mbar_init(smem_u32(&ctrl->a_empty[i]), 1); }
-    for (int i = 0; i < a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), 256); mbar_init(smem_u32(&ctrl->w_empty[i]), 1); }
-    for (int i = 0; i < a.NSETS; ++i) { mbar_init(smem_u32(&ctrl->acc_full[i]), 1); mbar_init(smem_u32(&ctrl->acc_empty[i]), 128); }
+    for (int i = 0; i < a.NA; ++i) { mbar_init(smem_u32(&ctrl->a_full[i]), 1); mbar_init(smem_u32(&ctrl->a_empty[i]), 1); }
+    for (int i = 0; i < a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), N_PROD_WARPS); mbar_init(smem_u32(&ctrl->w_empty[i]), N_MMA_WARPS); }
+    for (int i = 0; i < a.NSETS; ++i) { mbar_init(smem_u32(&ctrl->acc_full[i]), N_MMA_WARPS); mbar_init(smem_u32(&ctrl->acc_empty[i]), 128); }
     mbar_fence_init();
   }
-  for (int t = threadIdx.x; t < a.T; t += NUM_THREADS) {
-    const int kw = t % a.KW, kh = (t / a.KW) % a.KH, kd = t / (a.KW * a.KH);
-    ctrl->taps[t] = make_int4(kd * a.dd, kh * a.dh, kw * a.dw, 0);
-  }
-  if (warp == 16) tmem_alloc(smem_u32(&ctrl->tmem_base), 512);
+  if (warp == WARP_TMA && lane == 0) { prefetch_tmap(&tm_a); prefetch_tmap(&tm_out); }
+  if (warp == WARP_MMA) tmem_alloc(smem_u32(&ctrl->tmem_base), 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = ctrl->tmem_base;
 
-  // contiguous, balanced item range of this CTA
   const int64_t i0 = a.total_items * blockIdx.x / gridDim.x;
   const int64_t i1 = a.total_items * (blockIdx.x + 1) / gridDim.x;
+  const int n_items = (int)(i1 - i0);
+  // first item of this CTA, decoded once; the role loops then walk (s, nb, mg) incrementally --
+  // the single-thread TMA / MMA loops are instruction-latency bound, so no division or modulo
+  // by a run-time value may sit inside them.
+  const int64_t key0 = i0 / a.num_mg;
+  const int mg0 = (int)(i0 - key0 * a.num_mg);
+  const int s0 = (int)(key0 / a.NB), nb0 = (int)(key0 - (int64_t)s0 * a.NB);
 
   if (warp < 4) {
     // =========================== EPILOGUE ===========================
-    const int q = warp;  // TMEM lane quarter this warp may read
-    int64_t itcount = 0;
-    for (int64_t it = i0; it < i1; ++it, ++itcount) {
-      const int64_t key = it / a.num_mg;
-      const int mg = (int)(it - key * a.num_mg);
-      const int s = (int)(key / a.NB), nb = (int)(key % a.NB);
-      const int set = (int)(itcount % a.NSETS);
-      const uint32_t ph = (uint32_t)((itcount / a.NSETS) & 1);
-      // sampled bias of this (sample, n-block): mu_b + softplus(rho_b) * eps_b
-      named_bar_sync(1, 128);
-      for (int j = threadIdx.x; j < BN; j += 128) {
-        const int n = nb * BN + j;
-        float b = 0.f;
-        if (a.mu_b && n < a.N) {
-          const float e = a.eps_b ? a.eps_b[n]
-                                  : bt_normal1((uint64_t)n, bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_B));
-          b = a.mu_b[n] + bt_softplus(a.rho_b[n]) * e;
+    const int q = warp;
+    const uint32_t my_stage = stage_base + (uint32_t)(q * a.stage_bufs) * 4096u;
+    const uint32_t row_sw = (uint32_t)(lane & 7);
+    uint32_t nstore = 0;
+    int s = s0, nb = nb0, mg = mg0, set = 0;
+    uint32_t set_phase = 0;
+    for (int it = 0; it < n_items; ++it) {
+      if (a.mu_b) {
+        named_bar_sync(1, 128);  // previous item's readers of ctrl->bias are done
+        for (int j = threadIdx.x; j < BN; j += 128) {
+          const int n = nb * BN + j;
+          float b = 0.f;
+          if (n < a.N) {
+            const float e = a.eps_b ? a.eps_b[n]
+                                    : bt_normal1((uint64_t)n, bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_B));
+            b = a.mu_b[n] + bt_softplus(a.rho_b[n]) * e;
+          }
+          ctrl->bias[j] = b;
         }
-        ctrl->bias[j] = b;
+        named_bar_sync(1, 128);
       }
-      named_bar_sync(1, 128);
-      mbar_wait(smem_u32(&ctrl->acc_full[set]), ph);
+      mbar_wait(smem_u32(&ctrl->acc_full[set]), set_phase);
       tc_fence_after();
       const int mtv = min(a.MT, a.num_mt - mg * a.MT);
       for (int t = 0; t < mtv; ++t) {
-        const int64_t m = ((int64_t)(mg * a.MT + t)) * BM + q * 32 + lane;
-        const bool valid = m < a.M;
-        TO* orow = nullptr;
-        if (valid) {
-          int64_t r = m;
-          const int ow = (int)(r % a.OW); r /= a.OW;
-          const int oh = (int)(r % a.OH); r /= a.OH;
-          const int od = (int)(r % a.OD); r /= a.OD;
-          orow = reinterpret_cast<TO*>(a.out) + (int64_t)s * a.oss + r * a.obs + (int64_t)od * a.os0 +
-                 (int64_t)oh * a.os1 + (int64_t)ow * a.os2 + (int64_t)nb * BN;
-        }
+        const int m0 = (mg * a.MT + t) * BM + q * 32;  // first row of this warp's 32-row slab
+        if (m0 >= a.Ms) break;                          // slab entirely past the sample's last row (warp-uniform)
         const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)((set * a.MT + t) * BN);
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-          uint32_t v[32];
-          tmem_ld32(tacc + c * 32, v);
+        for (int sub = 0; sub < BN / SUBN; ++sub) {
+          const int n0 = nb * BN + sub * SUBN;
+          if (n0 >= a.N) break;  // warp-uniform
+          uint32_t v[SUBN];
+          if constexpr (SUBN == 64) {
+            tmem_ld32(tacc + sub * SUBN, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+            tmem_ld32(tacc + sub * SUBN + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+          } else {
+            tmem_ld32(tacc + sub * SUBN, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+          }
           tmem_ld_wait();
-          if (valid) {
-            const int ncol0 = nb * BN + c * 32;
+          // the TMA store that last read this staging buffer must have drained it
+          uint32_t buf = my_stage;
+          if (a.stage_bufs == 2) {
+            buf += (nstore & 1u) * 4096u;
+            if (nstore >= 2) {
+              if (lane == 0) tma_store_wait_read<1>();
+              __syncwarp();
+            }
+          } else if (nstore >= 1) {
+            if (lane == 0) tma_store_wait_read<0>();
+            __syncwarp();
+          }
+          const uint32_t rowaddr = buf + (uint32_t)lane * 128u;
 #pragma unroll
-            for (int j8 = 0; j8 < 4; ++j8) {
-              if (ncol0 + j8 * 8 >= a.N) break;  // N % 8 == 0: an 8-column chunk is all in or all out
+          for (int j = 0; j < 8; ++j) {  // 16-byte chunks of the 128-byte row
+            uint32_t w0, w1, w2, w3;
+            if constexpr (SUBN == 64) {
+              const float* bs = &ctrl->bias[sub * SUBN + j * 8];
               float f[8];
 #pragma unroll
-              for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[j8 * 8 + j]) + ctrl->bias[c * 32 + j8 * 8 + j];
-              if constexpr (sizeof(TO) == 2) {
-                uint4 pk;
-                __nv_bfloat162 h;
-                h = __floats2bfloat162_rn(f[0], f[1]); pk.x = *reinterpret_cast<uint32_t*>(&h);
-                h = __floats2bfloat162_rn(f[2], f[3]); pk.y = *reinterpret_cast<uint32_t*>(&h);
-                h = __floats2bfloat162_rn(f[4], f[5]); pk.z = *reinterpret_cast<uint32_t*>(&h);
-                h = __floats2bfloat162_rn(f[6], f[7]); pk.w = *reinterpret_cast<uint32_t*>(&h);
-                *reinterpret_cast<uint4*>(orow + c * 32 + j8 * 8) = pk;
-              } else {
-                *reinterpret_cast<float4*>(orow + c * 32 + j8 * 8) = make_float4(f[0], f[1], f[2], f[3]);
-                *reinterpret_cast<float4*>(orow + c * 32 + j8 * 8 + 4) = make_float4(f[4], f[5], f[6], f[7]);
-              }
+              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j * 8 + e]) + (a.mu_b ? bs[e] : 0.f);
+              w0 = pack_bf16(f[0], f[1]); w1 = pack_bf16(f[2], f[3]); w2 = pack_bf16(f[4], f[5]); w3 = pack_bf16(f[6], f[7]);
+            } else {
+              const float* bs = &ctrl->bias[sub * SUBN + j * 4];
+              w0 = __float_as_uint(__uint_as_float(v[j * 4 + 0]) + (a.mu_b ? bs[0] : 0.f));
+              w1 = __float_as_uint(__uint_as_float(v[j * 4 + 1]) + (a.mu_b ? bs[1] : 0.f));
+              w2 = __float_as_uint(__uint_as_float(v[j * 4 + 2]) + (a.mu_b ? bs[2] : 0.f));
+              w3 = __float_as_uint(__uint_as_float(v[j * 4 + 3]) + (a.mu_b ? bs[3] : 0.f));
             }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((uint32_t)j ^ row_sw) << 4)), "r"(w0),
+                         "r"(w1), "r"(w2), "r"(w3)
+                         : "memory");
           }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0 && !(a.debug & 1)) {
+            tma_store_3d(&tm_out, buf, n0, m0, s);  // rows >= Ms and columns >= N are clipped by the map
+            tma_store_commit();
+          }
+          ++nstore;
         }
       }
       tc_fence_before();
       mbar_arrive(smem_u32(&ctrl->acc_empty[set]));
+      if (++set == a.NSETS) { set = 0; set_phase ^= 1u; }
+      if (++mg == a.num_mg) { mg = 0; if (++nb == a.NB) { nb = 0; ++s; } }
     }
-  } else if (warp < 8) {
-    // =========================== A LOADERS (im2col, cp.async) ===========================
-    const int r = threadIdx.x - 128;  // tile row owned by this thread
-    const uint32_t row_off = (uint32_t)r * 128u;
-    const uint32_t sw = (uint32_t)(r & 7);
-    int64_t acount = 0;
-    for (int64_t it = i0; it < i1; ++it) {
-      const int64_t key = it / a.num_mg;
-      const int mg = (int)(it - key * a.num_mg);
-      const int s = (int)(key / a.NB);
+    if (lane == 0) tma_store_wait_all();
+  } else if (warp == WARP_TMA) {
+    // =========================== A LOADER (TMA) ===========================
+    // warp-uniform loop (every lane waits, the elected lane issues): keeps the loop state in
+    // uniform registers and off the divergent-code path.
+    const bool leader = elect_one();
+    // Every mbarrier has ONE waiter per side that observes each of its phases (parity waits
+    // alias when a waiter skips a phase): tile t of an m-group travels through ring t % NR,
+    // which only issuer t % NR consumes.
+    int s = s0, mg = mg0, nb = nb0;
+    int rslot[N_MMA_WARPS] = {0, 0};
+    uint32_t rphase[N_MMA_WARPS] = {0, 0};
+    const int Cin = a.CB * BK;
+    for (int it = 0; it < n_items; ++it) {
       const int mtv = min(a.MT, a.num_mt - mg * a.MT);
-      // decode this thread's row of every m-tile of the group once
-      int64_t xoff[MAX_MT];
-      int id0[MAX_MT], ih0[MAX_MT], iw0[MAX_MT];
+      int cw[MAX_MT], chh[MAX_MT], cn[MAX_MT];
 #pragma unroll
       for (int t = 0; t < MAX_MT; ++t) {
-        xoff[t] = -1; id0[t] = 0; ih0[t] = 0; iw0[t] = 0;
-        if (t < mtv) {
-          const int64_t m = ((int64_t)(mg * a.MT + t)) * BM + r;
-          if (m < a.M) {
-            int64_t rr = m;
-            const int ow = (int)(rr % a.OW); rr /= a.OW;
-            const int oh = (int)(rr % a.OH); rr /= a.OH;
-            const int od = (int)(rr % a.OD); rr /= a.OD;
-            xoff[t] = (int64_t)s * a.xss + rr * a.xbs;
-            id0[t] = od * a.sd - a.pd; ih0[t] = oh * a.sh - a.ph; iw0[t] = ow * a.sw - a.pw;
-          }
+        const int m = (mg * a.MT + t) * BM;
+        cw[t] = 0; chh[t] = 0;
+        cn[t] = s * a.x_rows_per_s + m;
+        if (a.conv) {
+          const int r = m / a.OW;
+          const int b = r / a.OH;
+          cw[t] = (m - r * a.OW) * a.sw - a.pw;
+          chh[t] = (r - b * a.OH) * a.sh - a.ph;
+          cn[t] = s * a.x_rows_per_s + b;
         }
       }
+      int c0 = 0, offw = 0, offh = 0, kw = 0;
       for (int kb = 0; kb < a.nkb; ++kb) {
-        const int q0 = kb * 8;  // first 16-byte chunk (8 channels) of this k-block
-        const int tap0 = q0 / a.C8, c80 = q0 - tap0 * a.C8;
 #pragma unroll
         for (int t = 0; t < MAX_MT; ++t) {
-          if (t >= mtv) break;
-          const int slot = (int)(acount % a.NA);
-          mbar_wait(smem_u32(&ctrl->a_empty[slot]), (uint32_t)(((acount / a.NA) & 1) ^ 1));
-          const uint32_t dst = a_base + slot * A_SLOT + row_off;
-          int tap = tap0, c8 = c80;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const void* src = a.x;
-            uint32_t nbytes = 0;
-            if (xoff[t] >= 0 && tap < a.T) {
-              const int4 tp = ctrl->taps[tap];
-              const int id = id0[t] + tp.x, ih = ih0[t] + tp.y, iw = iw0[t] + tp.z;
-              if ((unsigned)id < (unsigned)a.ID && (unsigned)ih < (unsigned)a.IH && (unsigned)iw < (unsigned)a.IW) {
-                src = a.x + xoff[t] + (int64_t)id * a.xs0 + (int64_t)ih * a.xs1 + (int64_t)iw * a.xs2 + c8 * 8;
-                nbytes = 16;
+          if (t < mtv) {
+            const int r = t % N_MMA_WARPS;
+            const int ring = a.NR == 2 ? r : 0;
+            const int slot = ring * a.NAr + (a.NR == 2 ? rslot[r] : rslot[0]);
+            mbar_wait(smem_u32(&ctrl->a_empty[slot]), (a.NR == 2 ? rphase[r] : rphase[0]) ^ 1u);
+            if (leader) {
+              const uint32_t bar = smem_u32(&ctrl->a_full[slot]);
+              if (a.debug & 8) {
+                mbar_arrive(bar);
+              } else {
+                mbar_expect_tx(bar, A_SLOT);
+                if (a.conv)
+                  tma_load_im2col_4d(a_base + slot * A_SLOT, &tm_a, bar, c0, cw[t], chh[t], cn[t], (uint16_t)offw, (uint16_t)offh);
+                else
+                  tma_load_2d(a_base + slot * A_SLOT, &tm_a, bar, c0, cn[t]);
               }
             }
-            cp_async_16(dst + (((uint32_t)j ^ sw) << 4), src, nbytes);
-            if (++c8 == a.C8) { c8 = 0; ++tap; }
-          }
-          cp_async_commit();
-          if (acount >= A_LAG) {
-            cp_async_wait<A_LAG>();
-            fence_proxy_async();
-            mbar_arrive(smem_u32(&ctrl->a_full[(acount - A_LAG) % a.NA]));
-          }
-          ++acount;
-        }
-      }
-    }
-    cp_async_wait<0>();
-    fence_proxy_async();
-    for (int64_t j = (acount > A_LAG ? acount - A_LAG : 0); j < acount; ++j) mbar_arrive(smem_u32(&ctrl->a_full[j % a.NA]));
-  } else if (warp < 16) {
-    // =========================== W PRODUCERS (sample in smem) ===========================
-    const int p = threadIdx.x - 256;
-    const int col4 = p & 15;        // float4 (4 consecutive k) within the 64-wide k-block
-    const int row_base = p >> 4;    // 0..15, rows row_base + 16*i
-    const uint32_t col_off = (uint32_t)(col4 & 1) * 8u;
-    const uint32_t chunk16 = (uint32_t)(col4 >> 1);
-    int64_t wcount = 0, prev_key = -1;
-    for (int64_t it = i0; it < i1; ++it) {
-      const int64_t key = it / a.num_mg;
-      const bool new_gen = !a.stationary || key != prev_key;
-      prev_key = key;
-      if (!new_gen) continue;
-      const int s = (int)(key / a.NB), nb = (int)(key % a.NB);
-      const BtRngKey rk = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_W);
-      for (int kb = 0; kb < a.nkb; ++kb, ++wcount) {
-        const int slot = (int)(wcount % a.RW);
-        const int k = kb * BK + col4 * 4;
-        const bool kin = k < a.K;  // K % 8 == 0: a float4 is all in or all out
-        constexpr int HALF = BN / 32;  // rows per thread per half-tile (register budget: 96/thread)
-        const uint32_t wdst = w_base + slot * W_SLOT;
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          float4 mu4[HALF], sg4[HALF];
-#pragma unroll
-          for (int i = 0; i < HALF; ++i) {  // loads first (L2-resident parameters)
-            const int n = nb * BN + row_base + 16 * (h * HALF + i);
-            mu4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            sg4[i] = mu4[i];
-            if (kin && n < a.N) {
-              const int64_t e = (int64_t)n * a.K + k;
-              mu4[i] = __ldg(reinterpret_cast<const float4*>(a.mu_p + e));
-              sg4[i] = __ldg(reinterpret_cast<const float4*>(a.sig_p + e));
-            }
-          }
-          if (h == 0) mbar_wait(smem_u32(&ctrl->w_empty[slot]), (uint32_t)(((wcount / a.RW) & 1) ^ 1));
-#pragma unroll
-          for (int i = 0; i < HALF; ++i) {
-            const int row = row_base + 16 * (h * HALF + i);
-            const int n = nb * BN + row;
-            float4 e4 = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (kin && n < a.N) {
-              const int64_t e = (int64_t)n * a.K + k;
-              e4 = a.eps_p ? __ldg(reinterpret_cast<const float4*>(a.eps_p + e)) : bt_normal4((uint64_t)e >> 2, rk);
-            }
-            const __nv_bfloat162 lo = __floats2bfloat162_rn(fmaf(sg4[i].x, e4.x, mu4[i].x), fmaf(sg4[i].y, e4.y, mu4[i].y));
-            const __nv_bfloat162 hi = __floats2bfloat162_rn(fmaf(sg4[i].z, e4.z, mu4[i].z), fmaf(sg4[i].w, e4.w, mu4[i].w));
-            const uint32_t addr = wdst + (uint32_t)row * 128u + ((chunk16 ^ (uint32_t)(row & 7)) << 4) + col_off;
-            asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(*reinterpret_cast<const uint32_t*>(&lo)),
-                         "r"(*reinterpret_cast<const uint32_t*>(&hi))
-                         : "memory");
+            if (a.NR == 2) { if (++rslot[r] == a.NAr) { rslot[r] = 0; rphase[r] ^= 1u; } }
+            else if (++rslot[0] == a.NAr) { rslot[0] = 0; rphase[0] ^= 1u; }
           }
         }
-        fence_proxy_async();
-        mbar_arrive(smem_u32(&ctrl->w_full[slot]));
-      }
-    }
-  } else {
-    // =========================== MMA ISSUER ===========================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
-      int64_t acount = 0, wuse = 0, gen_base = 0, itcount = 0, prev_key = -1;
-      for (int64_t it = i0; it < i1; ++it, ++itcount) {
-        const int64_t key = it / a.num_mg;
-        const int mg = (int)(it - key * a.num_mg);
-        const bool first = !a.stationary || key != prev_key;
-        const bool last = !a.stationary || it + 1 == i1 || (it + 1) / a.num_mg != key;
-        prev_key = key;
-        if (first) { gen_base = wuse; wuse += a.nkb; }
-        const int set = (int)(itcount % a.NSETS);
-        mbar_wait(smem_u32(&ctrl->acc_empty[set]), (uint32_t)(((itcount / a.NSETS) & 1) ^ 1));
-        tc_fence_after();
-        const int mtv = min(a.MT, a.num_mt - mg * a.MT);
-        for (int kb = 0; kb < a.nkb; ++kb) {
-          const int64_t widx = gen_base + kb;
-          const int wslot = (int)(widx % a.RW);
-          if (first) {
-            mbar_wait(smem_u32(&ctrl->w_full[wslot]), (uint32_t)((widx / a.RW) & 1));
-            tc_fence_after();
-          }
-          const uint64_t bdesc = umma_desc_sw128(w_base + wslot * W_SLOT);
-          for (int t = 0; t < mtv; ++t, ++acount) {
-            const int aslot = (int)(acount % a.NA);
-            mbar_wait(smem_u32(&ctrl->a_full[aslot]), (uint32_t)((acount / a.NA) & 1));
-            tc_fence_after();
-            const uint64_t adesc = umma_desc_sw128(a_base + aslot * A_SLOT);
-            const uint32_t d = tmem + (uint32_t)((set * a.MT + t) * BN);
-#pragma unroll
-            for (int k = 0; k < BK / 16; ++k)  // +32 bytes (>>4 = 2) per K=16 step inside the swizzle atom
-              umma_bf16(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
-            umma_commit(smem_u32(&ctrl->a_empty[aslot]));
-          }
-          if (last) umma_commit(smem_u32(&ctrl->w_empty[wslot]));
+        c0 += BK;
+        if (a.conv && c0 == Cin) {  // next filter tap
+          c0 = 0;
+          offw += a.dw;
+          if (++kw == a.KW) { kw = 0; offw = 0; offh += a.dh; }
         }
-        umma_commit(smem_u32(&ctrl->acc_full[set]));
       }
+      if (++mg == a.num_mg) { mg = 0; if (++nb == a.NB) { nb = 0; ++s; } }
     }
     __syncwarp();
+  } else if (warp < WARP_PROD0) {
+    // =========================== MMA ISSUERS ===========================
+    const int j = warp - WARP_MMA;  // this issuer owns tiles t with t % N_MMA_WARPS == j
+    const bool leader = elect_one();
+    constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+    int mg = mg0, set = 0, aslot = 0, wslot_r = 0;
+    uint32_t set_phase = 0, aphase = 0, wphase = 0;
+    bool first = true;  // first item of a (sample, n-block) key on this CTA: its W panel is new
+    const int ring0 = (a.NR == 2 ? j : 0) * a.NAr;  // first slot of the A ring this issuer consumes
+    for (int it = 0; it < n_items; ++it) {
+      const bool last = !a.stationary || it + 1 == n_items || mg + 1 == a.num_mg;
+      mbar_wait(smem_u32(&ctrl->acc_empty[set]), set_phase ^ 1u);
+      tc_fence_after();
+      const int mtv = min(a.MT, a.num_mt - mg * a.MT);
+      const uint32_t dbase = tmem + (uint32_t)(set * a.MT * BN);
+      for (int kb = 0; kb < a.nkb; ++kb) {
+        const int wslot = a.stationary ? kb : wslot_r;
+        if (first) {
+          mbar_wait(smem_u32(&ctrl->w_full[wslot]), wphase);
+          tc_fence_after();
+        }
+        const uint64_t bdesc = umma_desc_sw128(w_base + wslot * W_SLOT);
+#pragma unroll
+        for (int t = 0; t < MAX_MT; ++t) {
+          if (t < mtv) {
+            if ((a.NR == 2 ? (t % N_MMA_WARPS) : 0) == j) {
+              const int slot = ring0 + aslot;
+              mbar_wait(smem_u32(&ctrl->a_full[slot]), aphase);
+              tc_fence_after();
+              if (leader) {
+                const uint64_t adesc = umma_desc_sw128(a_base + slot * A_SLOT);
+                const uint32_t d = dbase + (uint32_t)(t * BN);
+                if (!(a.debug & 4)) {
+#pragma unroll
+                  for (int k = 0; k < BK / 16; ++k)
+                    umma_bf16(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                }
+                umma_commit(smem_u32(&ctrl->a_empty[slot]));
+              }
+              __syncwarp();
+              if (++aslot == a.NAr) { aslot = 0; aphase ^= 1u; }
+            }
+          }
+        }
+        if (last && leader) umma_commit(smem_u32(&ctrl->w_empty[wslot]));
+        if (!a.stationary && ++wslot_r == a.RW) { wslot_r = 0; wphase ^= 1u; }
+      }
+      if (leader) umma_commit(smem_u32(&ctrl->acc_full[set]));
+      __syncwarp();
+      if (++set == a.NSETS) { set = 0; set_phase ^= 1u; }
+      if (a.stationary) {
+        if (last) wphase ^= 1u;  // the next key's panel is the next generation of every slot
+        first = last;
+      }
+      if (++mg == a.num_mg) mg = 0;
+    }
+  } else {
+    // =========================== W PRODUCERS (sample in smem) ===========================
+    const int p = threadIdx.x - WARP_PROD0 * 32;
+    const int chunk = p & 7;      // 16-byte chunk (8 consecutive k) of the 128-byte row
+    const int row_base = p >> 3;  // rows row_base + 32*i
+    constexpr int ROWS_PER_THREAD = BN / (PROD_THREADS / 8);
+    int s = s0, nb = nb0, mg = mg0, wslot_r = 0;
+    uint32_t wphase = 0;
+    bool first = true;
+    for (int it = 0; it < n_items; ++it) {
+      if (first || !a.stationary) {
+        const BtRngKey rk = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_W);
+        for (int kb = 0; kb < a.nkb; ++kb) {
+          const int slot = a.stationary ? kb : wslot_r;
+          const int k = kb * BK + chunk * 8;
+          const bool kin = k < a.K;  // K % 8 == 0: a chunk is all in or all out
+          const uint32_t wdst = w_base + slot * W_SLOT;
+          float4 mu4[ROWS_PER_THREAD][2], sg4[ROWS_PER_THREAD][2];
+#pragma unroll
+          for (int i = 0; i < ROWS_PER_THREAD; ++i) {  // parameter loads first (L2 resident), then the slot wait
+            const int n = nb * BN + row_base + (PROD_THREADS / 8) * i;
+            mu4[i][0] = mu4[i][1] = sg4[i][0] = sg4[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (kin && n < a.N) {
+              const int64_t e = (int64_t)n * a.K + k;
+              mu4[i][0] = __ldg(reinterpret_cast<const float4*>(a.mu_p + e));
+              mu4[i][1] = __ldg(reinterpret_cast<const float4*>(a.mu_p + e + 4));
+              sg4[i][0] = __ldg(reinterpret_cast<const float4*>(a.sig_p + e));
+              sg4[i][1] = __ldg(reinterpret_cast<const float4*>(a.sig_p + e + 4));
+            }
+          }
+          mbar_wait(smem_u32(&ctrl->w_empty[slot]), wphase ^ 1u);
+#pragma unroll
+          for (int i = 0; i < ROWS_PER_THREAD; ++i) {
+            const int row = row_base + (PROD_THREADS / 8) * i;
+            const int n = nb * BN + row;
+            float z[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) z[e] = 0.f;
+            if (kin && n < a.N) {
+              const int64_t e = (int64_t)n * a.K + k;
+              if (a.eps_p) {
+                const float4 e0 = __ldg(reinterpret_cast<const float4*>(a.eps_p + e));
+                const float4 e1 = __ldg(reinterpret_cast<const float4*>(a.eps_p + e + 4));
+                z[0] = e0.x; z[1] = e0.y; z[2] = e0.z; z[3] = e0.w; z[4] = e1.x; z[5] = e1.y; z[6] = e1.z; z[7] = e1.w;
+              } else if (a.Kt == a.K) {
+                bt_normal8((uint64_t)e >> 3, rk, z);
+              } else {  // padded K (patch matrix): this chunk straddles two Philox blocks of the true stream
+                const uint64_t e0 = (uint64_t)n * a.Kt + k;
+                float zz[16];
+                bt_normal8(e0 >> 3, rk, *reinterpret_cast<float(*)[8]>(&zz[0]));
+                bt_normal8((e0 >> 3) + 1, rk, *reinterpret_cast<float(*)[8]>(&zz[8]));
+                const int off = (int)(e0 & 7);
+#pragma unroll
+                for (int o = 0; o < 8; ++o)
+                  if (o == off) {
+#pragma unroll
+                    for (int i2 = 0; i2 < 8; ++i2) z[i2] = (k + i2 < a.Kt) ? zz[o + i2] : 0.f;
+                  }
+              }
+            }
+            const uint32_t w0 = pack_bf16(fmaf(sg4[i][0].x, z[0], mu4[i][0].x), fmaf(sg4[i][0].y, z[1], mu4[i][0].y));
+            const uint32_t w1 = pack_bf16(fmaf(sg4[i][0].z, z[2], mu4[i][0].z), fmaf(sg4[i][0].w, z[3], mu4[i][0].w));
+            const uint32_t w2 = pack_bf16(fmaf(sg4[i][1].x, z[4], mu4[i][1].x), fmaf(sg4[i][1].y, z[5], mu4[i][1].y));
+            const uint32_t w3 = pack_bf16(fmaf(sg4[i][1].z, z[6], mu4[i][1].z), fmaf(sg4[i][1].w, z[7], mu4[i][1].w));
+            const uint32_t addr = wdst + (uint32_t)row * 128u + (((uint32_t)chunk ^ (uint32_t)(row & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&ctrl->w_full[slot]));
+          if (!a.stationary && ++wslot_r == a.RW) { wslot_r = 0; wphase ^= 1u; }
+        }
+        if (a.stationary) wphase ^= 1u;
+      }
+      first = false;
+      if (++mg == a.num_mg) { mg = 0; first = true; if (++nb == a.NB) { nb = 0; ++s; } }
+    }
   }
 
-  // ---- teardown
   tc_fence_before();
   __syncthreads();
-  if (warp == 16) tmem_dealloc(tmem, 512);
+  if (warp == WARP_MMA) tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------ host side ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+struct DriverFns {
+  EncodeTiledFn tiled = nullptr;
+  EncodeIm2colFn im2col = nullptr;
+  int driver_version = 0;
+  bool ok = false;
+};
+
+const DriverFns& driver_fns() {
+  static DriverFns f;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      f.tiled = (EncodeTiledFn)p;
+    p = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      f.im2col = (EncodeIm2colFn)p;
+    cudaDriverGetVersion(&f.driver_version);
+    f.ok = f.tiled && f.im2col;
+    cudaGetLastError();
+  });
+  return f;
+}
+
+struct Dense {  // the dense channels-last view the tensor maps describe
+  int64_t in[2], out[2], k[2], st[2], pd[2], dl[2];
+};
+
+// rank 1 is run as rank 2 with a unit H axis.
+bool conv_dims(const bt_geom* g, Dense* d, int64_t* xs_h, int64_t* xs_w, int64_t* os_h, int64_t* os_w) {
+  if (g->rank == 2) {
+    for (int i = 0; i < 2; ++i) {
+      d->in[i] = g->in_size[i]; d->out[i] = g->out_size[i]; d->k[i] = g->k_size[i];
+      d->st[i] = g->stride[i]; d->pd[i] = g->pad[i]; d->dl[i] = g->dil[i];
+    }
+    *xs_h = g->x_sp_stride[0]; *xs_w = g->x_sp_stride[1]; *os_h = g->out_sp_stride[0]; *os_w = g->out_sp_stride[1];
+    return true;
+  }
+  if (g->rank == 1) {
+    d->in[0] = d->out[0] = d->k[0] = d->st[0] = d->dl[0] = 1; d->pd[0] = 0;
+    d->in[1] = g->in_size[0]; d->out[1] = g->out_size[0]; d->k[1] = g->k_size[0];
+    d->st[1] = g->stride[0]; d->pd[1] = g->pad[0]; d->dl[1] = g->dil[0];
+    *xs_w = g->x_sp_stride[0]; *os_w = g->out_sp_stride[0];
+    *xs_h = d->in[1] * *xs_w; *os_h = d->out[1] * *os_w;
+    return true;
+  }
+  return false;
 }
 
 }  // namespace
 
-// ------------------------------------------------------------------------ host side ----
-static int64_t weight_elems(const bt_geom* g) {
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
+
+// How the A operand (activations) reaches shared memory.
+enum AMode { A_NONE = 0, A_GEMM = 1, A_IM2COL = 2, A_PATCH = 3 };
+
+struct Plan {
+  AMode mode;
+  int64_t rows_per_s;  // GEMM rows per sample
+  int64_t x_rows;      // rows (A_GEMM / A_PATCH) or images (A_IM2COL) per sample in the A source
+  int64_t pitch;       // A_GEMM: row pitch of x in elements
+  int T, K, Kp;        // taps, true reduction length, padded reduction length
+  Dense d;
+  int64_t xh, xw;
+};
+
+static int64_t prod_out(const bt_geom* g) {
   int64_t t = 1;
-  for (int i = 0; i < g->rank; ++i) t *= g->k_size[i];
-  return g->c_out * (g->c_in / g->groups) * t;
+  for (int i = 0; i < g->rank; ++i) t *= g->out_size[i];
+  return t;
 }
 
-// (mu, softplus(rho), eps) -> packed [N][tap][Cin] fp32 arrays shared by both tensor-core kernels.
-int bt_tc_pack(const bt_layer_params* p, int64_t wn, int Cin, int T, float* mu_p, float* sig_p, float* eps_p,
-               cudaStream_t stream) {
-  int64_t blocks = (wn + 255) / 256;
-  const int64_t cap = (int64_t)bt_num_sms() * 8;
-  if (blocks > cap) blocks = cap;
-  tc_pack_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, wn, Cin, T);
-  BT_LAUNCH_OK("tc_pack_kernel");
-  return BT_OK;
-}
-
-bool bt_tc1_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why) {
+static bool tc2_plan(const bt_geom* g, const bt_layer_params* p, bool flipout, Plan* pl, const char** why) {
 #define TC_NO(cond, msg) if (cond) { *why = msg; return false; }
-  TC_NO(flipout, "Flipout runs on the fp32 path in this build");
+  memset(pl, 0, sizeof(*pl));
+  TC_NO(flipout, "Flipout is not on the tensor-core path");
   TC_NO(g->groups != 1, "groups != 1");
   TC_NO(g->x_dtype != BT_BF16, "activations are not bf16");
-  TC_NO(g->x_chan_stride != 1 || g->out_chan_stride != 1, "channels are not the fastest axis (need channels-last)");
-  TC_NO(g->c_in % 8 != 0 || g->c_out % 8 != 0, "c_in / c_out not multiples of 8");
-  int64_t taps = 1;
-  for (int i = 0; i < g->rank; ++i) {
-    taps *= g->k_size[i];
-    TC_NO(g->x_sp_stride[i] % 8 != 0 || g->out_sp_stride[i] % 8 != 0, "spatial strides not multiples of 8 elements");
-  }
-  TC_NO(taps > MAX_TAPS, "kernel volume > 64 taps");
-  TC_NO(g->x_batch_stride % 8 != 0 || g->out_batch_stride % 8 != 0 || g->x_sample_stride % 8 != 0 ||
-            g->out_sample_stride % 8 != 0, "batch strides not multiples of 8 elements");
-  TC_NO(g->n_samples > 1 && (p->eps_w || p->eps_b), "tensor-fed eps with n_samples > 1");
+  TC_NO(g->out_chan_stride != 1, "output channels are not the fastest axis (need channels-last)");
+  TC_NO(g->c_out % 8 != 0, "c_out is not a multiple of 8");
   TC_NO(g->batch <= 0, "empty batch");
-#undef TC_NO
+  TC_NO(g->n_samples > 1 && (p->eps_w || p->eps_b), "tensor-fed eps with n_samples > 1");
+  TC_NO(!driver_fns().ok, "cuTensorMapEncode* entry points unavailable");
+  // the output must be one dense [samples][rows][c_out] matrix
+  int64_t dense = g->c_out, taps = 1;
+  for (int i = g->rank - 1; i >= 0; --i) {
+    TC_NO(g->out_sp_stride[i] != dense, "output is not dense channels-last");
+    dense *= g->out_size[i];
+    taps *= g->k_size[i];
+    TC_NO(g->in_size[i] <= 0 || g->k_size[i] <= 0 || g->stride[i] <= 0 || g->dil[i] <= 0 || g->pad[i] < 0, "bad conv parameters");
+    const int64_t expect = (g->in_size[i] + 2 * g->pad[i] - g->dil[i] * (g->k_size[i] - 1) - 1) / g->stride[i] + 1;
+    TC_NO(g->out_size[i] != expect || expect <= 0, "out_size inconsistent with the conv arithmetic");
+  }
+  TC_NO(g->out_batch_stride != dense, "output is not dense channels-last");
+  TC_NO(g->n_samples > 1 && g->out_sample_stride != g->batch * dense, "out samples are not stacked densely");
+  const bool x_shared = g->n_samples > 1 && g->x_sample_stride == 0;
+  TC_NO(g->n_samples > 1 && !x_shared && g->x_sample_stride != g->batch * g->x_batch_stride, "x samples are not stacked densely");
+  pl->rows_per_s = g->batch * prod_out(g);
+  TC_NO(pl->rows_per_s >= (1ll << 30), "too many output positions");
+  pl->T = (int)taps;
+  TC_NO(g->c_in * taps >= (1ll << 24), "reduction length too large");
+  pl->K = (int)(g->c_in * taps);
+  pl->Kp = (pl->K + 7) & ~7;
+  const int pin = env_int("BT_TC2_AMODE", 0);
+  if (g->rank == 0) {
+    if (g->x_chan_stride == 1 && g->x_batch_stride % 8 == 0 && g->c_in % 8 == 0 && pin != A_PATCH) {
+      pl->mode = A_GEMM; pl->x_rows = g->batch; pl->pitch = g->x_batch_stride;
+      return true;
+    }
+  } else if (g->rank <= 2 && g->x_chan_stride == 1 && g->c_in % 64 == 0 && pin != A_PATCH) {
+    conv_dims(g, &pl->d, &pl->xh, &pl->xw, &dense, &taps);
+    const Dense& d = pl->d;
+    bool ok = pl->xw % 8 == 0 && pl->xh % 8 == 0 && g->x_batch_stride % 8 == 0;
+    for (int i = 0; i < 2; ++i)
+      ok = ok && d.st[i] <= 8 && d.pd[i] <= 127 && (d.k[i] - 1) * d.dl[i] - d.pd[i] <= 128 && (d.k[i] - 1) * d.dl[i] <= 65535;
+    if (ok) {
+      // A 1x1 / stride 1 / unpadded convolution over a dense tensor IS a GEMM over [pixels, channels]
+      if (d.k[0] == 1 && d.k[1] == 1 && d.st[0] == 1 && d.st[1] == 1 && d.pd[0] == 0 && d.pd[1] == 0 &&
+          pl->xh == d.in[1] * pl->xw && g->x_batch_stride == d.in[0] * pl->xh && pin != A_IM2COL) {
+        pl->mode = A_GEMM; pl->x_rows = g->batch * d.in[0] * d.in[1]; pl->pitch = pl->xw;
+      } else {
+        pl->mode = A_IM2COL; pl->x_rows = g->batch;
+      }
+      return true;
+    }
+  }
+  // anything else with a dense channels-last output: explicit patch matrix, then a GEMM
+  TC_NO(taps > 4096, "kernel volume > 4096 taps");
+  pl->mode = A_PATCH;
+  pl->x_rows = pl->rows_per_s;
+  pl->pitch = pl->Kp;
   return true;
+#undef TC_NO
 }
 
+bool bt_tc_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why) {
+  Plan pl;
+  return tc2_plan(g, p, flipout, &pl, why);
+}
+
+// bytes of the caller's workspace the forward needs: packed (mu, sigma, eps) + the patch matrix
 int64_t bt_tc_workspace_bytes(const bt_geom* g) {
-  const int64_t wn = weight_elems(g);
-  return ((3 * wn * 4 + 255) / 256) * 256;  // mu_p, sigma_p, eps_p
+  int64_t taps = 1;
+  for (int i = 0; i < g->rank; ++i) taps *= g->k_size[i];
+  const int64_t Kp = (g->c_in / (g->groups > 0 ? g->groups : 1) * taps + 7) & ~7ll;
+  int64_t bytes = ((3 * g->c_out * Kp * 4 + 255) / 256) * 256;
+  const bool gemm_like = g->rank == 0 && g->x_chan_stride == 1 && g->c_in % 8 == 0 && g->x_batch_stride % 8 == 0;
+  const bool im2col_like = g->rank >= 1 && g->rank <= 2 && g->x_chan_stride == 1 && g->c_in % 64 == 0;
+  if ((!gemm_like && !im2col_like) || env_int("BT_TC2_AMODE", 0) == A_PATCH) {
+    const bool x_shared = g->n_samples > 1 && g->x_sample_stride == 0;
+    bytes += ((g->batch * prod_out(g) * (x_shared ? 1 : g->n_samples) * Kp * 2 + 255) / 256) * 256;
+  }
+  return bytes;
 }
 
 template <int BN, typename TO>
-static int tc_launch(const TcArgs& a, int grid, int smem_bytes, cudaStream_t stream) {
-  BT_CUDA_OK(cudaFuncSetAttribute(tc_fwd_kernel<BN, TO>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-  tc_fwd_kernel<BN, TO><<<grid, NUM_THREADS, smem_bytes, stream>>>(a);
-  BT_LAUNCH_OK("tc_fwd_kernel");
+static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const Tc2Args& a, int grid, int smem_bytes,
+                      cudaStream_t stream) {
+  BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  tc2_fwd_kernel<BN, TO><<<grid, NUM_THREADS, smem_bytes, stream>>>(ta, to, a);
+  BT_LAUNCH_OK("tc2_fwd_kernel");
   return BT_OK;
 }
 
-int bt_tc1_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
+int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
                    bool flipout, cudaStream_t stream) {
   const char* why = "";
-  BT_REQUIRE(bt_tc1_supported(g, p, flipout, &why), BT_ERR_UNSUPPORTED, "tensor-core forward: %s", why);
+  Plan pl;
+  BT_REQUIRE(tc2_plan(g, p, flipout, &pl, &why), BT_ERR_UNSUPPORTED, "tensor-core forward: %s", why);
   BT_REQUIRE(workspace, BT_ERR_INVALID, "tensor-core forward: workspace required (bt_workspace_bytes)");
-  BT_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 15) == 0 && ((uintptr_t)workspace & 15) == 0, BT_ERR_ALIGN,
-             "tensor-core forward: x / out / workspace must be 16-byte aligned");
-  TcArgs a;
+  BT_REQUIRE(((uintptr_t)out & 15) == 0 && ((uintptr_t)workspace & 15) == 0 && (pl.mode == A_PATCH || ((uintptr_t)x & 15) == 0),
+             BT_ERR_ALIGN, "tensor-core forward: x / out / workspace must be 16-byte aligned");
+  const DriverFns& drv = driver_fns();
+  Tc2Args a;
   memset(&a, 0, sizeof(a));
-  int64_t in[3] = {1, 1, 1}, o[3] = {1, 1, 1}, k[3] = {1, 1, 1}, s[3] = {1, 1, 1}, pd[3] = {0, 0, 0}, d[3] = {1, 1, 1},
-          xs[3] = {0, 0, 0}, os[3] = {0, 0, 0};
-  for (int i = 0; i < g->rank; ++i) {
-    const int j = 3 - g->rank + i;
-    in[j] = g->in_size[i]; o[j] = g->out_size[i]; k[j] = g->k_size[i]; s[j] = g->stride[i]; pd[j] = g->pad[i];
-    d[j] = g->dil[i]; xs[j] = g->x_sp_stride[i]; os[j] = g->out_sp_stride[i];
-    const int64_t expect = (in[j] + 2 * pd[j] - d[j] * (k[j] - 1) - 1) / s[j] + 1;
-    BT_REQUIRE(o[j] == expect && o[j] > 0, BT_ERR_INVALID, "tensor-core forward: inconsistent out_size[%d]", i);
-  }
-  a.x = (const __nv_bfloat16*)x;
-  a.out = out;
+  const int S = g->n_samples;
+  const bool x_shared = S > 1 && g->x_sample_stride == 0;
+  a.N = (int)g->c_out;
+  a.S = S;
   a.mu_b = p->mu_b; a.rho_b = p->rho_b; a.eps_b = p->eps_b;
-  a.M = g->batch * o[0] * o[1] * o[2];
-  a.N = (int)g->c_out; a.Cin = (int)g->c_in; a.C8 = a.Cin / 8;
-  a.T = (int)(k[0] * k[1] * k[2]);
-  a.K = a.Cin * a.T;
-  a.S = g->n_samples;
-  a.ID = (int)in[0]; a.IH = (int)in[1]; a.IW = (int)in[2];
-  a.OD = (int)o[0]; a.OH = (int)o[1]; a.OW = (int)o[2];
-  a.KH = (int)k[1]; a.KW = (int)k[2];
-  a.sd = (int)s[0]; a.sh = (int)s[1]; a.sw = (int)s[2];
-  a.pd = (int)pd[0]; a.ph = (int)pd[1]; a.pw = (int)pd[2];
-  a.dd = (int)d[0]; a.dh = (int)d[1]; a.dw = (int)d[2];
-  a.xss = g->x_sample_stride; a.xbs = g->x_batch_stride; a.xs0 = xs[0]; a.xs1 = xs[1]; a.xs2 = xs[2];
-  a.oss = g->out_sample_stride; a.obs = g->out_batch_stride; a.os0 = os[0]; a.os1 = os[1]; a.os2 = os[2];
   a.seed = p->seed; a.sample_id = p->sample_id; a.layer_id = p->layer_id;
+  a.debug = env_int("BT_TC2_DEBUG", 0);
+  a.Ms = (int)pl.rows_per_s;
+  a.Kt = pl.K;
+  a.K = pl.mode == A_PATCH ? pl.Kp : pl.K;
+  a.x_rows_per_s = x_shared ? 0 : (int)pl.x_rows;
+  alignas(64) CUtensorMap tm_a, tm_out;
+  const int es_o = g->out_dtype == BT_F32 ? 4 : 2;
 
-  // ---- pack (mu, softplus(rho), eps) into the kernel's k order
+  // ---- workspace carve-up: packed parameters, then (A_PATCH) the patch matrix
   const int64_t wn = (int64_t)a.N * a.K;
   float* mu_p = (float*)workspace;
   float* sig_p = mu_p + wn;
   float* eps_p = p->eps_w ? sig_p + wn : nullptr;
+  __nv_bfloat16* patches = (__nv_bfloat16*)((char*)workspace + ((3 * wn * 4 + 255) / 256) * 256);
   {
-    const int rc = bt_tc_pack(p, wn, a.Cin, a.T, mu_p, sig_p, eps_p, stream);
-    if (rc != BT_OK) return rc;
+    int64_t blocks = (wn + 255) / 256;
+    const int64_t cap = (int64_t)bt_num_sms() * 8;
+    if (blocks > cap) blocks = cap;
+    tc2_pack_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, wn, (int)g->c_in, pl.T, a.K);
+    BT_LAUNCH_OK("tc2_pack_kernel");
   }
   a.mu_p = mu_p; a.sig_p = sig_p; a.eps_p = eps_p;
 
+  const void* a_src = x;
+  if (pl.mode == A_PATCH) {
+    PatchGeo pg;
+    memset(&pg, 0, sizeof(pg));
+    int64_t in[3] = {1, 1, 1}, o[3] = {1, 1, 1}, k[3] = {1, 1, 1}, st[3] = {1, 1, 1}, pd[3] = {0, 0, 0}, dl[3] = {1, 1, 1}, xs[3] = {0, 0, 0};
+    for (int i = 0; i < g->rank; ++i) {
+      const int j = 3 - g->rank + i;
+      in[j] = g->in_size[i]; o[j] = g->out_size[i]; k[j] = g->k_size[i]; st[j] = g->stride[i]; pd[j] = g->pad[i];
+      dl[j] = g->dil[i]; xs[j] = g->x_sp_stride[i];
+    }
+    pg.rows = pl.rows_per_s * (x_shared ? 1 : S);
+    pg.xbs = g->x_batch_stride; pg.xcs = g->x_chan_stride; pg.xs0 = xs[0]; pg.xs1 = xs[1]; pg.xs2 = xs[2];
+    pg.Kp = pl.Kp; pg.K = pl.K; pg.Cin = (int)g->c_in; pg.KH = (int)k[1]; pg.KW = (int)k[2];
+    pg.OD = (int)o[0]; pg.OH = (int)o[1]; pg.OW = (int)o[2]; pg.ID = (int)in[0]; pg.IH = (int)in[1]; pg.IW = (int)in[2];
+    pg.sd = (int)st[0]; pg.sh = (int)st[1]; pg.sw = (int)st[2]; pg.pd = (int)pd[0]; pg.ph = (int)pd[1]; pg.pw = (int)pd[2];
+    pg.dd = (int)dl[0]; pg.dh = (int)dl[1]; pg.dw = (int)dl[2];
+    int64_t blocks = (pg.rows * (pg.Kp / 8) + 255) / 256;
+    const int64_t cap = (int64_t)bt_num_sms() * 16;
+    if (blocks > cap) blocks = cap;
+    // (stacked samples of x are just more images: the batch stride walks across them)
+    tc2_patch_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, stream>>>((const __nv_bfloat16*)x, patches, pg);
+    BT_LAUNCH_OK("tc2_patch_kernel");
+    a_src = patches;
+  }
+
+  if (pl.mode == A_GEMM || pl.mode == A_PATCH) {
+    a.conv = 0;
+    const cuuint64_t rows = (cuuint64_t)pl.x_rows * (x_shared ? 1 : S);
+    const cuuint64_t gdim[2] = {(cuuint64_t)a.K, rows};
+    const cuuint64_t gstr[1] = {(cuuint64_t)pl.pitch * 2};
+    const cuuint32_t box[2] = {BK, BM};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = drv.tiled(&tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(a_src), gdim, gstr, box, estr,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    BT_REQUIRE(r == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeTiled(x) failed with %d", (int)r);
+  } else {
+    const Dense& d = pl.d;
+    a.conv = 1;
+    a.CB = (int)g->c_in / BK;
+    a.OH = (int)d.out[0]; a.OW = (int)d.out[1]; a.KW = (int)d.k[1];
+    a.sh = (int)d.st[0]; a.sw = (int)d.st[1]; a.ph = (int)d.pd[0]; a.pw = (int)d.pd[1]; a.dh = (int)d.dl[0]; a.dw = (int)d.dl[1];
+    const cuuint64_t imgs = (cuuint64_t)g->batch * (x_shared ? 1 : S);
+    const cuuint64_t gdim[4] = {(cuuint64_t)g->c_in, (cuuint64_t)d.in[1], (cuuint64_t)d.in[0], imgs};
+    const cuuint64_t gstr[3] = {(cuuint64_t)pl.xw * 2, (cuuint64_t)pl.xh * 2, (cuuint64_t)g->x_batch_stride * 2};
+    // bounding box of the filter's top-left corner, in (W, H) order like the coordinates
+    const int lower[2] = {-(int)d.pd[1], -(int)d.pd[0]};
+    const int upper[2] = {(int)(d.pd[1] - (d.k[1] - 1) * d.dl[1]), (int)(d.pd[0] - (d.k[0] - 1) * d.dl[0])};
+    const cuuint32_t estr[4] = {1, (cuuint32_t)d.st[1], (cuuint32_t)d.st[0], 1};
+    const CUresult r = drv.im2col(&tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), gdim, gstr, lower, upper,
+                                  BK, BM, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    BT_REQUIRE(r == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeIm2col(x) failed with %d", (int)r);
+    // Small-tensor workaround of drivers <= 13.1 (same fix-up CUTLASS applies to im2col descriptors).
+    const int64_t span = (int64_t)imgs * g->x_batch_stride * 2;
+    if (drv.driver_version <= 13010 && span < 131072) reinterpret_cast<uint64_t*>(&tm_a)[1] &= ~(1ull << 21);
+  }
+  {
+    const cuuint64_t gdim[3] = {(cuuint64_t)a.N, (cuuint64_t)a.Ms, (cuuint64_t)S};
+    const cuuint64_t gstr[2] = {(cuuint64_t)a.N * es_o, (cuuint64_t)a.Ms * a.N * es_o};
+    const cuuint32_t box[3] = {(cuuint32_t)(128 / es_o), 32, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = drv.tiled(&tm_out, es_o == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3,
+                                 out, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    BT_REQUIRE(r == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeTiled(out) failed with %d", (int)r);
+  }
+
   // ---- tiling / pipeline configuration
-  const int BN = a.N <= 64 ? 64 : 128;
-  const int NSLOTS = 512 / BN;
+  const int sms = bt_num_sms();
+  a.num_mt = (a.Ms + BM - 1) / BM;
+  a.nkb = (a.K + BK - 1) / BK;
+  int BN = a.N <= 64 ? 64 : 128;
+  // a [BN x K] panel that fits next to a 4-deep A ring is generated once per (sample, n-block)
+  // (with single-buffered epilogue staging there are 16 KB more)
+  auto panel_fits = [&](int bn) { return a.nkb <= MAX_RW && (int64_t)a.nkb * bn * BK * 2 + 4 * A_SLOT <= RING_BYTES + STAGE_BYTES / 2; };
+  const int force_bn = env_int("BT_TC2_BN", 0), force_mt = env_int("BT_TC2_MT", 0), force_stat = env_int("BT_TC2_STATIONARY", -1);
+  if (BN == 128 && !panel_fits(128) && panel_fits(64)) BN = 64;
+  if (force_bn == 64 || force_bn == 128) BN = force_bn;
   const int WB = BN * BK * 2;
   a.NB = (a.N + BN - 1) / BN;
-  a.num_mt = (int)((a.M + BM - 1) / BM);
-  a.nkb = (a.K + BK - 1) / BK;
-  const int avail = SMEM_LIMIT - 1024 - CTRL_BYTES;
-  const int sms = bt_num_sms();
-  a.stationary = (a.nkb <= MAX_RW && (int64_t)a.nkb * WB + 4 * A_SLOT <= avail) ? 1 : 0;
+  a.stationary = panel_fits(BN) ? 1 : 0;
+  if (force_stat == 0) a.stationary = 0;
+  const int NSLOTS = 512 / BN;
   if (a.stationary) {
     a.RW = a.nkb;
-    a.MT = 1;
+    a.MT = a.num_mt >= 2 ? 2 : 1;  // one tile per issuer warp
+    if (force_mt >= 1 && force_mt <= MAX_MT && force_mt <= NSLOTS) a.MT = force_mt;
   } else {
-    a.RW = 3;
     a.MT = 1;
     for (int mt = NSLOTS < MAX_MT ? NSLOTS : MAX_MT; mt >= 1; mt >>= 1) {
       const int64_t items = (int64_t)a.S * a.NB * ((a.num_mt + mt - 1) / mt);
-      if (items >= sms || mt == 1) { a.MT = mt; break; }
+      if (items >= sms || mt == 1 || (mt == 2 && a.num_mt >= 2)) { a.MT = mt; break; }
     }
+    if (force_mt >= 1 && force_mt <= MAX_MT && force_mt <= NSLOTS) a.MT = force_mt;
+    a.RW = (RING_BYTES - 4 * A_SLOT) / WB;
+    if (a.RW > 8) a.RW = 8;
   }
   a.NSETS = NSLOTS / a.MT;
   if (a.NSETS > MAX_SETS) a.NSETS = MAX_SETS;
   a.num_mg = (a.num_mt + a.MT - 1) / a.MT;
-  a.NA = (avail - a.RW * WB) / A_SLOT;
+  a.stage_bufs = 2;
+  a.NA = (RING_BYTES - a.RW * WB) / A_SLOT;
+  if (a.NA < 4) { a.stage_bufs = 1; a.NA = (RING_BYTES + STAGE_BYTES / 2 - a.RW * WB) / A_SLOT; }
   if (a.NA > MAX_NA) a.NA = MAX_NA;
-  BT_REQUIRE(a.NA >= A_LAG + 1, BT_ERR_UNSUPPORTED, "tensor-core forward: no room for the A pipeline");
+  if (env_int("BT_TC2_NA", 0) >= 2 && env_int("BT_TC2_NA", 0) < a.NA) a.NA = env_int("BT_TC2_NA", 0);
+  a.NR = a.MT >= 2 ? N_MMA_WARPS : 1;
+  a.NAr = a.NA / a.NR;
+  a.NA = a.NAr * a.NR;
+  BT_REQUIRE(a.NA >= 2 && a.RW >= 1 && a.RW <= MAX_RW, BT_ERR_UNSUPPORTED, "tensor-core forward: no room for the pipelines");
   a.total_items = (int64_t)a.S * a.NB * a.num_mg;
   const int grid = (int)(a.total_items < sms ? a.total_items : sms);
-  const int smem_bytes = 1024 + CTRL_BYTES + a.NA * A_SLOT + a.RW * WB;
+  const int smem_bytes = 1024 + CTRL_BYTES + a.stage_bufs * (STAGE_BYTES / 2) + a.NA * A_SLOT + a.RW * WB;
+  if (env_int("BT_TC2_LOG", 0))
+    fprintf(stderr, "tc2: mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d\n",
+            (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,
+            (long long)a.total_items, grid, smem_bytes);
   const bool o32 = g->out_dtype == BT_F32;
-  if (BN == 64) return o32 ? tc_launch<64, float>(a, grid, smem_bytes, stream) : tc_launch<64, __nv_bfloat16>(a, grid, smem_bytes, stream);
-  return o32 ? tc_launch<128, float>(a, grid, smem_bytes, stream) : tc_launch<128, __nv_bfloat16>(a, grid, smem_bytes, stream);
-}
-
-// ---- dispatch between the two tensor-core kernels: the TMA-fed one (bt_tc2.cu) when the
-// tensors are dense channels-last with c_in % 64 == 0 (or Linear), else the cp.async one above.
-// BT_TC_IMPL=1|2 pins one of them (tests / profiling).
-static int tc_impl_env() {
-  const char* v = getenv("BT_TC_IMPL");
-  return v && *v ? atoi(v) : 0;
-}
-
-bool bt_tc_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why) {
-  const int pin = tc_impl_env();
-  if (pin != 1 && bt_tc2_supported(g, p, flipout, why)) return true;
-  if (pin == 2) return false;
-  return bt_tc1_supported(g, p, flipout, why);
-}
-
-int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
-                  bool flipout, cudaStream_t stream) {
-  const char* why = "";
-  if (tc_impl_env() != 1 && bt_tc2_supported(g, p, flipout, &why)) return bt_tc2_forward(g, p, x, out, workspace, flipout, stream);
-  return bt_tc1_forward(g, p, x, out, workspace, flipout, stream);
+  if (BN == 64)
+    return o32 ? tc2_launch<64, float>(tm_a, tm_out, a, grid, smem_bytes, stream)
+               : tc2_launch<64, __nv_bfloat16>(tm_a, tm_out, a, grid, smem_bytes, stream);
+  return o32 ? tc2_launch<128, float>(tm_a, tm_out, a, grid, smem_bytes, stream)
+             : tc2_launch<128, __nv_bfloat16>(tm_a, tm_out, a, grid, smem_bytes, stream);
 }

@@ -358,10 +358,13 @@ def _entry(call: LayerCall, bwd: bool):
 
 
 def _like_x_format(x: torch.Tensor, shape) -> torch.Tensor:
-    """Output allocated in x's memory format (channels-last stays channels-last)."""
-    if x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last) and not x.is_contiguous():
+    """Output allocated in x's memory format (channels-last stays channels-last).  A layout
+    that reads as both (one channel, or 1x1 images) goes channels-last for bf16 activations so
+    the next layer can stay on the tensor-core path."""
+    ambiguous_cl = x.dtype == torch.bfloat16
+    if x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last) and (not x.is_contiguous() or ambiguous_cl):
         return torch.empty(shape, dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
-    if x.dim() == 5 and x.is_contiguous(memory_format=torch.channels_last_3d) and not x.is_contiguous():
+    if x.dim() == 5 and x.is_contiguous(memory_format=torch.channels_last_3d) and (not x.is_contiguous() or ambiguous_cl):
         return torch.empty(shape, dtype=x.dtype, device=x.device, memory_format=torch.channels_last_3d)
     if x.dim() == 3 and not x.is_contiguous() and x.stride(1) == 1:
         return torch.empty((shape[0], shape[2], shape[1]), dtype=x.dtype, device=x.device).permute(0, 2, 1)

@@ -47,7 +47,9 @@ CONV_CASES = [
     (128, 128, 3, 1, 1, 2, 14, True),   # K=1152 > smem panel -> streaming, multi-accumulator
     (256, 136, 3, 2, 1, 2, 15, True),   # N tail (136 = 128 + 8), stride 2, K=2304
     (16, 32, 3, 1, 1, 2, 9, True),      # C_in < 64: several taps per k-block, K tail (144 = 2*64 + 16)
-    (8, 8, 5, 1, 2, 1, 11, False),      # 25 taps of 8 channels
+    (8, 8, 5, 1, 2, 1, 11, False),      # 25 taps of 8 channels (patch-matrix path)
+    (3, 64, 7, 2, 3, 2, 32, True),      # the RGB stem: K = 147 padded to 152, RNG stream pitch != GEMM pitch
+    (1, 32, 3, 1, 0, 4, 28, True),      # SCNN conv1: a single input channel
     (128, 256, 1, 1, 0, 4, 28, True),   # 1x1, two n-blocks, several m-tiles per CTA (TMA path)
     (512, 64, 3, 1, 1, 1, 7, False),    # deep K (72 k-blocks) streaming, tiny M
     (64, 72, 3, 1, 1, 2, 20, True),     # N = 72: second n-block has 8 live columns
@@ -108,7 +110,8 @@ def test_conv1d_tc_matches_oracle(cuda_device):
     assert err <= BF16_OUT_TOL, f"rel err {err}"
 
 
-@pytest.mark.parametrize("rows,k,n", [(300, 256, 192), (128, 2048, 1000), (4096, 1024, 1024), (5, 64, 8), (77, 72, 40)])
+@pytest.mark.parametrize("rows,k,n", [(300, 256, 192), (128, 2048, 1000), (4096, 1024, 1024), (5, 64, 8), (77, 72, 40),
+                                      (33, 100, 16)])
 def test_linear_tc_matches_oracle(rows, k, n, cuda_device):
     torch.manual_seed(rows + k + n)
     layer = L.LinearReparameterization(k, n).to(cuda_device)
@@ -120,13 +123,15 @@ def test_linear_tc_matches_oracle(rows, k, n, cuda_device):
     assert err <= BF16_OUT_TOL, f"rel err {err}"
 
 
-def test_tc_philox_equals_exported_stream_and_simt(cuda_device):
+@pytest.mark.parametrize("cin", [64, 3])
+def test_tc_philox_equals_exported_stream_and_simt(cin, cuda_device):
     """In-kernel Philox on the tensor-core path == the exported stream fed through the
-    deterministic mode == the same draw on the fp32 SIMT path (one RNG contract)."""
+    deterministic mode == the same draw on the fp32 SIMT path (one RNG contract).  cin=3 runs
+    the patch-matrix path, whose padded K makes weight chunks straddle Philox blocks."""
     torch.manual_seed(3)
     bt.manual_seed(99)
-    layer = L.Conv2dReparameterization(64, 128, 3, padding=1, prior_type="normal").to(cuda_device)
-    x = torch.randn(2, 64, 12, 12, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    layer = L.Conv2dReparameterization(cin, 128, 3, padding=1, prior_type="normal").to(cuda_device)
+    x = torch.randn(2, cin, 12, 12, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
     layer.sample_mode, layer.path = "philox", "tc"
     with bt.mc_sample(5):
         out_p, _ = layer(x)
@@ -164,11 +169,34 @@ def test_tc_mc_batched_equals_sample_loop(cuda_device):
     assert torch.equal(again, folded)
 
 
+def test_conv3d_tc_matches_oracle(cuda_device):
+    torch.manual_seed(12)
+    layer = L.Conv3dReparameterization(16, 24, 3, 0, 1, 0, -3.0, stride=1, padding=1).to(cuda_device)
+    layer.eps_kernel.normal_(); layer.eps_bias.normal_()
+    x = torch.randn(2, 16, 5, 6, 7, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last_3d)
+    out, _ = run_tc(layer, x)
+    assert out.is_contiguous(memory_format=torch.channels_last_3d)
+    w = bf16_round(oracle.sample_weight(layer.mu_kernel.detach().cpu(), layer.rho_kernel.detach().cpu(), layer.eps_kernel.cpu()))
+    b = oracle.sample_weight(layer.mu_bias.detach().cpu(), layer.rho_bias.detach().cpu(), layer.eps_bias.cpu())
+    want = torch.nn.functional.conv3d(bf16_round(x.cpu().float()).double(), w.double(), b.double(), padding=1)
+    err = float((out.detach().cpu().double() - want).abs().max() / want.abs().max())
+    assert err <= BF16_OUT_TOL, f"rel err {err}"
+
+
 def test_tc_rejects_what_it_cannot_run(cuda_device):
-    layer = L.Conv2dReparameterization(3, 16, 7, stride=2, padding=3, prior_type="normal").to(cuda_device)
+    layer = L.Conv2dReparameterization(16, 16, 3, padding=1, groups=2, prior_type="normal").to(cuda_device)
     layer.path = "tc"
     with pytest.raises(RuntimeError, match="tensor-core path unavailable"):
-        layer(torch.randn(1, 3, 32, 32, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last))
-    layer.path = "auto"                        # auto falls back to the fp32 kernel, loudly documented in DESIGN.md
-    out, _ = layer(torch.randn(1, 3, 32, 32, device=cuda_device))
-    assert out.shape == (1, 16, 16, 16)
+        layer(torch.randn(1, 16, 8, 8, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last))
+    with pytest.raises(RuntimeError, match="tensor-core path unavailable"):   # fp32 activations stay on the parity path
+        L.Conv2dReparameterization(64, 64, 1, prior_type="normal").to(cuda_device).__setattr__("path", "tc") or \
+            _tc_on_fp32(cuda_device)
+    layer.path = "auto"                        # auto falls back to the fp32 kernel, documented in DESIGN.md
+    out, _ = layer(torch.randn(1, 16, 8, 8, device=cuda_device))
+    assert out.shape == (1, 16, 8, 8)
+
+
+def _tc_on_fp32(cuda_device):
+    layer = L.Conv2dReparameterization(64, 64, 1, prior_type="normal").to(cuda_device)
+    layer.path = "tc"
+    return layer(torch.randn(1, 64, 8, 8, device=cuda_device))
