@@ -37,7 +37,8 @@ class LayerParams(C.Structure):
         "mu_w", "rho_w", "mu_b", "rho_b", "eps_w", "eps_b", "sign_in", "sign_out",
         "prior_mu_w_t", "prior_sigma_w_t", "prior_mu_b_t", "prior_sigma_b_t")] + [
         ("prior_mu", C.c_float), ("prior_sigma", C.c_float),
-        ("seed", C.c_uint64), ("sample_id", C.c_uint32), ("layer_id", C.c_uint32)]
+        ("seed", C.c_uint64), ("sample_id", C.c_uint32), ("layer_id", C.c_uint32),
+        ("out_scale", C.c_void_p), ("out_shift", C.c_void_p), ("out_relu", C.c_int32), ("reserved", C.c_int32)]
 
 
 class LayerGrads(C.Structure):
@@ -74,6 +75,7 @@ SIGNATURES = {
     "bt_philox_normal_fill": (C.c_int, [C.c_void_p, C.c_int64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]),
     "bt_philox_sign_fill": (C.c_int, [C.c_void_p, C.c_int64, C.c_uint64, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p]),
     "bt_moped_rho": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_float, C.c_void_p]),
+    "bt_add_relu": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p]),
 }
 
 _lib = None
@@ -92,7 +94,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
-        if handle.bt_abi_version() != 1:
+        if handle.bt_abi_version() != 2:
             raise RuntimeError("libbt_b200.so ABI version mismatch")
         _lib = handle
     return _lib

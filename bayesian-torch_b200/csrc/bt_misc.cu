@@ -118,6 +118,25 @@ __global__ void mc_finalize_kernel(const float* __restrict__ sum_p, const float*
   }
 }
 
+// y = relu(y + r), 16 bytes per thread per step.
+template <typename T>
+__global__ void add_relu_kernel(T* __restrict__ y, const T* __restrict__ r, int64_t n) {
+  constexpr int V = 16 / (int)sizeof(T);
+  const int64_t nv = n / V;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += stride) {
+    uint4 a = reinterpret_cast<const uint4*>(y)[i];
+    const uint4 b = __ldcs(reinterpret_cast<const uint4*>(r) + i);
+    T* av = reinterpret_cast<T*>(&a);
+    const T* bv = reinterpret_cast<const T*>(&b);
+#pragma unroll
+    for (int e = 0; e < V; ++e) av[e] = bt_from_float<T>(fmaxf(bt_to_float<T>(av[e]) + bt_to_float<T>(bv[e]), 0.f));
+    reinterpret_cast<uint4*>(y)[i] = a;
+  }
+  for (int64_t i = nv * V + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    y[i] = bt_from_float<T>(fmaxf(bt_to_float<T>(y[i]) + bt_to_float<T>(r[i]), 0.f));
+}
+
 int grid_for(int64_t work_items, int threads) {
   int64_t blocks = (work_items + threads - 1) / threads;
   const int64_t cap = (int64_t)bt_num_sms() * 8;
@@ -152,6 +171,20 @@ extern "C" int bt_moped_rho(const float* w, float* rho, int64_t n, float delta, 
   if (n == 0) return BT_OK;
   moped_rho_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(w, rho, n, delta);
   BT_LAUNCH_OK("moped_rho_kernel");
+  return BT_OK;
+}
+
+extern "C" int bt_add_relu(void* y, const void* r, int64_t n, int dtype, bt_stream_t stream) {
+  BT_REQUIRE(y && r && n >= 0, BT_ERR_INVALID, "bt_add_relu: bad argument");
+  BT_REQUIRE((((uintptr_t)y | (uintptr_t)r) & 15) == 0, BT_ERR_ALIGN, "bt_add_relu: pointers must be 16-byte aligned");
+  if (n == 0) return BT_OK;
+  if (dtype == BT_BF16)
+    add_relu_kernel<__nv_bfloat16><<<grid_for(n / 8 + 1, 256), 256, 0, (cudaStream_t)stream>>>((__nv_bfloat16*)y, (const __nv_bfloat16*)r, n);
+  else if (dtype == BT_F32)
+    add_relu_kernel<float><<<grid_for(n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>((float*)y, (const float*)r, n);
+  else
+    BT_REQUIRE(false, BT_ERR_UNSUPPORTED, "bt_add_relu: dtype %d", dtype);
+  BT_LAUNCH_OK("add_relu_kernel");
   return BT_OK;
 }
 

@@ -207,6 +207,9 @@ __global__ void __launch_bounds__(NT) simt_fwd_kernel(const SGeo g, const SParam
         }
         v += (acc[NA - 1][i][j] + b_pert[j]) * sg;
       }
+      if (p.out_scale) v *= p.out_scale[ngl[j]];
+      if (p.out_shift) v += p.out_shift[ngl[j]];
+      if (p.out_relu) v = fmaxf(v, 0.f);
       out[off] = bt_from_float<TO>(v);
     }
   }

@@ -40,7 +40,7 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int A_SLOT = BM * BK * 2;  // 16 KB
-constexpr int CTRL_BYTES = 2048;
+constexpr int CTRL_BYTES = 3072;
 constexpr int STAGE_BYTES = 4 * 2 * 4096;  // per epilogue warp: 2 buffers of 32 rows x 128 B (1 when smem is tight)
 constexpr int N_PROD_WARPS = 8;
 constexpr int N_MMA_WARPS = 2;  // issuer warps: tile t of an m-group belongs to issuer t % 2
@@ -54,6 +54,8 @@ constexpr int RING_BYTES = SMEM_LIMIT - 1024 - CTRL_BYTES - STAGE_BYTES;  // A r
 struct Tc2Args {
   const float *mu_p, *sig_p, *eps_p;  // packed [N][K], k = tap*Cin + c
   const float *mu_b, *rho_b, *eps_b;
+  const float *out_scale, *out_shift;  // folded BatchNorm (nullable)
+  int out_relu;
   int64_t total_items;
   int N, K, S, NB;   // K: GEMM reduction length = row pitch of the packed parameter arrays
   int Kt;            // true reduction length (pitch of the RNG stream); < K when the patch matrix pads K up to 8
@@ -76,7 +78,7 @@ struct Ctrl {
   uint64_t acc_full[MAX_SETS], acc_empty[MAX_SETS];
   uint32_t tmem_base;
   uint32_t pad[3];
-  float bias[256];
+  float2 aff[256];  // per output channel of the current n-block: (scale, bias * scale + shift)
 };
 static_assert(sizeof(Ctrl) <= CTRL_BYTES, "control block too large");
 
@@ -234,20 +236,25 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     const uint32_t my_stage = stage_base + (uint32_t)(q * a.stage_bufs) * 4096u;
     const uint32_t row_sw = (uint32_t)(lane & 7);
     uint32_t nstore = 0;
+    const bool has_aff = a.mu_b || a.out_scale || a.out_shift;
     int s = s0, nb = nb0, mg = mg0, set = 0;
     uint32_t set_phase = 0;
     for (int it = 0; it < n_items; ++it) {
-      if (a.mu_b) {
-        named_bar_sync(1, 128);  // previous item's readers of ctrl->bias are done
+      if (has_aff) {
+        named_bar_sync(1, 128);  // previous item's readers of ctrl->aff are done
         for (int j = threadIdx.x; j < BN; j += 128) {
           const int n = nb * BN + j;
-          float b = 0.f;
+          float b = 0.f, sc = 1.f, sh = 0.f;
           if (n < a.N) {
-            const float e = a.eps_b ? a.eps_b[n]
-                                    : bt_normal1((uint64_t)n, bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_B));
-            b = a.mu_b[n] + bt_softplus(a.rho_b[n]) * e;
+            if (a.mu_b) {
+              const float e = a.eps_b ? a.eps_b[n]
+                                      : bt_normal1((uint64_t)n, bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_B));
+              b = a.mu_b[n] + bt_softplus(a.rho_b[n]) * e;
+            }
+            if (a.out_scale) sc = a.out_scale[n];
+            if (a.out_shift) sh = a.out_shift[n];
           }
-          ctrl->bias[j] = b;
+          ctrl->aff[j] = make_float2(sc, fmaf(b, sc, sh));
         }
         named_bar_sync(1, 128);
       }
@@ -286,18 +293,21 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 #pragma unroll
           for (int j = 0; j < 8; ++j) {  // 16-byte chunks of the 128-byte row
             uint32_t w0, w1, w2, w3;
-            if constexpr (SUBN == 64) {
-              const float* bs = &ctrl->bias[sub * SUBN + j * 8];
-              float f[8];
+            constexpr int EPC = 16 / (int)sizeof(TO);  // elements per 16-byte chunk
+            float f[EPC];
 #pragma unroll
-              for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j * 8 + e]) + (a.mu_b ? bs[e] : 0.f);
+            for (int e = 0; e < EPC; ++e) {
+              f[e] = __uint_as_float(v[j * EPC + e]);
+              if (has_aff) {
+                const float2 af = ctrl->aff[sub * SUBN + j * EPC + e];
+                f[e] = fmaf(f[e], af.x, af.y);
+              }
+              if (a.out_relu) f[e] = fmaxf(f[e], 0.f);
+            }
+            if constexpr (SUBN == 64) {
               w0 = pack_bf16(f[0], f[1]); w1 = pack_bf16(f[2], f[3]); w2 = pack_bf16(f[4], f[5]); w3 = pack_bf16(f[6], f[7]);
             } else {
-              const float* bs = &ctrl->bias[sub * SUBN + j * 4];
-              w0 = __float_as_uint(__uint_as_float(v[j * 4 + 0]) + (a.mu_b ? bs[0] : 0.f));
-              w1 = __float_as_uint(__uint_as_float(v[j * 4 + 1]) + (a.mu_b ? bs[1] : 0.f));
-              w2 = __float_as_uint(__uint_as_float(v[j * 4 + 2]) + (a.mu_b ? bs[2] : 0.f));
-              w3 = __float_as_uint(__uint_as_float(v[j * 4 + 3]) + (a.mu_b ? bs[3] : 0.f));
+              w0 = __float_as_uint(f[0]); w1 = __float_as_uint(f[1]); w2 = __float_as_uint(f[2]); w3 = __float_as_uint(f[3]);
             }
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((uint32_t)j ^ row_sw) << 4)), "r"(w0),
                          "r"(w1), "r"(w2), "r"(w3)
@@ -715,6 +725,7 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.N = (int)g->c_out;
   a.S = S;
   a.mu_b = p->mu_b; a.rho_b = p->rho_b; a.eps_b = p->eps_b;
+  a.out_scale = p->out_scale; a.out_shift = p->out_shift; a.out_relu = p->out_relu;
   a.seed = p->seed; a.sample_id = p->sample_id; a.layer_id = p->layer_id;
   a.debug = env_int("BT_TC2_DEBUG", 0);
   a.Ms = (int)pl.rows_per_s;

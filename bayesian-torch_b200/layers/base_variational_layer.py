@@ -105,6 +105,10 @@ class _BayesLayer(BaseVariationalLayer_):
         self.sign_input = None   # 'buffer' mode: Flipout sign tensors supplied by the caller
         self.sign_output = None
         self.quant_prepare = False
+        # inference-time epilogue folded in by models.fuse.fold_batchnorm (None / False = plain layer)
+        self.register_buffer("_ep_scale", None, persistent=False)
+        self.register_buffer("_ep_shift", None, persistent=False)
+        self._ep_relu = False
         self.init_parameters()
 
     # -- reference API ---------------------------------------------------------------------
@@ -201,6 +205,7 @@ class _BayesLayer(BaseVariationalLayer_):
         call.x_shared = call.n_samples > 1 and ops._STATE.shared_batch is not None and x.shape[0] == ops._STATE.shared_batch
         call.want_kl = bool(return_kl)
         call.path = ops._PATHS[self.path or ops.get_path()]
+        call.out_scale, call.out_shift, call.out_relu = self._ep_scale, self._ep_shift, self._ep_relu
         if ops._STATE.sample_override is not None:
             call.sample_id = ops._STATE.sample_override
         else:

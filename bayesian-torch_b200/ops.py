@@ -292,6 +292,9 @@ class LayerCall:
     x_shared: bool = False                      # mc_batched: x is the un-folded model input
     want_kl: bool = True
     path: int = _lib.PATH_AUTO
+    out_scale: Optional[torch.Tensor] = None    # folded eval-mode BatchNorm (inference only)
+    out_shift: Optional[torch.Tensor] = None
+    out_relu: bool = False
 
 
 def _conv_out_size(i, k, s, p, d):
@@ -345,6 +348,9 @@ def _build_params(call: LayerCall, mu_w, rho_w, mu_b, rho_b) -> Tuple[LayerParam
     p.prior_mu_w_t, p.prior_sigma_w_t, p.prior_mu_b_t, p.prior_sigma_b_t = (_ptr(t) for t in pts)
     p.prior_mu, p.prior_sigma = float(call.prior_mu), float(call.prior_sigma)
     p.seed, p.sample_id, p.layer_id = call.seed, call.sample_id, call.layer_id
+    sc, sh = _f32c(call.out_scale, "out_scale"), _f32c(call.out_shift, "out_shift")
+    keep += [sc, sh]
+    p.out_scale, p.out_shift, p.out_relu = _ptr(sc), _ptr(sh), int(bool(call.out_relu))
     return p, keep
 
 
@@ -451,6 +457,8 @@ class _BayesLayerFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_out, g_kl):
         call: LayerCall = ctx.call
+        if call.out_scale is not None or call.out_shift is not None or call.out_relu:
+            raise RuntimeError("the folded BatchNorm / ReLU epilogue is inference-only; unfuse the model to train")
         x, mu_w, rho_w, mu_b, rho_b = ctx.saved_tensors
         dev = x.device
         mu_wc, rho_wc = _f32c(mu_w.detach(), "mu"), _f32c(rho_w.detach(), "rho")
@@ -522,6 +530,19 @@ def philox_eps_weight(w_shape, seed: int, sample_id: int, layer_id: int, device=
         taps *= int(k)
     flat = philox_normal(n * c * taps, seed, sample_id, layer_id, _lib.KIND_EPS_W, device)
     return flat.view(n, taps, c).permute(0, 2, 1).reshape(tuple(w_shape)).contiguous()
+
+
+def add_relu_(y: torch.Tensor, r: torch.Tensor) -> torch.Tensor:
+    """y <- relu(y + r) in one pass (the residual join of a ResNet block), in place."""
+    _require_cuda(y, r)
+    if y.shape != r.shape or y.dtype != r.dtype or y.stride() != r.stride() or y.dtype not in _DT:
+        return torch.relu_(y.add_(r))
+    if not (y.is_contiguous() or (y.dim() == 4 and y.is_contiguous(memory_format=torch.channels_last))):
+        return torch.relu_(y.add_(r))
+    with torch.cuda.device(y.device):
+        _lib.check(_lib.lib().bt_add_relu(_ptr(y), _ptr(r), y.numel(), _DT[y.dtype], _stream()), "add_relu")
+    PROFILE.launches += 1
+    return y
 
 
 def moped_rho(w: torch.Tensor, delta: float) -> torch.Tensor:

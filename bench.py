@@ -39,10 +39,11 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--samples", type=int, default=32)
-    ap.add_argument("--mc-batch", type=int, default=int(os.environ.get("BT_MC_BATCH", "1")),
+    ap.add_argument("--mc-batch", type=int, default=int(os.environ.get("BT_MC_BATCH", "8")),
                     help="weight samples folded into one model pass (ops.mc_batched)")
     ap.add_argument("--cpu-batch", type=int, default=8, help="images in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-fold-bn", action="store_true", help="keep BatchNorm / ReLU as separate torch ops")
     return ap.parse_args()
 
 
@@ -154,7 +155,7 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------
 # this repo's arm
 # ------------------------------------------------------------------------------------------
-def build_model(device):
+def build_model(device, fold_bn=True):
     import torch
     import torchvision
     import bayesian_torch_b200 as bt
@@ -166,6 +167,8 @@ def build_model(device):
     model = model.to(device).eval()
     # bf16 activations, channels-last; variational parameters stay fp32 masters (layers/_apply)
     model = model.to(memory_format=torch.channels_last).to(torch.bfloat16)
+    if fold_bn:   # eval-mode BatchNorm / ReLU / residual join folded into the layer kernels (exact up to rounding)
+        model = bt.fold_batchnorm(model, inplace=True)
     return model
 
 
@@ -186,7 +189,7 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
 
-    model = build_model(dev)
+    model = build_model(dev, fold_bn=not args.no_fold_bn)
     B, S = args.batch, args.samples
     g = torch.Generator().manual_seed(0)
     x_host = torch.randn(B, 3, 224, 224, generator=g).pin_memory()          # synthetic images, host resident
@@ -253,7 +256,7 @@ def run_b200(args):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic",
             "config": {"workload": "resnet50_dnn_to_bnn_reparam_mc_inference", "batch": B, "samples": S, "image": "3x224x224",
-                       "samples_per_gpu": S / world, "mc_batch": args.mc_batch, "parallelism": f"mc_samples_sharded_x{world}",
+                       "samples_per_gpu": S / world, "mc_batch": args.mc_batch, "bn_folded": not args.no_fold_bn, "parallelism": f"mc_samples_sharded_x{world}",
                        "l2": "activations per step (GBs) far exceed the 126 MB L2; no flush needed",
                        "image_samples_per_s": value * S,
                        "tflops_bayesian_layers": value * S * GFLOP_PER_IMAGE_SAMPLE / 1e3},

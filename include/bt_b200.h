@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define BT_ABI_VERSION 1
+#define BT_ABI_VERSION 2
 
 typedef void* bt_stream_t; /* cudaStream_t */
 
@@ -96,6 +96,16 @@ typedef struct bt_layer_params {
   uint64_t seed;
   uint32_t sample_id;
   uint32_t layer_id;
+  /* Inference-time output epilogue (forward only; NULL / 0 = off):
+   *   out = act((conv(x, W) + b) * out_scale[n] + out_shift[n]),  act = ReLU when out_relu != 0.
+   * Folds the eval-mode BatchNorm (scale = gamma / sqrt(var + eps), shift = beta - mean * scale)
+   * and ReLU that follow every Bayesian conv of the reference's ResNets
+   * (models/bayesian/resnet_variational_large.py:97-119) into the producing kernel, so the
+   * activation tensor is written once instead of three times. */
+  const float* out_scale;
+  const float* out_shift;
+  int32_t out_relu;
+  int32_t reserved;
 } bt_layer_params;
 
 /* Gradient outputs of a backward call (all fp32 device buffers shaped like the
@@ -193,6 +203,10 @@ int bt_mc_accumulate(const void* logits, int dtype, int64_t S, int64_t B, int64_
 int bt_mc_finalize(const float* sum_p, const float* sum_p2, const float* sum_plogp, int64_t S_total,
                    int64_t B, int64_t C, float* mean, float* var, float* entropy, float* mutual_info,
                    bt_stream_t stream);
+
+/* ---- Residual join of a ResNet block: y = relu(y + r) in place, one pass (replaces the
+ *      out += identity; out = relu(out) pair of torchvision / resnet_variational_large.py:113-118). */
+int bt_add_relu(void* y, const void* r, int64_t n, int dtype, bt_stream_t stream);
 
 /* ---- RNG stream export (test / interop hook): writes the exact N(0,1) or +-1
  *      values the fused kernels generate in registers for elements [0,n) of stream

@@ -15,7 +15,7 @@ from bench import build_model  # noqa: E402
 
 dev = torch.device("cuda:0")
 mc_batch = int(sys.argv[1]) if len(sys.argv) > 1 else 1
-model = build_model(dev)
+model = build_model(dev, fold_bn=os.environ.get('BT_FOLD', '1') == '1')
 x = torch.randn(128, 3, 224, 224, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
 names = {}
 for n, m in model.named_modules():
