@@ -54,6 +54,7 @@ SIGNATURES = {
     "bt_abi_version": (C.c_int, []),
     "bt_last_error": (C.c_char_p, []),
     "bt_shutdown": (C.c_int, []),
+    "bt_launch_count": (C.c_int64, []),
     "bt_workspace_bytes": (C.c_int64, [C.c_char_p, C.POINTER(Geom), C.c_int]),
     "bt_select_path": (C.c_int, [C.POINTER(Geom), C.POINTER(LayerParams), C.c_int, C.c_int]),
     "bt_kl_normal_multi": (C.c_int, [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int64),

@@ -28,6 +28,11 @@ int bt_num_sms() {
   return cached;
 }
 
+#include <atomic>
+static std::atomic<long long> g_launches{0};
+void bt_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+extern "C" int64_t bt_launch_count(void) { return (int64_t)g_launches.load(std::memory_order_relaxed); }
+
 extern "C" int bt_abi_version(void) { return BT_ABI_VERSION; }
 extern "C" const char* bt_last_error(void) { return g_err; }
 extern "C" int bt_shutdown(void) { return BT_OK; }

@@ -29,8 +29,11 @@ void bt_set_error(const char* fmt, ...);
     }                                                                               \
   } while (0)
 
+void bt_count_launch();  // process-wide tally of this library's kernel launches (bt_launch_count)
+
 #define BT_LAUNCH_OK(name)                                                      \
   do {                                                                          \
+    bt_count_launch();                                                          \
     cudaError_t _e = cudaGetLastError();                                        \
     if (_e != cudaSuccess) {                                                    \
       bt_set_error("launch of %s failed: %s", name, cudaGetErrorString(_e));    \

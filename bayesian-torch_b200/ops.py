@@ -37,12 +37,17 @@ class _Profile:
     """Launch counter + optional CUDA-event timing of every layer call (bench.py roofline)."""
 
     def __init__(self):
-        self.launches = 0        # kernels of libbt_b200.so launched (always counted)
+        self._base = 0
         self.timing = False      # record (path, flops, bytes, start, end) per layer call
         self.records = []
 
+    @property
+    def launches(self):
+        """Kernels of libbt_b200.so launched since the last reset (counted inside the library)."""
+        return int(_lib.lib().bt_launch_count()) - self._base
+
     def reset(self):
-        self.launches = 0
+        self._base = int(_lib.lib().bt_launch_count())
         self.records = []
 
 
@@ -445,7 +450,6 @@ class _BayesLayerFn(torch.autograd.Function):
                 nbytes = xd.numel() * xd.element_size() + out.numel() * out.element_size() + 8 * mu_wc.numel()
                 PROFILE.records.append((used, flops, nbytes, ev0, ev1))
         _lib.check(rc, "layer forward")
-        PROFILE.launches += (2 if used == _lib.PATH_TC_BF16 else 1) + (1 if call.want_kl else 0)
         ctx.call = call
         ctx.out_meta = (tuple(out.shape), tuple(out.stride()))
         ctx.save_for_backward(x, mu_w, rho_w, mu_b, rho_b)
@@ -541,7 +545,6 @@ def add_relu_(y: torch.Tensor, r: torch.Tensor) -> torch.Tensor:
         return torch.relu_(y.add_(r))
     with torch.cuda.device(y.device):
         _lib.check(_lib.lib().bt_add_relu(_ptr(y), _ptr(r), y.numel(), _DT[y.dtype], _stream()), "add_relu")
-    PROFILE.launches += 1
     return y
 
 

@@ -123,6 +123,8 @@ int bt_abi_version(void);
 const char* bt_last_error(void);
 /* Releases the lazily created per-device contexts (cached TMA descriptors). */
 int bt_shutdown(void);
+/* Number of kernels this library has launched in this process so far (all threads). */
+int64_t bt_launch_count(void);
 /* Bytes of scratch the caller must pass as `workspace` to the call named `op`
  * ("kl", "reparam_fwd", "reparam_bwd", "flipout_fwd", "flipout_bwd") for this
  * geometry; 0 when none is needed. */
