@@ -77,12 +77,10 @@ __device__ __forceinline__ uint4 bt_philox(uint64_t block, const BtRngKey& key) 
   uint32_t k0 = key.k0, k1 = key.k1;
 #pragma unroll
   for (int r = 0; r < 10; ++r) {
-    const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
-    const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
-    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
-    const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
-    c1 = (uint32_t)p1;
-    c3 = (uint32_t)p0;
+    const uint32_t n0 = __umulhi(0xCD9E8D57u, c2) ^ c1 ^ k0;
+    const uint32_t n2 = __umulhi(0xD2511F53u, c0) ^ c3 ^ k1;
+    c1 = 0xCD9E8D57u * c2;
+    c3 = 0xD2511F53u * c0;
     c0 = n0;
     c2 = n2;
     k0 += 0x9E3779B9u;
@@ -106,7 +104,7 @@ __device__ __forceinline__ float2 bt_box_muller16(uint32_t w) {
   const float x1 = __uint_as_float(0x3F800040u | ((w << 7) & 0x007FFF80u));  // 1 + u1
   const float rad = bt_sqrt_approx(-1.3862943611198906f * __log2f(x0 - 1.0f));
   float s, c;
-  __sincosf(6.2831853071795864f * (x1 - 1.5f), &s, &c);
+  __sincosf(fmaf(x1, 6.2831853071795864f, -9.4247779607693797f), &s, &c);  // 2 pi (u1 - 1/2)
   return make_float2(rad * c, rad * s);
 }
 

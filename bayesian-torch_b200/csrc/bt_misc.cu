@@ -137,6 +137,39 @@ __global__ void add_relu_kernel(T* __restrict__ y, const T* __restrict__ r, int6
     y[i] = bt_from_float<T>(fmaxf(bt_to_float<T>(y[i]) + bt_to_float<T>(r[i]), 0.f));
 }
 
+// Channels-last max pooling, 8 channels (16 bytes) per thread: the stem's MaxPool2d(3, 2, 1)
+// sits between two Bayesian layers of every ResNet and torch's NHWC kernel runs it at ~0.7 TB/s.
+__global__ void maxpool2d_nhwc_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t total,
+                                           int C8, int IH, int IW, int OH, int OW, int k, int st, int pd) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % C8);
+    int64_t r = i / C8;
+    const int ow = (int)(r % OW); r /= OW;
+    const int oh = (int)(r % OH); r /= OH;
+    const __nv_bfloat16* xb = x + r * (int64_t)IH * IW * C8 * 8 + c8 * 8;
+    float m[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) m[e] = -INFINITY;
+    for (int kh = 0; kh < k; ++kh) {
+      const int ih = oh * st - pd + kh;
+      if ((unsigned)ih >= (unsigned)IH) continue;
+      for (int kw = 0; kw < k; ++kw) {
+        const int iw = ow * st - pd + kw;
+        if ((unsigned)iw >= (unsigned)IW) continue;
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(xb + ((int64_t)ih * IW + iw) * C8 * 8));
+        const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) m[e] = fmaxf(m[e], __bfloat162float(h[e]));
+      }
+    }
+    uint4 o;
+    __nv_bfloat16* oh8 = reinterpret_cast<__nv_bfloat16*>(&o);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) oh8[e] = __float2bfloat16_rn(m[e]);
+    reinterpret_cast<uint4*>(y)[i] = o;
+  }
+}
+
 int grid_for(int64_t work_items, int threads) {
   int64_t blocks = (work_items + threads - 1) / threads;
   const int64_t cap = (int64_t)bt_num_sms() * 8;
@@ -171,6 +204,22 @@ extern "C" int bt_moped_rho(const float* w, float* rho, int64_t n, float delta, 
   if (n == 0) return BT_OK;
   moped_rho_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(w, rho, n, delta);
   BT_LAUNCH_OK("moped_rho_kernel");
+  return BT_OK;
+}
+
+extern "C" int bt_maxpool2d_nhwc(const void* x, void* y, int64_t batch, int64_t channels, int64_t ih, int64_t iw,
+                                 int kernel, int stride, int pad, int dtype, bt_stream_t stream) {
+  BT_REQUIRE(x && y && batch >= 0 && channels > 0 && ih > 0 && iw > 0 && kernel > 0 && stride > 0 && pad >= 0 && 2 * pad <= kernel,
+             BT_ERR_INVALID, "bt_maxpool2d_nhwc: bad argument");
+  BT_REQUIRE(dtype == BT_BF16 && channels % 8 == 0, BT_ERR_UNSUPPORTED, "bt_maxpool2d_nhwc: bf16 with channels %% 8 == 0 only");
+  BT_REQUIRE((((uintptr_t)x | (uintptr_t)y) & 15) == 0, BT_ERR_ALIGN, "bt_maxpool2d_nhwc: pointers must be 16-byte aligned");
+  const int64_t oh = (ih + 2 * pad - kernel) / stride + 1, ow = (iw + 2 * pad - kernel) / stride + 1;
+  BT_REQUIRE(oh > 0 && ow > 0, BT_ERR_INVALID, "bt_maxpool2d_nhwc: empty output");
+  const int64_t total = batch * oh * ow * (channels / 8);
+  if (total == 0) return BT_OK;
+  maxpool2d_nhwc_bf16_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, total, (int)(channels / 8), (int)ih, (int)iw, (int)oh, (int)ow, kernel, stride, pad);
+  BT_LAUNCH_OK("maxpool2d_nhwc_bf16_kernel");
   return BT_OK;
 }
 

@@ -18,7 +18,7 @@
 //                          K=16) into TMEM accumulators.  Measured on B200 (tools/ubench/pipe2.cu):
 //                          one issuing thread costs ~340 cycles per 4-MMA ring slot against 256
 //                          cycles of tensor work at N=128, two issuers overlap completely
-//   warps 7-14  W producers: mu + sigma * eps -> bf16 -> swizzled smem, eps from in-register
+//   warps 8-23  W producers: mu + sigma * eps -> bf16 -> swizzled smem, eps from in-register
 //                          Philox4x32-10 (8 normals per call) or the caller's tensor
 // mbarrier pipelines: A ring (TMA complete_tx / tcgen05.commit), W ring or stationary panel,
 // accumulator sets in TMEM.  The sampling cost is amortised over the batch either by keeping
@@ -42,10 +42,17 @@ constexpr int BK = 64;
 constexpr int A_SLOT = BM * BK * 2;  // 16 KB
 constexpr int CTRL_BYTES = 3072;
 constexpr int STAGE_BYTES = 4 * 2 * 4096;  // per epilogue warp: 2 buffers of 32 rows x 128 B (1 when smem is tight)
-constexpr int N_PROD_WARPS = 8;
+constexpr int N_PROD_WARPS = 16;
 constexpr int N_MMA_WARPS = 2;  // issuer warps: tile t of an m-group belongs to issuer t % 2
-constexpr int WARP_TMA = 4, WARP_MMA = 5, WARP_PROD0 = WARP_MMA + N_MMA_WARPS;
-constexpr int NUM_THREADS = (WARP_PROD0 + N_PROD_WARPS) * 32;  // 480
+// warp groups (setmaxnreg works on aligned groups of 4 warps): 0 = epilogue, 1 = TMA + 2 MMA issuers
+// + one idle warp, 2..5 = W producers
+constexpr int WARP_TMA = 4, WARP_MMA = 5, WARP_PROD0 = 8;
+constexpr int NUM_THREADS = (WARP_PROD0 + N_PROD_WARPS) * 32;  // 768
+// register budget: 768 threads launch with 80 registers each; the control warp group and
+// the producers shrink to 72, which lets the epilogue group (64 accumulator columns in flight per thread)
+// grow to 120. The pool setmaxnreg draws on is what the CTA was LAUNCHED with
+// (768 x 80 = 61440 registers), not the whole register file: 128*120 + 128*72 + 512*72 = 61440.
+constexpr int REGS_EPI = 120, REGS_CTRL = 72, REGS_PROD = 72;
 constexpr int PROD_THREADS = N_PROD_WARPS * 32;
 constexpr int MAX_NA = 8, MAX_RW = 24, MAX_SETS = 8, MAX_MT = 4;
 constexpr int SMEM_LIMIT = 232448;
@@ -112,6 +119,10 @@ __device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bu
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
+template <int N>
+__device__ __forceinline__ void reg_alloc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N>
+__device__ __forceinline__ void reg_dealloc() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 __device__ __forceinline__ bool elect_one() {  // one lane of the (converged) warp
   uint32_t is_leader;
   asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(is_leader));
@@ -232,6 +243,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 
   if (warp < 4) {
     // =========================== EPILOGUE ===========================
+    reg_alloc<REGS_EPI>();
     const int q = warp;
     const uint32_t my_stage = stage_base + (uint32_t)(q * a.stage_bufs) * 4096u;
     const uint32_t row_sw = (uint32_t)(lane & 7);
@@ -328,7 +340,9 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       if (++mg == a.num_mg) { mg = 0; if (++nb == a.NB) { nb = 0; ++s; } }
     }
     if (lane == 0) tma_store_wait_all();
-  } else if (warp == WARP_TMA) {
+  } else if (warp < WARP_PROD0) {
+    reg_dealloc<REGS_CTRL>();
+    if (warp == WARP_TMA) {
     // =========================== A LOADER (TMA) ===========================
     // warp-uniform loop (every lane waits, the elected lane issues): keeps the loop state in
     // uniform registers and off the divergent-code path.
@@ -391,7 +405,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       if (++mg == a.num_mg) { mg = 0; if (++nb == a.NB) { nb = 0; ++s; } }
     }
     __syncwarp();
-  } else if (warp < WARP_PROD0) {
+    } else if (warp < WARP_MMA + N_MMA_WARPS) {
     // =========================== MMA ISSUERS ===========================
     const int j = warp - WARP_MMA;  // this issuer owns tiles t with t % N_MMA_WARPS == j
     const bool leader = elect_one();
@@ -447,8 +461,10 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       }
       if (++mg == a.num_mg) mg = 0;
     }
+    }
   } else {
     // =========================== W PRODUCERS (sample in smem) ===========================
+    reg_dealloc<REGS_PROD>();
     const int p = threadIdx.x - WARP_PROD0 * 32;
     const int chunk = p & 7;      // 16-byte chunk (8 consecutive k) of the 128-byte row
     const int row_base = p >> 3;  // rows row_base + 32*i

@@ -79,6 +79,17 @@ def fold_batchnorm(model: nn.Module, inplace: bool = False) -> fx.GraphModule:
         if n.op == "call_module":
             calls[n.target] = calls.get(n.target, 0) + 1
     folded = {"bn": 0, "relu": 0, "join": 0}
+    pools = 0
+    for node in list(graph.nodes):   # square, floor-mode, undilated MaxPool2d -> the channels-last kernel
+        if node.op == "call_module" and isinstance(modules.get(node.target), nn.MaxPool2d):
+            mp = modules[node.target]
+            k, st, pd = mp.kernel_size, mp.stride if mp.stride is not None else mp.kernel_size, mp.padding
+            if all(isinstance(v, int) for v in (k, st, pd)) and mp.dilation == 1 and not mp.ceil_mode and not mp.return_indices:
+                with graph.inserting_after(node):
+                    new = graph.call_function(ops.maxpool2d, (node.args[0], k, st, pd))
+                node.replace_all_uses_with(new)
+                graph.erase_node(node)
+                pools += 1
     for node in list(graph.nodes):
         if node.op != "call_module" or not isinstance(modules.get(node.target), _BayesLayer):
             continue
@@ -118,4 +129,5 @@ def fold_batchnorm(model: nn.Module, inplace: bool = False) -> fx.GraphModule:
     graph.lint()
     gm.recompile()
     gm.folded = folded
+    gm.pools_rewritten = pools
     return gm

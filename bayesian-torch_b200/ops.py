@@ -548,6 +548,21 @@ def add_relu_(y: torch.Tensor, r: torch.Tensor) -> torch.Tensor:
     return y
 
 
+def maxpool2d(x: torch.Tensor, kernel_size: int, stride: int, padding: int) -> torch.Tensor:
+    """MaxPool2d (floor mode, square window) on a bf16 channels-last tensor in one 16-byte-per-thread
+    pass; anything else goes to torch."""
+    if not (x.is_cuda and x.dim() == 4 and x.dtype == torch.bfloat16 and x.shape[1] % 8 == 0
+            and x.is_contiguous(memory_format=torch.channels_last) and 2 * padding <= kernel_size):
+        return torch.nn.functional.max_pool2d(x, kernel_size, stride, padding)
+    B, Cc, H, W = x.shape
+    oh, ow = (H + 2 * padding - kernel_size) // stride + 1, (W + 2 * padding - kernel_size) // stride + 1
+    y = torch.empty((B, Cc, oh, ow), dtype=x.dtype, device=x.device, memory_format=torch.channels_last)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().bt_maxpool2d_nhwc(_ptr(x), _ptr(y), B, Cc, H, W, kernel_size, stride, padding, _lib.BT_BF16,
+                                                _stream()), "maxpool2d")
+    return y
+
+
 def moped_rho(w: torch.Tensor, delta: float) -> torch.Tensor:
     """rho = log(expm1(delta*|w|) + 1e-20)  (utils/util.py:63-69) as one kernel."""
     _require_cuda(w)

@@ -209,6 +209,10 @@ int bt_mc_finalize(const float* sum_p, const float* sum_p2, const float* sum_plo
 /* ---- Residual join of a ResNet block: y = relu(y + r) in place, one pass (replaces the
  *      out += identity; out = relu(out) pair of torchvision / resnet_variational_large.py:113-118). */
 int bt_add_relu(void* y, const void* r, int64_t n, int dtype, bt_stream_t stream);
+/* ---- Channels-last max pooling between two Bayesian layers (the ResNet stem's MaxPool2d(3, 2, 1)):
+ *      x [batch, ih, iw, channels] -> y [batch, oh, ow, channels], floor mode, bf16, channels % 8 == 0. */
+int bt_maxpool2d_nhwc(const void* x, void* y, int64_t batch, int64_t channels, int64_t ih, int64_t iw,
+                      int kernel, int stride, int pad, int dtype, bt_stream_t stream);
 
 /* ---- RNG stream export (test / interop hook): writes the exact N(0,1) or +-1
  *      values the fused kernels generate in registers for elements [0,n) of stream

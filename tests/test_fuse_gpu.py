@@ -95,3 +95,12 @@ def test_add_relu_inplace(cuda_device):
         got = bt.ops.add_relu_(y, r)
         assert got.data_ptr() == y.data_ptr()
         torch.testing.assert_close(got, want, rtol=0, atol=0)
+
+
+def test_maxpool_nhwc_matches_torch(cuda_device):
+    for shape, k, st, pd in [((3, 64, 17, 23), 3, 2, 1), ((2, 16, 8, 8), 2, 2, 0), ((1, 8, 5, 5), 3, 1, 1)]:
+        x = torch.randn(*shape, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+        got = bt.ops.maxpool2d(x, k, st, pd)
+        want = torch.nn.functional.max_pool2d(x, k, st, pd)
+        assert got.is_contiguous(memory_format=torch.channels_last)
+        torch.testing.assert_close(got, want, rtol=0, atol=0)
