@@ -79,6 +79,7 @@ SIGNATURES = {
     "bt_add_relu": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p]),
     "bt_maxpool2d_nhwc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
                                     C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "bt_debug_tc_profile": (C.c_int, [C.c_void_p, C.c_int]),
 }
 
 _lib = None

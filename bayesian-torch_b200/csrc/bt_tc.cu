@@ -40,7 +40,10 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int A_SLOT = BM * BK * 2;  // 16 KB
-constexpr int CTRL_BYTES = 3072;
+constexpr int BAR_BYTES = 1024;           // mbarriers + TMEM base
+constexpr int ONES_BYTES = BM * 32;       // [128 x 16] bf16 tile of the rank-1 "add shift" MMA (32-byte swizzle)
+constexpr int SHIFT_BYTES = 128 * 32;     // [BN x 16] bf16: per-channel shift split into three bf16 terms
+constexpr int CTRL_BYTES = BAR_BYTES + ONES_BYTES + SHIFT_BYTES;
 constexpr int STAGE_BYTES = 4 * 2 * 4096;  // per epilogue warp: 2 buffers of 32 rows x 128 B (1 when smem is tight)
 constexpr int N_PROD_WARPS = 16;
 constexpr int N_MMA_WARPS = 2;  // issuer warps: tile t of an m-group belongs to issuer t % 2
@@ -73,6 +76,7 @@ struct Tc2Args {
   int sh, sw, ph, pw, dh, dw;
   int num_mt, num_mg, MT, NSETS, nkb, NA, RW, stationary;
   int NR, NAr;       // A rings (one per active MMA issuer) and slots per ring; NA = NR * NAr
+  int has_shift;     // bias and/or folded BatchNorm shift: added by a rank-1 MMA that initialises each accumulator
   int stage_bufs;    // epilogue staging buffers per warp (2, or 1 when shared memory is tight)
   int debug;         // BT_TC2_DEBUG bits (timing experiments only): 1 = skip the output stores
   uint64_t seed;
@@ -81,13 +85,12 @@ struct Tc2Args {
 
 struct Ctrl {
   uint64_t a_full[MAX_NA], a_empty[MAX_NA];
-  uint64_t w_full[MAX_RW], w_empty[MAX_RW];
+  uint64_t w_full[MAX_RW + 1], w_empty[MAX_RW + 1];  // slot RW: the shift tile
   uint64_t acc_full[MAX_SETS], acc_empty[MAX_SETS];
   uint32_t tmem_base;
   uint32_t pad[3];
-  float2 aff[256];  // per output channel of the current n-block: (scale, bias * scale + shift)
 };
-static_assert(sizeof(Ctrl) <= CTRL_BYTES, "control block too large");
+static_assert(sizeof(Ctrl) <= BAR_BYTES, "control block too large");
 
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
@@ -132,13 +135,19 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<const uint32_t*>(&h);
 }
+__device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
 
 // ---------------------------------------------------------------- parameter packing ----
 // mu[n][c][tap] -> mu_p[n][tap*Cin + c] with row pitch Kp (zero beyond K), sigma_p = softplus(rho)
 // likewise (sigma does not depend on the sample: hoisted out of the per-sample work), eps likewise.
 __global__ void tc2_pack_kernel(const float* __restrict__ mu, const float* __restrict__ rho,
                                 const float* __restrict__ eps, float* __restrict__ mu_p, float* __restrict__ sig_p,
-                                float* __restrict__ eps_p, int64_t total, int Cin, int T, int Kp) {
+                                float* __restrict__ eps_p, const float* __restrict__ scale, int64_t total, int Cin, int T,
+                                int Kp) {
   const int K = Cin * T;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t n = i / Kp;
@@ -150,6 +159,11 @@ __global__ void tc2_pack_kernel(const float* __restrict__ mu, const float* __res
       m = mu[src];
       sg = bt_softplus(rho[src]);
       if (eps_p) e = eps[src];
+      if (scale) {  // folded BatchNorm scale of output channel n rides on the sampled weight row
+        const float sc = scale[n];
+        m *= sc;
+        sg *= sc;
+      }
     }
     mu_p[i] = m;
     sig_p[i] = sg;
@@ -202,7 +216,53 @@ __global__ void tc2_patch_kernel(const TX* __restrict__ x, __nv_bfloat16* __rest
   }
 }
 
-template <int BN, typename TO>
+// Epilogue of one 32-column unit of one accumulator row: ReLU, conversion and the swizzled stores
+// into chunks [cb, cb + 32/EPC) of the 128-byte staging row.  Bias and folded BatchNorm never show
+// up here: the scale is folded into the sampled weights and the shift is in the accumulator
+// already (rank-1 MMA), so for bf16 outputs this is one cvt (with .relu) per two elements.
+template <typename TO, bool RELU>
+__device__ __forceinline__ void epi_unit(const uint32_t (&v)[32], uint32_t rowaddr, int cb, uint32_t row_sw) {
+  constexpr int EPC = 16 / (int)sizeof(TO);  // elements per 16-byte chunk
+  constexpr int NCH = 32 / EPC;              // chunks per unit
+#pragma unroll
+  for (int j = 0; j < NCH; ++j) {
+    float f[EPC];
+#pragma unroll
+    for (int e = 0; e < EPC; ++e) f[e] = __uint_as_float(v[j * EPC + e]);
+    uint32_t w0, w1, w2, w3;
+    if constexpr (sizeof(TO) == 2) {
+      if constexpr (RELU) {  // cvt.rn.relu: the clamp rides on the conversion
+        w0 = pack_bf16_relu(f[0], f[1]); w1 = pack_bf16_relu(f[2], f[3]);
+        w2 = pack_bf16_relu(f[4], f[5]); w3 = pack_bf16_relu(f[6], f[7]);
+      } else {
+        w0 = pack_bf16(f[0], f[1]); w1 = pack_bf16(f[2], f[3]); w2 = pack_bf16(f[4], f[5]); w3 = pack_bf16(f[6], f[7]);
+      }
+    } else {
+      if constexpr (RELU) { f[0] = fmaxf(f[0], 0.f); f[1] = fmaxf(f[1], 0.f); f[2] = fmaxf(f[2], 0.f); f[3] = fmaxf(f[3], 0.f); }
+      w0 = __float_as_uint(f[0]); w1 = __float_as_uint(f[1]); w2 = __float_as_uint(f[2]); w3 = __float_as_uint(f[3]);
+    }
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((uint32_t)(cb + j) ^ row_sw) << 4)), "r"(w0),
+                 "r"(w1), "r"(w2), "r"(w3)
+                 : "memory");
+  }
+}
+
+// Cycle accounting for BT_TC2_PROF=1 (diagnostics; a separate instantiation, the product kernel
+// carries none of it): per CTA and role, cycles spent in each kind of wait.
+constexpr int PROF_ROLES = 6, PROF_SLOTS = 6;
+__device__ unsigned long long g_tc_prof[160 * PROF_ROLES * PROF_SLOTS];
+#define PW(i, ...)                                              \
+  do {                                                          \
+    if constexpr (PROF) {                                       \
+      const long long _t0 = clock64();                          \
+      __VA_ARGS__;                                              \
+      pc[i] += (unsigned long long)(clock64() - _t0);           \
+    } else {                                                    \
+      __VA_ARGS__;                                              \
+    }                                                           \
+  } while (0)
+
+template <int BN, typename TO, bool PROF>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_out,
                const __grid_constant__ Tc2Args a) {
@@ -212,15 +272,25 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   Ctrl* ctrl = reinterpret_cast<Ctrl*>(smem_raw + (base - raw));
   constexpr int W_SLOT = BN * BK * 2;
   constexpr int SUBN = 128 / (int)sizeof(TO);  // output columns per 128-byte staging row
+  const uint32_t ones_base = base + BAR_BYTES, shift_base = ones_base + ONES_BYTES;
   const uint32_t stage_base = base + CTRL_BYTES;
   const uint32_t a_base = stage_base + (uint32_t)a.stage_bufs * 16384u;
   const uint32_t w_base = a_base + a.NA * A_SLOT;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  unsigned long long pc[PROF_SLOTS] = {0, 0, 0, 0, 0, 0};
+  const long long prof_t0 = PROF ? clock64() : 0;
+  auto prof_flush = [&](int role) {
+    if constexpr (PROF) {
+      pc[PROF_SLOTS - 1] = (unsigned long long)(clock64() - prof_t0);
+      if (lane == 0 && blockIdx.x < 160)
+        for (int i = 0; i < PROF_SLOTS; ++i) g_tc_prof[(blockIdx.x * PROF_ROLES + role) * PROF_SLOTS + i] = pc[i];
+    }
+  };
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < a.NA; ++i) { mbar_init(smem_u32(&ctrl->a_full[i]), 1); mbar_init(smem_u32(&ctrl->a_empty[i]), 1); }
-    for (int i = 0; i < a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), N_PROD_WARPS); mbar_init(smem_u32(&ctrl->w_empty[i]), N_MMA_WARPS); }
+    for (int i = 0; i <= a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), N_PROD_WARPS); mbar_init(smem_u32(&ctrl->w_empty[i]), N_MMA_WARPS); }
     for (int i = 0; i < a.NSETS; ++i) { mbar_init(smem_u32(&ctrl->acc_full[i]), N_MMA_WARPS); mbar_init(smem_u32(&ctrl->acc_empty[i]), 128); }
     mbar_fence_init();
   }
@@ -247,91 +317,72 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     const int q = warp;
     const uint32_t my_stage = stage_base + (uint32_t)(q * a.stage_bufs) * 4096u;
     const uint32_t row_sw = (uint32_t)(lane & 7);
-    uint32_t nstore = 0;
-    const bool has_aff = a.mu_b || a.out_scale || a.out_shift;
+    uint32_t nstore = 0, sbuf = 0;
+    const bool relu = a.out_relu != 0;
+    constexpr int UPS = SUBN / 32;                    // 32-column units per staged sub-tile (2 bf16, 1 fp32)
+    constexpr int CPU = 8 / UPS;                      // 16-byte chunks of the staging row per unit
     int s = s0, nb = nb0, mg = mg0, set = 0;
     uint32_t set_phase = 0;
+    auto emit = [&](const uint32_t (&v)[32], uint32_t rowaddr, int cb) {
+      if (relu) epi_unit<TO, true>(v, rowaddr, cb, row_sw);  // warp-uniform; each side is straight-line code
+      else epi_unit<TO, false>(v, rowaddr, cb, row_sw);
+    };
     for (int it = 0; it < n_items; ++it) {
-      if (has_aff) {
-        named_bar_sync(1, 128);  // previous item's readers of ctrl->aff are done
-        for (int j = threadIdx.x; j < BN; j += 128) {
-          const int n = nb * BN + j;
-          float b = 0.f, sc = 1.f, sh = 0.f;
-          if (n < a.N) {
-            if (a.mu_b) {
-              const float e = a.eps_b ? a.eps_b[n]
-                                      : bt_normal1((uint64_t)n, bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_B));
-              b = a.mu_b[n] + bt_softplus(a.rho_b[n]) * e;
-            }
-            if (a.out_scale) sc = a.out_scale[n];
-            if (a.out_shift) sh = a.out_shift[n];
-          }
-          ctrl->aff[j] = make_float2(sc, fmaf(b, sc, sh));
-        }
-        named_bar_sync(1, 128);
-      }
-      mbar_wait(smem_u32(&ctrl->acc_full[set]), set_phase);
+      PW(0, mbar_wait(smem_u32(&ctrl->acc_full[set]), set_phase));
       tc_fence_after();
       const int mtv = min(a.MT, a.num_mt - mg * a.MT);
+      const int ncols = min(BN, a.N - nb * BN);
+      const int nsub = (ncols + SUBN - 1) / SUBN;  // staged sub-tiles with at least one real column
       for (int t = 0; t < mtv; ++t) {
         const int m0 = (mg * a.MT + t) * BM + q * 32;  // first row of this warp's 32-row slab
         if (m0 >= a.Ms) break;                          // slab entirely past the sample's last row (warp-uniform)
         const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)((set * a.MT + t) * BN);
+        // TMEM reads are software-pipelined in 32-column units: the load of unit u+1 is in
+        // flight while unit u is converted and staged.
+        uint32_t va[32], vb[32];
+        tmem_ld32(tacc, va);
 #pragma unroll 1
-        for (int sub = 0; sub < BN / SUBN; ++sub) {
-          const int n0 = nb * BN + sub * SUBN;
-          if (n0 >= a.N) break;  // warp-uniform
-          uint32_t v[SUBN];
-          if constexpr (SUBN == 64) {
-            tmem_ld32(tacc + sub * SUBN, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-            tmem_ld32(tacc + sub * SUBN + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
-          } else {
-            tmem_ld32(tacc + sub * SUBN, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-          }
-          tmem_ld_wait();
+        for (int sub = 0; sub < nsub; ++sub) {
           // the TMA store that last read this staging buffer must have drained it
-          uint32_t buf = my_stage;
-          if (a.stage_bufs == 2) {
-            buf += (nstore & 1u) * 4096u;
-            if (nstore >= 2) {
-              if (lane == 0) tma_store_wait_read<1>();
-              __syncwarp();
-            }
-          } else if (nstore >= 1) {
-            if (lane == 0) tma_store_wait_read<0>();
-            __syncwarp();
-          }
-          const uint32_t rowaddr = buf + (uint32_t)lane * 128u;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {  // 16-byte chunks of the 128-byte row
-            uint32_t w0, w1, w2, w3;
-            constexpr int EPC = 16 / (int)sizeof(TO);  // elements per 16-byte chunk
-            float f[EPC];
-#pragma unroll
-            for (int e = 0; e < EPC; ++e) {
-              f[e] = __uint_as_float(v[j * EPC + e]);
-              if (has_aff) {
-                const float2 af = ctrl->aff[sub * SUBN + j * EPC + e];
-                f[e] = fmaf(f[e], af.x, af.y);
+          if (nstore >= (uint32_t)a.stage_bufs) {
+            PW(3, {
+              if (lane == 0) {
+                if (a.stage_bufs == 4) tma_store_wait_read<3>();
+                else if (a.stage_bufs == 2) tma_store_wait_read<1>();
+                else tma_store_wait_read<0>();
               }
-              if (a.out_relu) f[e] = fmaxf(f[e], 0.f);
-            }
-            if constexpr (SUBN == 64) {
-              w0 = pack_bf16(f[0], f[1]); w1 = pack_bf16(f[2], f[3]); w2 = pack_bf16(f[4], f[5]); w3 = pack_bf16(f[6], f[7]);
+              __syncwarp();
+            });
+          }
+          const uint32_t buf = my_stage + sbuf * 4096u;
+          const uint32_t rowaddr = buf + (uint32_t)lane * 128u;
+          const int c0 = sub * SUBN;
+          if constexpr (UPS == 2) {
+            PW(2, tmem_ld_wait());
+            tmem_ld32(tacc + c0 + 32, vb);
+            PW(4, emit(va, rowaddr, 0));
+            PW(2, tmem_ld_wait());
+            if (sub + 1 < nsub) tmem_ld32(tacc + c0 + 64, va);
+            PW(4, emit(vb, rowaddr, CPU));
+          } else {
+            // fp32 output: one unit per sub-tile; ping-pong the two register arrays over pairs
+            tmem_ld_wait();
+            if (sub & 1) {
+              if (sub + 1 < nsub) tmem_ld32(tacc + c0 + 32, va);
+              emit(vb, rowaddr, 0);
             } else {
-              w0 = __float_as_uint(f[0]); w1 = __float_as_uint(f[1]); w2 = __float_as_uint(f[2]); w3 = __float_as_uint(f[3]);
+              if (sub + 1 < nsub) tmem_ld32(tacc + c0 + 32, vb);
+              emit(va, rowaddr, 0);
             }
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((uint32_t)j ^ row_sw) << 4)), "r"(w0),
-                         "r"(w1), "r"(w2), "r"(w3)
-                         : "memory");
           }
           fence_proxy_async();
           __syncwarp();
           if (lane == 0 && !(a.debug & 1)) {
-            tma_store_3d(&tm_out, buf, n0, m0, s);  // rows >= Ms and columns >= N are clipped by the map
+            tma_store_3d(&tm_out, buf, nb * BN + c0, m0, s);  // rows >= Ms and columns >= N are clipped by the map
             tma_store_commit();
           }
           ++nstore;
+          if (++sbuf == (uint32_t)a.stage_bufs) sbuf = 0;
         }
       }
       tc_fence_before();
@@ -340,6 +391,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       if (++mg == a.num_mg) { mg = 0; if (++nb == a.NB) { nb = 0; ++s; } }
     }
     if (lane == 0) tma_store_wait_all();
+    if (warp == 0) prof_flush(0);
   } else if (warp < WARP_PROD0) {
     reg_dealloc<REGS_CTRL>();
     if (warp == WARP_TMA) {
@@ -378,7 +430,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             const int r = t % N_MMA_WARPS;
             const int ring = a.NR == 2 ? r : 0;
             const int slot = ring * a.NAr + (a.NR == 2 ? rslot[r] : rslot[0]);
-            mbar_wait(smem_u32(&ctrl->a_empty[slot]), (a.NR == 2 ? rphase[r] : rphase[0]) ^ 1u);
+            PW(0, mbar_wait(smem_u32(&ctrl->a_empty[slot]), (a.NR == 2 ? rphase[r] : rphase[0]) ^ 1u));
             if (leader) {
               const uint32_t bar = smem_u32(&ctrl->a_full[slot]);
               if (a.debug & 8) {
@@ -405,25 +457,45 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       if (++mg == a.num_mg) { mg = 0; if (++nb == a.NB) { nb = 0; ++s; } }
     }
     __syncwarp();
+    prof_flush(1);
     } else if (warp < WARP_MMA + N_MMA_WARPS) {
     // =========================== MMA ISSUERS ===========================
     const int j = warp - WARP_MMA;  // this issuer owns tiles t with t % N_MMA_WARPS == j
     const bool leader = elect_one();
     constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
     int mg = mg0, set = 0, aslot = 0, wslot_r = 0;
-    uint32_t set_phase = 0, aphase = 0, wphase = 0;
+    uint32_t set_phase = 0, aphase = 0, wphase = 0, sphase = 0;
+    const uint32_t acc0 = a.has_shift ? 1u : 0u;  // accumulators start from the shift, not from zero
+    const uint64_t ones_desc = umma_desc_sw32(ones_base), shift_desc = umma_desc_sw32(shift_base);
     bool first = true;  // first item of a (sample, n-block) key on this CTA: its W panel is new
     const int ring0 = (a.NR == 2 ? j : 0) * a.NAr;  // first slot of the A ring this issuer consumes
     for (int it = 0; it < n_items; ++it) {
       const bool last = !a.stationary || it + 1 == n_items || mg + 1 == a.num_mg;
-      mbar_wait(smem_u32(&ctrl->acc_empty[set]), set_phase ^ 1u);
+      PW(0, mbar_wait(smem_u32(&ctrl->acc_empty[set]), set_phase ^ 1u));
       tc_fence_after();
       const int mtv = min(a.MT, a.num_mt - mg * a.MT);
       const uint32_t dbase = tmem + (uint32_t)(set * a.MT * BN);
+      if (a.has_shift) {
+        // D = ones[128 x 16] * shift[BN x 16]^T: every row of the accumulator starts as the
+        // per-channel shift (bias * scale + BatchNorm shift, split into three bf16 terms)
+        if (first) {
+          PW(1, mbar_wait(smem_u32(&ctrl->w_full[a.RW]), sphase));
+          tc_fence_after();
+        }
+        if (leader && !(a.debug & 4)) {
+#pragma unroll
+          for (int t = 0; t < MAX_MT; ++t)
+            if (t < mtv && (a.NR == 2 ? (t % N_MMA_WARPS) : 0) == j)
+              umma_bf16(dbase + (uint32_t)(t * BN), ones_desc, shift_desc, idesc, 0u);
+        }
+        if (last && leader) umma_commit(smem_u32(&ctrl->w_empty[a.RW]));
+        __syncwarp();
+        if (last) sphase ^= 1u;
+      }
       for (int kb = 0; kb < a.nkb; ++kb) {
         const int wslot = a.stationary ? kb : wslot_r;
         if (first) {
-          mbar_wait(smem_u32(&ctrl->w_full[wslot]), wphase);
+          PW(1, mbar_wait(smem_u32(&ctrl->w_full[wslot]), wphase));
           tc_fence_after();
         }
         const uint64_t bdesc = umma_desc_sw128(w_base + wslot * W_SLOT);
@@ -432,7 +504,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           if (t < mtv) {
             if ((a.NR == 2 ? (t % N_MMA_WARPS) : 0) == j) {
               const int slot = ring0 + aslot;
-              mbar_wait(smem_u32(&ctrl->a_full[slot]), aphase);
+              PW(2, mbar_wait(smem_u32(&ctrl->a_full[slot]), aphase));
               tc_fence_after();
               if (leader) {
                 const uint64_t adesc = umma_desc_sw128(a_base + slot * A_SLOT);
@@ -440,7 +512,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 if (!(a.debug & 4)) {
 #pragma unroll
                   for (int k = 0; k < BK / 16; ++k)
-                    umma_bf16(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                    umma_bf16(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : acc0);
                 }
                 umma_commit(smem_u32(&ctrl->a_empty[slot]));
               }
@@ -461,6 +533,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       }
       if (++mg == a.num_mg) mg = 0;
     }
+    prof_flush(2 + j);
     }
   } else {
     // =========================== W PRODUCERS (sample in smem) ===========================
@@ -470,10 +543,47 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     const int row_base = p >> 3;  // rows row_base + 32*i
     constexpr int ROWS_PER_THREAD = BN / (PROD_THREADS / 8);
     int s = s0, nb = nb0, mg = mg0, wslot_r = 0;
-    uint32_t wphase = 0;
+    uint32_t wphase = 0, sphase = 0;
     bool first = true;
+    if (a.has_shift && p < BM) {  // the constant ones tile (made visible by the first w_full[RW] arrival)
+      const uint32_t dst = ones_base + (uint32_t)p * 32u;
+      const uint32_t sw = (uint32_t)((p >> 2) & 1) << 4;  // 32-byte swizzle: chunk ^= bit 2 of the row
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + sw), "r"(0x3F803F80u), "r"(0x00003F80u), "r"(0u), "r"(0u) : "memory");
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (sw ^ 16u)), "r"(0u), "r"(0u), "r"(0u), "r"(0u) : "memory");
+    }
     for (int it = 0; it < n_items; ++it) {
       if (first || !a.stationary) {
+        if (a.has_shift) {
+          PW(0, mbar_wait(smem_u32(&ctrl->w_empty[a.RW]), sphase ^ 1u));
+          if (p < BN) {
+            const int n = nb * BN + p;
+            float sh = 0.f;
+            if (n < a.N) {
+              if (a.mu_b) {
+                const float e = a.eps_b ? a.eps_b[n]
+                                        : bt_normal1((uint64_t)n, bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_B));
+                sh = a.mu_b[n] + bt_softplus(a.rho_b[n]) * e;
+              }
+              if (a.out_scale) sh *= a.out_scale[n];
+              if (a.out_shift) sh += a.out_shift[n];
+            }
+            // three bf16 terms carry 24 bits of the fp32 shift through the bf16 MMA
+            const __nv_bfloat16 h0 = __float2bfloat16_rn(sh);
+            const float r1 = sh - __bfloat162float(h0);
+            const __nv_bfloat16 h1 = __float2bfloat16_rn(r1);
+            const __nv_bfloat16 h2 = __float2bfloat16_rn(r1 - __bfloat162float(h1));
+            const uint32_t w0 = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+            const uint32_t w1 = (uint32_t)__bfloat16_as_ushort(h2);
+            const uint32_t dst = shift_base + (uint32_t)p * 32u;
+            const uint32_t sw = (uint32_t)((p >> 2) & 1) << 4;
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + sw), "r"(w0), "r"(w1), "r"(0u), "r"(0u) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (sw ^ 16u)), "r"(0u), "r"(0u), "r"(0u), "r"(0u) : "memory");
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&ctrl->w_full[a.RW]));
+          sphase ^= 1u;
+        }
         const BtRngKey rk = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_W);
         for (int kb = 0; kb < a.nkb; ++kb) {
           const int slot = a.stationary ? kb : wslot_r;
@@ -485,7 +595,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           for (int i = 0; i < ROWS_PER_THREAD; ++i) {  // parameter loads first (L2 resident), then the slot wait
             const int n = nb * BN + row_base + (PROD_THREADS / 8) * i;
             mu4[i][0] = mu4[i][1] = sg4[i][0] = sg4[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (kin && n < a.N) {
+            if (kin && n < a.N && !(a.debug & 32)) {
               const int64_t e = (int64_t)n * a.K + k;
               mu4[i][0] = __ldg(reinterpret_cast<const float4*>(a.mu_p + e));
               mu4[i][1] = __ldg(reinterpret_cast<const float4*>(a.mu_p + e + 4));
@@ -493,7 +603,8 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               sg4[i][1] = __ldg(reinterpret_cast<const float4*>(a.sig_p + e + 4));
             }
           }
-          mbar_wait(smem_u32(&ctrl->w_empty[slot]), wphase ^ 1u);
+          PW(0, mbar_wait(smem_u32(&ctrl->w_empty[slot]), wphase ^ 1u));
+          const long long gen_t0 = PROF ? clock64() : 0;
 #pragma unroll
           for (int i = 0; i < ROWS_PER_THREAD; ++i) {
             const int row = row_base + (PROD_THREADS / 8) * i;
@@ -501,7 +612,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             float z[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) z[e] = 0.f;
-            if (kin && n < a.N) {
+            if (kin && n < a.N && !(a.debug & 16)) {
               const int64_t e = (int64_t)n * a.K + k;
               if (a.eps_p) {
                 const float4 e0 = __ldg(reinterpret_cast<const float4*>(a.eps_p + e));
@@ -533,6 +644,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           fence_proxy_async();
           __syncwarp();
           if (lane == 0) mbar_arrive(smem_u32(&ctrl->w_full[slot]));
+          if constexpr (PROF) pc[1] += (unsigned long long)(clock64() - gen_t0);
           if (!a.stationary && ++wslot_r == a.RW) { wslot_r = 0; wphase ^= 1u; }
         }
         if (a.stationary) wphase ^= 1u;
@@ -540,6 +652,8 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       first = false;
       if (++mg == a.num_mg) { mg = 0; first = true; if (++nb == a.NB) { nb = 0; ++s; } }
     }
+    if (warp == WARP_PROD0) prof_flush(4);
+    if (warp == WARP_PROD0 + N_PROD_WARPS - 1) prof_flush(5);
   }
 
   tc_fence_before();
@@ -719,9 +833,26 @@ int64_t bt_tc_workspace_bytes(const bt_geom* g) {
 template <int BN, typename TO>
 static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const Tc2Args& a, int grid, int smem_bytes,
                       cudaStream_t stream) {
-  BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-  tc2_fwd_kernel<BN, TO><<<grid, NUM_THREADS, smem_bytes, stream>>>(ta, to, a);
+  if constexpr (sizeof(TO) == 2) {
+    if (env_int("BT_TC2_PROF", 0)) {
+      BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+      tc2_fwd_kernel<BN, TO, true><<<grid, NUM_THREADS, smem_bytes, stream>>>(ta, to, a);
+      BT_LAUNCH_OK("tc2_fwd_kernel(prof)");
+      return BT_OK;
+    }
+  }
+  BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  tc2_fwd_kernel<BN, TO, false><<<grid, NUM_THREADS, smem_bytes, stream>>>(ta, to, a);
   BT_LAUNCH_OK("tc2_fwd_kernel");
+  return BT_OK;
+}
+
+// Diagnostics: cycle counters of the last BT_TC2_PROF=1 launch, [cta][role][slot] (see bt_b200.h).
+extern "C" int bt_debug_tc_profile(unsigned long long* host_out, int n_words) {
+  const int total = 160 * PROF_ROLES * PROF_SLOTS;
+  if (!host_out || n_words < total) { bt_set_error("bt_debug_tc_profile: need room for %d words", total); return BT_ERR_INVALID; }
+  BT_CUDA_OK(cudaDeviceSynchronize());
+  BT_CUDA_OK(cudaMemcpyFromSymbol(host_out, g_tc_prof, sizeof(unsigned long long) * total));
   return BT_OK;
 }
 
@@ -761,10 +892,12 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
     int64_t blocks = (wn + 255) / 256;
     const int64_t cap = (int64_t)bt_num_sms() * 8;
     if (blocks > cap) blocks = cap;
-    tc2_pack_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, wn, (int)g->c_in, pl.T, a.K);
+    tc2_pack_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, p->out_scale, wn, (int)g->c_in, pl.T,
+                                                     a.K);
     BT_LAUNCH_OK("tc2_pack_kernel");
   }
   a.mu_p = mu_p; a.sig_p = sig_p; a.eps_p = eps_p;
+  a.has_shift = (p->mu_b || p->out_shift) ? 1 : 0;
 
   const void* a_src = x;
   if (pl.mode == A_PATCH) {
@@ -871,6 +1004,14 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.NA = (RING_BYTES - a.RW * WB) / A_SLOT;
   if (a.NA < 4) { a.stage_bufs = 1; a.NA = (RING_BYTES + STAGE_BYTES / 2 - a.RW * WB) / A_SLOT; }
   if (a.NA > MAX_NA) a.NA = MAX_NA;
+  // leftover shared memory deepens the epilogue staging (4 TMA stores in flight per warp); a
+  // stationary layer with a long A ring trades two of its slots for it
+  if (a.stage_bufs == 2) {
+    const int left = RING_BYTES - a.RW * WB - a.NA * A_SLOT;
+    if (left >= STAGE_BYTES) a.stage_bufs = 4;
+    else if (a.stationary && a.NA >= 6) { a.stage_bufs = 4; a.NA -= 2; }
+  }
+  if (env_int("BT_TC2_STAGE", 0) == 2 && a.stage_bufs == 4) a.stage_bufs = 2;
   if (env_int("BT_TC2_NA", 0) >= 2 && env_int("BT_TC2_NA", 0) < a.NA) a.NA = env_int("BT_TC2_NA", 0);
   a.NR = a.MT >= 2 ? N_MMA_WARPS : 1;
   a.NAr = a.NA / a.NR;
@@ -879,6 +1020,7 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.total_items = (int64_t)a.S * a.NB * a.num_mg;
   const int grid = (int)(a.total_items < sms ? a.total_items : sms);
   const int smem_bytes = 1024 + CTRL_BYTES + a.stage_bufs * (STAGE_BYTES / 2) + a.NA * A_SLOT + a.RW * WB;
+  BT_REQUIRE(smem_bytes <= SMEM_LIMIT, BT_ERR_UNSUPPORTED, "tensor-core forward: shared memory plan %d exceeds %d", smem_bytes, SMEM_LIMIT);
   if (env_int("BT_TC2_LOG", 0))
     fprintf(stderr, "tc2: mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d\n",
             (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,

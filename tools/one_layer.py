@@ -18,7 +18,12 @@ torch.manual_seed(0)
 layer = L.Conv2dReparameterization(cin, cout, k, stride=stride, padding=pad, bias=False, prior_type="normal").to(dev)
 layer.path = "tc"
 layer.dnn_to_bnn_flag = True
-x = torch.randn(batch, cin, hw, hw, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+if os.environ.get("BT_AFF", "0") == "1":  # folded BatchNorm + ReLU epilogue
+    layer._ep_scale = torch.rand(cout, device=dev) + 0.5
+    layer._ep_shift = torch.randn(cout, device=dev)
+    layer._ep_relu = True
+XS = S if os.environ.get("BT_XS", "0") == "1" else 1  # per-sample activations (any layer but the first)
+x = torch.randn(XS * batch, cin, hw, hw, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
 with torch.no_grad():
     for i in range(iters + 2):
         if i == 2:
