@@ -38,7 +38,8 @@ class LayerParams(C.Structure):
         "prior_mu_w_t", "prior_sigma_w_t", "prior_mu_b_t", "prior_sigma_b_t")] + [
         ("prior_mu", C.c_float), ("prior_sigma", C.c_float),
         ("seed", C.c_uint64), ("sample_id", C.c_uint32), ("layer_id", C.c_uint32),
-        ("out_scale", C.c_void_p), ("out_shift", C.c_void_p), ("out_relu", C.c_int32), ("reserved", C.c_int32)]
+        ("out_scale", C.c_void_p), ("out_shift", C.c_void_p), ("out_relu", C.c_int32), ("reserved", C.c_int32),
+        ("residual", C.c_void_p)]
 
 
 class LayerGrads(C.Structure):
@@ -98,7 +99,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
-        if handle.bt_abi_version() != 2:
+        if handle.bt_abi_version() != 3:
             raise RuntimeError("libbt_b200.so ABI version mismatch")
         _lib = handle
     return _lib

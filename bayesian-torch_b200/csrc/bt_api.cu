@@ -108,8 +108,8 @@ static int backward_common(const bt_geom* g, const bt_layer_params* p, const voi
   int rc = check_common(g, p, x, grad_out, who);
   if (rc != BT_OK) return rc;
   BT_REQUIRE(grads, BT_ERR_INVALID, "%s: null grads", who);
-  BT_REQUIRE(!p->out_scale && !p->out_shift && !p->out_relu, BT_ERR_UNSUPPORTED,
-             "%s: the folded BatchNorm / ReLU epilogue is inference-only", who);
+  BT_REQUIRE(!p->out_scale && !p->out_shift && !p->out_relu && !p->residual, BT_ERR_UNSUPPORTED,
+             "%s: the folded BatchNorm / ReLU / residual epilogue is inference-only", who);
   BT_REQUIRE(path != BT_PATH_TC_BF16, BT_ERR_UNSUPPORTED, "%s: backward runs on the fp32 SIMT path in this build", who);
   return bt_simt_backward(g, p, x, grad_out, grad_kl, grads, workspace, flipout, (cudaStream_t)stream);
 }

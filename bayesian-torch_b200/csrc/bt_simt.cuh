@@ -20,6 +20,7 @@ struct SParams {
   const float *mu_w, *rho_w, *mu_b, *rho_b, *eps_w, *eps_b, *sign_in, *sign_out;
   const float *out_scale, *out_shift;  // folded BatchNorm epilogue (forward only)
   int out_relu;
+  const void* residual;  // out-shaped, out dtype (forward only)
   uint64_t seed;
   uint32_t sample_id, layer_id;
 };
@@ -74,7 +75,7 @@ static inline SParams bt_sparams_from(const bt_layer_params* p) {
   SParams s;
   s.mu_w = p->mu_w; s.rho_w = p->rho_w; s.mu_b = p->mu_b; s.rho_b = p->rho_b;
   s.eps_w = p->eps_w; s.eps_b = p->eps_b; s.sign_in = p->sign_in; s.sign_out = p->sign_out;
-  s.out_scale = p->out_scale; s.out_shift = p->out_shift; s.out_relu = p->out_relu;
+  s.out_scale = p->out_scale; s.out_shift = p->out_shift; s.out_relu = p->out_relu; s.residual = p->residual;
   s.seed = p->seed; s.sample_id = p->sample_id; s.layer_id = p->layer_id;
   return s;
 }

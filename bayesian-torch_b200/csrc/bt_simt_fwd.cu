@@ -209,6 +209,8 @@ __global__ void __launch_bounds__(NT) simt_fwd_kernel(const SGeo g, const SParam
       }
       if (p.out_scale) v *= p.out_scale[ngl[j]];
       if (p.out_shift) v += p.out_shift[ngl[j]];
+      if (p.residual)  // eager-graph rounding: the affine result is rounded to out's dtype before the add
+        v = bt_to_float<TO>(bt_from_float<TO>(v)) + bt_to_float<TO>(static_cast<const TO*>(p.residual)[off]);
       if (p.out_relu) v = fmaxf(v, 0.f);
       out[off] = bt_from_float<TO>(v);
     }

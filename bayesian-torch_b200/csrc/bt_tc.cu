@@ -29,6 +29,7 @@
 #include <string.h>
 
 #include <mutex>
+#include <type_traits>
 
 #include "bt_common.cuh"
 #include "bt_tc.cuh"
@@ -44,7 +45,7 @@ constexpr int BAR_BYTES = 1024;           // mbarriers + TMEM base
 constexpr int ONES_BYTES = BM * 32;       // [128 x 16] bf16 tile of the rank-1 "add shift" MMA (32-byte swizzle)
 constexpr int SHIFT_BYTES = 128 * 32;     // [BN x 16] bf16: per-channel shift split into three bf16 terms
 constexpr int CTRL_BYTES = BAR_BYTES + ONES_BYTES + SHIFT_BYTES;
-constexpr int STAGE_BYTES = 4 * 2 * 4096;  // per epilogue warp: 2 buffers of 32 rows x 128 B (1 when smem is tight)
+constexpr int STAGE_UNIT = 4 * 4096;  // one staging (or residual) buffer of 32 rows x 128 B for each of the 4 epilogue warps
 constexpr int N_PROD_WARPS = 16;
 constexpr int N_MMA_WARPS = 2;  // issuer warps: tile t of an m-group belongs to issuer t % 2
 // warp groups (setmaxnreg works on aligned groups of 4 warps): 0 = epilogue, 1 = TMA + 2 MMA issuers
@@ -59,7 +60,7 @@ constexpr int REGS_EPI = 120, REGS_CTRL = 72, REGS_PROD = 72;
 constexpr int PROD_THREADS = N_PROD_WARPS * 32;
 constexpr int MAX_NA = 8, MAX_RW = 24, MAX_SETS = 8, MAX_MT = 4;
 constexpr int SMEM_LIMIT = 232448;
-constexpr int RING_BYTES = SMEM_LIMIT - 1024 - CTRL_BYTES - STAGE_BYTES;  // A ring + W ring / panel
+constexpr int AVAIL_BYTES = SMEM_LIMIT - 1024 - CTRL_BYTES;  // staging + residual ring + A ring + W ring / panel
 
 struct Tc2Args {
   const float *mu_p, *sig_p, *eps_p;  // packed [N][K], k = tap*Cin + c
@@ -77,8 +78,10 @@ struct Tc2Args {
   int num_mt, num_mg, MT, NSETS, nkb, NA, RW, stationary;
   int NR, NAr;       // A rings (one per active MMA issuer) and slots per ring; NA = NR * NAr
   int has_shift;     // bias and/or folded BatchNorm shift: added by a rank-1 MMA that initialises each accumulator
+  int res_bufs;      // residual tiles in flight per epilogue warp (0: no residual input)
   int stage_bufs;    // epilogue staging buffers per warp (2, or 1 when shared memory is tight)
-  int debug;         // BT_TC2_DEBUG bits (timing experiments only): 1 = skip the output stores
+  int debug;         // BT_TC2_DEBUG bits, honoured by the BT_TC2_PROF=1 instantiation only: 1 skip output stores, 4 skip MMAs,
+                     // 8 skip A loads, 16 skip the normal draws, 32 skip the parameter loads
   uint64_t seed;
   uint32_t sample_id, layer_id;
 };
@@ -87,6 +90,7 @@ struct Ctrl {
   uint64_t a_full[MAX_NA], a_empty[MAX_NA];
   uint64_t w_full[MAX_RW + 1], w_empty[MAX_RW + 1];  // slot RW: the shift tile
   uint64_t acc_full[MAX_SETS], acc_empty[MAX_SETS];
+  uint64_t res_full[4][4];  // [epilogue warp][residual buffer]
   uint32_t tmem_base;
   uint32_t pad[3];
 };
@@ -107,6 +111,11 @@ __device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const CUtensorM
       "[%2], {%7, %8};"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
       : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+               ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
 }
 __device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
@@ -220,29 +229,49 @@ __global__ void tc2_patch_kernel(const TX* __restrict__ x, __nv_bfloat16* __rest
 // into chunks [cb, cb + 32/EPC) of the 128-byte staging row.  Bias and folded BatchNorm never show
 // up here: the scale is folded into the sampled weights and the shift is in the accumulator
 // already (rank-1 MMA), so for bf16 outputs this is one cvt (with .relu) per two elements.
-template <typename TO, bool RELU>
-__device__ __forceinline__ void epi_unit(const uint32_t (&v)[32], uint32_t rowaddr, int cb, uint32_t row_sw) {
+template <typename TO, bool RELU, bool RES>
+__device__ __forceinline__ void epi_unit(const uint32_t (&v)[32], uint32_t rowaddr, uint32_t resaddr, int cb, uint32_t row_sw) {
   constexpr int EPC = 16 / (int)sizeof(TO);  // elements per 16-byte chunk
   constexpr int NCH = 32 / EPC;              // chunks per unit
+  uint32_t r[RES ? NCH : 1][4];
+  if constexpr (RES) {  // the residual tile sits in shared memory in the staging layout: all loads first
+#pragma unroll
+    for (int j = 0; j < NCH; ++j)
+      asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(r[j][0]), "=r"(r[j][1]), "=r"(r[j][2]), "=r"(r[j][3])
+                   : "r"(resaddr + (((uint32_t)(cb + j) ^ row_sw) << 4)));
+  }
 #pragma unroll
   for (int j = 0; j < NCH; ++j) {
     float f[EPC];
 #pragma unroll
     for (int e = 0; e < EPC; ++e) f[e] = __uint_as_float(v[j * EPC + e]);
-    uint32_t w0, w1, w2, w3;
+    uint32_t w[4];
     if constexpr (sizeof(TO) == 2) {
-      if constexpr (RELU) {  // cvt.rn.relu: the clamp rides on the conversion
-        w0 = pack_bf16_relu(f[0], f[1]); w1 = pack_bf16_relu(f[2], f[3]);
-        w2 = pack_bf16_relu(f[4], f[5]); w3 = pack_bf16_relu(f[6], f[7]);
+      if constexpr (RELU && !RES) {  // cvt.rn.relu: the clamp rides on the conversion
+        w[0] = pack_bf16_relu(f[0], f[1]); w[1] = pack_bf16_relu(f[2], f[3]);
+        w[2] = pack_bf16_relu(f[4], f[5]); w[3] = pack_bf16_relu(f[6], f[7]);
       } else {
-        w0 = pack_bf16(f[0], f[1]); w1 = pack_bf16(f[2], f[3]); w2 = pack_bf16(f[4], f[5]); w3 = pack_bf16(f[6], f[7]);
+        w[0] = pack_bf16(f[0], f[1]); w[1] = pack_bf16(f[2], f[3]); w[2] = pack_bf16(f[4], f[5]); w[3] = pack_bf16(f[6], f[7]);
+      }
+      if constexpr (RES) {  // bf16(bf16(affine) + residual), then the clamp: what the eager bf16 graph computes
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          __nv_bfloat162 t = __hadd2(*reinterpret_cast<const __nv_bfloat162*>(&w[i]), *reinterpret_cast<const __nv_bfloat162*>(&r[j][i]));
+          if constexpr (RELU) t = __hmax2(t, __floats2bfloat162_rn(0.f, 0.f));
+          w[i] = *reinterpret_cast<const uint32_t*>(&t);
+        }
       }
     } else {
-      if constexpr (RELU) { f[0] = fmaxf(f[0], 0.f); f[1] = fmaxf(f[1], 0.f); f[2] = fmaxf(f[2], 0.f); f[3] = fmaxf(f[3], 0.f); }
-      w0 = __float_as_uint(f[0]); w1 = __float_as_uint(f[1]); w2 = __float_as_uint(f[2]); w3 = __float_as_uint(f[3]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if constexpr (RES) f[i] += __uint_as_float(r[j][i]);
+        if constexpr (RELU) f[i] = fmaxf(f[i], 0.f);
+        w[i] = __float_as_uint(f[i]);
+      }
     }
-    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((uint32_t)(cb + j) ^ row_sw) << 4)), "r"(w0),
-                 "r"(w1), "r"(w2), "r"(w3)
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + (((uint32_t)(cb + j) ^ row_sw) << 4)), "r"(w[0]),
+                 "r"(w[1]), "r"(w[2]), "r"(w[3])
                  : "memory");
   }
 }
@@ -265,7 +294,7 @@ __device__ unsigned long long g_tc_prof[160 * PROF_ROLES * PROF_SLOTS];
 template <int BN, typename TO, bool PROF>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_out,
-               const __grid_constant__ Tc2Args a) {
+               const __grid_constant__ CUtensorMap tm_res, const __grid_constant__ Tc2Args a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -274,7 +303,8 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   constexpr int SUBN = 128 / (int)sizeof(TO);  // output columns per 128-byte staging row
   const uint32_t ones_base = base + BAR_BYTES, shift_base = ones_base + ONES_BYTES;
   const uint32_t stage_base = base + CTRL_BYTES;
-  const uint32_t a_base = stage_base + (uint32_t)a.stage_bufs * 16384u;
+  const uint32_t res_base = stage_base + (uint32_t)a.stage_bufs * STAGE_UNIT;
+  const uint32_t a_base = res_base + (uint32_t)a.res_bufs * STAGE_UNIT;
   const uint32_t w_base = a_base + a.NA * A_SLOT;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -292,9 +322,10 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     for (int i = 0; i < a.NA; ++i) { mbar_init(smem_u32(&ctrl->a_full[i]), 1); mbar_init(smem_u32(&ctrl->a_empty[i]), 1); }
     for (int i = 0; i <= a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), N_PROD_WARPS); mbar_init(smem_u32(&ctrl->w_empty[i]), N_MMA_WARPS); }
     for (int i = 0; i < a.NSETS; ++i) { mbar_init(smem_u32(&ctrl->acc_full[i]), N_MMA_WARPS); mbar_init(smem_u32(&ctrl->acc_empty[i]), 128); }
+    for (int i = 0; i < 16; ++i) mbar_init(smem_u32(&ctrl->res_full[i >> 2][i & 3]), 1);
     mbar_fence_init();
   }
-  if (warp == WARP_TMA && lane == 0) { prefetch_tmap(&tm_a); prefetch_tmap(&tm_out); }
+  if (warp == WARP_TMA && lane == 0) { prefetch_tmap(&tm_a); prefetch_tmap(&tm_out); if (a.res_bufs) prefetch_tmap(&tm_res); }
   if (warp == WARP_MMA) tmem_alloc(smem_u32(&ctrl->tmem_base), 512);
   tc_fence_before();
   __syncthreads();
@@ -323,9 +354,38 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     constexpr int CPU = 8 / UPS;                      // 16-byte chunks of the staging row per unit
     int s = s0, nb = nb0, mg = mg0, set = 0;
     uint32_t set_phase = 0;
-    auto emit = [&](const uint32_t (&v)[32], uint32_t rowaddr, int cb) {
-      if (relu) epi_unit<TO, true>(v, rowaddr, cb, row_sw);  // warp-uniform; each side is straight-line code
-      else epi_unit<TO, false>(v, rowaddr, cb, row_sw);
+    const bool has_res = a.res_bufs != 0;
+    // Residual tiles are fetched by TMA res_bufs sub-tiles ahead of their use: a second cursor
+    // walks the same (item, tile, sub-tile) sequence as the loops below, skipping slabs past Ms.
+    int pf_it = 0, pf_s = s0, pf_nb = nb0, pf_mg = mg0, pf_t = 0, pf_sub = 0;
+    const uint32_t my_res = res_base + (uint32_t)(q * a.res_bufs) * 4096u;
+    auto pf_issue = [&](int slot) {
+      while (pf_it < n_items) {
+        if (pf_t < min(a.MT, a.num_mt - pf_mg * a.MT) && (pf_mg * a.MT + pf_t) * BM + q * 32 < a.Ms) {
+          if (pf_sub < (min(BN, a.N - pf_nb * BN) + SUBN - 1) / SUBN) break;
+          pf_sub = 0; ++pf_t;
+          continue;
+        }
+        pf_t = 0; pf_sub = 0; ++pf_it;
+        if (++pf_mg == a.num_mg) { pf_mg = 0; if (++pf_nb == a.NB) { pf_nb = 0; ++pf_s; } }
+      }
+      if (pf_it >= n_items) return;
+      if (lane == 0) {
+        const uint32_t bar = smem_u32(&ctrl->res_full[q][slot]);
+        mbar_expect_tx(bar, 4096);
+        tma_load_3d(my_res + (uint32_t)slot * 4096u, &tm_res, bar, pf_nb * BN + pf_sub * SUBN, (pf_mg * a.MT + pf_t) * BM + q * 32, pf_s);
+      }
+      ++pf_sub;
+    };
+    int rslot = 0;
+    uint32_t rphase = 0;
+    for (int i = 0; i < a.res_bufs; ++i) pf_issue(i);
+    // the whole loop is instantiated per (ReLU, residual) combination: the variant that runs is
+    // straight-line code, and the other three never enter the instruction cache
+    auto epi_loop = [&](auto relu_c, auto res_c) {
+    constexpr bool RELU = decltype(relu_c)::value, RES = decltype(res_c)::value;
+    auto emit = [&](const uint32_t (&v)[32], uint32_t rowaddr, uint32_t resaddr, int cb) {
+      epi_unit<TO, RELU, RES>(v, rowaddr, resaddr, cb, row_sw);
     };
     for (int it = 0; it < n_items; ++it) {
       PW(0, mbar_wait(smem_u32(&ctrl->acc_full[set]), set_phase));
@@ -356,33 +416,39 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           }
           const uint32_t buf = my_stage + sbuf * 4096u;
           const uint32_t rowaddr = buf + (uint32_t)lane * 128u;
+          const uint32_t resaddr = my_res + (uint32_t)rslot * 4096u + (uint32_t)lane * 128u;
+          if constexpr (RES) PW(1, mbar_wait(smem_u32(&ctrl->res_full[q][rslot]), rphase));
           const int c0 = sub * SUBN;
           if constexpr (UPS == 2) {
             PW(2, tmem_ld_wait());
             tmem_ld32(tacc + c0 + 32, vb);
-            PW(4, emit(va, rowaddr, 0));
+            PW(4, emit(va, rowaddr, resaddr, 0));
             PW(2, tmem_ld_wait());
             if (sub + 1 < nsub) tmem_ld32(tacc + c0 + 64, va);
-            PW(4, emit(vb, rowaddr, CPU));
+            PW(4, emit(vb, rowaddr, resaddr, CPU));
           } else {
             // fp32 output: one unit per sub-tile; ping-pong the two register arrays over pairs
             tmem_ld_wait();
             if (sub & 1) {
               if (sub + 1 < nsub) tmem_ld32(tacc + c0 + 32, va);
-              emit(vb, rowaddr, 0);
+              emit(vb, rowaddr, resaddr, 0);
             } else {
               if (sub + 1 < nsub) tmem_ld32(tacc + c0 + 32, vb);
-              emit(va, rowaddr, 0);
+              emit(va, rowaddr, resaddr, 0);
             }
           }
           fence_proxy_async();
           __syncwarp();
-          if (lane == 0 && !(a.debug & 1)) {
+          if (lane == 0 && !(PROF && (a.debug & 1))) {
             tma_store_3d(&tm_out, buf, nb * BN + c0, m0, s);  // rows >= Ms and columns >= N are clipped by the map
             tma_store_commit();
           }
           ++nstore;
           if (++sbuf == (uint32_t)a.stage_bufs) sbuf = 0;
+          if constexpr (RES) {  // every lane is done reading the tile (fence + __syncwarp above): refill its buffer
+            pf_issue(rslot);
+            if (++rslot == a.res_bufs) { rslot = 0; rphase ^= 1u; }
+          }
         }
       }
       tc_fence_before();
@@ -390,6 +456,11 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       if (++set == a.NSETS) { set = 0; set_phase ^= 1u; }
       if (++mg == a.num_mg) { mg = 0; if (++nb == a.NB) { nb = 0; ++s; } }
     }
+    };
+    using T_ = std::true_type;
+    using F_ = std::false_type;
+    if (has_res) { if (relu) epi_loop(T_{}, T_{}); else epi_loop(F_{}, T_{}); }
+    else { if (relu) epi_loop(T_{}, F_{}); else epi_loop(F_{}, F_{}); }
     if (lane == 0) tma_store_wait_all();
     if (warp == 0) prof_flush(0);
   } else if (warp < WARP_PROD0) {
@@ -433,7 +504,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             PW(0, mbar_wait(smem_u32(&ctrl->a_empty[slot]), (a.NR == 2 ? rphase[r] : rphase[0]) ^ 1u));
             if (leader) {
               const uint32_t bar = smem_u32(&ctrl->a_full[slot]);
-              if (a.debug & 8) {
+              if (PROF && (a.debug & 8)) {
                 mbar_arrive(bar);
               } else {
                 mbar_expect_tx(bar, A_SLOT);
@@ -482,7 +553,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           PW(1, mbar_wait(smem_u32(&ctrl->w_full[a.RW]), sphase));
           tc_fence_after();
         }
-        if (leader && !(a.debug & 4)) {
+        if (leader && !(PROF && (a.debug & 4))) {
 #pragma unroll
           for (int t = 0; t < MAX_MT; ++t)
             if (t < mtv && (a.NR == 2 ? (t % N_MMA_WARPS) : 0) == j)
@@ -509,7 +580,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               if (leader) {
                 const uint64_t adesc = umma_desc_sw128(a_base + slot * A_SLOT);
                 const uint32_t d = dbase + (uint32_t)(t * BN);
-                if (!(a.debug & 4)) {
+                if (!(PROF && (a.debug & 4))) {
 #pragma unroll
                   for (int k = 0; k < BK / 16; ++k)
                     umma_bf16(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : acc0);
@@ -595,7 +666,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           for (int i = 0; i < ROWS_PER_THREAD; ++i) {  // parameter loads first (L2 resident), then the slot wait
             const int n = nb * BN + row_base + (PROD_THREADS / 8) * i;
             mu4[i][0] = mu4[i][1] = sg4[i][0] = sg4[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (kin && n < a.N && !(a.debug & 32)) {
+            if (kin && n < a.N && !(PROF && (a.debug & 32))) {
               const int64_t e = (int64_t)n * a.K + k;
               mu4[i][0] = __ldg(reinterpret_cast<const float4*>(a.mu_p + e));
               mu4[i][1] = __ldg(reinterpret_cast<const float4*>(a.mu_p + e + 4));
@@ -612,7 +683,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             float z[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) z[e] = 0.f;
-            if (kin && n < a.N && !(a.debug & 16)) {
+            if (kin && n < a.N && !(PROF && (a.debug & 16))) {
               const int64_t e = (int64_t)n * a.K + k;
               if (a.eps_p) {
                 const float4 e0 = __ldg(reinterpret_cast<const float4*>(a.eps_p + e));
@@ -831,18 +902,18 @@ int64_t bt_tc_workspace_bytes(const bt_geom* g) {
 }
 
 template <int BN, typename TO>
-static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const Tc2Args& a, int grid, int smem_bytes,
+static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const Tc2Args& a, int grid, int smem_bytes,
                       cudaStream_t stream) {
   if constexpr (sizeof(TO) == 2) {
     if (env_int("BT_TC2_PROF", 0)) {
       BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-      tc2_fwd_kernel<BN, TO, true><<<grid, NUM_THREADS, smem_bytes, stream>>>(ta, to, a);
+      tc2_fwd_kernel<BN, TO, true><<<grid, NUM_THREADS, smem_bytes, stream>>>(ta, to, tr, a);
       BT_LAUNCH_OK("tc2_fwd_kernel(prof)");
       return BT_OK;
     }
   }
   BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-  tc2_fwd_kernel<BN, TO, false><<<grid, NUM_THREADS, smem_bytes, stream>>>(ta, to, a);
+  tc2_fwd_kernel<BN, TO, false><<<grid, NUM_THREADS, smem_bytes, stream>>>(ta, to, tr, a);
   BT_LAUNCH_OK("tc2_fwd_kernel");
   return BT_OK;
 }
@@ -879,7 +950,7 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.Kt = pl.K;
   a.K = pl.mode == A_PATCH ? pl.Kp : pl.K;
   a.x_rows_per_s = x_shared ? 0 : (int)pl.x_rows;
-  alignas(64) CUtensorMap tm_a, tm_out;
+  alignas(64) CUtensorMap tm_a, tm_out, tm_res;
   const int es_o = g->out_dtype == BT_F32 ? 4 : 2;
 
   // ---- workspace carve-up: packed parameters, then (A_PATCH) the patch matrix
@@ -965,6 +1036,14 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
                                  out, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                  CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     BT_REQUIRE(r == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeTiled(out) failed with %d", (int)r);
+    tm_res = tm_out;  // placeholder when there is no residual (never dereferenced)
+    if (p->residual) {  // same shape, dtype and strides as out: the same map over another base
+      BT_REQUIRE(((uintptr_t)p->residual & 15) == 0, BT_ERR_ALIGN, "tensor-core forward: residual must be 16-byte aligned");
+      const CUresult r2 = drv.tiled(&tm_res, es_o == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3,
+                                    const_cast<void*>(p->residual), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      BT_REQUIRE(r2 == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeTiled(residual) failed with %d", (int)r2);
+    }
   }
 
   // ---- tiling / pipeline configuration
@@ -972,9 +1051,13 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.num_mt = (a.Ms + BM - 1) / BM;
   a.nkb = (a.K + BK - 1) / BK;
   int BN = a.N <= 64 ? 64 : 128;
+  // shared-memory budget: staging (1, 2 or 4 buffers per epilogue warp) + residual ring (0, 2 or 4)
+  // + A ring + W ring / panel
+  const int res_min = p->residual ? 2 : 0;
+  auto ring_bytes = [&](int stage_bufs, int res_bufs) { return AVAIL_BYTES - (stage_bufs + res_bufs) * STAGE_UNIT; };
   // a [BN x K] panel that fits next to a 4-deep A ring is generated once per (sample, n-block)
-  // (with single-buffered epilogue staging there are 16 KB more)
-  auto panel_fits = [&](int bn) { return a.nkb <= MAX_RW && (int64_t)a.nkb * bn * BK * 2 + 4 * A_SLOT <= RING_BYTES + STAGE_BYTES / 2; };
+  // (single-buffered epilogue staging is accepted for that)
+  auto panel_fits = [&](int bn) { return a.nkb <= MAX_RW && (int64_t)a.nkb * bn * BK * 2 + 4 * A_SLOT <= ring_bytes(1, res_min); };
   const int force_bn = env_int("BT_TC2_BN", 0), force_mt = env_int("BT_TC2_MT", 0), force_stat = env_int("BT_TC2_STATIONARY", -1);
   if (BN == 128 && !panel_fits(128) && panel_fits(64)) BN = 64;
   if (force_bn == 64 || force_bn == 128) BN = force_bn;
@@ -994,22 +1077,27 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
       if (items >= sms || mt == 1 || (mt == 2 && a.num_mt >= 2)) { a.MT = mt; break; }
     }
     if (force_mt >= 1 && force_mt <= MAX_MT && force_mt <= NSLOTS) a.MT = force_mt;
-    a.RW = (RING_BYTES - 4 * A_SLOT) / WB;
+    a.RW = (ring_bytes(2, res_min) - 4 * A_SLOT) / WB;
     if (a.RW > 8) a.RW = 8;
   }
   a.NSETS = NSLOTS / a.MT;
   if (a.NSETS > MAX_SETS) a.NSETS = MAX_SETS;
   a.num_mg = (a.num_mt + a.MT - 1) / a.MT;
   a.stage_bufs = 2;
-  a.NA = (RING_BYTES - a.RW * WB) / A_SLOT;
-  if (a.NA < 4) { a.stage_bufs = 1; a.NA = (RING_BYTES + STAGE_BYTES / 2 - a.RW * WB) / A_SLOT; }
+  a.res_bufs = res_min;
+  a.NA = (ring_bytes(2, res_min) - a.RW * WB) / A_SLOT;
+  if (a.NA < 4) { a.stage_bufs = 1; a.NA = (ring_bytes(1, res_min) - a.RW * WB) / A_SLOT; }
   if (a.NA > MAX_NA) a.NA = MAX_NA;
-  // leftover shared memory deepens the epilogue staging (4 TMA stores in flight per warp); a
-  // stationary layer with a long A ring trades two of its slots for it
-  if (a.stage_bufs == 2) {
-    const int left = RING_BYTES - a.RW * WB - a.NA * A_SLOT;
-    if (left >= STAGE_BYTES) a.stage_bufs = 4;
-    else if (a.stationary && a.NA >= 6) { a.stage_bufs = 4; a.NA -= 2; }
+  // leftover shared memory first deepens the residual prefetch (its tiles come from L2 / HBM, a
+  // microsecond away), then the store staging; a stationary layer with a long A ring trades two
+  // of its slots for the former
+  {
+    int left = ring_bytes(a.stage_bufs, a.res_bufs) - a.RW * WB - a.NA * A_SLOT;
+    if (a.res_bufs == 2) {
+      if (left >= 2 * STAGE_UNIT) { a.res_bufs = 4; left -= 2 * STAGE_UNIT; }
+      else if (a.stationary && a.NA >= 6) { a.res_bufs = 4; a.NA -= 2; left += 2 * A_SLOT - 2 * STAGE_UNIT; }
+    }
+    if (a.stage_bufs == 2 && left >= 2 * STAGE_UNIT) a.stage_bufs = 4;
   }
   if (env_int("BT_TC2_STAGE", 0) == 2 && a.stage_bufs == 4) a.stage_bufs = 2;
   if (env_int("BT_TC2_NA", 0) >= 2 && env_int("BT_TC2_NA", 0) < a.NA) a.NA = env_int("BT_TC2_NA", 0);
@@ -1019,16 +1107,16 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   BT_REQUIRE(a.NA >= 2 && a.RW >= 1 && a.RW <= MAX_RW, BT_ERR_UNSUPPORTED, "tensor-core forward: no room for the pipelines");
   a.total_items = (int64_t)a.S * a.NB * a.num_mg;
   const int grid = (int)(a.total_items < sms ? a.total_items : sms);
-  const int smem_bytes = 1024 + CTRL_BYTES + a.stage_bufs * (STAGE_BYTES / 2) + a.NA * A_SLOT + a.RW * WB;
+  const int smem_bytes = 1024 + CTRL_BYTES + (a.stage_bufs + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT + a.RW * WB;
   BT_REQUIRE(smem_bytes <= SMEM_LIMIT, BT_ERR_UNSUPPORTED, "tensor-core forward: shared memory plan %d exceeds %d", smem_bytes, SMEM_LIMIT);
   if (env_int("BT_TC2_LOG", 0))
-    fprintf(stderr, "tc2: mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d\n",
+    fprintf(stderr, "tc2: mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d\n",
             (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,
-            (long long)a.total_items, grid, smem_bytes);
+            (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs);
   const bool o32 = g->out_dtype == BT_F32;
   if (BN == 64)
-    return o32 ? tc2_launch<64, float>(tm_a, tm_out, a, grid, smem_bytes, stream)
-               : tc2_launch<64, __nv_bfloat16>(tm_a, tm_out, a, grid, smem_bytes, stream);
-  return o32 ? tc2_launch<128, float>(tm_a, tm_out, a, grid, smem_bytes, stream)
-             : tc2_launch<128, __nv_bfloat16>(tm_a, tm_out, a, grid, smem_bytes, stream);
+    return o32 ? tc2_launch<64, float>(tm_a, tm_out, tm_res, a, grid, smem_bytes, stream)
+               : tc2_launch<64, __nv_bfloat16>(tm_a, tm_out, tm_res, a, grid, smem_bytes, stream);
+  return o32 ? tc2_launch<128, float>(tm_a, tm_out, tm_res, a, grid, smem_bytes, stream)
+             : tc2_launch<128, __nv_bfloat16>(tm_a, tm_out, tm_res, a, grid, smem_bytes, stream);
 }

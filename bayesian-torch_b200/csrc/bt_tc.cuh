@@ -32,6 +32,10 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 // a short system time limit passes, so the loop is not a busy spin; the hang guard reads the
 // cheap SM-local clock, and only once every 4096 failed probes (%globaltimer costs about a
 // microsecond per read and used to dominate every wait that did not succeed at once).
+// Hang guard: a wait that spins for ~4 s records where it was stuck and traps (the host sees a
+// launch failure instead of a dead GPU).  No printf here: a call in every wait site forces the
+// role loops to keep their state in local memory across it.
+__device__ unsigned int g_bt_hang[4];
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   uint32_t spins = 0;
@@ -41,8 +45,8 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       const long long now = clock64();
       if (t0 == 0) t0 = now;
       if (now - t0 > 8000000000ll) {  // ~4 s at 2 GHz
-        printf("bt_b200: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n", (int)blockIdx.x,
-               (int)threadIdx.x, bar, parity);
+        g_bt_hang[0] = blockIdx.x; g_bt_hang[1] = threadIdx.x; g_bt_hang[2] = bar; g_bt_hang[3] = parity;
+        __threadfence();
         __trap();
       }
     }

@@ -182,7 +182,10 @@ class _BayesLayer(BaseVariationalLayer_):
         r = self._rank
         return (_ntuple(self.stride, r), _ntuple(self.padding, r), _ntuple(self.dilation, r), int(self.groups))
 
-    def forward(self, input, return_kl=True):
+    def forward(self, input, return_kl=True, residual=None):
+        """forward(input, return_kl) as in the reference.  residual (an extension used by
+        fold_batchnorm; inference only) is an output-shaped tensor added after the folded
+        BatchNorm and before the folded ReLU: the identity branch of a residual block."""
         if self.dnn_to_bnn_flag:
             return_kl = False
         mu_w, rho_w = self._w()
@@ -206,6 +209,7 @@ class _BayesLayer(BaseVariationalLayer_):
         call.want_kl = bool(return_kl)
         call.path = ops._PATHS[self.path or ops.get_path()]
         call.out_scale, call.out_shift, call.out_relu = self._ep_scale, self._ep_shift, self._ep_relu
+        call.residual = residual
         if ops._STATE.sample_override is not None:
             call.sample_id = ops._STATE.sample_override
         else:

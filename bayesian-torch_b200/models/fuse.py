@@ -9,10 +9,12 @@ bound by activation bandwidth).  fold_batchnorm() traces the model
 torch.fx (Bayesian layers are leaves) and rewrites
 
     y = relu(bn(conv(x)))            ->  y = conv(x)            [scale/shift/ReLU in the kernel epilogue]
-    y = relu(bn(conv(x)) + r)        ->  y = add_relu_(conv(x), r)   [scale/shift in the epilogue, one join pass]
+    y = relu(bn(conv(x)) + r)        ->  y = conv(x, residual=r)   [r is read tile by tile by the conv's epilogue]
+                                         (join_in_epilogue=False: y = add_relu_(conv(x), r), one separate join pass)
 
-It is exact up to rounding (the affine is applied in fp32 on the fp32 accumulator, before the
-single rounding to the output dtype).  Eval mode only; the result is a torch.fx.GraphModule
+It is exact up to rounding: scale rides on the sampled weights, shift enters the fp32
+accumulator, one rounding to the output dtype; the residual sum is rounded like the eager
+graph rounds it.  Eval mode only; the result is a torch.fx.GraphModule
 sharing no state with the input model unless inplace=True.
 """
 from __future__ import annotations
@@ -66,7 +68,7 @@ def bn_scale_shift(bn):
     return scale.contiguous(), (b - mean * scale).contiguous()
 
 
-def fold_batchnorm(model: nn.Module, inplace: bool = False) -> fx.GraphModule:
+def fold_batchnorm(model: nn.Module, inplace: bool = False, join_in_epilogue: bool = True) -> fx.GraphModule:
     if model.training:
         raise RuntimeError("fold_batchnorm is an inference-time rewrite: call model.eval() first")
     if not inplace:
@@ -78,7 +80,7 @@ def fold_batchnorm(model: nn.Module, inplace: bool = False) -> fx.GraphModule:
     for n in graph.nodes:
         if n.op == "call_module":
             calls[n.target] = calls.get(n.target, 0) + 1
-    folded = {"bn": 0, "relu": 0, "join": 0}
+    folded = {"bn": 0, "relu": 0, "join": 0, "residual": 0}
     pools = 0
     for node in list(graph.nodes):   # square, floor-mode, undilated MaxPool2d -> the channels-last kernel
         if node.op == "call_module" and isinstance(modules.get(node.target), nn.MaxPool2d):
@@ -120,6 +122,19 @@ def fold_batchnorm(model: nn.Module, inplace: bool = False) -> fx.GraphModule:
             if not isinstance(other, fx.Node) or other is node:
                 continue
             relu = next(iter(u.users))
+            if join_in_epilogue and not layer._ep_relu:
+                # out = relu(bn(conv(x)) + identity): the identity tile is read by the conv's own
+                # epilogue.  The conv must run after the identity branch (a downsample conv).
+                order = {n: i for i, n in enumerate(graph.nodes)}
+                if order[other] > order[node]:
+                    other.append(node)
+                node.kwargs = {**node.kwargs, "residual": other}
+                layer._ep_relu = True
+                relu.replace_all_uses_with(node)
+                graph.erase_node(relu)
+                graph.erase_node(u)
+                folded["residual"] += 1
+                continue
             with graph.inserting_after(u):
                 joined = graph.call_function(ops.add_relu_, (node, other))
             relu.replace_all_uses_with(joined)

@@ -300,6 +300,7 @@ class LayerCall:
     out_scale: Optional[torch.Tensor] = None    # folded eval-mode BatchNorm (inference only)
     out_shift: Optional[torch.Tensor] = None
     out_relu: bool = False
+    residual: Optional[torch.Tensor] = None     # added after the affine, before the ReLU (inference only)
 
 
 def _conv_out_size(i, k, s, p, d):
@@ -356,6 +357,8 @@ def _build_params(call: LayerCall, mu_w, rho_w, mu_b, rho_b) -> Tuple[LayerParam
     sc, sh = _f32c(call.out_scale, "out_scale"), _f32c(call.out_shift, "out_shift")
     keep += [sc, sh]
     p.out_scale, p.out_shift, p.out_relu = _ptr(sc), _ptr(sh), int(bool(call.out_relu))
+    p.residual = _ptr(call.residual)
+    keep.append(call.residual)
     return p, keep
 
 
@@ -430,6 +433,13 @@ class _BayesLayerFn(torch.autograd.Function):
             call.sign_in = _match_strides(call.sign_in, xd)
         if call.sign_out is not None:
             call.sign_out = _match_strides(call.sign_out, out)
+        if call.residual is not None:
+            res = call.residual.detach()
+            if tuple(res.shape) != tuple(out.shape):
+                raise RuntimeError(f"residual has shape {tuple(res.shape)}, the layer output is {tuple(out.shape)}")
+            if res.dtype != out.dtype or res.stride() != out.stride() or res.device != out.device:
+                res = torch.empty_like(out).copy_(res)   # the kernels index it with out's offsets
+            call.residual = res
         g = _build_geom(call, xd, mu_wc.shape, out)
         p, keep = _build_params(call, mu_wc, rho_wc, mu_bc, rho_bc)
         L = _lib.lib()
@@ -461,8 +471,8 @@ class _BayesLayerFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_out, g_kl):
         call: LayerCall = ctx.call
-        if call.out_scale is not None or call.out_shift is not None or call.out_relu:
-            raise RuntimeError("the folded BatchNorm / ReLU epilogue is inference-only; unfuse the model to train")
+        if call.out_scale is not None or call.out_shift is not None or call.out_relu or call.residual is not None:
+            raise RuntimeError("the folded BatchNorm / ReLU / residual epilogue is inference-only; unfuse the model to train")
         x, mu_w, rho_w, mu_b, rho_b = ctx.saved_tensors
         dev = x.device
         mu_wc, rho_wc = _f32c(mu_w.detach(), "mu"), _f32c(rho_w.detach(), "rho")

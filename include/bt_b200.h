@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define BT_ABI_VERSION 2
+#define BT_ABI_VERSION 3
 
 typedef void* bt_stream_t; /* cudaStream_t */
 
@@ -97,15 +97,19 @@ typedef struct bt_layer_params {
   uint32_t sample_id;
   uint32_t layer_id;
   /* Inference-time output epilogue (forward only; NULL / 0 = off):
-   *   out = act((conv(x, W) + b) * out_scale[n] + out_shift[n]),  act = ReLU when out_relu != 0.
+   *   out = act((conv(x, W) + b) * out_scale[n] + out_shift[n] + residual),  act = ReLU when out_relu != 0.
    * Folds the eval-mode BatchNorm (scale = gamma / sqrt(var + eps), shift = beta - mean * scale)
    * and ReLU that follow every Bayesian conv of the reference's ResNets
    * (models/bayesian/resnet_variational_large.py:97-119) into the producing kernel, so the
-   * activation tensor is written once instead of three times. */
+   * activation tensor is written once instead of three times.  residual (NULL = none) is the
+   * identity branch of a residual block (resnet_variational_large.py:113-118, out += identity;
+   * relu): a tensor with out's dtype, shape and strides; for bf16 the sum is rounded the way
+   * the eager graph rounds it, bf16(bf16(affine) + residual). */
   const float* out_scale;
   const float* out_shift;
   int32_t out_relu;
   int32_t reserved;
+  const void* residual;
 } bt_layer_params;
 
 /* Gradient outputs of a backward call (all fp32 device buffers shaped like the

@@ -18,12 +18,20 @@ def test_resnet18_graph_is_folded():
         bt.fold_batchnorm(m)
     f = bt.fold_batchnorm(m.eval())
     # 20 convs each followed by a BatchNorm; conv1 of the stem and of every block also by a ReLU;
-    # 8 residual joins
-    assert f.folded == {"bn": 20, "relu": 9, "join": 8}
+    # 8 residual joins, each read by the epilogue of the block's last conv
+    assert f.folded == {"bn": 20, "relu": 9, "join": 0, "residual": 8}
+    last = getattr(f.layer2, "0").conv2
+    assert last._ep_relu                                      # ReLU after the residual sum
+    calls = {n.target: n for n in f.graph.nodes if n.op == "call_module"}
+    order = {n: i for i, n in enumerate(f.graph.nodes)}
+    res = calls["layer2.0.conv2"].kwargs["residual"]
+    assert res.target == "layer2.0.downsample.0" and order[res] < order[calls["layer2.0.conv2"]]
+    g = bt.fold_batchnorm(m, join_in_epilogue=False)
+    assert g.folded == {"bn": 20, "relu": 9, "join": 8, "residual": 0}
     targets = {n.target for n in f.graph.nodes if n.op == "call_module"}
     assert not any("bn" in t or "downsample.1" in t for t in targets)
     assert f.conv1._ep_relu and f.conv1._ep_scale.shape == (64,)
-    assert not getattr(f.layer1, "0").conv2._ep_relu          # its ReLU comes after the join
+    assert not getattr(g.layer1, "0").conv2._ep_relu          # separate join pass: its ReLU comes after the join
     assert m.conv1._ep_scale is None                          # the input model is untouched
 
 

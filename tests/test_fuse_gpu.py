@@ -53,7 +53,11 @@ def test_fold_batchnorm_fp32_matches_unfused(cuda_device):
     with torch.no_grad(), bt.path("simt"), bt.mc_sample(3):
         want = m(x)
     f = bt.fold_batchnorm(m)
-    assert f.folded == {"bn": 7, "relu": 5, "join": 2}
+    assert f.folded == {"bn": 7, "relu": 5, "join": 0, "residual": 2}
+    f2 = bt.fold_batchnorm(m, join_in_epilogue=False)
+    assert f2.folded == {"bn": 7, "relu": 5, "join": 2, "residual": 0}
+    with torch.no_grad(), bt.path("simt"), bt.mc_sample(3):
+        torch.testing.assert_close(f2(x), want, rtol=1e-5, atol=1e-5)
     assert not any(isinstance(mod, nn.BatchNorm2d) for n, mod in f.named_modules() if n in {nd.target for nd in f.graph.nodes})
     with torch.no_grad(), bt.path("simt"), bt.mc_sample(3):
         got = f(x)

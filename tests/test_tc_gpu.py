@@ -200,3 +200,40 @@ def _tc_on_fp32(cuda_device):
     layer = L.Conv2dReparameterization(64, 64, 1, prior_type="normal").to(cuda_device)
     layer.path = "tc"
     return layer(torch.randn(1, 64, 8, 8, device=cuda_device))
+
+
+RESIDUAL_CASES = [
+    # cin, cout, k, pad, batch, hw, S, relu
+    (64, 256, 1, 0, 4, 14, 1, True),    # bottleneck conv3: BN=128, two n-blocks, stationary
+    (128, 64, 3, 1, 3, 7, 1, True),     # BN=64, ragged M (147 rows): residual rows past Ms are never fetched
+    (64, 192, 1, 0, 2, 9, 3, True),     # N tail (128 + 64), three stacked samples
+    (256, 256, 3, 1, 2, 14, 2, False),  # streaming W ring, MT accumulators, no ReLU
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,pad,batch,hw,S,relu", RESIDUAL_CASES)
+def test_conv2d_tc_residual_epilogue(cin, cout, k, pad, batch, hw, S, relu, cuda_device):
+    """out = relu(bf16(affine(conv)) + residual), rounded like the eager bf16 graph: bit-exact
+    against the same kernel without the residual followed by torch's bf16 add and relu."""
+    torch.manual_seed(cin + cout + k)
+    layer = L.Conv2dReparameterization(cin, cout, k, padding=pad, bias=True, prior_type="normal").to(cuda_device)
+    layer.dnn_to_bnn_flag = True
+    layer.path = "tc"
+    layer._ep_scale = torch.rand(cout, device=cuda_device) + 0.5
+    layer._ep_shift = torch.randn(cout, device=cuda_device)
+    x = torch.randn(S * batch, cin, hw, hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    res = torch.randn(S * batch, cout, hw, hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    with torch.no_grad():
+        with bt.mc_batched(S, 5):
+            plain = layer(x)
+        layer._ep_relu = relu
+        with bt.mc_batched(S, 5):
+            fused = layer(x, residual=res)
+            fused_nchw = layer(x, residual=res.contiguous())      # another layout: copied to out's strides
+    want = plain + res
+    if relu:
+        want = torch.relu(want)
+    torch.testing.assert_close(fused, want, rtol=0, atol=0)
+    torch.testing.assert_close(fused_nchw, want, rtol=0, atol=0)
+    with pytest.raises(RuntimeError, match="residual has shape"):
+        layer(x, residual=res[:, :1])
