@@ -139,17 +139,19 @@ __global__ void add_relu_kernel(T* __restrict__ y, const T* __restrict__ r, int6
 
 // Channels-last max pooling, 8 channels (16 bytes) per thread: the stem's MaxPool2d(3, 2, 1)
 // sits between two Bayesian layers of every ResNet and torch's NHWC kernel runs it at ~0.7 TB/s.
-__global__ void maxpool2d_nhwc_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t total,
-                                           int C8, int IH, int IW, int OH, int OW, int k, int st, int pd) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    int64_t r = i / C8;
-    const int ow = (int)(r % OW); r /= OW;
-    const int oh = (int)(r % OH); r /= OH;
-    const __nv_bfloat16* xb = x + r * (int64_t)IH * IW * C8 * 8 + c8 * 8;
-    float m[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) m[e] = -INFINITY;
+template <typename IDX>
+__global__ void __launch_bounds__(256) maxpool2d_nhwc_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                                                  int64_t total64, int C8, int IH, int IW, int OH, int OW, int k,
+                                                                  int st, int pd) {
+  const IDX total = (IDX)total64, stride = (IDX)gridDim.x * blockDim.x;
+  for (IDX i = (IDX)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c8 = (int)(i % (IDX)C8);
+    IDX r = i / (IDX)C8;
+    const int ow = (int)(r % (IDX)OW); r /= (IDX)OW;
+    const int oh = (int)(r % (IDX)OH); r /= (IDX)OH;
+    const __nv_bfloat16* xb = x + (int64_t)r * IH * IW * C8 * 8 + c8 * 8;
+    const __nv_bfloat162 ninf = __floats2bfloat162_rn(-INFINITY, -INFINITY);
+    __nv_bfloat162 m[4] = {ninf, ninf, ninf, ninf};  // max is exact in bf16: no widening needed
     for (int kh = 0; kh < k; ++kh) {
       const int ih = oh * st - pd + kh;
       if ((unsigned)ih >= (unsigned)IH) continue;
@@ -157,16 +159,12 @@ __global__ void maxpool2d_nhwc_bf16_kernel(const __nv_bfloat16* __restrict__ x, 
         const int iw = ow * st - pd + kw;
         if ((unsigned)iw >= (unsigned)IW) continue;
         const uint4 v = __ldg(reinterpret_cast<const uint4*>(xb + ((int64_t)ih * IW + iw) * C8 * 8));
-        const __nv_bfloat16* h = reinterpret_cast<const __nv_bfloat16*>(&v);
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) m[e] = fmaxf(m[e], __bfloat162float(h[e]));
+        for (int e = 0; e < 4; ++e) m[e] = __hmax2_nan(m[e], h[e]);  // NaN propagates like torch's max_pool2d
       }
     }
-    uint4 o;
-    __nv_bfloat16* oh8 = reinterpret_cast<__nv_bfloat16*>(&o);
-#pragma unroll
-    for (int e = 0; e < 8; ++e) oh8[e] = __float2bfloat16_rn(m[e]);
-    reinterpret_cast<uint4*>(y)[i] = o;
+    reinterpret_cast<uint4*>(y)[i] = *reinterpret_cast<const uint4*>(m);
   }
 }
 
@@ -217,8 +215,15 @@ extern "C" int bt_maxpool2d_nhwc(const void* x, void* y, int64_t batch, int64_t 
   BT_REQUIRE(oh > 0 && ow > 0, BT_ERR_INVALID, "bt_maxpool2d_nhwc: empty output");
   const int64_t total = batch * oh * ow * (channels / 8);
   if (total == 0) return BT_OK;
-  maxpool2d_nhwc_bf16_kernel<<<grid_for(total, 256), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, total, (int)(channels / 8), (int)ih, (int)iw, (int)oh, (int)ow, kernel, stride, pad);
+  int64_t blocks = (total + 255) / 256;
+  const int64_t cap = (int64_t)bt_num_sms() * 64;
+  if (blocks > cap) blocks = cap;
+  if (total + cap * 256 < 0x7fffffffll)
+    maxpool2d_nhwc_bf16_kernel<uint32_t><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)x, (__nv_bfloat16*)y, total, (int)(channels / 8), (int)ih, (int)iw, (int)oh, (int)ow, kernel, stride, pad);
+  else
+    maxpool2d_nhwc_bf16_kernel<int64_t><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)x, (__nv_bfloat16*)y, total, (int)(channels / 8), (int)ih, (int)iw, (int)oh, (int)ow, kernel, stride, pad);
   BT_LAUNCH_OK("maxpool2d_nhwc_bf16_kernel");
   return BT_OK;
 }

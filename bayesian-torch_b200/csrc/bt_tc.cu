@@ -192,22 +192,29 @@ struct PatchGeo {
   int sd, sh, sw, pd, ph, pw, dd, dh, dw;
 };
 
-template <typename TX>
-__global__ void tc2_patch_kernel(const TX* __restrict__ x, __nv_bfloat16* __restrict__ A, const PatchGeo g) {
-  const int C8 = g.Kp >> 3;
-  const int64_t total = g.rows * C8;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t row = i / C8;
+// One thread per 16-byte chunk (8 consecutive k) of the patch matrix: consecutive threads write
+// consecutive chunks and read neighbouring input elements.  Index arithmetic is 32-bit whenever
+// the chunk count allows (64-bit division is ~10x the cost and was most of this kernel's time).
+template <typename TX, typename IDX>
+__global__ void __launch_bounds__(256) tc2_patch_kernel(const TX* __restrict__ x, __nv_bfloat16* __restrict__ A, const PatchGeo g) {
+  const IDX C8 = (IDX)(g.Kp >> 3);
+  const IDX total = (IDX)g.rows * C8;
+  const IDX stride = (IDX)gridDim.x * blockDim.x;
+  for (IDX i = (IDX)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const IDX row = i / C8;
     const int chunk = (int)(i - row * C8);
-    int64_t r = row;
-    const int ow = (int)(r % g.OW); r /= g.OW;
-    const int oh = (int)(r % g.OH); r /= g.OH;
-    const int od = (int)(r % g.OD); r /= g.OD;
-    const TX* xi = x + r * g.xbs;
+    IDX r = row;
+    const int ow = (int)(r % (IDX)g.OW); r /= (IDX)g.OW;
+    const int oh = (int)(r % (IDX)g.OH); r /= (IDX)g.OH;
+    const int od = (int)(r % (IDX)g.OD); r /= (IDX)g.OD;
+    const TX* xi = x + (int64_t)r * g.xbs;
     const int id0 = od * g.sd - g.pd, ih0 = oh * g.sh - g.ph, iw0 = ow * g.sw - g.pw;
     int k = chunk * 8;
-    int tap = k / g.Cin, c = k - tap * g.Cin;
-    int kw = tap % g.KW, kh = (tap / g.KW) % g.KH, kd = tap / (g.KW * g.KH);
+    const int tap = k / g.Cin;
+    int c = k - tap * g.Cin;
+    int kw = tap % g.KW;
+    const int t2 = tap / g.KW;
+    int kh = t2 % g.KH, kd = t2 / g.KH;
     float v[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e, ++k) {
@@ -221,7 +228,7 @@ __global__ void tc2_patch_kernel(const TX* __restrict__ x, __nv_bfloat16* __rest
     }
     uint4 pk;
     pk.x = pack_bf16(v[0], v[1]); pk.y = pack_bf16(v[2], v[3]); pk.z = pack_bf16(v[4], v[5]); pk.w = pack_bf16(v[6], v[7]);
-    *reinterpret_cast<uint4*>(A + row * g.Kp + chunk * 8) = pk;
+    *reinterpret_cast<uint4*>(A + (int64_t)row * g.Kp + chunk * 8) = pk;
   }
 }
 
@@ -986,11 +993,15 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
     pg.OD = (int)o[0]; pg.OH = (int)o[1]; pg.OW = (int)o[2]; pg.ID = (int)in[0]; pg.IH = (int)in[1]; pg.IW = (int)in[2];
     pg.sd = (int)st[0]; pg.sh = (int)st[1]; pg.sw = (int)st[2]; pg.pd = (int)pd[0]; pg.ph = (int)pd[1]; pg.pw = (int)pd[2];
     pg.dd = (int)dl[0]; pg.dh = (int)dl[1]; pg.dw = (int)dl[2];
-    int64_t blocks = (pg.rows * (pg.Kp / 8) + 255) / 256;
-    const int64_t cap = (int64_t)bt_num_sms() * 16;
+    const int64_t chunks = pg.rows * (pg.Kp / 8);
+    int64_t blocks = (chunks + 255) / 256;
+    const int64_t cap = (int64_t)bt_num_sms() * 32;
     if (blocks > cap) blocks = cap;
     // (stacked samples of x are just more images: the batch stride walks across them)
-    tc2_patch_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, stream>>>((const __nv_bfloat16*)x, patches, pg);
+    if (chunks + cap * 256 < 0x7fffffffll)
+      tc2_patch_kernel<__nv_bfloat16, uint32_t><<<(int)blocks, 256, 0, stream>>>((const __nv_bfloat16*)x, patches, pg);
+    else
+      tc2_patch_kernel<__nv_bfloat16, int64_t><<<(int)blocks, 256, 0, stream>>>((const __nv_bfloat16*)x, patches, pg);
     BT_LAUNCH_OK("tc2_patch_kernel");
     a_src = patches;
   }
@@ -1059,7 +1070,10 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   // (single-buffered epilogue staging is accepted for that)
   auto panel_fits = [&](int bn) { return a.nkb <= MAX_RW && (int64_t)a.nkb * bn * BK * 2 + 4 * A_SLOT <= ring_bytes(1, res_min); };
   const int force_bn = env_int("BT_TC2_BN", 0), force_mt = env_int("BT_TC2_MT", 0), force_stat = env_int("BT_TC2_STATIONARY", -1);
-  if (BN == 128 && !panel_fits(128) && panel_fits(64)) BN = 64;
+  // N > 64 whose [128 x K] panel does not fit streams at BN = 128 rather than keeping a BN = 64
+  // panel: the narrow panel re-reads every A tile once per 64 output channels, and the A stream
+  // (L2 -> shared memory, then shared memory -> tensor core) is the scarcer resource
+  // (1024 -> 256 1x1 at 14x14: 0.34 ms stationary/64, 0.23 ms streaming/128).
   if (force_bn == 64 || force_bn == 128) BN = force_bn;
   const int WB = BN * BK * 2;
   a.NB = (a.N + BN - 1) / BN;
@@ -1078,7 +1092,8 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
     }
     if (force_mt >= 1 && force_mt <= MAX_MT && force_mt <= NSLOTS) a.MT = force_mt;
     a.RW = (ring_bytes(2, res_min) - 4 * A_SLOT) / WB;
-    if (a.RW > 8) a.RW = 8;
+    if (a.RW > 5) a.RW = 5;  // deeper W rings measured no faster; the space goes to the A ring
+    if (env_int("BT_TC2_RW", 0) >= 2 && env_int("BT_TC2_RW", 0) < a.RW) a.RW = env_int("BT_TC2_RW", 0);
   }
   a.NSETS = NSLOTS / a.MT;
   if (a.NSETS > MAX_SETS) a.NSETS = MAX_SETS;

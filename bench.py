@@ -228,7 +228,12 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     ops.PROFILE.reset()
+    ncu_range = os.environ.get("BT_NCU_RANGE") == "1"   # `ncu --profile-from-start off`: capture the timed steps only
+    if ncu_range:
+        torch.cuda.cudart().cudaProfilerStart()
     ms_step, res = timed(step_resident, args.steps)
+    if ncu_range:
+        torch.cuda.cudart().cudaProfilerStop()
     launches = ops.PROFILE.launches
     clocks = sampler.stop() if rank == 0 else None
 
