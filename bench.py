@@ -269,7 +269,7 @@ def run_b200(args):
             "e2e": {"value": B * 1e3 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": x_host.numel() * 4,
                     "d2h_bytes_per_step": 2 * res.mean.numel() * 4},
             "gpu_launches": launches,
-            "roofline": {"bound": "tensor", "kernel": "tc_fwd_kernel (all launches of one step)", "achieved": achieved,
+            "roofline": {"bound": "tensor", "kernel": "tc2_fwd_kernel (all launches of one step)", "achieved": achieved,
                          "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"], "traffic": None,
                          "peak_source": pk["source"], "launches_per_step": len(tc), "ms_per_step_in_kernel": tc_ms,
                          "ms_per_step_other_bt_kernels": other_ms,
