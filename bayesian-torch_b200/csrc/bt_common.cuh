@@ -77,10 +77,18 @@ __device__ __forceinline__ uint4 bt_philox(uint64_t block, const BtRngKey& key) 
   uint32_t k0 = key.k0, k1 = key.k1;
 #pragma unroll
   for (int r = 0; r < 10; ++r) {
+#ifdef BT_PHILOX_WIDE
+    const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2, p0 = (uint64_t)0xD2511F53u * c0;  // IMAD.WIDE: hi and lo in one issue
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+    const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    c1 = (uint32_t)p1;
+    c3 = (uint32_t)p0;
+#else
     const uint32_t n0 = __umulhi(0xCD9E8D57u, c2) ^ c1 ^ k0;
     const uint32_t n2 = __umulhi(0xD2511F53u, c0) ^ c3 ^ k1;
     c1 = 0xCD9E8D57u * c2;
     c3 = 0xD2511F53u * c0;
+#endif
     c0 = n0;
     c2 = n2;
     k0 += 0x9E3779B9u;

@@ -48,10 +48,13 @@ constexpr int CTRL_BYTES = BAR_BYTES + ONES_BYTES + SHIFT_BYTES;
 constexpr int STAGE_UNIT = 4 * 4096;  // one staging (or residual) buffer of 32 rows x 128 B for each of the 4 epilogue warps
 constexpr int N_PROD_WARPS = 16;
 constexpr int N_MMA_WARPS = 2;  // issuer warps: tile t of an m-group belongs to issuer t % 2
-// warp groups (setmaxnreg works on aligned groups of 4 warps): 0 = epilogue, 1 = TMA + 2 MMA issuers
-// + one idle warp, 2..5 = W producers
-constexpr int WARP_TMA = 4, WARP_MMA = 5, WARP_PROD0 = 8;
-constexpr int NUM_THREADS = (WARP_PROD0 + N_PROD_WARPS) * 32;  // 768
+// warp groups (setmaxnreg works on aligned groups of 4 warps): 0..3 = W producers, 4 = epilogue,
+// 5 = TMA + 2 MMA issuers + one idle warp
+// Warp ids are priorities: the SM's issue arbiter prefers the highest warp id among eligible
+// warps, so the latency-critical single-lane loops (TMA, MMA issue) sit above the epilogue,
+// and the 16 throughput-bound producer warps take whatever issue slots are left.
+constexpr int WARP_PROD0 = 0, WARP_EPI0 = N_PROD_WARPS, WARP_TMA = WARP_EPI0 + 4, WARP_MMA = WARP_TMA + 1;
+constexpr int NUM_THREADS = (N_PROD_WARPS + 8) * 32;  // 768
 // register budget: 768 threads launch with 80 registers each; the control warp group and
 // the producers shrink to 72, which lets the epilogue group (64 accumulator columns in flight per thread)
 // grow to 120. The pool setmaxnreg draws on is what the CTA was LAUNCHED with
@@ -63,7 +66,8 @@ constexpr int SMEM_LIMIT = 232448;
 constexpr int AVAIL_BYTES = SMEM_LIMIT - 1024 - CTRL_BYTES;  // staging + residual ring + A ring + W ring / panel
 
 struct Tc2Args {
-  const float *mu_p, *sig_p, *eps_p;  // packed [N][K], k = tap*Cin + c
+  const __nv_bfloat16 *mu_p, *sig_p;  // packed [N][K], k = tap*Cin + c, scale folded in, rounded to bf16
+  const float* eps_p;                 // caller's eps in the same order (deterministic mode), else null
   const float *mu_b, *rho_b, *eps_b;
   const float *out_scale, *out_shift;  // folded BatchNorm (nullable)
   int out_relu;
@@ -75,7 +79,9 @@ struct Tc2Args {
   int conv;          // 1: im2col map, 0: tiled 2-d map
   int OH, OW, KW, CB;  // CB = Cin / 64: k-blocks per filter tap
   int sh, sw, ph, pw, dh, dw;
-  int num_mt, num_mg, MT, NSETS, nkb, NA, RW, stationary;
+  int num_mt, num_mg, MT, NSETS, nkb, NA, RW, stationary;  // num_mg: m-groups per key as walked by one cluster
+  int CL;            // CTAs per cluster (1 or 2). CL = 2: the pair walks the same (sample, n-block, k-block) sequence on
+                     // neighbouring m-groups, each CTA samples half of every W k-block and stores it into both CTAs' rings
   int NR, NAr;       // A rings (one per active MMA issuer) and slots per ring; NA = NR * NAr
   int has_shift;     // bias and/or folded BatchNorm shift: added by a rank-1 MMA that initialises each accumulator
   int res_bufs;      // residual tiles in flight per epilogue warp (0: no residual input)
@@ -144,6 +150,11 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<const uint32_t*>(&h);
 }
+__device__ __forceinline__ uint32_t fma_bf16x2(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
 __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
   uint32_t d;
   asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
@@ -154,7 +165,7 @@ __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
 // mu[n][c][tap] -> mu_p[n][tap*Cin + c] with row pitch Kp (zero beyond K), sigma_p = softplus(rho)
 // likewise (sigma does not depend on the sample: hoisted out of the per-sample work), eps likewise.
 __global__ void tc2_pack_kernel(const float* __restrict__ mu, const float* __restrict__ rho,
-                                const float* __restrict__ eps, float* __restrict__ mu_p, float* __restrict__ sig_p,
+                                const float* __restrict__ eps, __nv_bfloat16* __restrict__ mu_p, __nv_bfloat16* __restrict__ sig_p,
                                 float* __restrict__ eps_p, const float* __restrict__ scale, int64_t total, int Cin, int T,
                                 int Kp) {
   const int K = Cin * T;
@@ -174,8 +185,8 @@ __global__ void tc2_pack_kernel(const float* __restrict__ mu, const float* __res
         sg *= sc;
       }
     }
-    mu_p[i] = m;
-    sig_p[i] = sg;
+    mu_p[i] = __float2bfloat16_rn(m);
+    sig_p[i] = __float2bfloat16_rn(sg);
     if (eps_p) eps_p[i] = e;
   }
 }
@@ -298,7 +309,7 @@ __device__ unsigned long long g_tc_prof[160 * PROF_ROLES * PROF_SLOTS];
     }                                                           \
   } while (0)
 
-template <int BN, typename TO, bool PROF>
+template <int BN, typename TO, bool PROF, int CL>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_out,
                const __grid_constant__ CUtensorMap tm_res, const __grid_constant__ Tc2Args a) {
@@ -327,7 +338,9 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < a.NA; ++i) { mbar_init(smem_u32(&ctrl->a_full[i]), 1); mbar_init(smem_u32(&ctrl->a_empty[i]), 1); }
-    for (int i = 0; i <= a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), N_PROD_WARPS); mbar_init(smem_u32(&ctrl->w_empty[i]), N_MMA_WARPS); }
+    for (int i = 0; i < a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), N_PROD_WARPS); mbar_init(smem_u32(&ctrl->w_empty[i]), N_MMA_WARPS * CL); }
+    mbar_init(smem_u32(&ctrl->w_full[a.RW]), N_PROD_WARPS);  // the shift tile stays CTA-local
+    mbar_init(smem_u32(&ctrl->w_empty[a.RW]), N_MMA_WARPS);
     for (int i = 0; i < a.NSETS; ++i) { mbar_init(smem_u32(&ctrl->acc_full[i]), N_MMA_WARPS); mbar_init(smem_u32(&ctrl->acc_empty[i]), 128); }
     for (int i = 0; i < 16; ++i) mbar_init(smem_u32(&ctrl->res_full[i >> 2][i & 3]), 1);
     mbar_fence_init();
@@ -336,12 +349,19 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   if (warp == WARP_MMA) tmem_alloc(smem_u32(&ctrl->tmem_base), 512);
   tc_fence_before();
   __syncthreads();
+  if constexpr (CL > 1) cluster_sync_all();  // the peer's mbarriers are initialised before anything arrives on them
   tc_fence_after();
   const uint32_t tmem = ctrl->tmem_base;
 
-  const int64_t i0 = a.total_items * blockIdx.x / gridDim.x;
-  const int64_t i1 = a.total_items * (blockIdx.x + 1) / gridDim.x;
+  const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
+  const int cid = blockIdx.x / CL, ncl = gridDim.x / CL;
+  const int64_t i0 = a.total_items * cid / ncl;
+  const int64_t i1 = a.total_items * (cid + 1) / ncl;
   const int n_items = (int)(i1 - i0);
+  // first m-tile of this CTA's m-group within cluster step mg (may lie past num_mt for the odd
+  // tail of a pair: such an item has no tiles, but its W k-blocks are still produced and consumed)
+  auto tile0 = [&](int mg) { return (mg * CL + crank) * a.MT; };
+  auto tiles_of = [&](int mg) { return max(0, min(a.MT, a.num_mt - tile0(mg))); };
   // first item of this CTA, decoded once; the role loops then walk (s, nb, mg) incrementally --
   // the single-thread TMA / MMA loops are instruction-latency bound, so no division or modulo
   // by a run-time value may sit inside them.
@@ -349,10 +369,10 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   const int mg0 = (int)(i0 - key0 * a.num_mg);
   const int s0 = (int)(key0 / a.NB), nb0 = (int)(key0 - (int64_t)s0 * a.NB);
 
-  if (warp < 4) {
+  if (warp >= WARP_EPI0 && warp < WARP_EPI0 + 4) {
     // =========================== EPILOGUE ===========================
     reg_alloc<REGS_EPI>();
-    const int q = warp;
+    const int q = warp - WARP_EPI0;  // TMEM lane quarter: WARP_EPI0 is a multiple of 4
     const uint32_t my_stage = stage_base + (uint32_t)(q * a.stage_bufs) * 4096u;
     const uint32_t row_sw = (uint32_t)(lane & 7);
     uint32_t nstore = 0, sbuf = 0;
@@ -368,7 +388,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     const uint32_t my_res = res_base + (uint32_t)(q * a.res_bufs) * 4096u;
     auto pf_issue = [&](int slot) {
       while (pf_it < n_items) {
-        if (pf_t < min(a.MT, a.num_mt - pf_mg * a.MT) && (pf_mg * a.MT + pf_t) * BM + q * 32 < a.Ms) {
+        if (pf_t < tiles_of(pf_mg) && (tile0(pf_mg) + pf_t) * BM + q * 32 < a.Ms) {
           if (pf_sub < (min(BN, a.N - pf_nb * BN) + SUBN - 1) / SUBN) break;
           pf_sub = 0; ++pf_t;
           continue;
@@ -380,7 +400,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       if (lane == 0) {
         const uint32_t bar = smem_u32(&ctrl->res_full[q][slot]);
         mbar_expect_tx(bar, 4096);
-        tma_load_3d(my_res + (uint32_t)slot * 4096u, &tm_res, bar, pf_nb * BN + pf_sub * SUBN, (pf_mg * a.MT + pf_t) * BM + q * 32, pf_s);
+        tma_load_3d(my_res + (uint32_t)slot * 4096u, &tm_res, bar, pf_nb * BN + pf_sub * SUBN, (tile0(pf_mg) + pf_t) * BM + q * 32, pf_s);
       }
       ++pf_sub;
     };
@@ -395,13 +415,17 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       epi_unit<TO, RELU, RES>(v, rowaddr, resaddr, cb, row_sw);
     };
     for (int it = 0; it < n_items; ++it) {
+      const int mtv = tiles_of(mg);
+      if (mtv == 0) {  // tail of a CTA pair: nothing was accumulated for this CTA
+        if (++mg == a.num_mg) { mg = 0; if (++nb == a.NB) { nb = 0; ++s; } }
+        continue;
+      }
       PW(0, mbar_wait(smem_u32(&ctrl->acc_full[set]), set_phase));
       tc_fence_after();
-      const int mtv = min(a.MT, a.num_mt - mg * a.MT);
       const int ncols = min(BN, a.N - nb * BN);
       const int nsub = (ncols + SUBN - 1) / SUBN;  // staged sub-tiles with at least one real column
       for (int t = 0; t < mtv; ++t) {
-        const int m0 = (mg * a.MT + t) * BM + q * 32;  // first row of this warp's 32-row slab
+        const int m0 = (tile0(mg) + t) * BM + q * 32;  // first row of this warp's 32-row slab
         if (m0 >= a.Ms) break;                          // slab entirely past the sample's last row (warp-uniform)
         const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)((set * a.MT + t) * BN);
         // TMEM reads are software-pipelined in 32-column units: the load of unit u+1 is in
@@ -469,8 +493,8 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     if (has_res) { if (relu) epi_loop(T_{}, T_{}); else epi_loop(F_{}, T_{}); }
     else { if (relu) epi_loop(T_{}, F_{}); else epi_loop(F_{}, F_{}); }
     if (lane == 0) tma_store_wait_all();
-    if (warp == 0) prof_flush(0);
-  } else if (warp < WARP_PROD0) {
+    if (warp == WARP_EPI0) prof_flush(0);
+  } else if (warp >= WARP_TMA) {
     reg_dealloc<REGS_CTRL>();
     if (warp == WARP_TMA) {
     // =========================== A LOADER (TMA) ===========================
@@ -485,11 +509,11 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     uint32_t rphase[N_MMA_WARPS] = {0, 0};
     const int Cin = a.CB * BK;
     for (int it = 0; it < n_items; ++it) {
-      const int mtv = min(a.MT, a.num_mt - mg * a.MT);
+      const int mtv = tiles_of(mg);
       int cw[MAX_MT], chh[MAX_MT], cn[MAX_MT];
 #pragma unroll
       for (int t = 0; t < MAX_MT; ++t) {
-        const int m = (mg * a.MT + t) * BM;
+        const int m = (tile0(mg) + t) * BM;
         cw[t] = 0; chh[t] = 0;
         cn[t] = s * a.x_rows_per_s + m;
         if (a.conv) {
@@ -549,9 +573,11 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     const int ring0 = (a.NR == 2 ? j : 0) * a.NAr;  // first slot of the A ring this issuer consumes
     for (int it = 0; it < n_items; ++it) {
       const bool last = !a.stationary || it + 1 == n_items || mg + 1 == a.num_mg;
-      PW(0, mbar_wait(smem_u32(&ctrl->acc_empty[set]), set_phase ^ 1u));
-      tc_fence_after();
-      const int mtv = min(a.MT, a.num_mt - mg * a.MT);
+      const int mtv = tiles_of(mg);  // 0 for the odd tail of a CTA pair: W slots are still consumed, nothing is issued
+      if (mtv > 0) {
+        PW(0, mbar_wait(smem_u32(&ctrl->acc_empty[set]), set_phase ^ 1u));
+        tc_fence_after();
+      }
       const uint32_t dbase = tmem + (uint32_t)(set * a.MT * BN);
       if (a.has_shift) {
         // D = ones[128 x 16] * shift[BN x 16]^T: every row of the accumulator starts as the
@@ -573,7 +599,8 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       for (int kb = 0; kb < a.nkb; ++kb) {
         const int wslot = a.stationary ? kb : wslot_r;
         if (first) {
-          PW(1, mbar_wait(smem_u32(&ctrl->w_full[wslot]), wphase));
+          if constexpr (CL > 1) PW(1, mbar_wait_cluster(smem_u32(&ctrl->w_full[wslot]), wphase));  // half of the rows come from the peer CTA
+          else PW(1, mbar_wait(smem_u32(&ctrl->w_full[wslot]), wphase));
           tc_fence_after();
         }
         const uint64_t bdesc = umma_desc_sw128(w_base + wslot * W_SLOT);
@@ -599,12 +626,17 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             }
           }
         }
-        if (last && leader) umma_commit(smem_u32(&ctrl->w_empty[wslot]));
+        if (last && leader) {  // the slot is free once BOTH CTAs' tensor cores have read it: its producers sit in both
+          if constexpr (CL > 1) umma_commit_multicast(smem_u32(&ctrl->w_empty[wslot]), (uint16_t)3);
+          else umma_commit(smem_u32(&ctrl->w_empty[wslot]));
+        }
         if (!a.stationary && ++wslot_r == a.RW) { wslot_r = 0; wphase ^= 1u; }
       }
-      if (leader) umma_commit(smem_u32(&ctrl->acc_full[set]));
-      __syncwarp();
-      if (++set == a.NSETS) { set = 0; set_phase ^= 1u; }
+      if (mtv > 0) {
+        if (leader) umma_commit(smem_u32(&ctrl->acc_full[set]));
+        __syncwarp();
+        if (++set == a.NSETS) { set = 0; set_phase ^= 1u; }
+      }
       if (a.stationary) {
         if (last) wphase ^= 1u;  // the next key's panel is the next generation of every slot
         first = last;
@@ -618,8 +650,12 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     reg_dealloc<REGS_PROD>();
     const int p = threadIdx.x - WARP_PROD0 * 32;
     const int chunk = p & 7;      // 16-byte chunk (8 consecutive k) of the 128-byte row
-    const int row_base = p >> 3;  // rows row_base + 32*i
+    const int row_base = p >> 3;  // rows row_base + 64*i of this CTA's share of the k-block
     constexpr int ROWS_PER_THREAD = BN / (PROD_THREADS / 8);
+    constexpr int rows_cta = BN / CL;        // CL = 2: each CTA of the pair samples half of the rows of a k-block
+    const int row_first = crank * rows_cta;
+    const uint32_t peer_w_base = CL > 1 ? mapa_shared(w_base, (uint32_t)(crank ^ 1)) : 0u;
+    const uint32_t peer_w_full = CL > 1 ? mapa_shared(smem_u32(&ctrl->w_full[0]), (uint32_t)(crank ^ 1)) : 0u;
     int s = s0, nb = nb0, mg = mg0, wslot_r = 0;
     uint32_t wphase = 0, sphase = 0;
     bool first = true;
@@ -663,29 +699,41 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           sphase ^= 1u;
         }
         const BtRngKey rk = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_W);
+        // packed bf16 (mu, sigma) of this thread's chunk of k-block kb2, eight weights per row
+        uint4 nmu8[ROWS_PER_THREAD], nsg8[ROWS_PER_THREAD];
+        auto load_params = [&](int kb2) {
+          const int k2 = kb2 * BK + chunk * 8;
+#pragma unroll
+          for (int i = 0; i < ROWS_PER_THREAD; ++i) {
+            const int lrow = row_base + (PROD_THREADS / 8) * i;
+            const int n = nb * BN + row_first + lrow;
+            nmu8[i] = nsg8[i] = make_uint4(0u, 0u, 0u, 0u);
+            if (lrow < rows_cta && k2 < a.K && n < a.N && !(PROF && (a.debug & 32))) {
+              const int64_t e = (int64_t)n * a.K + k2;
+              nmu8[i] = __ldg(reinterpret_cast<const uint4*>(a.mu_p + e));
+              nsg8[i] = __ldg(reinterpret_cast<const uint4*>(a.sig_p + e));
+            }
+          }
+        };
+        load_params(0);
         for (int kb = 0; kb < a.nkb; ++kb) {
           const int slot = a.stationary ? kb : wslot_r;
           const int k = kb * BK + chunk * 8;
           const bool kin = k < a.K;  // K % 8 == 0: a chunk is all in or all out
-          const uint32_t wdst = w_base + slot * W_SLOT;
-          float4 mu4[ROWS_PER_THREAD][2], sg4[ROWS_PER_THREAD][2];
+          // parameters of this k-block were requested one k-block ago (cur <- nxt); the requests for
+          // the next one go out now, a whole k-block of Philox / Box-Muller work ahead of their use
+          uint4 mu8[ROWS_PER_THREAD], sg8[ROWS_PER_THREAD];
 #pragma unroll
-          for (int i = 0; i < ROWS_PER_THREAD; ++i) {  // parameter loads first (L2 resident), then the slot wait
-            const int n = nb * BN + row_base + (PROD_THREADS / 8) * i;
-            mu4[i][0] = mu4[i][1] = sg4[i][0] = sg4[i][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (kin && n < a.N && !(PROF && (a.debug & 32))) {
-              const int64_t e = (int64_t)n * a.K + k;
-              mu4[i][0] = __ldg(reinterpret_cast<const float4*>(a.mu_p + e));
-              mu4[i][1] = __ldg(reinterpret_cast<const float4*>(a.mu_p + e + 4));
-              sg4[i][0] = __ldg(reinterpret_cast<const float4*>(a.sig_p + e));
-              sg4[i][1] = __ldg(reinterpret_cast<const float4*>(a.sig_p + e + 4));
-            }
-          }
-          PW(0, mbar_wait(smem_u32(&ctrl->w_empty[slot]), wphase ^ 1u));
+          for (int i = 0; i < ROWS_PER_THREAD; ++i) { mu8[i] = nmu8[i]; sg8[i] = nsg8[i]; }
+          if (kb + 1 < a.nkb) load_params(kb + 1);
+          if constexpr (CL > 1) PW(0, mbar_wait_cluster(smem_u32(&ctrl->w_empty[slot]), wphase ^ 1u));
+          else PW(0, mbar_wait(smem_u32(&ctrl->w_empty[slot]), wphase ^ 1u));
           const long long gen_t0 = PROF ? clock64() : 0;
 #pragma unroll
           for (int i = 0; i < ROWS_PER_THREAD; ++i) {
-            const int row = row_base + (PROD_THREADS / 8) * i;
+            const int lrow = row_base + (PROD_THREADS / 8) * i;
+            if (lrow >= rows_cta) break;
+            const int row = row_first + lrow;
             const int n = nb * BN + row;
             float z[8];
 #pragma unroll
@@ -712,16 +760,30 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                   }
               }
             }
-            const uint32_t w0 = pack_bf16(fmaf(sg4[i][0].x, z[0], mu4[i][0].x), fmaf(sg4[i][0].y, z[1], mu4[i][0].y));
-            const uint32_t w1 = pack_bf16(fmaf(sg4[i][0].z, z[2], mu4[i][0].z), fmaf(sg4[i][0].w, z[3], mu4[i][0].w));
-            const uint32_t w2 = pack_bf16(fmaf(sg4[i][1].x, z[4], mu4[i][1].x), fmaf(sg4[i][1].y, z[5], mu4[i][1].y));
-            const uint32_t w3 = pack_bf16(fmaf(sg4[i][1].z, z[6], mu4[i][1].z), fmaf(sg4[i][1].w, z[7], mu4[i][1].w));
-            const uint32_t addr = wdst + (uint32_t)row * 128u + (((uint32_t)chunk ^ (uint32_t)(row & 7)) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+            // w = bf16(sigma * eps + mu) on packed pairs: fp32 fused multiply-add of the bf16 operands, one rounding
+            const uint32_t w0 = fma_bf16x2(sg8[i].x, pack_bf16(z[0], z[1]), mu8[i].x);
+            const uint32_t w1 = fma_bf16x2(sg8[i].y, pack_bf16(z[2], z[3]), mu8[i].y);
+            const uint32_t w2 = fma_bf16x2(sg8[i].z, pack_bf16(z[4], z[5]), mu8[i].z);
+            const uint32_t w3 = fma_bf16x2(sg8[i].w, pack_bf16(z[6], z[7]), mu8[i].w);
+            const uint32_t off = (uint32_t)(slot * W_SLOT) + (uint32_t)row * 128u + (((uint32_t)chunk ^ (uint32_t)(row & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(w_base + off), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
           }
           fence_proxy_async();
           __syncwarp();
-          if (lane == 0) mbar_arrive(smem_u32(&ctrl->w_full[slot]));
+          if (lane == 0) {
+            const uint32_t bar = smem_u32(&ctrl->w_full[slot]);
+            if (CL > 1 && row_base < rows_cta) {
+              // This warp's four rows (512 contiguous bytes) travel to the same place in the peer's ring
+              // as an asynchronous bulk copy that completes (complete_tx) on the PEER's w_full barrier;
+              // symmetrically this warp's own arrival expects the 512 bytes its counterpart warp in the
+              // peer sends here.  No remote arrive, no remote store, nothing waits on the DSMEM round trip.
+              const uint32_t off = (uint32_t)(slot * W_SLOT) + (uint32_t)(row_first + (row_base & ~3)) * 128u;
+              mbar_expect_tx(bar, 512u);
+              bulk_copy_to_cluster(peer_w_base + off, w_base + off, 512u, peer_w_full + (uint32_t)slot * 8u);
+            } else {
+              mbar_arrive(bar);
+            }
+          }
           if constexpr (PROF) pc[1] += (unsigned long long)(clock64() - gen_t0);
           if (!a.stationary && ++wslot_r == a.RW) { wslot_r = 0; wphase ^= 1u; }
         }
@@ -736,6 +798,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 
   tc_fence_before();
   __syncthreads();
+  if constexpr (CL > 1) cluster_sync_all();  // no CTA leaves while its peer may still store into / arrive on its shared memory
   if (warp == WARP_MMA) tmem_dealloc(tmem, 512);
 }
 
@@ -908,21 +971,38 @@ int64_t bt_tc_workspace_bytes(const bt_geom* g) {
   return bytes;
 }
 
+template <int BN, typename TO, bool PROF, int CL>
+static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const Tc2Args& a, int grid,
+                          int smem_bytes, cudaStream_t stream) {
+  BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, PROF, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = (size_t)smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = (unsigned)CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_fwd_kernel<BN, TO, PROF, CL>, ta, to, tr, a));
+  BT_LAUNCH_OK(PROF ? "tc2_fwd_kernel(prof)" : "tc2_fwd_kernel");
+  return BT_OK;
+}
+
 template <int BN, typename TO>
 static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const Tc2Args& a, int grid, int smem_bytes,
                       cudaStream_t stream) {
   if constexpr (sizeof(TO) == 2) {
-    if (env_int("BT_TC2_PROF", 0)) {
-      BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-      tc2_fwd_kernel<BN, TO, true><<<grid, NUM_THREADS, smem_bytes, stream>>>(ta, to, tr, a);
-      BT_LAUNCH_OK("tc2_fwd_kernel(prof)");
-      return BT_OK;
-    }
+    if (env_int("BT_TC2_PROF", 0))
+      return a.CL == 2 ? tc2_launch_one<BN, TO, true, 2>(ta, to, tr, a, grid, smem_bytes, stream)
+                       : tc2_launch_one<BN, TO, true, 1>(ta, to, tr, a, grid, smem_bytes, stream);
   }
-  BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-  tc2_fwd_kernel<BN, TO, false><<<grid, NUM_THREADS, smem_bytes, stream>>>(ta, to, tr, a);
-  BT_LAUNCH_OK("tc2_fwd_kernel");
-  return BT_OK;
+  return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2>(ta, to, tr, a, grid, smem_bytes, stream)
+                   : tc2_launch_one<BN, TO, false, 1>(ta, to, tr, a, grid, smem_bytes, stream);
 }
 
 // Diagnostics: cycle counters of the last BT_TC2_PROF=1 launch, [cta][role][slot] (see bt_b200.h).
@@ -962,9 +1042,9 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
 
   // ---- workspace carve-up: packed parameters, then (A_PATCH) the patch matrix
   const int64_t wn = (int64_t)a.N * a.K;
-  float* mu_p = (float*)workspace;
-  float* sig_p = mu_p + wn;
-  float* eps_p = p->eps_w ? sig_p + wn : nullptr;
+  __nv_bfloat16* mu_p = (__nv_bfloat16*)workspace;
+  __nv_bfloat16* sig_p = mu_p + wn;
+  float* eps_p = p->eps_w ? (float*)(sig_p + wn) : nullptr;
   __nv_bfloat16* patches = (__nv_bfloat16*)((char*)workspace + ((3 * wn * 4 + 255) / 256) * 256);
   {
     int64_t blocks = (wn + 255) / 256;
@@ -1098,6 +1178,13 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.NSETS = NSLOTS / a.MT;
   if (a.NSETS > MAX_SETS) a.NSETS = MAX_SETS;
   a.num_mg = (a.num_mt + a.MT - 1) / a.MT;
+  // Streaming layers are bound by the W producers (~30 issue slots and 2 MUFU per sampled weight):
+  // a CTA pair walks the same k-block sequence on neighbouring m-groups and each CTA samples half
+  // of every k-block, storing it into both rings over DSMEM.
+  a.CL = (!a.stationary && a.num_mg >= 2 && sms % 2 == 0) ? 2 : 1;
+  if (env_int("BT_TC2_CL", 0) == 1) a.CL = 1;
+  if (env_int("BT_TC2_CL", 0) == 2 && a.num_mg >= 2 && sms % 2 == 0) a.CL = 2;
+  a.num_mg = (a.num_mg + a.CL - 1) / a.CL;
   a.stage_bufs = 2;
   a.res_bufs = res_min;
   a.NA = (ring_bytes(2, res_min) - a.RW * WB) / A_SLOT;
@@ -1121,13 +1208,14 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.NA = a.NAr * a.NR;
   BT_REQUIRE(a.NA >= 2 && a.RW >= 1 && a.RW <= MAX_RW, BT_ERR_UNSUPPORTED, "tensor-core forward: no room for the pipelines");
   a.total_items = (int64_t)a.S * a.NB * a.num_mg;
-  const int grid = (int)(a.total_items < sms ? a.total_items : sms);
+  const int ncl = sms / a.CL;
+  const int grid = (int)(a.total_items < ncl ? a.total_items : ncl) * a.CL;
   const int smem_bytes = 1024 + CTRL_BYTES + (a.stage_bufs + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT + a.RW * WB;
   BT_REQUIRE(smem_bytes <= SMEM_LIMIT, BT_ERR_UNSUPPORTED, "tensor-core forward: shared memory plan %d exceeds %d", smem_bytes, SMEM_LIMIT);
   if (env_int("BT_TC2_LOG", 0))
-    fprintf(stderr, "tc2: mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d\n",
+    fprintf(stderr, "tc2: mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d\n",
             (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,
-            (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs);
+            (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs, a.CL);
   const bool o32 = g->out_dtype == BT_F32;
   if (BN == 64)
     return o32 ? tc2_launch<64, float>(tm_a, tm_out, tm_res, a, grid, smem_bytes, stream)

@@ -15,7 +15,7 @@ HEADERS = ["bt_common.cuh", "bt_simt.cuh", "bt_tc.cuh", os.path.join("..", "..",
 LIB = os.path.join(HERE, "libbt_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
-         "--expt-relaxed-constexpr", "-Xptxas", "-v"]
+         "--expt-relaxed-constexpr", "-Xptxas", "-v"] + os.environ.get("BT_NVCC_EXTRA", "").split()
 
 
 def _mtime(p):

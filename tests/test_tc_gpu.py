@@ -1,6 +1,6 @@
 """tcgen05 / TMEM path (bf16 operands, fp32 accumulate, weight sampled in shared memory)
 against the CPU oracle.  The oracle is evaluated on the SAME rounded operands the kernel
-multiplies -- x in bf16 and W = bf16(mu + softplus(rho)*eps) -- so the only differences
+multiplies -- x in bf16 and W = bf16(bf16(softplus(rho))*bf16(eps) + bf16(mu)) -- so the only differences
 left are fp32 accumulation order and the bf16 rounding of the output: documented bound
 |err| <= 2^-8 * max|out| for bf16 outputs (observed ~2e-3)."""
 import pytest
@@ -22,7 +22,11 @@ def bf16_round(t):
 def oracle_bf16(layer, x, conv_kw=None):
     mu, rho = layer._w()
     eps = getattr(layer, "eps_" + layer._wname)
-    w = bf16_round(oracle.sample_weight(mu.detach().cpu(), rho.detach().cpu(), eps.cpu()))
+    # the tensor-core path's weight contract: mu, sigma = softplus(rho) and eps are rounded to bf16 (what
+    # model.bfloat16() does to the reference's parameters), w = bf16(sigma * eps + mu) with one rounding
+    mu_c, rho_c = mu.detach().cpu(), rho.detach().cpu()
+    sigma = oracle.sample_weight(torch.zeros_like(mu_c), rho_c, torch.ones_like(mu_c))
+    w = bf16_round((bf16_round(sigma).double() * bf16_round(eps.cpu()).double() + bf16_round(mu_c).double()).float())
     b = None
     if layer.mu_bias is not None:
         b = oracle.sample_weight(layer.mu_bias.detach().cpu(), layer.rho_bias.detach().cpu(), layer.eps_bias.cpu())
@@ -237,3 +241,34 @@ def test_conv2d_tc_residual_epilogue(cin, cout, k, pad, batch, hw, S, relu, cuda
     torch.testing.assert_close(fused_nchw, want, rtol=0, atol=0)
     with pytest.raises(RuntimeError, match="residual has shape"):
         layer(x, residual=res[:, :1])
+
+
+CLUSTER_CASES = [
+    # cin, cout, k, pad, batch, hw, S     streaming layers with >= 2 m-groups
+    (128, 128, 3, 1, 8, 14, 2),    # K=1152, 13 tiles per sample: odd tail of a CTA pair
+    (256, 256, 3, 1, 16, 14, 1),   # MT=4 groups, two n-blocks
+    (1024, 256, 1, 0, 8, 14, 3),   # K=1024 1x1 (tiled map), three samples
+    (512, 72, 3, 1, 6, 9, 1),      # N tail, BN=128 with 72 live rows split 64 + 8 between the CTAs
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,pad,batch,hw,S", CLUSTER_CASES)
+def test_cluster_pair_matches_single_cta(cin, cout, k, pad, batch, hw, S, cuda_device, monkeypatch):
+    """CTA pairs that split the sampling of every W k-block (DSMEM stores into both rings) must
+    give bit-identical outputs to the single-CTA schedule: same Philox stream, same MMA order."""
+    torch.manual_seed(cin + cout)
+    layer = L.Conv2dReparameterization(cin, cout, k, padding=pad, bias=True, prior_type="normal").to(cuda_device)
+    layer.dnn_to_bnn_flag = True
+    layer.path = "tc"
+    layer._ep_scale = torch.rand(cout, device=cuda_device) + 0.5
+    layer._ep_shift = torch.randn(cout, device=cuda_device)
+    layer._ep_relu = True
+    x = torch.randn(S * batch, cin, hw, hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    outs = {}
+    for cl in ("1", "2"):
+        monkeypatch.setenv("BT_TC2_CL", cl)
+        with torch.no_grad(), bt.mc_batched(S, 3):
+            outs[cl] = layer(x)
+        torch.cuda.synchronize()
+    assert float(outs["1"].float().abs().max()) > 0
+    torch.testing.assert_close(outs["2"], outs["1"], rtol=0, atol=0)
