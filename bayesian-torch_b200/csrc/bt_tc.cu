@@ -80,6 +80,7 @@ struct Tc2Args {
   int OH, OW, KW, CB;  // CB = Cin / 64: k-blocks per filter tap
   int sh, sw, ph, pw, dh, dw;
   int num_mt, num_mg, MT, NSETS, nkb, NA, RW, stationary;  // num_mg: m-groups per key as walked by one cluster
+  int nb_inner;      // item order: 1 = (sample, m-group, n-block), n-block fastest (streaming only); 0 = m-group fastest
   int CL;            // CTAs per cluster (1 or 2). CL = 2: the pair walks the same (sample, n-block, k-block) sequence on
                      // neighbouring m-groups, each CTA samples half of every W k-block and stores it into both CTAs' rings
   int NR, NAr;       // A rings (one per active MMA issuer) and slots per ring; NA = NR * NAr
@@ -96,7 +97,7 @@ struct Ctrl {
   uint64_t a_full[MAX_NA], a_empty[MAX_NA];
   uint64_t w_full[MAX_RW + 1], w_empty[MAX_RW + 1];  // slot RW: the shift tile
   uint64_t acc_full[MAX_SETS], acc_empty[MAX_SETS];
-  uint64_t res_full[4][4];  // [epilogue warp][residual buffer]
+  uint64_t res_full[4], res_empty[4];  // residual ring: one 128-row x 128-byte tile per slot, a 32-row slab per epilogue warp
   uint32_t tmem_base;
   uint32_t pad[3];
 };
@@ -296,7 +297,7 @@ __device__ __forceinline__ void epi_unit(const uint32_t (&v)[32], uint32_t rowad
 
 // Cycle accounting for BT_TC2_PROF=1 (diagnostics; a separate instantiation, the product kernel
 // carries none of it): per CTA and role, cycles spent in each kind of wait.
-constexpr int PROF_ROLES = 6, PROF_SLOTS = 6;
+constexpr int PROF_ROLES = 6, PROF_SLOTS = 8;
 __device__ unsigned long long g_tc_prof[160 * PROF_ROLES * PROF_SLOTS];
 #define PW(i, ...)                                              \
   do {                                                          \
@@ -326,7 +327,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   const uint32_t w_base = a_base + a.NA * A_SLOT;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  unsigned long long pc[PROF_SLOTS] = {0, 0, 0, 0, 0, 0};
+  unsigned long long pc[PROF_SLOTS] = {0, 0, 0, 0, 0, 0, 0, 0};
   const long long prof_t0 = PROF ? clock64() : 0;
   auto prof_flush = [&](int role) {
     if constexpr (PROF) {
@@ -342,7 +343,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     mbar_init(smem_u32(&ctrl->w_full[a.RW]), N_PROD_WARPS);  // the shift tile stays CTA-local
     mbar_init(smem_u32(&ctrl->w_empty[a.RW]), N_MMA_WARPS);
     for (int i = 0; i < a.NSETS; ++i) { mbar_init(smem_u32(&ctrl->acc_full[i]), N_MMA_WARPS); mbar_init(smem_u32(&ctrl->acc_empty[i]), 128); }
-    for (int i = 0; i < 16; ++i) mbar_init(smem_u32(&ctrl->res_full[i >> 2][i & 3]), 1);
+    for (int i = 0; i < 4; ++i) { mbar_init(smem_u32(&ctrl->res_full[i]), 1); mbar_init(smem_u32(&ctrl->res_empty[i]), 4); }
     mbar_fence_init();
   }
   if (warp == WARP_TMA && lane == 0) { prefetch_tmap(&tm_a); prefetch_tmap(&tm_out); if (a.res_bufs) prefetch_tmap(&tm_res); }
@@ -365,9 +366,31 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   // first item of this CTA, decoded once; the role loops then walk (s, nb, mg) incrementally --
   // the single-thread TMA / MMA loops are instruction-latency bound, so no division or modulo
   // by a run-time value may sit inside them.
-  const int64_t key0 = i0 / a.num_mg;
-  const int mg0 = (int)(i0 - key0 * a.num_mg);
-  const int s0 = (int)(key0 / a.NB), nb0 = (int)(key0 - (int64_t)s0 * a.NB);
+  // Item order: (sample, n-block, m-group) with the m-group fastest when a sampled panel is kept
+  // across m-groups (stationary), (sample, m-group, n-block) with the n-block fastest when W is
+  // streamed: then the NB passes over one group of A tiles follow each other on the same SM and
+  // all but the first are L2 hits (measured before: every pass re-read A from HBM).
+  int s0, nb0, mg0;
+  if (a.nb_inner) {
+    const int64_t key0 = i0 / a.NB;
+    nb0 = (int)(i0 - key0 * a.NB);
+    s0 = (int)(key0 / a.num_mg);
+    mg0 = (int)(key0 - (int64_t)s0 * a.num_mg);
+  } else {
+    const int64_t key0 = i0 / a.num_mg;
+    mg0 = (int)(i0 - key0 * a.num_mg);
+    s0 = (int)(key0 / a.NB);
+    nb0 = (int)(key0 - (int64_t)s0 * a.NB);
+  }
+  // advances (s, nb, mg) to the next item; true when a new (sample, n-block) panel starts (stationary order only)
+  auto walk = [&](int& ws, int& wnb, int& wmg) -> bool {
+    if (a.nb_inner) {
+      if (++wnb == a.NB) { wnb = 0; if (++wmg == a.num_mg) { wmg = 0; ++ws; } }
+      return false;
+    }
+    if (++wmg == a.num_mg) { wmg = 0; if (++wnb == a.NB) { wnb = 0; ++ws; } return true; }
+    return false;
+  };
 
   if (warp >= WARP_EPI0 && warp < WARP_EPI0 + 4) {
     // =========================== EPILOGUE ===========================
@@ -382,31 +405,11 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     int s = s0, nb = nb0, mg = mg0, set = 0;
     uint32_t set_phase = 0;
     const bool has_res = a.res_bufs != 0;
-    // Residual tiles are fetched by TMA res_bufs sub-tiles ahead of their use: a second cursor
-    // walks the same (item, tile, sub-tile) sequence as the loops below, skipping slabs past Ms.
-    int pf_it = 0, pf_s = s0, pf_nb = nb0, pf_mg = mg0, pf_t = 0, pf_sub = 0;
-    const uint32_t my_res = res_base + (uint32_t)(q * a.res_bufs) * 4096u;
-    auto pf_issue = [&](int slot) {
-      while (pf_it < n_items) {
-        if (pf_t < tiles_of(pf_mg) && (tile0(pf_mg) + pf_t) * BM + q * 32 < a.Ms) {
-          if (pf_sub < (min(BN, a.N - pf_nb * BN) + SUBN - 1) / SUBN) break;
-          pf_sub = 0; ++pf_t;
-          continue;
-        }
-        pf_t = 0; pf_sub = 0; ++pf_it;
-        if (++pf_mg == a.num_mg) { pf_mg = 0; if (++pf_nb == a.NB) { pf_nb = 0; ++pf_s; } }
-      }
-      if (pf_it >= n_items) return;
-      if (lane == 0) {
-        const uint32_t bar = smem_u32(&ctrl->res_full[q][slot]);
-        mbar_expect_tx(bar, 4096);
-        tma_load_3d(my_res + (uint32_t)slot * 4096u, &tm_res, bar, pf_nb * BN + pf_sub * SUBN, (tile0(pf_mg) + pf_t) * BM + q * 32, pf_s);
-      }
-      ++pf_sub;
-    };
+    // Residual tiles arrive through a ring filled by the residual-loader warp (one 128-row TMA box
+    // per sub-tile, res_bufs sub-tiles ahead); this warp reads its 32-row slab of each.
+    const uint32_t my_res = res_base + (uint32_t)q * 4096u;
     int rslot = 0;
     uint32_t rphase = 0;
-    for (int i = 0; i < a.res_bufs; ++i) pf_issue(i);
     // the whole loop is instantiated per (ReLU, residual) combination: the variant that runs is
     // straight-line code, and the other three never enter the instruction cache
     auto epi_loop = [&](auto relu_c, auto res_c) {
@@ -417,7 +420,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     for (int it = 0; it < n_items; ++it) {
       const int mtv = tiles_of(mg);
       if (mtv == 0) {  // tail of a CTA pair: nothing was accumulated for this CTA
-        if (++mg == a.num_mg) { mg = 0; if (++nb == a.NB) { nb = 0; ++s; } }
+        walk(s, nb, mg);
         continue;
       }
       PW(0, mbar_wait(smem_u32(&ctrl->acc_full[set]), set_phase));
@@ -426,7 +429,16 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       const int nsub = (ncols + SUBN - 1) / SUBN;  // staged sub-tiles with at least one real column
       for (int t = 0; t < mtv; ++t) {
         const int m0 = (tile0(mg) + t) * BM + q * 32;  // first row of this warp's 32-row slab
-        if (m0 >= a.Ms) break;                          // slab entirely past the sample's last row (warp-uniform)
+        if (m0 >= a.Ms) {  // slab entirely past the sample's last row (warp-uniform): only the residual ring moves on
+          if constexpr (RES) {
+            for (int sub = 0; sub < nsub; ++sub) {
+              mbar_wait(smem_u32(&ctrl->res_full[rslot]), rphase);
+              if (lane == 0) mbar_arrive(smem_u32(&ctrl->res_empty[rslot]));
+              if (++rslot == a.res_bufs) { rslot = 0; rphase ^= 1u; }
+            }
+          }
+          continue;
+        }
         const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)((set * a.MT + t) * BN);
         // TMEM reads are software-pipelined in 32-column units: the load of unit u+1 is in
         // flight while unit u is converted and staged.
@@ -447,8 +459,8 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           }
           const uint32_t buf = my_stage + sbuf * 4096u;
           const uint32_t rowaddr = buf + (uint32_t)lane * 128u;
-          const uint32_t resaddr = my_res + (uint32_t)rslot * 4096u + (uint32_t)lane * 128u;
-          if constexpr (RES) PW(1, mbar_wait(smem_u32(&ctrl->res_full[q][rslot]), rphase));
+          const uint32_t resaddr = my_res + (uint32_t)rslot * (uint32_t)STAGE_UNIT + (uint32_t)lane * 128u;
+          if constexpr (RES) PW(1, mbar_wait(smem_u32(&ctrl->res_full[rslot]), rphase));
           const int c0 = sub * SUBN;
           if constexpr (UPS == 2) {
             PW(2, tmem_ld_wait());
@@ -468,16 +480,18 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               emit(va, rowaddr, resaddr, 0);
             }
           }
-          fence_proxy_async();
-          __syncwarp();
-          if (lane == 0 && !(PROF && (a.debug & 1))) {
-            tma_store_3d(&tm_out, buf, nb * BN + c0, m0, s);  // rows >= Ms and columns >= N are clipped by the map
-            tma_store_commit();
-          }
+          PW(5, {
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0 && !(PROF && (a.debug & 1))) {
+              tma_store_3d(&tm_out, buf, nb * BN + c0, m0, s);  // rows >= Ms and columns >= N are clipped by the map
+              tma_store_commit();
+            }
+          });
           ++nstore;
           if (++sbuf == (uint32_t)a.stage_bufs) sbuf = 0;
-          if constexpr (RES) {  // every lane is done reading the tile (fence + __syncwarp above): refill its buffer
-            pf_issue(rslot);
+          if constexpr (RES) {  // every lane is done reading the slab (fence + __syncwarp above): hand it back
+            if (lane == 0) mbar_arrive(smem_u32(&ctrl->res_empty[rslot]));
             if (++rslot == a.res_bufs) { rslot = 0; rphase ^= 1u; }
           }
         }
@@ -485,7 +499,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       tc_fence_before();
       mbar_arrive(smem_u32(&ctrl->acc_empty[set]));
       if (++set == a.NSETS) { set = 0; set_phase ^= 1u; }
-      if (++mg == a.num_mg) { mg = 0; if (++nb == a.NB) { nb = 0; ++s; } }
+      walk(s, nb, mg);
     }
     };
     using T_ = std::true_type;
@@ -556,7 +570,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           if (++kw == a.KW) { kw = 0; offw = 0; offh += a.dh; }
         }
       }
-      if (++mg == a.num_mg) { mg = 0; if (++nb == a.NB) { nb = 0; ++s; } }
+      walk(s, nb, mg);
     }
     __syncwarp();
     prof_flush(1);
@@ -565,7 +579,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     const int j = warp - WARP_MMA;  // this issuer owns tiles t with t % N_MMA_WARPS == j
     const bool leader = elect_one();
     constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
-    int mg = mg0, set = 0, aslot = 0, wslot_r = 0;
+    int mg = mg0, nb_unused = nb0, s_unused = s0, set = 0, aslot = 0, wslot_r = 0;
     uint32_t set_phase = 0, aphase = 0, wphase = 0, sphase = 0;
     const uint32_t acc0 = a.has_shift ? 1u : 0u;  // accumulators start from the shift, not from zero
     const uint64_t ones_desc = umma_desc_sw32(ones_base), shift_desc = umma_desc_sw32(shift_base);
@@ -641,9 +655,32 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         if (last) wphase ^= 1u;  // the next key's panel is the next generation of every slot
         first = last;
       }
-      if (++mg == a.num_mg) mg = 0;
+      walk(s_unused, nb_unused, mg);
     }
     prof_flush(2 + j);
+    } else if (a.res_bufs) {
+    // =========================== RESIDUAL LOADER ===========================
+    // walks the same (item, tile, sub-tile) sequence as the epilogue, res_bufs sub-tiles ahead of it
+    const bool leader = elect_one();
+    int s = s0, nb = nb0, mg = mg0, slot = 0;
+    uint32_t phase = 0;
+    for (int it = 0; it < n_items; ++it) {
+      const int mtv = tiles_of(mg);
+      const int nsub = (min(BN, a.N - nb * BN) + SUBN - 1) / SUBN;
+      for (int t = 0; t < mtv; ++t) {
+        for (int sub = 0; sub < nsub; ++sub) {
+          mbar_wait(smem_u32(&ctrl->res_empty[slot]), phase ^ 1u);
+          if (leader) {
+            const uint32_t bar = smem_u32(&ctrl->res_full[slot]);
+            mbar_expect_tx(bar, (uint32_t)STAGE_UNIT);
+            tma_load_3d(res_base + (uint32_t)slot * (uint32_t)STAGE_UNIT, &tm_res, bar, nb * BN + sub * SUBN, (tile0(mg) + t) * BM, s);
+          }
+          if (++slot == a.res_bufs) { slot = 0; phase ^= 1u; }
+        }
+      }
+      walk(s, nb, mg);
+    }
+    __syncwarp();
     }
   } else {
     // =========================== W PRODUCERS (sample in smem) ===========================
@@ -790,7 +827,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         if (a.stationary) wphase ^= 1u;
       }
       first = false;
-      if (++mg == a.num_mg) { mg = 0; first = true; if (++nb == a.NB) { nb = 0; ++s; } }
+      if (walk(s, nb, mg)) first = true;
     }
     if (warp == WARP_PROD0) prof_flush(4);
     if (warp == WARP_PROD0 + N_PROD_WARPS - 1) prof_flush(5);
@@ -1130,8 +1167,9 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
     tm_res = tm_out;  // placeholder when there is no residual (never dereferenced)
     if (p->residual) {  // same shape, dtype and strides as out: the same map over another base
       BT_REQUIRE(((uintptr_t)p->residual & 15) == 0, BT_ERR_ALIGN, "tensor-core forward: residual must be 16-byte aligned");
+      const cuuint32_t rbox[3] = {box[0], BM, 1};  // one box = the residual of a whole 128-row tile, 32 rows per epilogue warp
       const CUresult r2 = drv.tiled(&tm_res, es_o == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3,
-                                    const_cast<void*>(p->residual), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                    const_cast<void*>(p->residual), gdim, gstr, rbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
       BT_REQUIRE(r2 == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeTiled(residual) failed with %d", (int)r2);
     }
@@ -1158,7 +1196,12 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   const int WB = BN * BK * 2;
   a.NB = (a.N + BN - 1) / BN;
   a.stationary = panel_fits(BN) ? 1 : 0;
+  // Wide layers with a short reduction (the 1x1 expansions, N >= 4 n-blocks) stream instead: with
+  // the n-block innermost in the item order every group of A tiles is fetched from HBM once rather
+  // than once per n-block, and a CTA pair halves the sampling cost that streaming re-pays per item.
+  if (a.stationary && a.NB >= 4 && a.nkb >= 2 && a.num_mt >= 4) a.stationary = 0;
   if (force_stat == 0) a.stationary = 0;
+  if (force_stat == 1 && panel_fits(BN)) a.stationary = 1;
   const int NSLOTS = 512 / BN;
   if (a.stationary) {
     a.RW = a.nkb;
@@ -1170,6 +1213,8 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
       const int64_t items = (int64_t)a.S * a.NB * ((a.num_mt + mt - 1) / mt);
       if (items >= sms || mt == 1 || (mt == 2 && a.num_mt >= 2)) { a.MT = mt; break; }
     }
+    // short reductions: two accumulator sets of two tiles, so the epilogue of one item overlaps the MMAs of the next
+    if (a.nkb <= 8 && a.MT > 2) a.MT = 2;
     if (force_mt >= 1 && force_mt <= MAX_MT && force_mt <= NSLOTS) a.MT = force_mt;
     a.RW = (ring_bytes(2, res_min) - 4 * A_SLOT) / WB;
     if (a.RW > 5) a.RW = 5;  // deeper W rings measured no faster; the space goes to the A ring
@@ -1185,6 +1230,8 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   if (env_int("BT_TC2_CL", 0) == 1) a.CL = 1;
   if (env_int("BT_TC2_CL", 0) == 2 && a.num_mg >= 2 && sms % 2 == 0) a.CL = 2;
   a.num_mg = (a.num_mg + a.CL - 1) / a.CL;
+  a.nb_inner = (!a.stationary && a.NB > 1) ? 1 : 0;
+  if (env_int("BT_TC2_NBINNER", -1) == 0) a.nb_inner = 0;
   a.stage_bufs = 2;
   a.res_bufs = res_min;
   a.NA = (ring_bytes(2, res_min) - a.RW * WB) / A_SLOT;

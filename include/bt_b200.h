@@ -233,7 +233,7 @@ int bt_moped_rho(const float* w, float* rho, int64_t n, float delta, bt_stream_t
 /* Diagnostics (not on any product path): with BT_TC2_PROF=1 in the environment the tensor-core
  * forward runs an instrumented instantiation that records, per CTA and warp role, the cycles
  * spent in each kind of pipeline wait.  Copies the counters of the last such launch to
- * host_out[160 ctas][6 roles][6 slots]; roles: 0 epilogue, 1 TMA loader, 2/3 MMA issuers,
+ * host_out[160 ctas][6 roles][8 slots]; roles: 0 epilogue, 1 TMA loader, 2/3 MMA issuers,
  * 4/5 first/last W-producer warp; the last slot of each role is its total cycle count. */
 int bt_debug_tc_profile(unsigned long long* host_out, int n_words);
 

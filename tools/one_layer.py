@@ -24,6 +24,10 @@ if os.environ.get("BT_AFF", "0") == "1":  # folded BatchNorm + ReLU epilogue
     layer._ep_relu = True
 XS = S if os.environ.get("BT_XS", "0") == "1" else 1  # per-sample activations (any layer but the first)
 x = torch.randn(XS * batch, cin, hw, hw, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+res = None
+if os.environ.get("BT_RES", "0") == "1":  # residual input (the identity branch), read by the epilogue
+    ho = (hw + 2 * pad - k) // stride + 1
+    res = torch.randn(S * batch, cout, ho, ho, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
 with torch.no_grad():
     for i in range(iters + 2):
         if i == 2:
@@ -31,7 +35,7 @@ with torch.no_grad():
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
         with bt.mc_batched(S, 0, shared_batch=batch):
-            y = layer(x)
+            y = layer(x, residual=res) if res is not None else layer(x)
     e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / iters
