@@ -1217,7 +1217,7 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
     if (a.nkb <= 8 && a.MT > 2) a.MT = 2;
     if (force_mt >= 1 && force_mt <= MAX_MT && force_mt <= NSLOTS) a.MT = force_mt;
     a.RW = (ring_bytes(2, res_min) - 4 * A_SLOT) / WB;
-    if (a.RW > 5) a.RW = 5;  // deeper W rings measured no faster; the space goes to the A ring
+    if (a.RW > 4) a.RW = 4;  // deeper W rings measured no faster; the space goes to the A ring
     if (env_int("BT_TC2_RW", 0) >= 2 && env_int("BT_TC2_RW", 0) < a.RW) a.RW = env_int("BT_TC2_RW", 0);
   }
   a.NSETS = NSLOTS / a.MT;

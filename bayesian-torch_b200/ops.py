@@ -458,6 +458,8 @@ class _BayesLayerFn(torch.autograd.Function):
                 kred = mu_wc.numel() // mu_wc.shape[0]
                 flops = 2.0 * m * out.shape[1] * kred * (2 if call.flipout else 1)
                 nbytes = xd.numel() * xd.element_size() + out.numel() * out.element_size() + 8 * mu_wc.numel()
+                if call.residual is not None:
+                    nbytes += call.residual.numel() * call.residual.element_size()
                 PROFILE.records.append((used, flops, nbytes, ev0, ev1))
         _lib.check(rc, "layer forward")
         ctx.call = call

@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--samples", type=int, default=32)
-    ap.add_argument("--mc-batch", type=int, default=int(os.environ.get("BT_MC_BATCH", "8")),
+    ap.add_argument("--mc-batch", type=int, default=int(os.environ.get("BT_MC_BATCH", "32")),
                     help="weight samples folded into one model pass (ops.mc_batched)")
     ap.add_argument("--cpu-batch", type=int, default=8, help="images in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -155,6 +155,21 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------
 # this repo's arm
 # ------------------------------------------------------------------------------------------
+def tc_traffic(launches_per_step):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu pass over one timed step
+    of this same command (profiles/r1_tc2_traffic.json, tools/summarize_launches.py); None when the
+    capture does not match the launch count of this run."""
+    path = os.path.join(ROOT, "profiles", "r1_tc2_traffic.json")
+    try:
+        with open(path) as f:
+            t = json.load(f)
+        if t.get("launches") == launches_per_step:
+            return t["dram_bytes_per_launch"]
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
+
+
 def build_model(device, fold_bn=True):
     import torch
     import torchvision
@@ -270,7 +285,7 @@ def run_b200(args):
                     "d2h_bytes_per_step": 2 * res.mean.numel() * 4},
             "gpu_launches": launches,
             "roofline": {"bound": "tensor", "kernel": "tc2_fwd_kernel (all launches of one step)", "achieved": achieved,
-                         "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"], "traffic": None,
+                         "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"], "traffic": tc_traffic(len(tc)), "algorithmic_bytes_per_launch": (sum(b for _, b, _ in tc) / len(tc)) if tc else None,
                          "peak_source": pk["source"], "launches_per_step": len(tc), "ms_per_step_in_kernel": tc_ms,
                          "ms_per_step_other_bt_kernels": other_ms,
                          "share_of_step": tc_ms / ms_step if ms_step > 0 else None},

@@ -171,3 +171,27 @@ def test_mc_predict_single_rank(cuda_device):
     torch.testing.assert_close(res_b.mean, res.mean, rtol=1e-5, atol=1e-6)
     torch.testing.assert_close(res.var.cpu().double(), probs.var(0, unbiased=False), rtol=1e-3, atol=1e-6)
     torch.testing.assert_close(res.mutual_info.cpu().double(), oracle.mutual_information(probs), rtol=1e-3, atol=1e-5)
+
+
+def test_full_size_mc_batching_is_consistent(cuda_device):
+    """BASELINE config at full size (ResNet-50, batch 128, 32 samples): all 32 samples folded
+    into ONE model pass (activations beyond 2^31 elements, CTA pairs, residual epilogues) must
+    give the same predictive moments as four passes of 8 -- sample s is the same draw either way."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    model = bench.build_model(cuda_device)
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(128, 3, 224, 224, generator=g).to(cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    bt.manual_seed(77)
+    with torch.no_grad():
+        a = bt.mc_predict(model, x, 32, batch_samples=8)
+    bt.manual_seed(77)
+    with torch.no_grad():
+        b = bt.mc_predict(model, x, 32, batch_samples=32)
+    assert torch.isfinite(a.mean).all() and float(a.var.max()) > 0
+    # same weights and inputs; only the accumulation order over samples differs (fp32 sums)
+    torch.testing.assert_close(b.mean, a.mean, rtol=1e-4, atol=1e-6)
+    torch.testing.assert_close(b.var, a.var, rtol=1e-3, atol=1e-7)
+    torch.testing.assert_close(b.entropy, a.entropy, rtol=1e-4, atol=1e-5)
