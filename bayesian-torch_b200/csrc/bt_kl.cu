@@ -38,29 +38,43 @@ struct KlElem {
   float kl, dmu, drho;
 };
 
+// Per-prior constants of the KL term: log(sigma_p) and 1 / sigma_p^2.  With the reference's
+// constant-filled priors they are loop invariants (computed once per thread, not per element).
+struct KlPrior {
+  float log_ps, inv2;
+};
+__device__ __forceinline__ KlPrior kl_prior(float ps) {
+  KlPrior p;
+  p.log_ps = logf(ps);
+  p.inv2 = __frcp_rn(ps * ps);
+  return p;
+}
+
+// The pass is HBM-bound only if an element costs ~20 issue slots: softplus and the two logs use
+// the MUFU approximations (ex2 / lg2, relative error ~2^-22) with a series for small exp(rho),
+// where log(1 + t) computed as such would lose the low bits of t.  Checked against the fp64
+// oracle at rtol 1e-5 on the mean (tests/test_parity_gpu.py).
 template <bool kGrad>
-__device__ __forceinline__ KlElem kl_elem(float mu, float rho, float pm, float ps, bool q_is_sigma) {
+__device__ __forceinline__ KlElem kl_elem(float mu, float rho, float pm, const KlPrior pr, bool q_is_sigma) {
   // sigma = log1p(exp(rho)) (linear_variational.py:163); sigmoid(rho) = t/(1+t) with t = exp(rho)
   float sig, dsig_drho;
   if (q_is_sigma) {
     sig = rho;
     dsig_drho = 1.f;
-  } else if (rho > 20.f) {
-    sig = rho;
-    dsig_drho = 1.f;
   } else {
-    const float t = expf(rho);
-    sig = log1pf(t);
-    dsig_drho = kGrad ? __fdividef(t, 1.f + t) : 0.f;
+    const float t = __expf(fminf(rho, 30.f));
+    const float series = t * (1.f - t * (0.5f - t * (0.33333334f - 0.25f * t)));  // log1p(t), t < 2^-5: error < t^5/5
+    const float big = __logf(1.f + t);
+    sig = rho > 20.f ? rho : (t < 0.03125f ? series : big);
+    dsig_drho = kGrad ? (rho > 20.f ? 1.f : __fdividef(t, 1.f + t)) : 0.f;
   }
-  const float inv2 = __frcp_rn(ps * ps);  // 1 / sigma_p^2
   const float d = mu - pm;
   KlElem e;
   // log(sigma_p) - log(sigma_q) + (sigma_q^2 + (mu_q-mu_p)^2) / (2 sigma_p^2) - 0.5
-  e.kl = (logf(ps) - logf(sig)) + 0.5f * (sig * sig + d * d) * inv2 - 0.5f;
+  e.kl = (pr.log_ps - __logf(sig)) + 0.5f * (sig * sig + d * d) * pr.inv2 - 0.5f;
   if (kGrad) {
-    e.dmu = d * inv2;
-    e.drho = (sig * inv2 - __frcp_rn(sig)) * dsig_drho;
+    e.dmu = d * pr.inv2;
+    e.drho = (sig * pr.inv2 - __frcp_rn(sig)) * dsig_drho;
   } else {
     e.dmu = 0.f;
     e.drho = 0.f;
@@ -79,6 +93,7 @@ __global__ void __launch_bounds__(KL_THREADS) kl_normal_multi_kernel(const __gri
   __shared__ bool is_last;
   const int tid = threadIdx.x;
   const float gscale = (kGrad && grad_scale != nullptr) ? __ldg(grad_scale) : 1.f;
+  const KlPrior prior_c = kl_prior(tab.prior_sigma);
 
   for (int chunk = blockIdx.x; chunk < tab.total_chunks; chunk += gridDim.x) {
     // which tensor owns this chunk (binary search over the chunk prefix)
@@ -121,10 +136,11 @@ __global__ void __launch_bounds__(KL_THREADS) kl_normal_multi_kernel(const __gri
           if (pmu) pm4 = __ldcs(reinterpret_cast<const float4*>(pmu + off));
           if (psig) ps4 = __ldcs(reinterpret_cast<const float4*>(psig + off));
         }
-        const KlElem e0 = kl_elem<kGrad>(m4[i].x, r4[i].x, pm4.x, ps4.x, qsig);
-        const KlElem e1 = kl_elem<kGrad>(m4[i].y, r4[i].y, pm4.y, ps4.y, qsig);
-        const KlElem e2 = kl_elem<kGrad>(m4[i].z, r4[i].z, pm4.z, ps4.z, qsig);
-        const KlElem e3 = kl_elem<kGrad>(m4[i].w, r4[i].w, pm4.w, ps4.w, qsig);
+        const bool tp = kTensorPrior && psig != nullptr;
+        const KlElem e0 = kl_elem<kGrad>(m4[i].x, r4[i].x, pm4.x, tp ? kl_prior(ps4.x) : prior_c, qsig);
+        const KlElem e1 = kl_elem<kGrad>(m4[i].y, r4[i].y, pm4.y, tp ? kl_prior(ps4.y) : prior_c, qsig);
+        const KlElem e2 = kl_elem<kGrad>(m4[i].z, r4[i].z, pm4.z, tp ? kl_prior(ps4.z) : prior_c, qsig);
+        const KlElem e3 = kl_elem<kGrad>(m4[i].w, r4[i].w, pm4.w, tp ? kl_prior(ps4.w) : prior_c, qsig);
         part += (e0.kl + e1.kl) + (e2.kl + e3.kl);
         if (kGrad) {
           if (dmu) __stcs(reinterpret_cast<float4*>(dmu + off), make_float4(e0.dmu * gs, e1.dmu * gs, e2.dmu * gs, e3.dmu * gs));
@@ -135,7 +151,7 @@ __global__ void __launch_bounds__(KL_THREADS) kl_normal_multi_kernel(const __gri
       for (int64_t i = base + tid; i < end; i += KL_THREADS) {
         const float pm = (kTensorPrior && pmu) ? pmu[i] : tab.prior_mu;
         const float ps = (kTensorPrior && psig) ? psig[i] : tab.prior_sigma;
-        const KlElem e = kl_elem<kGrad>(mu[i], rho[i], pm, ps, qsig);
+        const KlElem e = kl_elem<kGrad>(mu[i], rho[i], pm, (kTensorPrior && psig) ? kl_prior(ps) : prior_c, qsig);
         part += e.kl;
         if (kGrad) {
           if (dmu) dmu[i] = e.dmu * gs;

@@ -1,3 +1,4 @@
 mkdir -p gpurun_out
-BT_NCU_RANGE=1 timeout 900 ncu --profile-from-start off --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv python bench.py --steps 1 --warmup 3 --no-cpu-baseline > gpurun_out/ncu.log 2>&1
-python tools/summarize_launches.py gpurun_out/launches.csv 12 gpurun_out/tc2_traffic.json
+(timeout 300 python tools/linear_sweep.py 4096 1; timeout 300 python tools/linear_sweep.py 4096 8) > gpurun_out/linear_sweep.txt 2>&1
+tail -14 gpurun_out/linear_sweep.txt
+timeout 600 python -m pytest tests -x -q -m gpu 2>&1 | tail -2
