@@ -140,12 +140,24 @@ __device__ __forceinline__ float bt_normal1(uint64_t idx, const BtRngKey& key) {
   return (idx & 1) ? z.y : z.x;
 }
 
-// Rademacher sign of stream element idx: bit (idx % 128) of the 128-bit block idx / 128; 1 -> -1.
+// Rademacher sign of stream element idx: block idx / 128 -> four 32-bit words; element j = idx % 32 of
+// word (idx / 32) % 4 reads bit (j / 2) + 16 * (j % 2); 1 -> -1.  With this layout the sign bits of the
+// bf16 PAIR (2p, 2p+1) are bits p and p+16 of the word: (word << (15 - p)) & 0x80008000 is the XOR mask
+// that flips both halves of the packed pair (the tensor-core Flipout path flips activations that way).
+__device__ __forceinline__ int bt_sign_bitpos(uint32_t j) { return (int)((j >> 1) + ((j & 1u) << 4)); }
 __device__ __forceinline__ float bt_sign1(uint64_t idx, const BtRngKey& key) {
   const uint4 r = bt_philox(idx >> 7, key);
   const int w = (int)((idx >> 5) & 3);
   const uint32_t word = w == 0 ? r.x : (w == 1 ? r.y : (w == 2 ? r.z : r.w));
-  return ((word >> (idx & 31)) & 1u) ? -1.f : 1.f;
+  return ((word >> bt_sign_bitpos((uint32_t)idx & 31u)) & 1u) ? -1.f : 1.f;
+}
+// Position of element (b, c, d, h, w) of a logical [B, C, D, H, W] activation tensor in the sign
+// streams: CHANNELS-LAST order, whatever the tensor's memory layout -- the 64 channels of one pixel
+// that make a row of a tensor-core A tile are then 64 consecutive stream elements (two words of one
+// Philox block), and so are 32 consecutive output channels of one accumulator row.
+__device__ __forceinline__ uint64_t bt_sign_index(uint64_t b, int64_t C, int64_t c, int D, int d, int H, int h, int W,
+                                                  int w) {
+  return ((((b * (uint64_t)D + (uint64_t)d) * (uint64_t)H + (uint64_t)h) * (uint64_t)W + (uint64_t)w) * (uint64_t)C) + (uint64_t)c;
 }
 
 // --------------------------------------------------------------- dtypes ----

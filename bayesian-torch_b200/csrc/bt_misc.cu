@@ -26,7 +26,7 @@ __global__ void philox_sign_fill_kernel(float* __restrict__ out, int64_t n, BtRn
     const int q = (int)(w & 3);
     const uint32_t word = q == 0 ? r.x : (q == 1 ? r.y : (q == 2 ? r.z : r.w));
     const int64_t i0 = w << 5;
-    for (int j = 0; j < 32 && i0 + j < n; ++j) out[i0 + j] = ((word >> j) & 1u) ? -1.f : 1.f;
+    for (int j = 0; j < 32 && i0 + j < n; ++j) out[i0 + j] = ((word >> bt_sign_bitpos((uint32_t)j)) & 1u) ? -1.f : 1.f;
   }
 }
 

@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(NT) simt_dgrad_kernel(const SGeo g, const SPar
               if (p.sign_out) {
                 sg = p.sign_out[off];
               } else {
-                const uint64_t li = ((((uint64_t)ab * Cout + ng) * g.OD + od) * g.OH + oh) * g.OW + ow;
+                const uint64_t li = bt_sign_index((uint64_t)ab, Cout, ng, g.OD, od, g.OH, oh, g.OW, ow);
                 sg = bt_sign1(li, key_so);
               }
               v2 = v * sg;
@@ -170,7 +170,7 @@ __global__ void __launch_bounds__(NT) simt_dgrad_kernel(const SGeo g, const SPar
         if (p.sign_in) {
           sg = p.sign_in[off];
         } else {
-          const uint64_t li = ((((uint64_t)b * Cin + cg) * g.ID + id) * g.IH + ih) * g.IW + iw;
+          const uint64_t li = bt_sign_index((uint64_t)b, Cin, cg, g.ID, id, g.IH, ih, g.IW, iw);
           sg = bt_sign1(li, key_si);
         }
         v += acc[NA - 1][i][j] * sg;

@@ -93,7 +93,7 @@ __global__ void __launch_bounds__(NT) simt_fwd_kernel(const SGeo g, const SParam
               sg = p.sign_in[off];
             } else {
               const int64_t cg = (int64_t)grp * g.Cg + a_c;
-              const uint64_t li = ((((uint64_t)ab * (g.Cg * g.groups) + cg) * g.ID + id) * g.IH + ih) * g.IW + iw;
+              const uint64_t li = bt_sign_index((uint64_t)ab, (int64_t)g.Cg * g.groups, cg, g.ID, id, g.IH, ih, g.IW, iw);
               sg = bt_sign1(li, key_si);
             }
             v2 = v * sg;
@@ -202,7 +202,7 @@ __global__ void __launch_bounds__(NT) simt_fwd_kernel(const SGeo g, const SParam
         if (p.sign_out) {
           sg = p.sign_out[off];
         } else {
-          const uint64_t li = ((((uint64_t)b * ((int64_t)g.Ng * g.groups) + ngl[j]) * g.OD + od) * g.OH + oh) * g.OW + ow;
+          const uint64_t li = bt_sign_index((uint64_t)b, (int64_t)g.Ng * g.groups, ngl[j], g.OD, od, g.OH, oh, g.OW, ow);
           sg = bt_sign1(li, key_so);
         }
         v += (acc[NA - 1][i][j] + b_pert[j]) * sg;

@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(NT) simt_wgrad_kernel(const SGeo g, const SPar
           yv[0][i] = v;
           if (kFlip) {
             const float sg = p.sign_out ? p.sign_out[off]
-                                        : bt_sign1(((((uint64_t)b * Cout + ng) * g.OD + od) * g.OH + oh) * g.OW + ow, key_so);
+                                        : bt_sign1(bt_sign_index((uint64_t)b, Cout, ng, g.OD, od, g.OH, oh, g.OW, ow), key_so);
             yv[NA - 1][i] = v * sg;
           }
         }
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(NT) simt_wgrad_kernel(const SGeo g, const SPar
           xv[0][i] = v;
           if (kFlip) {
             const float sg = p.sign_in ? p.sign_in[off]
-                                       : bt_sign1(((((uint64_t)b * Cin + cg) * g.ID + id) * g.IH + ih) * g.IW + iw, key_si);
+                                       : bt_sign1(bt_sign_index((uint64_t)b, Cin, cg, g.ID, id, g.IH, ih, g.IW, iw), key_si);
             xv[NA - 1][i] = v * sg;
           }
         }
@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(256) bias_grad_kernel(const SGeo g, const SPar
     s1 += v;
     if (kFlip) {
       const float sg = p.sign_out ? p.sign_out[off]
-                                  : bt_sign1(((((uint64_t)b * Cout + n) * g.OD + od) * g.OH + oh) * g.OW + ow, key_so);
+                                  : bt_sign1(bt_sign_index((uint64_t)b, Cout, n, g.OD, od, g.OH, oh, g.OW, ow), key_so);
       s2 += v * sg;
     }
   }

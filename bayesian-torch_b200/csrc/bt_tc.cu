@@ -46,7 +46,8 @@ constexpr int ONES_BYTES = BM * 32;       // [128 x 16] bf16 tile of the rank-1 
 constexpr int SHIFT_BYTES = 128 * 32;     // [BN x 16] bf16: per-channel shift split into three bf16 terms
 constexpr int CTRL_BYTES = BAR_BYTES + ONES_BYTES + SHIFT_BYTES;
 constexpr int STAGE_UNIT = 4 * 4096;  // one staging (or residual) buffer of 32 rows x 128 B for each of the 4 epilogue warps
-constexpr int N_PROD_WARPS = 16;
+constexpr int N_PROD_WARPS = 16;  // warps 0..15: W producers; the Flipout instantiation turns warps 12..15 into A flippers
+constexpr int N_FLIP_WARPS = 4;
 constexpr int N_MMA_WARPS = 2;  // issuer warps: tile t of an m-group belongs to issuer t % 2
 // warp groups (setmaxnreg works on aligned groups of 4 warps): 0..3 = W producers, 4 = epilogue,
 // 5 = TMA + 2 MMA issuers + one idle warp
@@ -91,10 +92,16 @@ struct Tc2Args {
                      // 8 skip A loads, 16 skip the normal draws, 32 skip the parameter loads
   uint64_t seed;
   uint32_t sample_id, layer_id;
+  // Flipout (FLIP instantiation): tensor-fed signs (deterministic mode; fp32 +-1 laid out like x / out) or null
+  // for Philox bits, and the geometry the A flippers need to find the sign-stream position of a tile row
+  const float *sign_in, *sign_out;
+  int IH, IW, Cin;                 // dense logical input image (conv) / features (linear)
+  int64_t x_bs, x_hs, x_ws, x_pitch;  // strides of x in elements (tensor-fed sign_in shares them)
 };
 
 struct Ctrl {
   uint64_t a_full[MAX_NA], a_empty[MAX_NA];
+  uint64_t af_full[MAX_NA];  // Flipout: the sign-flipped copy of the A slot is in place
   uint64_t w_full[MAX_RW + 1], w_empty[MAX_RW + 1];  // slot RW: the shift tile
   uint64_t acc_full[MAX_SETS], acc_empty[MAX_SETS];
   uint64_t res_full[4], res_empty[4];  // residual ring: one 128-row x 128-byte tile per slot, a 32-row slab per epilogue warp
@@ -310,7 +317,7 @@ __device__ unsigned long long g_tc_prof[160 * PROF_ROLES * PROF_SLOTS];
     }                                                           \
   } while (0)
 
-template <int BN, typename TO, bool PROF, int CL>
+template <int BN, typename TO, bool PROF, int CL, bool FLIP>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_out,
                const __grid_constant__ CUtensorMap tm_res, const __grid_constant__ Tc2Args a) {
@@ -318,13 +325,21 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   Ctrl* ctrl = reinterpret_cast<Ctrl*>(smem_raw + (base - raw));
-  constexpr int W_SLOT = BN * BK * 2;
+  // Flipout: every k-block carries TWO weight sub-tiles (mu, then sigma*eps), every A slot a second,
+  // sign-flipped copy of the tile, and every output tile two accumulators (mean path, perturbation path)
+  constexpr int NSUBW = FLIP ? 2 : 1;
+  constexpr int W_SUB = BN * BK * 2;
+  constexpr int W_SLOT = NSUBW * W_SUB;
+  constexpr int A_SLOT_T = NSUBW * A_SLOT;
+  constexpr int ACC_COLS = NSUBW * BN;
+  constexpr int NPW = FLIP ? N_PROD_WARPS - N_FLIP_WARPS : N_PROD_WARPS;  // producer warps
+  constexpr int PT = NPW * 32;
   constexpr int SUBN = 128 / (int)sizeof(TO);  // output columns per 128-byte staging row
   const uint32_t ones_base = base + BAR_BYTES, shift_base = ones_base + ONES_BYTES;
-  const uint32_t stage_base = base + CTRL_BYTES;
+  const uint32_t stage_base = base + CTRL_BYTES + (FLIP ? SHIFT_BYTES : 0);  // Flipout: a second shift tile (perturbation bias)
   const uint32_t res_base = stage_base + (uint32_t)a.stage_bufs * STAGE_UNIT;
   const uint32_t a_base = res_base + (uint32_t)a.res_bufs * STAGE_UNIT;
-  const uint32_t w_base = a_base + a.NA * A_SLOT;
+  const uint32_t w_base = a_base + a.NA * A_SLOT_T;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   unsigned long long pc[PROF_SLOTS] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -338,9 +353,12 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   };
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < a.NA; ++i) { mbar_init(smem_u32(&ctrl->a_full[i]), 1); mbar_init(smem_u32(&ctrl->a_empty[i]), 1); }
-    for (int i = 0; i < a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), N_PROD_WARPS); mbar_init(smem_u32(&ctrl->w_empty[i]), N_MMA_WARPS * CL); }
-    mbar_init(smem_u32(&ctrl->w_full[a.RW]), N_PROD_WARPS);  // the shift tile stays CTA-local
+    for (int i = 0; i < a.NA; ++i) {
+      mbar_init(smem_u32(&ctrl->a_full[i]), 1); mbar_init(smem_u32(&ctrl->a_empty[i]), 1);
+      mbar_init(smem_u32(&ctrl->af_full[i]), N_FLIP_WARPS);
+    }
+    for (int i = 0; i < a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), NPW); mbar_init(smem_u32(&ctrl->w_empty[i]), N_MMA_WARPS * CL); }
+    mbar_init(smem_u32(&ctrl->w_full[a.RW]), NPW);  // the shift tile stays CTA-local
     mbar_init(smem_u32(&ctrl->w_empty[a.RW]), N_MMA_WARPS);
     for (int i = 0; i < a.NSETS; ++i) { mbar_init(smem_u32(&ctrl->acc_full[i]), N_MMA_WARPS); mbar_init(smem_u32(&ctrl->acc_empty[i]), 128); }
     for (int i = 0; i < 4; ++i) { mbar_init(smem_u32(&ctrl->res_full[i]), 1); mbar_init(smem_u32(&ctrl->res_empty[i]), 4); }
@@ -439,11 +457,11 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           }
           continue;
         }
-        const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)((set * a.MT + t) * BN);
+        const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)((set * a.MT + t) * ACC_COLS);
         // TMEM reads are software-pipelined in 32-column units: the load of unit u+1 is in
         // flight while unit u is converted and staged.
         uint32_t va[32], vb[32];
-        tmem_ld32(tacc, va);
+        if constexpr (!FLIP) tmem_ld32(tacc, va);
 #pragma unroll 1
         for (int sub = 0; sub < nsub; ++sub) {
           // the TMA store that last read this staging buffer must have drained it
@@ -462,7 +480,45 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           const uint32_t resaddr = my_res + (uint32_t)rslot * (uint32_t)STAGE_UNIT + (uint32_t)lane * 128u;
           if constexpr (RES) PW(1, mbar_wait(smem_u32(&ctrl->res_full[rslot]), rphase));
           const int c0 = sub * SUBN;
-          if constexpr (UPS == 2) {
+          if constexpr (FLIP) {
+            // out = mean + pert * s_out: the two accumulators of the tile are joined here; s_out is
+            // one word of the SIGN_OUT stream per row and 32-column unit (position m * N + n,
+            // N % 32 == 0), or the caller's +-1 tensor (deterministic mode)
+            const int mrow = m0 + lane;
+#pragma unroll
+            for (int u = 0; u < UPS; ++u) {
+              const int c = c0 + 32 * u;
+              tmem_ld32(tacc + c, va);
+              tmem_ld32(tacc + BN + c, vb);
+              uint32_t word = 0;
+              const int n0 = nb * BN + c;
+              if (a.sign_out) {
+                if (mrow < a.Ms && n0 + 32 <= a.N) {
+                  const float4* sp = reinterpret_cast<const float4*>(a.sign_out + ((int64_t)s * a.Ms + mrow) * a.N + n0);
+#pragma unroll
+                  for (int j4 = 0; j4 < 8; ++j4) {
+                    const float4 f = __ldg(sp + j4);
+                    word |= (__float_as_uint(f.x) >> 31) << bt_sign_bitpos(4 * j4 + 0);
+                    word |= (__float_as_uint(f.y) >> 31) << bt_sign_bitpos(4 * j4 + 1);
+                    word |= (__float_as_uint(f.z) >> 31) << bt_sign_bitpos(4 * j4 + 2);
+                    word |= (__float_as_uint(f.w) >> 31) << bt_sign_bitpos(4 * j4 + 3);
+                  }
+                }
+              } else {
+                const uint64_t idx = (uint64_t)mrow * (uint64_t)a.N + (uint64_t)n0;
+                const uint4 r = bt_philox(idx >> 7, bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_SIGN_OUT));
+                const int wq = (int)((idx >> 5) & 3);
+                word = wq == 0 ? r.x : (wq == 1 ? r.y : (wq == 2 ? r.z : r.w));
+              }
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                const int bp = (j >> 1) + ((j & 1) << 4);
+                va[j] = __float_as_uint(__uint_as_float(va[j]) + __uint_as_float(vb[j] ^ ((word << (31 - bp)) & 0x80000000u)));
+              }
+              emit(va, rowaddr, resaddr, u * CPU);
+            }
+          } else if constexpr (UPS == 2) {
             PW(2, tmem_ld_wait());
             tmem_ld32(tacc + c0 + 32, vb);
             PW(4, emit(va, rowaddr, resaddr, 0));
@@ -554,9 +610,9 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               } else {
                 mbar_expect_tx(bar, A_SLOT);
                 if (a.conv)
-                  tma_load_im2col_4d(a_base + slot * A_SLOT, &tm_a, bar, c0, cw[t], chh[t], cn[t], (uint16_t)offw, (uint16_t)offh);
+                  tma_load_im2col_4d(a_base + slot * A_SLOT_T, &tm_a, bar, c0, cw[t], chh[t], cn[t], (uint16_t)offw, (uint16_t)offh);
                 else
-                  tma_load_2d(a_base + slot * A_SLOT, &tm_a, bar, c0, cn[t]);
+                  tma_load_2d(a_base + slot * A_SLOT_T, &tm_a, bar, c0, cn[t]);
               }
             }
             if (a.NR == 2) { if (++rslot[r] == a.NAr) { rslot[r] = 0; rphase[r] ^= 1u; } }
@@ -583,6 +639,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     uint32_t set_phase = 0, aphase = 0, wphase = 0, sphase = 0;
     const uint32_t acc0 = a.has_shift ? 1u : 0u;  // accumulators start from the shift, not from zero
     const uint64_t ones_desc = umma_desc_sw32(ones_base), shift_desc = umma_desc_sw32(shift_base);
+    const uint64_t shift2_desc = umma_desc_sw32(shift_base + SHIFT_BYTES);  // Flipout: perturbation bias
     bool first = true;  // first item of a (sample, n-block) key on this CTA: its W panel is new
     const int ring0 = (a.NR == 2 ? j : 0) * a.NAr;  // first slot of the A ring this issuer consumes
     for (int it = 0; it < n_items; ++it) {
@@ -592,7 +649,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         PW(0, mbar_wait(smem_u32(&ctrl->acc_empty[set]), set_phase ^ 1u));
         tc_fence_after();
       }
-      const uint32_t dbase = tmem + (uint32_t)(set * a.MT * BN);
+      const uint32_t dbase = tmem + (uint32_t)(set * a.MT * ACC_COLS);
       if (a.has_shift) {
         // D = ones[128 x 16] * shift[BN x 16]^T: every row of the accumulator starts as the
         // per-channel shift (bias * scale + BatchNorm shift, split into three bf16 terms)
@@ -603,8 +660,10 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         if (leader && !(PROF && (a.debug & 4))) {
 #pragma unroll
           for (int t = 0; t < MAX_MT; ++t)
-            if (t < mtv && (a.NR == 2 ? (t % N_MMA_WARPS) : 0) == j)
-              umma_bf16(dbase + (uint32_t)(t * BN), ones_desc, shift_desc, idesc, 0u);
+            if (t < mtv && (a.NR == 2 ? (t % N_MMA_WARPS) : 0) == j) {
+              umma_bf16(dbase + (uint32_t)(t * ACC_COLS), ones_desc, shift_desc, idesc, 0u);
+              if constexpr (FLIP) umma_bf16(dbase + (uint32_t)(t * ACC_COLS + BN), ones_desc, shift2_desc, idesc, 0u);
+            }
         }
         if (last && leader) umma_commit(smem_u32(&ctrl->w_empty[a.RW]));
         __syncwarp();
@@ -624,14 +683,22 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             if ((a.NR == 2 ? (t % N_MMA_WARPS) : 0) == j) {
               const int slot = ring0 + aslot;
               PW(2, mbar_wait(smem_u32(&ctrl->a_full[slot]), aphase));
+              if constexpr (FLIP) mbar_wait(smem_u32(&ctrl->af_full[slot]), aphase);  // the flipped copy is in place too
               tc_fence_after();
               if (leader) {
-                const uint64_t adesc = umma_desc_sw128(a_base + slot * A_SLOT);
-                const uint32_t d = dbase + (uint32_t)(t * BN);
+                const uint64_t adesc = umma_desc_sw128(a_base + slot * A_SLOT_T);
+                const uint32_t d = dbase + (uint32_t)(t * ACC_COLS);
                 if (!(PROF && (a.debug & 4))) {
 #pragma unroll
                   for (int k = 0; k < BK / 16; ++k)
                     umma_bf16(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : acc0);
+                  if constexpr (FLIP) {  // perturbation path: (x * s_in) tile against the sigma * eps sub-tile
+                    const uint64_t adesc2 = umma_desc_sw128(a_base + slot * A_SLOT_T + A_SLOT);
+                    const uint64_t bdesc2 = umma_desc_sw128(w_base + wslot * W_SLOT + W_SUB);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k)
+                      umma_bf16(d + (uint32_t)BN, adesc2 + (uint64_t)(2 * k), bdesc2 + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : acc0);
+                  }
                 }
                 umma_commit(smem_u32(&ctrl->a_empty[slot]));
               }
@@ -682,13 +749,112 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     }
     __syncwarp();
     }
+  } else if (FLIP && warp >= NPW) {
+    // =========================== A FLIPPERS (Flipout: x * s_in in shared memory) ===========================
+    // One thread per tile row: waits for the TMA of an A slot, XORs the sign bits of the 64 bf16 of its
+    // row with 64 bits of the SIGN_IN stream and writes the result to the slot's second half, the A
+    // operand of the perturbation MMAs.  The stream position of a row is the CHANNELS-LAST index of its
+    // first element, (pixel * C_in + c0): 64-aligned, so the row takes words (x, y) or (z, w) of ONE
+    // Philox block; the bits of the packed pair (2p, 2p+1) are bits p and p+16 of a word, so the mask of
+    // a pair is one shift and the flip rides on a 3-input logic op.
+    reg_dealloc<REGS_PROD>();
+    const int f = threadIdx.x - NPW * 32;  // tile row
+    int s = s0, nb = nb0, mg = mg0;
+    int rslot[N_MMA_WARPS] = {0, 0};
+    uint32_t rphase[N_MMA_WARPS] = {0, 0};
+    const uint32_t row_off = (uint32_t)f * 128u, row_sw = (uint32_t)(f & 7);
+    for (int it = 0; it < n_items; ++it) {
+      const int mtv = tiles_of(mg);
+      const BtRngKey key = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_SIGN_IN);
+      int fb[MAX_MT], fh[MAX_MT], fw[MAX_MT], fm[MAX_MT];
+#pragma unroll
+      for (int t = 0; t < MAX_MT; ++t) {
+        const int m = (tile0(mg) + t) * BM + f;  // row within the sample
+        fm[t] = m; fb[t] = 0; fh[t] = 0; fw[t] = 0;
+        if (a.conv) {
+          const int r = m / a.OW;
+          fb[t] = r / a.OH;
+          fw[t] = (m - r * a.OW) * a.sw - a.pw;
+          fh[t] = (r - fb[t] * a.OH) * a.sh - a.ph;
+        }
+      }
+      int c0 = 0, offw = 0, offh = 0, kw = 0;
+      for (int kb = 0; kb < a.nkb; ++kb) {
+#pragma unroll
+        for (int t = 0; t < MAX_MT; ++t) {
+          if (t < mtv) {
+            const int r = t % N_MMA_WARPS;
+            const int ring = a.NR == 2 ? r : 0;
+            const int slot = ring * a.NAr + (a.NR == 2 ? rslot[r] : rslot[0]);
+            uint32_t w0 = 0, w1 = 0;
+            const int ih = fh[t] + offh, iw = fw[t] + offw;
+            const bool inb = fm[t] < a.Ms && (!a.conv || ((unsigned)ih < (unsigned)a.IH && (unsigned)iw < (unsigned)a.IW));
+            if (a.sign_in) {  // deterministic mode: the caller's +-1 tensor, laid out like x
+              if (inb) {
+                const int64_t off = a.conv ? (int64_t)fb[t] * a.x_bs + (int64_t)ih * a.x_hs + (int64_t)iw * a.x_ws + c0
+                                           : (int64_t)fm[t] * a.x_pitch + c0;
+                const float4* sp = reinterpret_cast<const float4*>(a.sign_in + off);
+#pragma unroll
+                for (int j4 = 0; j4 < 16; ++j4) {
+                  const float4 v = __ldg(sp + j4);
+                  const int j = (4 * j4) & 31;
+                  const uint32_t bits = ((__float_as_uint(v.x) >> 31) << bt_sign_bitpos(j)) | ((__float_as_uint(v.y) >> 31) << bt_sign_bitpos(j + 1)) |
+                                        ((__float_as_uint(v.z) >> 31) << bt_sign_bitpos(j + 2)) | ((__float_as_uint(v.w) >> 31) << bt_sign_bitpos(j + 3));
+                  if (j4 < 8) w0 |= bits; else w1 |= bits;
+                }
+              }
+            } else if (inb) {  // zero-filled (padding) and out-of-range rows need no signs
+              const uint64_t pix = a.conv ? ((uint64_t)fb[t] * (uint64_t)a.IH + (uint64_t)ih) * (uint64_t)a.IW + (uint64_t)iw : (uint64_t)fm[t];
+              const uint64_t idx = pix * (uint64_t)a.Cin + (uint64_t)c0;
+              const uint4 rr = bt_philox(idx >> 7, key);
+              const bool hi = ((idx >> 6) & 1) != 0;
+              w0 = hi ? rr.z : rr.x;
+              w1 = hi ? rr.w : rr.y;
+            }
+            mbar_wait(smem_u32(&ctrl->a_full[slot]), (a.NR == 2 ? rphase[r] : rphase[0]));
+            const uint32_t src = a_base + (uint32_t)slot * (uint32_t)A_SLOT_T + row_off;
+            uint32_t d[8][4];
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(d[c][0]), "=r"(d[c][1]), "=r"(d[c][2]), "=r"(d[c][3])
+                           : "r"(src + (((uint32_t)c ^ row_sw) << 4)));
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              const uint32_t wsel = c < 4 ? w0 : w1;
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const int pp = (4 * c + i) & 15;  // pair within the word
+                d[c][i] ^= (wsel << (15 - pp)) & 0x80008000u;
+              }
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(src + (uint32_t)A_SLOT + (((uint32_t)c ^ row_sw) << 4)),
+                           "r"(d[c][0]), "r"(d[c][1]), "r"(d[c][2]), "r"(d[c][3])
+                           : "memory");
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&ctrl->af_full[slot]));
+            if (a.NR == 2) { if (++rslot[r] == a.NAr) { rslot[r] = 0; rphase[r] ^= 1u; } }
+            else if (++rslot[0] == a.NAr) { rslot[0] = 0; rphase[0] ^= 1u; }
+          }
+        }
+        c0 += BK;
+        if (a.conv && c0 == a.Cin) {  // next filter tap
+          c0 = 0;
+          offw += a.dw;
+          if (++kw == a.KW) { kw = 0; offw = 0; offh += a.dh; }
+        }
+      }
+      walk(s, nb, mg);
+    }
   } else {
     // =========================== W PRODUCERS (sample in smem) ===========================
     reg_dealloc<REGS_PROD>();
     const int p = threadIdx.x - WARP_PROD0 * 32;
     const int chunk = p & 7;      // 16-byte chunk (8 consecutive k) of the 128-byte row
     const int row_base = p >> 3;  // rows row_base + 64*i of this CTA's share of the k-block
-    constexpr int ROWS_PER_THREAD = BN / (PROD_THREADS / 8);
+    constexpr int RPP = PT / 8;                              // rows of a k-block covered by one pass of the producers
+    constexpr int ROWS_PER_THREAD = (BN + RPP - 1) / RPP;
     constexpr int rows_cta = BN / CL;        // CL = 2: each CTA of the pair samples half of the rows of a k-block
     const int row_first = crank * rows_cta;
     const uint32_t peer_w_base = CL > 1 ? mapa_shared(w_base, (uint32_t)(crank ^ 1)) : 0u;
@@ -706,17 +872,21 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       if (first || !a.stationary) {
         if (a.has_shift) {
           PW(0, mbar_wait(smem_u32(&ctrl->w_empty[a.RW]), sphase ^ 1u));
-          if (p < BN) {
-            const int n = nb * BN + p;
+          if (p < NSUBW * BN) {
+            // Flipout: threads [BN, 2 BN) fill the second tile, the bias perturbation sigma_b * eps_b of the
+            // perturbation accumulator (inside the s_out product, linear_flipout.py:162,172-173)
+            const bool pert = FLIP && p >= BN;
+            const int n = nb * BN + (pert ? p - BN : p);
             float sh = 0.f;
             if (n < a.N) {
               if (a.mu_b) {
                 const float e = a.eps_b ? a.eps_b[n]
                                         : bt_normal1((uint64_t)n, bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_B));
-                sh = a.mu_b[n] + bt_softplus(a.rho_b[n]) * e;
+                const float db = bt_softplus(a.rho_b[n]) * e;
+                sh = FLIP ? (pert ? db : a.mu_b[n]) : a.mu_b[n] + db;
               }
               if (a.out_scale) sh *= a.out_scale[n];
-              if (a.out_shift) sh += a.out_shift[n];
+              if (a.out_shift && !pert) sh += a.out_shift[n];
             }
             // three bf16 terms carry 24 bits of the fp32 shift through the bf16 MMA
             const __nv_bfloat16 h0 = __float2bfloat16_rn(sh);
@@ -725,8 +895,11 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             const __nv_bfloat16 h2 = __float2bfloat16_rn(r1 - __bfloat162float(h1));
             const uint32_t w0 = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
             const uint32_t w1 = (uint32_t)__bfloat16_as_ushort(h2);
-            const uint32_t dst = shift_base + (uint32_t)p * 32u;
-            const uint32_t sw = (uint32_t)((p >> 2) & 1) << 4;
+            // (tile rows are 32 bytes and BN = 64 / 128 rows keep the 8-row swizzle phase, so the second tile,
+            // SHIFT_BYTES further on, is addressed by its own row index)
+            const int prow = pert ? p - BN : p;
+            const uint32_t dst = shift_base + (pert ? (uint32_t)SHIFT_BYTES : 0u) + (uint32_t)prow * 32u;
+            const uint32_t sw = (uint32_t)((prow >> 2) & 1) << 4;
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + sw), "r"(w0), "r"(w1), "r"(0u), "r"(0u) : "memory");
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (sw ^ 16u)), "r"(0u), "r"(0u), "r"(0u), "r"(0u) : "memory");
           }
@@ -742,7 +915,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           const int k2 = kb2 * BK + chunk * 8;
 #pragma unroll
           for (int i = 0; i < ROWS_PER_THREAD; ++i) {
-            const int lrow = row_base + (PROD_THREADS / 8) * i;
+            const int lrow = row_base + RPP * i;
             const int n = nb * BN + row_first + lrow;
             nmu8[i] = nsg8[i] = make_uint4(0u, 0u, 0u, 0u);
             if (lrow < rows_cta && k2 < a.K && n < a.N && !(PROF && (a.debug & 32))) {
@@ -768,7 +941,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           const long long gen_t0 = PROF ? clock64() : 0;
 #pragma unroll
           for (int i = 0; i < ROWS_PER_THREAD; ++i) {
-            const int lrow = row_base + (PROD_THREADS / 8) * i;
+            const int lrow = row_base + RPP * i;
             if (lrow >= rows_cta) break;
             const int row = row_first + lrow;
             const int n = nb * BN + row;
@@ -798,25 +971,44 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               }
             }
             // w = bf16(sigma * eps + mu) on packed pairs: fp32 fused multiply-add of the bf16 operands, one rounding
-            const uint32_t w0 = fma_bf16x2(sg8[i].x, pack_bf16(z[0], z[1]), mu8[i].x);
-            const uint32_t w1 = fma_bf16x2(sg8[i].y, pack_bf16(z[2], z[3]), mu8[i].y);
-            const uint32_t w2 = fma_bf16x2(sg8[i].z, pack_bf16(z[4], z[5]), mu8[i].z);
-            const uint32_t w3 = fma_bf16x2(sg8[i].w, pack_bf16(z[6], z[7]), mu8[i].w);
+            // Flipout keeps the two terms apart: the mu sub-tile as packed, then bf16(sigma * eps)
+            const uint32_t w0 = fma_bf16x2(sg8[i].x, pack_bf16(z[0], z[1]), FLIP ? 0u : mu8[i].x);
+            const uint32_t w1 = fma_bf16x2(sg8[i].y, pack_bf16(z[2], z[3]), FLIP ? 0u : mu8[i].y);
+            const uint32_t w2 = fma_bf16x2(sg8[i].z, pack_bf16(z[4], z[5]), FLIP ? 0u : mu8[i].z);
+            const uint32_t w3 = fma_bf16x2(sg8[i].w, pack_bf16(z[6], z[7]), FLIP ? 0u : mu8[i].w);
             const uint32_t off = (uint32_t)(slot * W_SLOT) + (uint32_t)row * 128u + (((uint32_t)chunk ^ (uint32_t)(row & 7)) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(w_base + off), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+            if constexpr (FLIP) {
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(w_base + off), "r"(mu8[i].x), "r"(mu8[i].y), "r"(mu8[i].z), "r"(mu8[i].w) : "memory");
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(w_base + off + (uint32_t)W_SUB), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+            } else {
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(w_base + off), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
+            }
           }
           fence_proxy_async();
           __syncwarp();
           if (lane == 0) {
             const uint32_t bar = smem_u32(&ctrl->w_full[slot]);
-            if (CL > 1 && row_base < rows_cta) {
-              // This warp's four rows (512 contiguous bytes) travel to the same place in the peer's ring
-              // as an asynchronous bulk copy that completes (complete_tx) on the PEER's w_full barrier;
-              // symmetrically this warp's own arrival expects the 512 bytes its counterpart warp in the
-              // peer sends here.  No remote arrive, no remote store, nothing waits on the DSMEM round trip.
-              const uint32_t off = (uint32_t)(slot * W_SLOT) + (uint32_t)(row_first + (row_base & ~3)) * 128u;
-              mbar_expect_tx(bar, 512u);
-              bulk_copy_to_cluster(peer_w_base + off, w_base + off, 512u, peer_w_full + (uint32_t)slot * 8u);
+            // This warp's four rows of a pass (512 contiguous bytes per sub-tile) travel to the same place in
+            // the peer's ring as asynchronous bulk copies that complete (complete_tx) on the PEER's w_full
+            // barrier; symmetrically this warp's own arrival expects the bytes its counterpart warp in the
+            // peer sends here.  No remote arrive, no remote store, nothing waits on the DSMEM round trip.
+            int npieces = 0;  // lane 0: row_base is the first of the warp's four rows
+            if constexpr (CL > 1) {
+#pragma unroll
+              for (int i = 0; i < ROWS_PER_THREAD; ++i) npieces += (row_base + RPP * i < rows_cta) ? 1 : 0;
+            }
+            if (npieces > 0) {
+              mbar_expect_tx(bar, 512u * (uint32_t)(npieces * NSUBW));
+#pragma unroll
+              for (int i = 0; i < ROWS_PER_THREAD; ++i) {
+                if (row_base + RPP * i < rows_cta) {
+#pragma unroll
+                  for (int sub = 0; sub < NSUBW; ++sub) {
+                    const uint32_t off = (uint32_t)(slot * W_SLOT + sub * W_SUB) + (uint32_t)(row_first + row_base + RPP * i) * 128u;
+                    bulk_copy_to_cluster(peer_w_base + off, w_base + off, 512u, peer_w_full + (uint32_t)slot * 8u);
+                  }
+                }
+              }
             } else {
               mbar_arrive(bar);
             }
@@ -830,7 +1022,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       if (walk(s, nb, mg)) first = true;
     }
     if (warp == WARP_PROD0) prof_flush(4);
-    if (warp == WARP_PROD0 + N_PROD_WARPS - 1) prof_flush(5);
+    if (warp == WARP_PROD0 + NPW - 1) prof_flush(5);
   }
 
   tc_fence_before();
@@ -928,7 +1120,11 @@ static int64_t prod_out(const bt_geom* g) {
 static bool tc2_plan(const bt_geom* g, const bt_layer_params* p, bool flipout, Plan* pl, const char** why) {
 #define TC_NO(cond, msg) if (cond) { *why = msg; return false; }
   memset(pl, 0, sizeof(*pl));
-  TC_NO(flipout, "Flipout is not on the tensor-core path");
+  // Flipout: a tile row's 64 input channels / 32 output channels must be aligned runs of the sign streams
+  TC_NO(flipout && (g->c_in % 64 != 0 || g->c_out % 32 != 0), "Flipout needs c_in % 64 == 0 and c_out % 32 == 0");
+  TC_NO(flipout && g->n_samples > 1 && (p->sign_in || p->sign_out), "tensor-fed signs with n_samples > 1");
+  TC_NO(flipout && ((p->sign_in == nullptr) != (p->sign_out == nullptr)), "sign_in and sign_out must both be given or both be null");
+  TC_NO(flipout && g->rank > 2, "Flipout rank 3");
   TC_NO(g->groups != 1, "groups != 1");
   TC_NO(g->x_dtype != BT_BF16, "activations are not bf16");
   TC_NO(g->out_chan_stride != 1, "output channels are not the fastest axis (need channels-last)");
@@ -980,6 +1176,7 @@ static bool tc2_plan(const bt_geom* g, const bt_layer_params* p, bool flipout, P
     }
   }
   // anything else with a dense channels-last output: explicit patch matrix, then a GEMM
+  TC_NO(flipout, "Flipout needs the im2col / GEMM operand modes (channels-last x, 16-byte aligned strides)");
   TC_NO(taps > 4096, "kernel volume > 4096 taps");
   pl->mode = A_PATCH;
   pl->x_rows = pl->rows_per_s;
@@ -1008,10 +1205,10 @@ int64_t bt_tc_workspace_bytes(const bt_geom* g) {
   return bytes;
 }
 
-template <int BN, typename TO, bool PROF, int CL>
+template <int BN, typename TO, bool PROF, int CL, bool FLIP>
 static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const Tc2Args& a, int grid,
                           int smem_bytes, cudaStream_t stream) {
-  BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, PROF, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, PROF, CL, FLIP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3((unsigned)grid);
@@ -1025,21 +1222,24 @@ static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CU
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_fwd_kernel<BN, TO, PROF, CL>, ta, to, tr, a));
-  BT_LAUNCH_OK(PROF ? "tc2_fwd_kernel(prof)" : "tc2_fwd_kernel");
+  BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_fwd_kernel<BN, TO, PROF, CL, FLIP>, ta, to, tr, a));
+  BT_LAUNCH_OK(PROF ? "tc2_fwd_kernel(prof)" : (FLIP ? "tc2_fwd_kernel(flipout)" : "tc2_fwd_kernel"));
   return BT_OK;
 }
 
 template <int BN, typename TO>
 static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const Tc2Args& a, int grid, int smem_bytes,
-                      cudaStream_t stream) {
+                      bool flip, cudaStream_t stream) {
+  if (flip)
+    return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, true>(ta, to, tr, a, grid, smem_bytes, stream)
+                     : tc2_launch_one<BN, TO, false, 1, true>(ta, to, tr, a, grid, smem_bytes, stream);
   if constexpr (sizeof(TO) == 2) {
     if (env_int("BT_TC2_PROF", 0))
-      return a.CL == 2 ? tc2_launch_one<BN, TO, true, 2>(ta, to, tr, a, grid, smem_bytes, stream)
-                       : tc2_launch_one<BN, TO, true, 1>(ta, to, tr, a, grid, smem_bytes, stream);
+      return a.CL == 2 ? tc2_launch_one<BN, TO, true, 2, false>(ta, to, tr, a, grid, smem_bytes, stream)
+                       : tc2_launch_one<BN, TO, true, 1, false>(ta, to, tr, a, grid, smem_bytes, stream);
   }
-  return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2>(ta, to, tr, a, grid, smem_bytes, stream)
-                   : tc2_launch_one<BN, TO, false, 1>(ta, to, tr, a, grid, smem_bytes, stream);
+  return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, false>(ta, to, tr, a, grid, smem_bytes, stream)
+                   : tc2_launch_one<BN, TO, false, 1, false>(ta, to, tr, a, grid, smem_bytes, stream);
 }
 
 // Diagnostics: cycle counters of the last BT_TC2_PROF=1 launch, [cta][role][slot] (see bt_b200.h).
@@ -1070,6 +1270,10 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.out_scale = p->out_scale; a.out_shift = p->out_shift; a.out_relu = p->out_relu;
   a.seed = p->seed; a.sample_id = p->sample_id; a.layer_id = p->layer_id;
   a.debug = env_int("BT_TC2_DEBUG", 0);
+  a.sign_in = flipout ? p->sign_in : nullptr;
+  a.sign_out = flipout ? p->sign_out : nullptr;
+  a.Cin = (int)g->c_in;
+  a.x_pitch = pl.pitch;
   a.Ms = (int)pl.rows_per_s;
   a.Kt = pl.K;
   a.K = pl.mode == A_PATCH ? pl.Kp : pl.K;
@@ -1140,6 +1344,8 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
     a.CB = (int)g->c_in / BK;
     a.OH = (int)d.out[0]; a.OW = (int)d.out[1]; a.KW = (int)d.k[1];
     a.sh = (int)d.st[0]; a.sw = (int)d.st[1]; a.ph = (int)d.pd[0]; a.pw = (int)d.pd[1]; a.dh = (int)d.dl[0]; a.dw = (int)d.dl[1];
+    a.IH = (int)d.in[0]; a.IW = (int)d.in[1];
+    a.x_bs = g->x_batch_stride; a.x_hs = pl.xh; a.x_ws = pl.xw;
     const cuuint64_t imgs = (cuuint64_t)g->batch * (x_shared ? 1 : S);
     const cuuint64_t gdim[4] = {(cuuint64_t)g->c_in, (cuuint64_t)d.in[1], (cuuint64_t)d.in[0], imgs};
     const cuuint64_t gstr[3] = {(cuuint64_t)pl.xw * 2, (cuuint64_t)pl.xh * 2, (cuuint64_t)g->x_batch_stride * 2};
@@ -1183,17 +1389,22 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   // shared-memory budget: staging (1, 2 or 4 buffers per epilogue warp) + residual ring (0, 2 or 4)
   // + A ring + W ring / panel
   const int res_min = p->residual ? 2 : 0;
-  auto ring_bytes = [&](int stage_bufs, int res_bufs) { return AVAIL_BYTES - (stage_bufs + res_bufs) * STAGE_UNIT; };
+  // Flipout doubles a W slot (mu and sigma*eps sub-tiles), an A slot (the tile and its sign-flipped copy)
+  // and the accumulator columns of a tile, and adds a second shift tile
+  const int NSUBW = flipout ? 2 : 1;
+  const int A_SLOT_T = NSUBW * A_SLOT;
+  const int avail = AVAIL_BYTES - (flipout ? SHIFT_BYTES : 0);
+  auto ring_bytes = [&](int stage_bufs, int res_bufs) { return avail - (stage_bufs + res_bufs) * STAGE_UNIT; };
   // a [BN x K] panel that fits next to a 4-deep A ring is generated once per (sample, n-block)
   // (single-buffered epilogue staging is accepted for that)
-  auto panel_fits = [&](int bn) { return a.nkb <= MAX_RW && (int64_t)a.nkb * bn * BK * 2 + 4 * A_SLOT <= ring_bytes(1, res_min); };
+  auto panel_fits = [&](int bn) { return a.nkb <= MAX_RW && (int64_t)a.nkb * NSUBW * bn * BK * 2 + 4 * A_SLOT_T <= ring_bytes(1, res_min); };
   const int force_bn = env_int("BT_TC2_BN", 0), force_mt = env_int("BT_TC2_MT", 0), force_stat = env_int("BT_TC2_STATIONARY", -1);
   // N > 64 whose [128 x K] panel does not fit streams at BN = 128 rather than keeping a BN = 64
   // panel: the narrow panel re-reads every A tile once per 64 output channels, and the A stream
   // (L2 -> shared memory, then shared memory -> tensor core) is the scarcer resource
   // (1024 -> 256 1x1 at 14x14: 0.34 ms stationary/64, 0.23 ms streaming/128).
   if (force_bn == 64 || force_bn == 128) BN = force_bn;
-  const int WB = BN * BK * 2;
+  const int WB = NSUBW * BN * BK * 2;
   a.NB = (a.N + BN - 1) / BN;
   a.stationary = panel_fits(BN) ? 1 : 0;
   // Wide layers with a short reduction (the 1x1 expansions, N >= 4 n-blocks) stream instead: with
@@ -1202,7 +1413,7 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   if (a.stationary && a.NB >= 4 && a.nkb >= 2 && a.num_mt >= 4) a.stationary = 0;
   if (force_stat == 0) a.stationary = 0;
   if (force_stat == 1 && panel_fits(BN)) a.stationary = 1;
-  const int NSLOTS = 512 / BN;
+  const int NSLOTS = 512 / (NSUBW * BN);
   if (a.stationary) {
     a.RW = a.nkb;
     a.MT = a.num_mt >= 2 ? 2 : 1;  // one tile per issuer warp
@@ -1216,8 +1427,9 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
     // short reductions: two accumulator sets of two tiles, so the epilogue of one item overlaps the MMAs of the next
     if (a.nkb <= 8 && a.MT > 2) a.MT = 2;
     if (force_mt >= 1 && force_mt <= MAX_MT && force_mt <= NSLOTS) a.MT = force_mt;
-    a.RW = (ring_bytes(2, res_min) - 4 * A_SLOT) / WB;
+    a.RW = (ring_bytes(2, res_min) - 4 * A_SLOT_T) / WB;
     if (a.RW > 4) a.RW = 4;  // deeper W rings measured no faster; the space goes to the A ring
+    if (flipout) a.RW = 2;   // 32 KB slots: two W k-blocks, the rest of shared memory goes to the A ring
     if (env_int("BT_TC2_RW", 0) >= 2 && env_int("BT_TC2_RW", 0) < a.RW) a.RW = env_int("BT_TC2_RW", 0);
   }
   a.NSETS = NSLOTS / a.MT;
@@ -1234,18 +1446,19 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   if (env_int("BT_TC2_NBINNER", -1) == 0) a.nb_inner = 0;
   a.stage_bufs = 2;
   a.res_bufs = res_min;
-  a.NA = (ring_bytes(2, res_min) - a.RW * WB) / A_SLOT;
-  if (a.NA < 4) { a.stage_bufs = 1; a.NA = (ring_bytes(1, res_min) - a.RW * WB) / A_SLOT; }
+  a.NA = (ring_bytes(2, res_min) - a.RW * WB) / A_SLOT_T;
+  if (a.NA < 4 || flipout) { a.stage_bufs = 1; a.NA = (ring_bytes(1, res_min) - a.RW * WB) / A_SLOT_T; }
   if (a.NA > MAX_NA) a.NA = MAX_NA;
   // leftover shared memory first deepens the residual prefetch (its tiles come from L2 / HBM, a
   // microsecond away), then the store staging; a stationary layer with a long A ring trades two
   // of its slots for the former
   {
-    int left = ring_bytes(a.stage_bufs, a.res_bufs) - a.RW * WB - a.NA * A_SLOT;
+    int left = ring_bytes(a.stage_bufs, a.res_bufs) - a.RW * WB - a.NA * A_SLOT_T;
     if (a.res_bufs == 2) {
       if (left >= 2 * STAGE_UNIT) { a.res_bufs = 4; left -= 2 * STAGE_UNIT; }
-      else if (a.stationary && a.NA >= 6) { a.res_bufs = 4; a.NA -= 2; left += 2 * A_SLOT - 2 * STAGE_UNIT; }
+      else if (a.stationary && a.NA >= 6) { a.res_bufs = 4; a.NA -= 2; left += 2 * A_SLOT_T - 2 * STAGE_UNIT; }
     }
+    if (a.stage_bufs == 1 && left >= STAGE_UNIT) { a.stage_bufs = 2; left -= STAGE_UNIT; }
     if (a.stage_bufs == 2 && left >= 2 * STAGE_UNIT) a.stage_bufs = 4;
   }
   if (env_int("BT_TC2_STAGE", 0) == 2 && a.stage_bufs == 4) a.stage_bufs = 2;
@@ -1257,16 +1470,16 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.total_items = (int64_t)a.S * a.NB * a.num_mg;
   const int ncl = sms / a.CL;
   const int grid = (int)(a.total_items < ncl ? a.total_items : ncl) * a.CL;
-  const int smem_bytes = 1024 + CTRL_BYTES + (a.stage_bufs + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT + a.RW * WB;
+  const int smem_bytes = 1024 + CTRL_BYTES + (flipout ? SHIFT_BYTES : 0) + (a.stage_bufs + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT_T + a.RW * WB;
   BT_REQUIRE(smem_bytes <= SMEM_LIMIT, BT_ERR_UNSUPPORTED, "tensor-core forward: shared memory plan %d exceeds %d", smem_bytes, SMEM_LIMIT);
   if (env_int("BT_TC2_LOG", 0))
-    fprintf(stderr, "tc2: mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d\n",
-            (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,
+    fprintf(stderr, "tc2: flip=%d mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d\n",
+            (int)flipout, (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,
             (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs, a.CL);
   const bool o32 = g->out_dtype == BT_F32;
   if (BN == 64)
-    return o32 ? tc2_launch<64, float>(tm_a, tm_out, tm_res, a, grid, smem_bytes, stream)
-               : tc2_launch<64, __nv_bfloat16>(tm_a, tm_out, tm_res, a, grid, smem_bytes, stream);
-  return o32 ? tc2_launch<128, float>(tm_a, tm_out, tm_res, a, grid, smem_bytes, stream)
-             : tc2_launch<128, __nv_bfloat16>(tm_a, tm_out, tm_res, a, grid, smem_bytes, stream);
+    return o32 ? tc2_launch<64, float>(tm_a, tm_out, tm_res, a, grid, smem_bytes, flipout, stream)
+               : tc2_launch<64, __nv_bfloat16>(tm_a, tm_out, tm_res, a, grid, smem_bytes, flipout, stream);
+  return o32 ? tc2_launch<128, float>(tm_a, tm_out, tm_res, a, grid, smem_bytes, flipout, stream)
+             : tc2_launch<128, __nv_bfloat16>(tm_a, tm_out, tm_res, a, grid, smem_bytes, flipout, stream);
 }

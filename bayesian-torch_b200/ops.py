@@ -536,6 +536,17 @@ def philox_sign(n: int, seed: int, sample_id: int, layer_id: int, kind: int, dev
     return out
 
 
+def philox_sign_like(t: torch.Tensor, seed: int, sample_id: int, layer_id: int, kind: int) -> torch.Tensor:
+    """+-1 tensor shaped like t ([B, C, *spatial]) holding the signs the kernels generate for each
+    element: the sign streams run over an activation tensor in CHANNELS-LAST order ((b, spatial...), c),
+    whatever its memory layout (csrc/bt_common.cuh: bt_sign_index)."""
+    flat = philox_sign(t.numel(), seed, sample_id, layer_id, kind, t.device)
+    if t.dim() <= 2:
+        return flat.view(t.shape)
+    shape = tuple(t.shape)
+    return flat.view((shape[0],) + shape[2:] + (shape[1],)).movedim(-1, 1)
+
+
 def philox_eps_weight(w_shape, seed: int, sample_id: int, layer_id: int, device="cuda") -> torch.Tensor:
     """eps tensor in the weight's logical layout [c_out, c_in/g, *k] holding the values the
     kernels use: the stream is indexed in packed (n, tap, channel) order (shared with the

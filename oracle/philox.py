@@ -11,7 +11,11 @@ predict it:
   normals : block = elem_idx // 8; word r_i -> (z_2i, z_2i+1) by Box-Muller with
             u0 = ((r_i >> 16) + 0.5) * 2^-16 (radius), u1 = ((r_i & 0xFFFF) + 0.5) * 2^-16 (angle):
             z_2i = sqrt(-2 ln u0) cos(2 pi (u1 - 1/2)), z_2i+1 = sqrt(-2 ln u0) sin(2 pi (u1 - 1/2))
-  signs   : block = elem_idx // 128; bit (elem_idx % 128) of r0|r1<<32|..., 1 -> -1
+  signs   : block = elem_idx // 128; word r_((elem_idx // 32) % 4); element j = elem_idx % 32 reads bit
+            (j // 2) + 16 * (j % 2) of that word, 1 -> -1 (the two halves of a packed bf16 pair sit 16 bits
+            apart, so one shift + mask flips both).  elem_idx of an activation element (b, c, spatial...)
+            is its CHANNELS-LAST position ((b, spatial...), c), whatever the tensor's memory layout
+            (sign_like() below).
   stream_id = layer_id << 4 | kind, kind: 0 eps_weight, 1 eps_bias, 2 sign_in, 3 sign_out
 """
 from __future__ import annotations
@@ -82,5 +86,18 @@ def sign(n: int, seed: int, sample_id: int, stream: int, start: int = 0) -> np.n
     words = np.stack(r, axis=1)  # [nblocks, 4]
     within = (idx % np.uint64(128)).astype(np.int64)
     w = words[inv, within // 32]
-    bit = (w >> (within % 32).astype(np.uint32)) & np.uint32(1)
+    j = within % 32
+    bit = (w >> ((j // 2) + 16 * (j % 2)).astype(np.uint32)) & np.uint32(1)
     return np.where(bit == 1, -1.0, 1.0).astype(np.float32)
+
+
+def sign_like(shape, seed: int, sample_id: int, stream: int) -> np.ndarray:
+    """+-1 tensor of logical shape [B, C, *spatial] holding the signs the kernels use for each element:
+    the stream runs over the tensor in channels-last order ((b, spatial...), c)."""
+    shape = tuple(int(v) for v in shape)
+    n = int(np.prod(shape))
+    flat = sign(n, seed, sample_id, stream)
+    if len(shape) <= 2:
+        return flat.reshape(shape)
+    cl = flat.reshape((shape[0],) + shape[2:] + (shape[1],))
+    return np.ascontiguousarray(np.moveaxis(cl, -1, 1))

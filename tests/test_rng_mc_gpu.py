@@ -89,8 +89,9 @@ def test_philox_mode_equals_deterministic_mode_on_exported_stream(kind, cuda_dev
     getattr(layer, "eps_" + layer._wname).copy_(ops.philox_eps_weight(w.shape, seed, 11, layer_id, cuda_device))
     layer.eps_bias.copy_(ops.philox_normal(w.shape[0], seed, 11, layer_id, _lib.KIND_EPS_B, cuda_device))
     if "fo" in kind:
-        layer.sign_input = ops.philox_sign(x.numel(), seed, 11, layer_id, _lib.KIND_SIGN_IN, cuda_device).view_as(x)
-        layer.sign_output = ops.philox_sign(out_p.numel(), seed, 11, layer_id, _lib.KIND_SIGN_OUT, cuda_device).view_as(out_p)
+        # the sign streams run over activations in channels-last order, whatever the memory layout
+        layer.sign_input = ops.philox_sign_like(x, seed, 11, layer_id, _lib.KIND_SIGN_IN)
+        layer.sign_output = ops.philox_sign_like(out_p, seed, 11, layer_id, _lib.KIND_SIGN_OUT)
     out_b, dx_b, g_b = run("buffer")
     torch.testing.assert_close(out_p, out_b, rtol=1e-5, atol=1e-5)
     torch.testing.assert_close(dx_p, dx_b, rtol=1e-4, atol=1e-4)
