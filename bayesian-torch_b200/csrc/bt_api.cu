@@ -49,7 +49,7 @@ extern "C" int64_t bt_workspace_bytes(const char* op, const bt_geom* g, int n_te
   if (!op) return 0;
   if (!strcmp(op, "kl")) return bt_kl_workspace_bytes_internal(n_tensors);
   if (!strcmp(op, "reparam_fwd") || !strcmp(op, "flipout_fwd"))
-    return KL_SCRATCH + (g ? bt_tc_workspace_bytes(g) : 0);
+    return KL_SCRATCH + (g ? bt_tc_workspace_bytes(g, !strcmp(op, "flipout_fwd")) : 0);
   if (!strcmp(op, "reparam_bwd") || !strcmp(op, "flipout_bwd")) return KL_SCRATCH;
   return 0;
 }

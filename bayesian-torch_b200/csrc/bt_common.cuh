@@ -198,4 +198,4 @@ bool bt_tc_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, c
 
 int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
                   bool flipout, cudaStream_t stream);
-int64_t bt_tc_workspace_bytes(const bt_geom* g);
+int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout);

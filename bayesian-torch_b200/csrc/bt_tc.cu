@@ -61,7 +61,6 @@ constexpr int NUM_THREADS = (N_PROD_WARPS + 8) * 32;  // 768
 // grow to 120. The pool setmaxnreg draws on is what the CTA was LAUNCHED with
 // (768 x 80 = 61440 registers), not the whole register file: 128*120 + 128*72 + 512*72 = 61440.
 constexpr int REGS_EPI = 120, REGS_CTRL = 72, REGS_PROD = 72;
-constexpr int PROD_THREADS = N_PROD_WARPS * 32;
 constexpr int MAX_NA = 8, MAX_RW = 24, MAX_SETS = 8, MAX_MT = 4;
 constexpr int SMEM_LIMIT = 232448;
 constexpr int AVAIL_BYTES = SMEM_LIMIT - 1024 - CTRL_BYTES;  // staging + residual ring + A ring + W ring / panel
@@ -96,6 +95,7 @@ struct Tc2Args {
   // for Philox bits, and the geometry the A flippers need to find the sign-stream position of a tile row
   const float *sign_in, *sign_out;
   int IH, IW, Cin;                 // dense logical input image (conv) / features (linear)
+  int a2_tma;                      // the sign-flipped A tiles come from a second tensor map (patch-matrix mode) instead of the flippers
   int64_t x_bs, x_hs, x_ws, x_pitch;  // strides of x in elements (tensor-fed sign_in shares them)
 };
 
@@ -251,6 +251,39 @@ __global__ void __launch_bounds__(256) tc2_patch_kernel(const TX* __restrict__ x
   }
 }
 
+// x * s_in as a bf16 tensor with x's strides (patch-matrix Flipout: the RGB stem, odd C_in): one thread per
+// word of the SIGN_IN stream, i.e. 32 consecutive elements of the sample in channels-last order.
+struct FlipGeo {
+  int64_t words_per_s, elems_per_s, xss, xbs, xcs, xs0, xs1, xs2;
+  int C, ID, IH, IW, S;
+  uint64_t seed;
+  uint32_t sample_id, layer_id;
+};
+__global__ void __launch_bounds__(256) tc2_flipx_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ xf, const FlipGeo g) {
+  const int64_t total = g.words_per_s * g.S;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int s = (int)(i / g.words_per_s);
+    const int64_t w = i - (int64_t)s * g.words_per_s;
+    const BtRngKey key = bt_rng_key(g.seed, g.sample_id + (uint32_t)s, g.layer_id, BT_KIND_SIGN_IN);
+    const uint4 r = bt_philox((uint64_t)(w >> 2), key);
+    const int q = (int)(w & 3);
+    const uint32_t word = q == 0 ? r.x : (q == 1 ? r.y : (q == 2 ? r.z : r.w));
+    int64_t li = w << 5;
+    int c = (int)(li % g.C);
+    int64_t pix = li / g.C;
+    int iw = (int)(pix % g.IW); pix /= g.IW;
+    int ih = (int)(pix % g.IH); pix /= g.IH;
+    int id = (int)(pix % g.ID);
+    int64_t b = pix / g.ID;
+    for (int j = 0; j < 32 && li < g.elems_per_s; ++j, ++li) {
+      const int64_t off = (int64_t)s * g.xss + b * g.xbs + (int64_t)c * g.xcs + (int64_t)id * g.xs0 + (int64_t)ih * g.xs1 + (int64_t)iw * g.xs2;
+      const unsigned short v = __bfloat16_as_ushort(x[off]);
+      xf[off] = __ushort_as_bfloat16((unsigned short)(v ^ (((word >> bt_sign_bitpos((uint32_t)j)) & 1u) << 15)));
+      if (++c == g.C) { c = 0; if (++iw == g.IW) { iw = 0; if (++ih == g.IH) { ih = 0; if (++id == g.ID) { id = 0; ++b; } } } }
+    }
+  }
+}
+
 // Epilogue of one 32-column unit of one accumulator row: ReLU, conversion and the swizzled stores
 // into chunks [cb, cb + 32/EPC) of the 128-byte staging row.  Bias and folded BatchNorm never show
 // up here: the scale is folded into the sampled weights and the shift is in the accumulator
@@ -320,7 +353,8 @@ __device__ unsigned long long g_tc_prof[160 * PROF_ROLES * PROF_SLOTS];
 template <int BN, typename TO, bool PROF, int CL, bool FLIP>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_out,
-               const __grid_constant__ CUtensorMap tm_res, const __grid_constant__ Tc2Args a) {
+               const __grid_constant__ CUtensorMap tm_res, const __grid_constant__ CUtensorMap tm_a2,
+               const __grid_constant__ Tc2Args a) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
@@ -364,7 +398,11 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     for (int i = 0; i < 4; ++i) { mbar_init(smem_u32(&ctrl->res_full[i]), 1); mbar_init(smem_u32(&ctrl->res_empty[i]), 4); }
     mbar_fence_init();
   }
-  if (warp == WARP_TMA && lane == 0) { prefetch_tmap(&tm_a); prefetch_tmap(&tm_out); if (a.res_bufs) prefetch_tmap(&tm_res); }
+  if (warp == WARP_TMA && lane == 0) {
+    prefetch_tmap(&tm_a); prefetch_tmap(&tm_out);
+    if (a.res_bufs) prefetch_tmap(&tm_res);
+    if (FLIP && a.a2_tma) prefetch_tmap(&tm_a2);
+  }
   if (warp == WARP_MMA) tmem_alloc(smem_u32(&ctrl->tmem_base), 512);
   tc_fence_before();
   __syncthreads();
@@ -493,10 +531,11 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               uint32_t word = 0;
               const int n0 = nb * BN + c;
               if (a.sign_out) {
-                if (mrow < a.Ms && n0 + 32 <= a.N) {
+                if (mrow < a.Ms) {
                   const float4* sp = reinterpret_cast<const float4*>(a.sign_out + ((int64_t)s * a.Ms + mrow) * a.N + n0);
 #pragma unroll
                   for (int j4 = 0; j4 < 8; ++j4) {
+                    if (n0 + 4 * j4 + 4 > a.N) break;  // N % 8 == 0: a group of four is all in or all out
                     const float4 f = __ldg(sp + j4);
                     word |= (__float_as_uint(f.x) >> 31) << bt_sign_bitpos(4 * j4 + 0);
                     word |= (__float_as_uint(f.y) >> 31) << bt_sign_bitpos(4 * j4 + 1);
@@ -506,9 +545,26 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 }
               } else {
                 const uint64_t idx = (uint64_t)mrow * (uint64_t)a.N + (uint64_t)n0;
-                const uint4 r = bt_philox(idx >> 7, bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_SIGN_OUT));
+                const BtRngKey key_so = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_SIGN_OUT);
+                const uint4 r = bt_philox(idx >> 7, key_so);
                 const int wq = (int)((idx >> 5) & 3);
                 word = wq == 0 ? r.x : (wq == 1 ? r.y : (wq == 2 ? r.z : r.w));
+                if ((a.N & 31) != 0) {
+                  // c_out % 32 != 0: the unit starts inside a word of the stream; gather its 32 bits from
+                  // that word and the next one (rare shapes only, e.g. a 1000-class head)
+                  const uint32_t sh = (uint32_t)idx & 31u;
+                  const uint4 r2 = bt_philox(((idx >> 5) + 1) >> 2, key_so);
+                  const int wq2 = (int)(((idx >> 5) + 1) & 3);
+                  const uint32_t word2 = wq2 == 0 ? r2.x : (wq2 == 1 ? r2.y : (wq2 == 2 ? r2.z : r2.w));
+                  uint32_t g = 0;
+#pragma unroll
+                  for (int j = 0; j < 32; ++j) {
+                    const uint32_t e = sh + (uint32_t)j;
+                    const uint32_t src = e < 32u ? word : word2;
+                    g |= ((src >> bt_sign_bitpos(e & 31u)) & 1u) << ((j >> 1) + ((j & 1) << 4));
+                  }
+                  word = g;
+                }
               }
               tmem_ld_wait();
 #pragma unroll
@@ -607,6 +663,10 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               const uint32_t bar = smem_u32(&ctrl->a_full[slot]);
               if (PROF && (a.debug & 8)) {
                 mbar_arrive(bar);
+              } else if (FLIP && a.a2_tma) {  // patch-matrix Flipout: the tile and its sign-flipped twin, two loads on one barrier
+                mbar_expect_tx(bar, 2 * A_SLOT);
+                tma_load_2d(a_base + slot * A_SLOT_T, &tm_a, bar, c0, cn[t]);
+                tma_load_2d(a_base + slot * A_SLOT_T + A_SLOT, &tm_a2, bar, c0, cn[t]);
               } else {
                 mbar_expect_tx(bar, A_SLOT);
                 if (a.conv)
@@ -683,7 +743,9 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             if ((a.NR == 2 ? (t % N_MMA_WARPS) : 0) == j) {
               const int slot = ring0 + aslot;
               PW(2, mbar_wait(smem_u32(&ctrl->a_full[slot]), aphase));
-              if constexpr (FLIP) mbar_wait(smem_u32(&ctrl->af_full[slot]), aphase);  // the flipped copy is in place too
+              if constexpr (FLIP) {  // the flipped copy is in place too
+                if (!a.a2_tma) mbar_wait(smem_u32(&ctrl->af_full[slot]), aphase);
+              }
               tc_fence_after();
               if (leader) {
                 const uint64_t adesc = umma_desc_sw128(a_base + slot * A_SLOT_T);
@@ -763,7 +825,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     int rslot[N_MMA_WARPS] = {0, 0};
     uint32_t rphase[N_MMA_WARPS] = {0, 0};
     const uint32_t row_off = (uint32_t)f * 128u, row_sw = (uint32_t)(f & 7);
-    for (int it = 0; it < n_items; ++it) {
+    for (int it = 0; it < (a.a2_tma ? 0 : n_items); ++it) {
       const int mtv = tiles_of(mg);
       const BtRngKey key = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_SIGN_IN);
       int fb[MAX_MT], fh[MAX_MT], fw[MAX_MT], fm[MAX_MT];
@@ -1120,8 +1182,8 @@ static int64_t prod_out(const bt_geom* g) {
 static bool tc2_plan(const bt_geom* g, const bt_layer_params* p, bool flipout, Plan* pl, const char** why) {
 #define TC_NO(cond, msg) if (cond) { *why = msg; return false; }
   memset(pl, 0, sizeof(*pl));
-  // Flipout: a tile row's 64 input channels / 32 output channels must be aligned runs of the sign streams
-  TC_NO(flipout && (g->c_in % 64 != 0 || g->c_out % 32 != 0), "Flipout needs c_in % 64 == 0 and c_out % 32 == 0");
+  // Flipout: the 64 input channels of a tile row must be an aligned run of the sign stream (anything else
+  // goes through the patch matrix, built twice: from x and from x * s_in)
   TC_NO(flipout && g->n_samples > 1 && (p->sign_in || p->sign_out), "tensor-fed signs with n_samples > 1");
   TC_NO(flipout && ((p->sign_in == nullptr) != (p->sign_out == nullptr)), "sign_in and sign_out must both be given or both be null");
   TC_NO(flipout && g->rank > 2, "Flipout rank 3");
@@ -1154,7 +1216,7 @@ static bool tc2_plan(const bt_geom* g, const bt_layer_params* p, bool flipout, P
   pl->Kp = (pl->K + 7) & ~7;
   const int pin = env_int("BT_TC2_AMODE", 0);
   if (g->rank == 0) {
-    if (g->x_chan_stride == 1 && g->x_batch_stride % 8 == 0 && g->c_in % 8 == 0 && pin != A_PATCH) {
+    if (g->x_chan_stride == 1 && g->x_batch_stride % 8 == 0 && g->c_in % 8 == 0 && (!flipout || g->c_in % 64 == 0) && pin != A_PATCH) {
       pl->mode = A_GEMM; pl->x_rows = g->batch; pl->pitch = g->x_batch_stride;
       return true;
     }
@@ -1176,7 +1238,8 @@ static bool tc2_plan(const bt_geom* g, const bt_layer_params* p, bool flipout, P
     }
   }
   // anything else with a dense channels-last output: explicit patch matrix, then a GEMM
-  TC_NO(flipout, "Flipout needs the im2col / GEMM operand modes (channels-last x, 16-byte aligned strides)");
+  TC_NO(flipout && x_shared, "Flipout through the patch matrix with x shared between samples");
+  TC_NO(flipout && (p->sign_in != nullptr), "Flipout through the patch matrix with tensor-fed signs");
   TC_NO(taps > 4096, "kernel volume > 4096 taps");
   pl->mode = A_PATCH;
   pl->x_rows = pl->rows_per_s;
@@ -1190,24 +1253,34 @@ bool bt_tc_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, c
   return tc2_plan(g, p, flipout, &pl, why);
 }
 
+// elements spanned by the x operand of a call (all samples), for the sign-flipped copy of the patch-matrix Flipout
+static int64_t x_span_elems(const bt_geom* g) {
+  const bool x_shared = g->n_samples > 1 && g->x_sample_stride == 0;
+  return g->batch * g->x_batch_stride * (x_shared ? 1 : g->n_samples);
+}
+
 // bytes of the caller's workspace the forward needs: packed (mu, sigma, eps) + the patch matrix
-int64_t bt_tc_workspace_bytes(const bt_geom* g) {
+// (Flipout: two patch matrices and the sign-flipped copy of x they are built from)
+int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout) {
   int64_t taps = 1;
   for (int i = 0; i < g->rank; ++i) taps *= g->k_size[i];
   const int64_t Kp = (g->c_in / (g->groups > 0 ? g->groups : 1) * taps + 7) & ~7ll;
   int64_t bytes = ((3 * g->c_out * Kp * 4 + 255) / 256) * 256;
-  const bool gemm_like = g->rank == 0 && g->x_chan_stride == 1 && g->c_in % 8 == 0 && g->x_batch_stride % 8 == 0;
+  const bool gemm_like = g->rank == 0 && g->x_chan_stride == 1 && g->c_in % 8 == 0 && g->x_batch_stride % 8 == 0 &&
+                         (!flipout || g->c_in % 64 == 0);
   const bool im2col_like = g->rank >= 1 && g->rank <= 2 && g->x_chan_stride == 1 && g->c_in % 64 == 0;
   if ((!gemm_like && !im2col_like) || env_int("BT_TC2_AMODE", 0) == A_PATCH) {
     const bool x_shared = g->n_samples > 1 && g->x_sample_stride == 0;
-    bytes += ((g->batch * prod_out(g) * (x_shared ? 1 : g->n_samples) * Kp * 2 + 255) / 256) * 256;
+    const int64_t pm = ((g->batch * prod_out(g) * (x_shared ? 1 : g->n_samples) * Kp * 2 + 255) / 256) * 256;
+    bytes += pm;
+    if (flipout) bytes += pm + ((x_span_elems(g) * 2 + 255) / 256) * 256;
   }
   return bytes;
 }
 
 template <int BN, typename TO, bool PROF, int CL, bool FLIP>
-static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const Tc2Args& a, int grid,
-                          int smem_bytes, cudaStream_t stream) {
+static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const CUtensorMap& ta2,
+                          const Tc2Args& a, int grid, int smem_bytes, cudaStream_t stream) {
   BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, PROF, CL, FLIP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
@@ -1222,24 +1295,24 @@ static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CU
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_fwd_kernel<BN, TO, PROF, CL, FLIP>, ta, to, tr, a));
+  BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_fwd_kernel<BN, TO, PROF, CL, FLIP>, ta, to, tr, ta2, a));
   BT_LAUNCH_OK(PROF ? "tc2_fwd_kernel(prof)" : (FLIP ? "tc2_fwd_kernel(flipout)" : "tc2_fwd_kernel"));
   return BT_OK;
 }
 
 template <int BN, typename TO>
-static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const Tc2Args& a, int grid, int smem_bytes,
-                      bool flip, cudaStream_t stream) {
+static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const CUtensorMap& ta2, const Tc2Args& a,
+                      int grid, int smem_bytes, bool flip, cudaStream_t stream) {
   if (flip)
-    return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, true>(ta, to, tr, a, grid, smem_bytes, stream)
-                     : tc2_launch_one<BN, TO, false, 1, true>(ta, to, tr, a, grid, smem_bytes, stream);
+    return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream)
+                     : tc2_launch_one<BN, TO, false, 1, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream);
   if constexpr (sizeof(TO) == 2) {
     if (env_int("BT_TC2_PROF", 0))
-      return a.CL == 2 ? tc2_launch_one<BN, TO, true, 2, false>(ta, to, tr, a, grid, smem_bytes, stream)
-                       : tc2_launch_one<BN, TO, true, 1, false>(ta, to, tr, a, grid, smem_bytes, stream);
+      return a.CL == 2 ? tc2_launch_one<BN, TO, true, 2, false>(ta, to, tr, ta2, a, grid, smem_bytes, stream)
+                       : tc2_launch_one<BN, TO, true, 1, false>(ta, to, tr, ta2, a, grid, smem_bytes, stream);
   }
-  return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, false>(ta, to, tr, a, grid, smem_bytes, stream)
-                   : tc2_launch_one<BN, TO, false, 1, false>(ta, to, tr, a, grid, smem_bytes, stream);
+  return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, false>(ta, to, tr, ta2, a, grid, smem_bytes, stream)
+                   : tc2_launch_one<BN, TO, false, 1, false>(ta, to, tr, ta2, a, grid, smem_bytes, stream);
 }
 
 // Diagnostics: cycle counters of the last BT_TC2_PROF=1 launch, [cta][role][slot] (see bt_b200.h).
@@ -1278,7 +1351,7 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.Kt = pl.K;
   a.K = pl.mode == A_PATCH ? pl.Kp : pl.K;
   a.x_rows_per_s = x_shared ? 0 : (int)pl.x_rows;
-  alignas(64) CUtensorMap tm_a, tm_out, tm_res;
+  alignas(64) CUtensorMap tm_a, tm_out, tm_res, tm_a2;
   const int es_o = g->out_dtype == BT_F32 ? 4 : 2;
 
   // ---- workspace carve-up: packed parameters, then (A_PATCH) the patch matrix
@@ -1299,6 +1372,7 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.has_shift = (p->mu_b || p->out_shift) ? 1 : 0;
 
   const void* a_src = x;
+  __nv_bfloat16* patches2 = nullptr;
   if (pl.mode == A_PATCH) {
     PatchGeo pg;
     memset(&pg, 0, sizeof(pg));
@@ -1319,12 +1393,38 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
     const int64_t cap = (int64_t)bt_num_sms() * 32;
     if (blocks > cap) blocks = cap;
     // (stacked samples of x are just more images: the batch stride walks across them)
-    if (chunks + cap * 256 < 0x7fffffffll)
-      tc2_patch_kernel<__nv_bfloat16, uint32_t><<<(int)blocks, 256, 0, stream>>>((const __nv_bfloat16*)x, patches, pg);
-    else
-      tc2_patch_kernel<__nv_bfloat16, int64_t><<<(int)blocks, 256, 0, stream>>>((const __nv_bfloat16*)x, patches, pg);
-    BT_LAUNCH_OK("tc2_patch_kernel");
+    auto build_patches = [&](const __nv_bfloat16* src, __nv_bfloat16* dst) -> int {
+      if (chunks + cap * 256 < 0x7fffffffll)
+        tc2_patch_kernel<__nv_bfloat16, uint32_t><<<(int)blocks, 256, 0, stream>>>(src, dst, pg);
+      else
+        tc2_patch_kernel<__nv_bfloat16, int64_t><<<(int)blocks, 256, 0, stream>>>(src, dst, pg);
+      BT_LAUNCH_OK("tc2_patch_kernel");
+      return BT_OK;
+    };
+    int rc = build_patches((const __nv_bfloat16*)x, patches);
+    if (rc != BT_OK) return rc;
     a_src = patches;
+    if (flipout) {
+      // Flipout through the patch matrix: x * s_in is materialised once (x is the SMALL tensor here -- the RGB
+      // stem, an odd C_in) and a second patch matrix is built from it; the kernel loads both tiles by TMA.
+      const int64_t pm_bytes = ((pg.rows * pg.Kp * 2 + 255) / 256) * 256;
+      patches2 = (__nv_bfloat16*)((char*)patches + pm_bytes);
+      __nv_bfloat16* xf = (__nv_bfloat16*)((char*)patches2 + pm_bytes);
+      FlipGeo fg;
+      memset(&fg, 0, sizeof(fg));
+      fg.C = (int)g->c_in; fg.ID = (int)in[0]; fg.IH = (int)in[1]; fg.IW = (int)in[2]; fg.S = S;
+      fg.elems_per_s = g->batch * g->c_in * in[0] * in[1] * in[2];
+      fg.words_per_s = (fg.elems_per_s + 31) / 32;
+      fg.xss = g->x_sample_stride; fg.xbs = g->x_batch_stride; fg.xcs = g->x_chan_stride; fg.xs0 = xs[0]; fg.xs1 = xs[1]; fg.xs2 = xs[2];
+      fg.seed = p->seed; fg.sample_id = p->sample_id; fg.layer_id = p->layer_id;
+      int64_t fb = (fg.words_per_s * S + 255) / 256;
+      if (fb > cap) fb = cap;
+      tc2_flipx_kernel<<<(int)fb, 256, 0, stream>>>((const __nv_bfloat16*)x, xf, fg);
+      BT_LAUNCH_OK("tc2_flipx_kernel");
+      rc = build_patches(xf, patches2);
+      if (rc != BT_OK) return rc;
+      a.a2_tma = 1;
+    }
   }
 
   if (pl.mode == A_GEMM || pl.mode == A_PATCH) {
@@ -1338,6 +1438,13 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     BT_REQUIRE(r == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeTiled(x) failed with %d", (int)r);
+    tm_a2 = tm_a;
+    if (patches2) {
+      const CUresult r2 = drv.tiled(&tm_a2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, patches2, gdim, gstr, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      BT_REQUIRE(r2 == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeTiled(x * s_in) failed with %d", (int)r2);
+    }
   } else {
     const Dense& d = pl.d;
     a.conv = 1;
@@ -1360,6 +1467,7 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
     // Small-tensor workaround of drivers <= 13.1 (same fix-up CUTLASS applies to im2col descriptors).
     const int64_t span = (int64_t)imgs * g->x_batch_stride * 2;
     if (drv.driver_version <= 13010 && span < 131072) reinterpret_cast<uint64_t*>(&tm_a)[1] &= ~(1ull << 21);
+    tm_a2 = tm_a;
   }
   {
     const cuuint64_t gdim[3] = {(cuuint64_t)a.N, (cuuint64_t)a.Ms, (cuuint64_t)S};
@@ -1478,8 +1586,8 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
             (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs, a.CL);
   const bool o32 = g->out_dtype == BT_F32;
   if (BN == 64)
-    return o32 ? tc2_launch<64, float>(tm_a, tm_out, tm_res, a, grid, smem_bytes, flipout, stream)
-               : tc2_launch<64, __nv_bfloat16>(tm_a, tm_out, tm_res, a, grid, smem_bytes, flipout, stream);
-  return o32 ? tc2_launch<128, float>(tm_a, tm_out, tm_res, a, grid, smem_bytes, flipout, stream)
-             : tc2_launch<128, __nv_bfloat16>(tm_a, tm_out, tm_res, a, grid, smem_bytes, flipout, stream);
+    return o32 ? tc2_launch<64, float>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream)
+               : tc2_launch<64, __nv_bfloat16>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream);
+  return o32 ? tc2_launch<128, float>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream)
+             : tc2_launch<128, __nv_bfloat16>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream);
 }

@@ -45,6 +45,44 @@ def allreduce_moments(buf: torch.Tensor, group=None) -> torch.Tensor:
     return buf
 
 
+def allreduce_gradients(model, group=None, average: bool = True, bucket_mb: float = 256.0) -> int:
+    """Data-parallel training step of the path: every rank ran forward/backward on its
+    shard of the batch (and of the S weight samples); the gradients of the variational parameters
+    (mu_*, rho_*, and whatever else the model trains) are summed across ranks in flat fp32 buckets --
+    ONE NCCL all-reduce per bucket over NVLink instead of one per tensor (ResNet-18: 93 MB, ResNet-50:
+    204 MB of mu/rho gradients fit one bucket) -- and divided by the world size when `average`.
+
+    The KL term and its gradient are replica-identical: scale the KL by 1/world in the loss (or leave
+    `average` on and keep kl/batch_size as the reference does, main_bayesian_cifar_dnn2bnn.py:411-415,
+    with batch_size the GLOBAL batch).  Replaces the DistributedDataParallel wrapper of
+    utils/utils.py:482-495.  Returns the number of collectives issued (0 without a process group)."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return 0
+    world = dist.get_world_size(group)
+    grads = [p.grad for p in model.parameters() if p.grad is not None]
+    limit = int(bucket_mb * (1 << 20))
+    buckets, cur, cur_bytes = [], [], 0
+    for g in grads:
+        nbytes = g.numel() * 4
+        if cur and (cur_bytes + nbytes > limit or g.device != cur[0].device):
+            buckets.append(cur); cur, cur_bytes = [], 0
+        cur.append(g); cur_bytes += nbytes
+    if cur:
+        buckets.append(cur)
+    for b in buckets:
+        flat = torch.cat([g.detach().reshape(-1).to(torch.float32) for g in b])
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        if average:
+            flat.div_(world)
+        off = 0
+        for g in b:
+            n = g.numel()
+            g.copy_(flat[off:off + n].view_as(g))
+            off += n
+    return len(buckets)
+
+
 class MCAccumulator:
     """Packed fp32 device buffer [sum_p | sum_p2 | sum_plogp] fed by bt_mc_accumulate."""
 

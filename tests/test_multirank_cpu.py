@@ -53,3 +53,38 @@ def test_two_rank_moment_allreduce_matches_single_rank():
     p = torch.softmax(logits.double(), -1)
     mi = oracle.predictive_entropy(p) + buf[2 * bc:].double() / S
     torch.testing.assert_close(mi, oracle.mutual_information(p), rtol=1e-4, atol=1e-5)
+
+
+def _grad_worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import bayesian_torch_b200 as bt
+    torch.manual_seed(0)                                  # replicated parameters
+    model = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.Tanh(), torch.nn.Linear(5, 3))
+    x, y = torch.randn(8, 6), torch.randn(8, 3)
+    lo, hi = rank * 4, rank * 4 + 4                       # batch shard of this rank
+    torch.nn.functional.mse_loss(model(x[lo:hi]), y[lo:hi]).backward()
+    n = bt.allreduce_gradients(model, bucket_mb=1e-4)     # tiny buckets: several collectives
+    if rank == 0:
+        ret.put((n, [p.grad.clone() for p in model.parameters()]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_gradient_allreduce_matches_full_batch():
+    """Batch sharded over two ranks + bucketed gradient all-reduce (mean) == the full-batch gradient."""
+    ctx = mp.get_context("spawn")
+    ret = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_grad_worker, args=(r, 2, port, ret)) for r in range(2)]
+    [p.start() for p in procs]
+    n, grads = ret.get(timeout=120)
+    [p.join(timeout=120) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    assert n >= 2
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.Tanh(), torch.nn.Linear(5, 3))
+    x, y = torch.randn(8, 6), torch.randn(8, 3)
+    torch.nn.functional.mse_loss(model(x), y).backward()
+    for g, p in zip(grads, model.parameters()):
+        torch.testing.assert_close(g, p.grad, rtol=1e-5, atol=1e-6)

@@ -166,14 +166,44 @@ def test_flipout_cluster_pair_matches_single_cta(cin, cout, k, pad, batch, hw, c
     torch.testing.assert_close(outs["2"], outs["1"], rtol=0, atol=0)
 
 
-def test_flipout_tc_falls_back_when_unaligned(cuda_device):
-    """c_out % 32 != 0 (or c_in % 64 != 0) cannot take aligned runs of the sign streams: 'tc' raises,
-    'auto' runs the fp32 kernel."""
-    layer = L.LinearFlipout(128, 40).to(cuda_device)
-    x = torch.randn(9, 128, device=cuda_device).bfloat16()
+@pytest.mark.parametrize("kind", ["stem", "linear_odd", "head1000"])
+def test_flipout_tc_unaligned_shapes_match_oracle_on_exported_streams(kind, cuda_device):
+    """Shapes whose tile rows are not aligned runs of the sign streams: C_in % 64 != 0 goes through two patch
+    matrices (x and x * s_in, the RGB stem), c_out % 32 != 0 gathers s_out from two stream words.  The oracle
+    is fed the exported Philox streams."""
+    torch.manual_seed(8)
+    bt.manual_seed(31)
+    if kind == "stem":
+        layer = L.Conv2dFlipout(3, 64, 7, stride=2, padding=3).to(cuda_device)
+        x = torch.randn(2, 3, 32, 32, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+        kw = dict(stride=2, padding=3)
+    elif kind == "linear_odd":
+        layer, kw = L.LinearFlipout(100, 40).to(cuda_device), None
+        x = torch.randn(37, 100, device=cuda_device).bfloat16()
+    else:
+        layer, kw = L.LinearFlipout(512, 1000).to(cuda_device), None
+        x = torch.randn(128, 512, device=cuda_device).bfloat16()
+    layer.sample_mode, layer.path = "philox", "tc"
+    with bt.mc_sample(9):
+        out, _ = layer(x)
+    torch.cuda.synchronize()
+    seed, lid = ops.get_seed(), layer._layer_id
+    w = layer._w()[0]
+    getattr(layer, "eps_" + layer._wname).copy_(ops.philox_eps_weight(w.shape, seed, 9, lid, cuda_device))
+    layer.eps_bias.copy_(ops.philox_normal(w.shape[0], seed, 9, lid, _lib.KIND_EPS_B, cuda_device))
+    layer.sign_input = ops.philox_sign_like(x, seed, 9, lid, _lib.KIND_SIGN_IN)
+    layer.sign_output = ops.philox_sign_like(out, seed, 9, lid, _lib.KIND_SIGN_OUT)
+    want = oracle_flipout_bf16(layer, x, kw)
+    err = float((out.detach().cpu().double() - want).abs().max() / want.abs().max())
+    assert err <= 2.0 ** -7, f"rel err {err}"     # + bf16 rounding of the in-kernel eps (exported stream is fp32)
+
+
+def test_flipout_tc_rejects_what_it_cannot_run(cuda_device):
+    layer = L.Conv2dFlipout(64, 64, 3, padding=1, groups=2).to(cuda_device)
+    x = torch.randn(1, 64, 8, 8, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
     layer.path = "tc"
     with pytest.raises(RuntimeError, match="tensor-core path unavailable"):
         layer(x)
     layer.path = "auto"
     out, _ = layer(x)
-    assert out.shape == (9, 40)
+    assert out.shape == (1, 64, 8, 8)
