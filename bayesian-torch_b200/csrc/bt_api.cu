@@ -50,7 +50,8 @@ extern "C" int64_t bt_workspace_bytes(const char* op, const bt_geom* g, int n_te
   if (!strcmp(op, "kl")) return bt_kl_workspace_bytes_internal(n_tensors);
   if (!strcmp(op, "reparam_fwd") || !strcmp(op, "flipout_fwd"))
     return KL_SCRATCH + (g ? bt_tc_workspace_bytes(g, !strcmp(op, "flipout_fwd")) : 0);
-  if (!strcmp(op, "reparam_bwd") || !strcmp(op, "flipout_bwd")) return KL_SCRATCH;
+  if (!strcmp(op, "reparam_bwd") || !strcmp(op, "flipout_bwd"))
+    return KL_SCRATCH + (g ? bt_tc_dgrad_workspace_bytes(g, !strcmp(op, "flipout_bwd")) : 0);
   return 0;
 }
 
@@ -110,8 +111,21 @@ static int backward_common(const bt_geom* g, const bt_layer_params* p, const voi
   BT_REQUIRE(grads, BT_ERR_INVALID, "%s: null grads", who);
   BT_REQUIRE(!p->out_scale && !p->out_shift && !p->out_relu && !p->residual, BT_ERR_UNSUPPORTED,
              "%s: the folded BatchNorm / ReLU / residual epilogue is inference-only", who);
-  BT_REQUIRE(path != BT_PATH_TC_BF16, BT_ERR_UNSUPPORTED, "%s: backward runs on the fp32 SIMT path in this build", who);
-  return bt_simt_backward(g, p, x, grad_out, grad_kl, grads, workspace, flipout, (cudaStream_t)stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  bt_layer_grads rest = *grads;
+  // grad_x on the tensor-core kernel when the problem qualifies (bf16 channels-last activations): the forward
+  // kernel run on grad_out with the transposed, regenerated weights
+  if (grads->grad_x && path != BT_PATH_SIMT_F32 && workspace) {
+    const char* why = "";
+    if (bt_tc_dgrad_supported(g, p, flipout, &why)) {
+      rc = bt_tc_dgrad(g, p, grad_out, grads->grad_x, (char*)workspace + KL_SCRATCH, flipout, st);
+      if (rc != BT_OK) return rc;
+      rest.grad_x = nullptr;
+    } else {
+      BT_REQUIRE(path != BT_PATH_TC_BF16, BT_ERR_UNSUPPORTED, "%s: tensor-core backward unavailable: %s", who, why);
+    }
+  }
+  return bt_simt_backward(g, p, x, grad_out, grad_kl, &rest, workspace, flipout, st);
 }
 
 extern "C" int bt_linear_reparam_fwd(const bt_geom* g, const bt_layer_params* p, const void* x, void* out,

@@ -199,3 +199,8 @@ bool bt_tc_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, c
 int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
                   bool flipout, cudaStream_t stream);
 int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout);
+// backward data on the tensor-core kernel (grad_out convolved with the transposed, regenerated weights)
+bool bt_tc_dgrad_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why);
+int64_t bt_tc_dgrad_workspace_bytes(const bt_geom* g, bool flipout);
+int bt_tc_dgrad(const bt_geom* g, const bt_layer_params* p, const void* grad_out, void* grad_x, void* workspace, bool flipout,
+                cudaStream_t stream);

@@ -95,6 +95,9 @@ struct Tc2Args {
   // for Philox bits, and the geometry the A flippers need to find the sign-stream position of a tile row
   const float *sign_in, *sign_out;
   int IH, IW, Cin;                 // dense logical input image (conv) / features (linear)
+  int kind_a, kind_o;              // sign streams of the A flippers / of the epilogue (forward: SIGN_IN / SIGN_OUT; dgrad: swapped)
+  int a_dil_h, a_dil_w, SH, SW;    // dgrad of a strided conv: the A tensor is grad_out with zeros inserted (factor a_dil); SH x SW is
+                                   // the un-inserted image the sign stream (and a tensor-fed sign tensor) is indexed by
   int a2_tma;                      // the sign-flipped A tiles come from a second tensor map (patch-matrix mode) instead of the flippers
   int64_t x_bs, x_hs, x_ws, x_pitch;  // strides of x in elements (tensor-fed sign_in shares them)
 };
@@ -199,6 +202,47 @@ __global__ void tc2_pack_kernel(const float* __restrict__ mu, const float* __res
   }
 }
 
+// Backward-data packing: dX = conv(dY [zero-inserted], W') with W'[c][tap'][n] = W[n][c][T-1-tap'] (the
+// transposed, tap-reversed filter).  mu_p[c][tap'*Cout + n], sigma_p likewise, and eps_p = the SAME draw
+// the forward used for that weight: stream position (n*T + tap)*Cin + c, regenerated here (one Philox call
+// per weight; |W| is small next to the activations) or taken from the caller's eps tensor.
+__global__ void tc2_pack_dgrad_kernel(const float* __restrict__ mu, const float* __restrict__ rho,
+                                      const float* __restrict__ eps, __nv_bfloat16* __restrict__ mu_p, __nv_bfloat16* __restrict__ sig_p,
+                                      float* __restrict__ eps_p, int64_t total, int Cin, int Cout, int T, int Kp, BtRngKey key) {
+  const int K = Cout * T;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t c = i / Kp;
+    const int k = (int)(i - c * Kp);
+    float m = 0.f, sg = 0.f, e = 0.f;
+    if (k < K) {
+      const int tap2 = k / Cout, n = k - tap2 * Cout;
+      const int tap = T - 1 - tap2;
+      const int64_t src = ((int64_t)n * Cin + c) * T + tap;
+      m = mu[src];
+      sg = bt_softplus(rho[src]);
+      e = eps ? eps[src] : bt_normal1((uint64_t)(((int64_t)n * T + tap) * Cin + c), key);
+    }
+    mu_p[i] = __float2bfloat16_rn(m);
+    sig_p[i] = __float2bfloat16_rn(sg);
+    eps_p[i] = e;
+  }
+}
+
+// grad_out with (stride - 1) zeros between pixels: dst[b][oh*sh][ow*sw][:] = src[b][oh][ow][:], 16 bytes per thread
+// (dst is zero-filled by the caller).
+__global__ void tc2_zero_insert_kernel(const __nv_bfloat16* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t chunks, int C8,
+                                       int OH, int OW, int sh, int sw, int64_t sbs, int64_t shs, int64_t sws, int HZ, int WZ, int C) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < chunks; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = i / C8;
+    const int c8 = (int)(i - r * C8);
+    const int ow = (int)(r % OW); r /= OW;
+    const int oh = (int)(r % OH);
+    const int64_t b = r / OH;
+    const uint4 v = *reinterpret_cast<const uint4*>(src + b * sbs + (int64_t)oh * shs + (int64_t)ow * sws + c8 * 8);
+    *reinterpret_cast<uint4*>(dst + ((b * HZ + (int64_t)oh * sh) * WZ + (int64_t)ow * sw) * C + c8 * 8) = v;
+  }
+}
+
 // ---------------------------------------------------------------- patch matrix ----
 // Explicit im2col of x into a dense bf16 matrix A[row][k], k = tap*Cin + c, row pitch Kp, for
 // convolutions the im2col tensor map cannot describe (C_in not a multiple of 64 -- the RGB stem --
@@ -255,7 +299,7 @@ __global__ void __launch_bounds__(256) tc2_patch_kernel(const TX* __restrict__ x
 // word of the SIGN_IN stream, i.e. 32 consecutive elements of the sample in channels-last order.
 struct FlipGeo {
   int64_t words_per_s, elems_per_s, xss, xbs, xcs, xs0, xs1, xs2;
-  int C, ID, IH, IW, S;
+  int C, ID, IH, IW, S, kind;
   uint64_t seed;
   uint32_t sample_id, layer_id;
 };
@@ -264,7 +308,7 @@ __global__ void __launch_bounds__(256) tc2_flipx_kernel(const __nv_bfloat16* __r
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int s = (int)(i / g.words_per_s);
     const int64_t w = i - (int64_t)s * g.words_per_s;
-    const BtRngKey key = bt_rng_key(g.seed, g.sample_id + (uint32_t)s, g.layer_id, BT_KIND_SIGN_IN);
+    const BtRngKey key = bt_rng_key(g.seed, g.sample_id + (uint32_t)s, g.layer_id, g.kind);
     const uint4 r = bt_philox((uint64_t)(w >> 2), key);
     const int q = (int)(w & 3);
     const uint32_t word = q == 0 ? r.x : (q == 1 ? r.y : (q == 2 ? r.z : r.w));
@@ -545,7 +589,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 }
               } else {
                 const uint64_t idx = (uint64_t)mrow * (uint64_t)a.N + (uint64_t)n0;
-                const BtRngKey key_so = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_SIGN_OUT);
+                const BtRngKey key_so = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, a.kind_o);
                 const uint4 r = bt_philox(idx >> 7, key_so);
                 const int wq = (int)((idx >> 5) & 3);
                 word = wq == 0 ? r.x : (wq == 1 ? r.y : (wq == 2 ? r.z : r.w));
@@ -827,7 +871,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     const uint32_t row_off = (uint32_t)f * 128u, row_sw = (uint32_t)(f & 7);
     for (int it = 0; it < (a.a2_tma ? 0 : n_items); ++it) {
       const int mtv = tiles_of(mg);
-      const BtRngKey key = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_SIGN_IN);
+      const BtRngKey key = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, a.kind_a);
       int fb[MAX_MT], fh[MAX_MT], fw[MAX_MT], fm[MAX_MT];
 #pragma unroll
       for (int t = 0; t < MAX_MT; ++t) {
@@ -849,8 +893,12 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             const int ring = a.NR == 2 ? r : 0;
             const int slot = ring * a.NAr + (a.NR == 2 ? rslot[r] : rslot[0]);
             uint32_t w0 = 0, w1 = 0;
-            const int ih = fh[t] + offh, iw = fw[t] + offw;
-            const bool inb = fm[t] < a.Ms && (!a.conv || ((unsigned)ih < (unsigned)a.IH && (unsigned)iw < (unsigned)a.IW));
+            int ih = fh[t] + offh, iw = fw[t] + offw;
+            bool inb = fm[t] < a.Ms && (!a.conv || ((unsigned)ih < (unsigned)a.IH && (unsigned)iw < (unsigned)a.IW));
+            if (a.a_dil_h > 1 || a.a_dil_w > 1) {  // zero-inserted grad_out: only every a_dil-th pixel is data
+              inb = inb && (ih % a.a_dil_h == 0) && (iw % a.a_dil_w == 0);
+              ih /= a.a_dil_h; iw /= a.a_dil_w;
+            }
             if (a.sign_in) {  // deterministic mode: the caller's +-1 tensor, laid out like x
               if (inb) {
                 const int64_t off = a.conv ? (int64_t)fb[t] * a.x_bs + (int64_t)ih * a.x_hs + (int64_t)iw * a.x_ws + c0
@@ -866,7 +914,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 }
               }
             } else if (inb) {  // zero-filled (padding) and out-of-range rows need no signs
-              const uint64_t pix = a.conv ? ((uint64_t)fb[t] * (uint64_t)a.IH + (uint64_t)ih) * (uint64_t)a.IW + (uint64_t)iw : (uint64_t)fm[t];
+              const uint64_t pix = a.conv ? ((uint64_t)fb[t] * (uint64_t)a.SH + (uint64_t)ih) * (uint64_t)a.SW + (uint64_t)iw : (uint64_t)fm[t];
               const uint64_t idx = pix * (uint64_t)a.Cin + (uint64_t)c0;
               const uint4 rr = bt_philox(idx >> 7, key);
               const bool hi = ((idx >> 6) & 1) != 0;
@@ -1179,7 +1227,7 @@ static int64_t prod_out(const bt_geom* g) {
   return t;
 }
 
-static bool tc2_plan(const bt_geom* g, const bt_layer_params* p, bool flipout, Plan* pl, const char** why) {
+static bool tc2_plan(const bt_geom* g, const bt_layer_params* p, bool flipout, Plan* pl, const char** why, bool no_gemm = false) {
 #define TC_NO(cond, msg) if (cond) { *why = msg; return false; }
   memset(pl, 0, sizeof(*pl));
   // Flipout: the 64 input channels of a tile row must be an aligned run of the sign stream (anything else
@@ -1229,7 +1277,7 @@ static bool tc2_plan(const bt_geom* g, const bt_layer_params* p, bool flipout, P
     if (ok) {
       // A 1x1 / stride 1 / unpadded convolution over a dense tensor IS a GEMM over [pixels, channels]
       if (d.k[0] == 1 && d.k[1] == 1 && d.st[0] == 1 && d.st[1] == 1 && d.pd[0] == 0 && d.pd[1] == 0 &&
-          pl->xh == d.in[1] * pl->xw && g->x_batch_stride == d.in[0] * pl->xh && pin != A_IM2COL) {
+          pl->xh == d.in[1] * pl->xw && g->x_batch_stride == d.in[0] * pl->xh && pin != A_IM2COL && !no_gemm) {
         pl->mode = A_GEMM; pl->x_rows = g->batch * d.in[0] * d.in[1]; pl->pitch = pl->xw;
       } else {
         pl->mode = A_IM2COL; pl->x_rows = g->batch;
@@ -1324,11 +1372,21 @@ extern "C" int bt_debug_tc_profile(unsigned long long* host_out, int n_words) {
   return BT_OK;
 }
 
-int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
-                   bool flipout, cudaStream_t stream) {
+// What distinguishes a backward-data run of the kernel from a forward run.
+struct RunOpt {
+  bool dgrad = false;        // pack W transposed / tap-reversed with regenerated eps (tc2_pack_dgrad_kernel)
+  int cin_w = 0, cout_w = 0; // the layer's own (C_in, C_out) when dgrad
+  int a_dil_h = 1, a_dil_w = 1, SH = 0, SW = 0;
+  int64_t s_bs = 0, s_hs = 0, s_ws = 0;  // strides of the un-inserted grad_out (tensor-fed signs)
+};
+
+static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
+                   bool flipout, const RunOpt& opt, cudaStream_t stream) {
   const char* why = "";
   Plan pl;
-  BT_REQUIRE(tc2_plan(g, p, flipout, &pl, &why), BT_ERR_UNSUPPORTED, "tensor-core forward: %s", why);
+  // (zero-inserted grad_out: the flippers need image coordinates, so a 1x1 filter stays in im2col mode)
+  BT_REQUIRE(tc2_plan(g, p, flipout, &pl, &why, opt.a_dil_h > 1 || opt.a_dil_w > 1), BT_ERR_UNSUPPORTED, "tensor-core %s: %s",
+             opt.dgrad ? "dgrad" : "forward", why);
   BT_REQUIRE(workspace, BT_ERR_INVALID, "tensor-core forward: workspace required (bt_workspace_bytes)");
   BT_REQUIRE(((uintptr_t)out & 15) == 0 && ((uintptr_t)workspace & 15) == 0 && (pl.mode == A_PATCH || ((uintptr_t)x & 15) == 0),
              BT_ERR_ALIGN, "tensor-core forward: x / out / workspace must be 16-byte aligned");
@@ -1345,6 +1403,9 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   a.debug = env_int("BT_TC2_DEBUG", 0);
   a.sign_in = flipout ? p->sign_in : nullptr;
   a.sign_out = flipout ? p->sign_out : nullptr;
+  a.kind_a = opt.dgrad ? BT_KIND_SIGN_OUT : BT_KIND_SIGN_IN;
+  a.kind_o = opt.dgrad ? BT_KIND_SIGN_IN : BT_KIND_SIGN_OUT;
+  a.a_dil_h = opt.a_dil_h; a.a_dil_w = opt.a_dil_w;
   a.Cin = (int)g->c_in;
   a.x_pitch = pl.pitch;
   a.Ms = (int)pl.rows_per_s;
@@ -1358,15 +1419,21 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
   const int64_t wn = (int64_t)a.N * a.K;
   __nv_bfloat16* mu_p = (__nv_bfloat16*)workspace;
   __nv_bfloat16* sig_p = mu_p + wn;
-  float* eps_p = p->eps_w ? (float*)(sig_p + wn) : nullptr;
+  float* eps_p = (p->eps_w || opt.dgrad) ? (float*)(sig_p + wn) : nullptr;
   __nv_bfloat16* patches = (__nv_bfloat16*)((char*)workspace + ((3 * wn * 4 + 255) / 256) * 256);
   {
     int64_t blocks = (wn + 255) / 256;
     const int64_t cap = (int64_t)bt_num_sms() * 8;
     if (blocks > cap) blocks = cap;
-    tc2_pack_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, p->out_scale, wn, (int)g->c_in, pl.T,
-                                                     a.K);
-    BT_LAUNCH_OK("tc2_pack_kernel");
+    if (opt.dgrad) {
+      tc2_pack_dgrad_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, wn, opt.cin_w, opt.cout_w, pl.T,
+                                                             a.K, bt_rng_key(p->seed, p->sample_id, p->layer_id, BT_KIND_EPS_W));
+      BT_LAUNCH_OK("tc2_pack_dgrad_kernel");
+    } else {
+      tc2_pack_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, p->out_scale, wn, (int)g->c_in, pl.T,
+                                                       a.K);
+      BT_LAUNCH_OK("tc2_pack_kernel");
+    }
   }
   a.mu_p = mu_p; a.sig_p = sig_p; a.eps_p = eps_p;
   a.has_shift = (p->mu_b || p->out_shift) ? 1 : 0;
@@ -1416,7 +1483,7 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
       fg.elems_per_s = g->batch * g->c_in * in[0] * in[1] * in[2];
       fg.words_per_s = (fg.elems_per_s + 31) / 32;
       fg.xss = g->x_sample_stride; fg.xbs = g->x_batch_stride; fg.xcs = g->x_chan_stride; fg.xs0 = xs[0]; fg.xs1 = xs[1]; fg.xs2 = xs[2];
-      fg.seed = p->seed; fg.sample_id = p->sample_id; fg.layer_id = p->layer_id;
+      fg.seed = p->seed; fg.sample_id = p->sample_id; fg.layer_id = p->layer_id; fg.kind = a.kind_a;
       int64_t fb = (fg.words_per_s * S + 255) / 256;
       if (fb > cap) fb = cap;
       tc2_flipx_kernel<<<(int)fb, 256, 0, stream>>>((const __nv_bfloat16*)x, xf, fg);
@@ -1452,7 +1519,9 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
     a.OH = (int)d.out[0]; a.OW = (int)d.out[1]; a.KW = (int)d.k[1];
     a.sh = (int)d.st[0]; a.sw = (int)d.st[1]; a.ph = (int)d.pd[0]; a.pw = (int)d.pd[1]; a.dh = (int)d.dl[0]; a.dw = (int)d.dl[1];
     a.IH = (int)d.in[0]; a.IW = (int)d.in[1];
+    a.SH = a.IH; a.SW = a.IW;
     a.x_bs = g->x_batch_stride; a.x_hs = pl.xh; a.x_ws = pl.xw;
+    if (opt.a_dil_h > 1 || opt.a_dil_w > 1) { a.SH = opt.SH; a.SW = opt.SW; a.x_bs = opt.s_bs; a.x_hs = opt.s_hs; a.x_ws = opt.s_ws; }
     const cuuint64_t imgs = (cuuint64_t)g->batch * (x_shared ? 1 : S);
     const cuuint64_t gdim[4] = {(cuuint64_t)g->c_in, (cuuint64_t)d.in[1], (cuuint64_t)d.in[0], imgs};
     const cuuint64_t gstr[3] = {(cuuint64_t)pl.xw * 2, (cuuint64_t)pl.xh * 2, (cuuint64_t)g->x_batch_stride * 2};
@@ -1590,4 +1659,120 @@ int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, voi
                : tc2_launch<64, __nv_bfloat16>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream);
   return o32 ? tc2_launch<128, float>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream)
              : tc2_launch<128, __nv_bfloat16>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream);
+}
+
+int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
+                  bool flipout, cudaStream_t stream) {
+  return tc2_run(g, p, x, out, workspace, flipout, RunOpt(), stream);
+}
+
+// ------------------------------------------------------------------ backward data ----
+// dX = conv_transpose(dY, W) [Flipout: conv_transpose(dY, mu) + conv_transpose(dY * s_out, sigma*eps) * s_in] runs on
+// the SAME kernel as the forward: a stride-1 convolution of grad_out (zeros inserted between its pixels when the
+// layer is strided) with the transposed, tap-reversed filter, whose sampled tile the producers rebuild from the
+// regenerated eps.  The geometry below is that convolution's.
+static bool dgrad_geom(const bt_geom* g, bt_geom* t, bool* inserted, const char** why) {
+#define DG_NO(cond, msg) if (cond) { *why = msg; return false; }
+  DG_NO(g->rank > 2, "rank 3");
+  DG_NO(g->groups != 1, "groups != 1");
+  DG_NO(g->n_samples != 1, "n_samples != 1");
+  DG_NO(g->x_dtype != BT_BF16 || g->out_dtype != BT_BF16, "activations / gradients are not bf16");
+  memset(t, 0, sizeof(*t));
+  t->rank = g->rank; t->groups = 1; t->n_samples = 1; t->x_dtype = BT_BF16; t->out_dtype = BT_BF16;
+  t->batch = g->batch; t->c_in = g->c_out; t->c_out = g->c_in;
+  *inserted = false;
+  for (int i = 0; i < g->rank; ++i) {
+    const int64_t pd = g->dil[i] * (g->k_size[i] - 1) - g->pad[i];
+    DG_NO(pd < 0, "padding larger than the filter reach");
+    t->k_size[i] = g->k_size[i]; t->stride[i] = 1; t->dil[i] = g->dil[i]; t->pad[i] = pd;
+    t->out_size[i] = g->in_size[i];
+    t->in_size[i] = g->in_size[i] + 2 * g->pad[i] - g->dil[i] * (g->k_size[i] - 1);  // == out_size when stride 1
+    if (g->stride[i] != 1) *inserted = true;
+    DG_NO((g->out_size[i] - 1) * g->stride[i] + 1 > t->in_size[i], "inconsistent conv arithmetic");
+  }
+  // grad_x has x's strides (the "out" of this convolution)
+  t->out_batch_stride = g->x_batch_stride; t->out_chan_stride = g->x_chan_stride;
+  for (int i = 0; i < g->rank; ++i) t->out_sp_stride[i] = g->x_sp_stride[i];
+  if (!*inserted) {  // grad_out is read in place
+    t->x_batch_stride = g->out_batch_stride; t->x_chan_stride = g->out_chan_stride;
+    for (int i = 0; i < g->rank; ++i) t->x_sp_stride[i] = g->out_sp_stride[i];
+  } else {           // dense channels-last copy with zeros inserted
+    DG_NO(g->out_chan_stride != 1 || g->c_out % 8 != 0, "strided layer: grad_out must be channels-last with c_out % 8 == 0");
+    for (int i = 0; i < g->rank; ++i) DG_NO(g->out_sp_stride[i] % 8 != 0, "strided layer: grad_out strides must be 16-byte aligned");
+    DG_NO(g->out_batch_stride % 8 != 0, "strided layer: grad_out strides must be 16-byte aligned");
+    int64_t st = g->c_out;
+    t->x_chan_stride = 1;
+    for (int i = g->rank - 1; i >= 0; --i) { t->x_sp_stride[i] = st; st *= t->in_size[i]; }
+    t->x_batch_stride = st;
+  }
+  return true;
+#undef DG_NO
+}
+
+static bt_layer_params dgrad_params(const bt_layer_params* p) {
+  bt_layer_params q = *p;
+  q.mu_b = q.rho_b = q.eps_b = nullptr;
+  q.out_scale = q.out_shift = nullptr; q.out_relu = 0; q.residual = nullptr;
+  q.sign_in = p->sign_out;   // the A operand (grad_out) is flipped by s_out, the result by s_in
+  q.sign_out = p->sign_in;
+  return q;
+}
+
+bool bt_tc_dgrad_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why) {
+  bt_geom t;
+  bool inserted;
+  if (!dgrad_geom(g, &t, &inserted, why)) return false;
+  const bt_layer_params q = dgrad_params(p);
+  Plan pl;
+  if (!tc2_plan(&t, &q, flipout, &pl, why, inserted)) return false;
+  if (inserted && pl.mode == A_PATCH && flipout) { *why = "strided Flipout layer through the patch matrix"; return false; }
+  return true;
+}
+
+static int64_t dgrad_insert_bytes(const bt_geom* t) { return ((t->batch * t->x_batch_stride * 2 + 255) / 256) * 256; }
+
+int64_t bt_tc_dgrad_workspace_bytes(const bt_geom* g, bool flipout) {
+  bt_geom t;
+  bool inserted;
+  const char* why = "";
+  if (!dgrad_geom(g, &t, &inserted, &why)) return 0;
+  return bt_tc_workspace_bytes(&t, flipout) + (inserted ? dgrad_insert_bytes(&t) : 0);
+}
+
+int bt_tc_dgrad(const bt_geom* g, const bt_layer_params* p, const void* grad_out, void* grad_x, void* workspace, bool flipout,
+                cudaStream_t stream) {
+  bt_geom t;
+  bool inserted;
+  const char* why = "";
+  BT_REQUIRE(dgrad_geom(g, &t, &inserted, &why), BT_ERR_UNSUPPORTED, "tensor-core dgrad: %s", why);
+  BT_REQUIRE(workspace, BT_ERR_INVALID, "tensor-core dgrad: workspace required (bt_workspace_bytes)");
+  const bt_layer_params q = dgrad_params(p);
+  RunOpt opt;
+  opt.dgrad = true;
+  opt.cin_w = (int)g->c_in; opt.cout_w = (int)g->c_out;
+  const void* a_src = grad_out;
+  void* ws = workspace;
+  if (inserted) {
+    const int r = g->rank;
+    const int64_t OH = r == 2 ? g->out_size[0] : 1, OW = g->out_size[r - 1];
+    const int64_t HZ = r == 2 ? t.in_size[0] : 1, WZ = t.in_size[r - 1];
+    const int sh = r == 2 ? (int)g->stride[0] : 1, sw = (int)g->stride[r - 1];
+    const int64_t ohs = r == 2 ? g->out_sp_stride[0] : 0, ows = g->out_sp_stride[r - 1];
+    const int64_t bytes = dgrad_insert_bytes(&t);
+    BT_REQUIRE(((uintptr_t)grad_out & 15) == 0, BT_ERR_ALIGN, "tensor-core dgrad: grad_out must be 16-byte aligned");
+    BT_CUDA_OK(cudaMemsetAsync(workspace, 0, (size_t)(t.batch * t.x_batch_stride * 2), stream));
+    const int C8 = (int)(g->c_out / 8);
+    const int64_t chunks = g->batch * OH * OW * C8;
+    int64_t blocks = (chunks + 255) / 256;
+    const int64_t cap = (int64_t)bt_num_sms() * 16;
+    if (blocks > cap) blocks = cap;
+    tc2_zero_insert_kernel<<<(int)blocks, 256, 0, stream>>>((const __nv_bfloat16*)grad_out, (__nv_bfloat16*)workspace, chunks, C8, (int)OH,
+                                                            (int)OW, sh, sw, g->out_batch_stride, ohs, ows, (int)HZ, (int)WZ, (int)g->c_out);
+    BT_LAUNCH_OK("tc2_zero_insert_kernel");
+    a_src = workspace;
+    ws = (char*)workspace + bytes;
+    opt.a_dil_h = sh; opt.a_dil_w = sw; opt.SH = (int)OH; opt.SW = (int)OW;
+    opt.s_bs = g->out_batch_stride; opt.s_hs = ohs; opt.s_ws = ows;
+  }
+  return tc2_run(&t, &q, a_src, grad_x, ws, flipout, opt, stream);
 }

@@ -503,10 +503,11 @@ class _BayesLayerFn(torch.autograd.Function):
         gk = None
         if call.want_kl and g_kl is not None:
             gk = g_kl.detach().to(torch.float32).contiguous()
-        ws = torch.empty(256, dtype=torch.uint8, device=dev)
+        op = b"flipout_bwd" if call.flipout else b"reparam_bwd"
+        ws = torch.empty(max(int(_lib.lib().bt_workspace_bytes(op, C.byref(geom), 2)), 256), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             rc = _entry(call, True)(C.byref(geom), C.byref(p), _ptr(xd), _ptr(go), _ptr(gk), C.byref(grads), _ptr(ws),
-                                    _lib.PATH_AUTO, _stream())
+                                    call.path, _stream())
         _lib.check(rc, "layer backward")
         if gx is not None and gx.shape != x.shape:
             gx = gx.view_as(x)
