@@ -51,7 +51,12 @@ extern "C" int64_t bt_workspace_bytes(const char* op, const bt_geom* g, int n_te
   if (!strcmp(op, "reparam_fwd") || !strcmp(op, "flipout_fwd"))
     return KL_SCRATCH + (g ? bt_tc_workspace_bytes(g, !strcmp(op, "flipout_fwd")) : 0);
   if (!strcmp(op, "reparam_bwd") || !strcmp(op, "flipout_bwd"))
-    return KL_SCRATCH + (g ? bt_tc_dgrad_workspace_bytes(g, !strcmp(op, "flipout_bwd")) : 0);
+  {  // dgrad and wgrad run one after the other on the stream and share the area
+    if (!g) return KL_SCRATCH;
+    const bool flip = !strcmp(op, "flipout_bwd");
+    const int64_t d = bt_tc_dgrad_workspace_bytes(g, flip), w = bt_tc_wgrad_workspace_bytes(g, flip);
+    return KL_SCRATCH + (d > w ? d : w);
+  }
   return 0;
 }
 
@@ -125,6 +130,18 @@ static int backward_common(const bt_geom* g, const bt_layer_params* p, const voi
       BT_REQUIRE(path != BT_PATH_TC_BF16, BT_ERR_UNSUPPORTED, "%s: tensor-core backward unavailable: %s", who, why);
     }
   }
+  // weight gradients likewise (bias gradients stay on the small SIMT reduction)
+  if (grads->grad_mu_w && grads->grad_rho_w && path != BT_PATH_SIMT_F32 && workspace) {
+    const char* why = "";
+    if (bt_tc_wgrad_supported(g, p, flipout, &why)) {
+      rc = bt_tc_wgrad(g, p, x, grad_out, grad_kl, grads->grad_mu_w, grads->grad_rho_w, (char*)workspace + KL_SCRATCH, flipout, st);
+      if (rc != BT_OK) return rc;
+      rest.grad_mu_w = rest.grad_rho_w = nullptr;
+    } else {
+      BT_REQUIRE(path != BT_PATH_TC_BF16, BT_ERR_UNSUPPORTED, "%s: tensor-core backward unavailable: %s", who, why);
+    }
+  }
+  if (!rest.grad_x && !rest.grad_mu_w && !rest.grad_rho_w && !rest.grad_mu_b && !rest.grad_rho_b) return BT_OK;
   return bt_simt_backward(g, p, x, grad_out, grad_kl, &rest, workspace, flipout, st);
 }
 

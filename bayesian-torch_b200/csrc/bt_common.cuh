@@ -202,5 +202,10 @@ int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout);
 // backward data on the tensor-core kernel (grad_out convolved with the transposed, regenerated weights)
 bool bt_tc_dgrad_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why);
 int64_t bt_tc_dgrad_workspace_bytes(const bt_geom* g, bool flipout);
+// backward weights on tensor cores (MN-major operands, split over pixels, packed fp32 accumulators in the workspace)
+bool bt_tc_wgrad_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why);
+int64_t bt_tc_wgrad_workspace_bytes(const bt_geom* g, bool flipout);
+int bt_tc_wgrad(const bt_geom* g, const bt_layer_params* p, const void* x, const void* grad_out, const float* grad_kl,
+                float* grad_mu_w, float* grad_rho_w, void* workspace, bool flipout, cudaStream_t stream);
 int bt_tc_dgrad(const bt_geom* g, const bt_layer_params* p, const void* grad_out, void* grad_x, void* workspace, bool flipout,
                 cudaStream_t stream);
