@@ -36,61 +36,59 @@ __global__ void moped_rho_kernel(const float* __restrict__ w, float* __restrict_
     rho[i] = logf(expm1f(delta * fabsf(w[i])) + 1e-20f);
 }
 
-// One warp per (s, b) row of logits[S,B,C]: softmax in registers/strided passes, then
-// atomically accumulate p, p^2 into [B,C] and sum_c p log p into [B].
+// One block per batch row b of logits[S,B,C].  Phase 1: the warps split the samples and reduce each
+// row's softmax max / denominator into shared memory.  Phase 2: every thread owns columns
+// c = tid, tid + blockDim, ... and adds p, p^2 over the samples IN SAMPLE ORDER (no atomics:
+// the [B,C] accumulators and the result are deterministic), plus its share of sum_c p log p.
+constexpr int MC_THREADS = 256, MC_SCHUNK = 64;
 template <typename T>
-__global__ void mc_accumulate_kernel(const T* __restrict__ logits, int64_t S, int64_t B, int64_t C, int softmax,
+__global__ void __launch_bounds__(MC_THREADS) mc_accumulate_kernel(const T* __restrict__ logits, int64_t S, int64_t B, int64_t C, int softmax,
                                      float* __restrict__ sum_p, float* __restrict__ sum_p2,
                                      float* __restrict__ sum_plogp) {
-  const int lane = threadIdx.x & 31;
-  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  // a warp owns batch row b and loops over s, so the [B,C] accumulators need no atomics
-  for (int64_t b = warp; b < B; b += nwarps) {
-    for (int64_t c0 = 0; c0 < C; c0 += 32 * 8) {  // register tile of 8 columns per lane
-      float ap[8], ap2[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { ap[j] = 0.f; ap2[j] = 0.f; }
-      for (int64_t s = 0; s < S; ++s) {
-        const T* row = logits + (s * B + b) * C;
-        float mx = -INFINITY, den = 1.f;
-        if (softmax) {
+  __shared__ float s_mx[MC_SCHUNK], s_inv[MC_SCHUNK], s_red[MC_THREADS / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = MC_THREADS / 32;
+  for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
+    float plogp = 0.f;
+    for (int64_t sc = 0; sc < S; sc += MC_SCHUNK) {
+      const int ns = (int)(S - sc < MC_SCHUNK ? S - sc : MC_SCHUNK);
+      if (softmax) {
+        for (int s = warp; s < ns; s += nw) {
+          const T* row = logits + ((sc + s) * B + b) * C;
+          float mx = -INFINITY;
           for (int64_t c = lane; c < C; c += 32) mx = fmaxf(mx, bt_to_float<T>(row[c]));
 #pragma unroll
           for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
           float d = 0.f;
           for (int64_t c = lane; c < C; c += 32) d += expf(bt_to_float<T>(row[c]) - mx);
-          den = bt_warp_sum(d);
-        }
-        float plogp = 0.f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int64_t c = c0 + lane + 32 * j;
-          if (c < C) {
-            const float v = bt_to_float<T>(row[c]);
-            const float pr = softmax ? expf(v - mx) / den : v;
-            ap[j] += pr;
-            ap2[j] += pr * pr;
-          }
-        }
-        if (sum_plogp && c0 == 0) {  // entropy term needs the whole row: separate strided pass
-          for (int64_t c = lane; c < C; c += 32) {
-            const float v = bt_to_float<T>(row[c]);
-            const float pr = softmax ? expf(v - mx) / den : v;
-            plogp += pr * logf(pr + 1e-15f);
-          }
-          plogp = bt_warp_sum(plogp);
-          if (lane == 0) sum_plogp[b] += plogp;
+          d = bt_warp_sum(d);
+          if (lane == 0) { s_mx[s] = mx; s_inv[s] = 1.f / d; }
         }
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int64_t c = c0 + lane + 32 * j;
-        if (c < C) {
-          if (sum_p) sum_p[b * C + c] += ap[j];
-          if (sum_p2) sum_p2[b * C + c] += ap2[j];
+      __syncthreads();
+      for (int64_t c = threadIdx.x; c < C; c += MC_THREADS) {
+        float ap = 0.f, ap2 = 0.f;
+        for (int s = 0; s < ns; ++s) {
+          const float v = bt_to_float<T>(logits[((sc + s) * B + b) * C + c]);
+          const float pr = softmax ? expf(v - s_mx[s]) * s_inv[s] : v;
+          ap += pr;
+          ap2 += pr * pr;
+          plogp += pr * logf(pr + 1e-15f);
         }
+        if (sum_p) sum_p[b * C + c] += ap;
+        if (sum_p2) sum_p2[b * C + c] += ap2;
       }
+      __syncthreads();
+    }
+    if (sum_plogp) {  // fixed-order block reduction: warp shuffles, then warp 0 over the per-warp partials
+      plogp = bt_warp_sum(plogp);
+      if (lane == 0) s_red[warp] = plogp;
+      __syncthreads();
+      if (warp == 0) {
+        float t = lane < nw ? s_red[lane] : 0.f;
+        t = bt_warp_sum(t);
+        if (lane == 0) sum_plogp[b] += t;
+      }
+      __syncthreads();
     }
   }
 }
@@ -246,12 +244,12 @@ extern "C" int bt_mc_accumulate(const void* logits, int dtype, int64_t S, int64_
                                 float* sum_p, float* sum_p2, float* sum_plogp, bt_stream_t stream) {
   BT_REQUIRE(logits && S >= 0 && B >= 0 && C > 0, BT_ERR_INVALID, "bt_mc_accumulate: bad argument");
   if (S == 0 || B == 0) return BT_OK;
-  const int grid = grid_for(B * 32, 256);
+  const int grid = (int)(B < 65535 ? B : 65535);
   if (dtype == BT_F32)
-    mc_accumulate_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)logits, S, B, C, apply_softmax,
+    mc_accumulate_kernel<float><<<grid, MC_THREADS, 0, (cudaStream_t)stream>>>((const float*)logits, S, B, C, apply_softmax,
                                                                          sum_p, sum_p2, sum_plogp);
   else if (dtype == BT_BF16)
-    mc_accumulate_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(
+    mc_accumulate_kernel<__nv_bfloat16><<<grid, MC_THREADS, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)logits, S, B, C, apply_softmax, sum_p, sum_p2, sum_plogp);
   else
     BT_REQUIRE(false, BT_ERR_UNSUPPORTED, "bt_mc_accumulate: dtype %d", dtype);

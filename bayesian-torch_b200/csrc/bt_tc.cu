@@ -80,7 +80,10 @@ struct Tc2Args {
   int OH, OW, KW, CB;  // CB = Cin / 64: k-blocks per filter tap
   int sh, sw, ph, pw, dh, dw;
   int num_mt, num_mg, MT, NSETS, nkb, NA, RW, stationary;  // num_mg: m-groups per key as walked by one cluster
-  int nb_inner;      // item order: 1 = (sample, m-group, n-block), n-block fastest (streaming only); 0 = m-group fastest
+  int nb_inner;      // item order: 1 = (sample, m-group, n-block), n-block fastest (streaming only); 0 = m-group fastest;
+                     // 2 = (m-group, n-block, sample), sample fastest: layers whose x is shared by all samples
+  int a_keep;        // order 2 with an A ring of exactly one item's tiles: the tiles stay in shared memory while
+                     // the samples of an m-group go by (the loader re-arms the slots instead of re-loading them)
   int CL;            // CTAs per cluster (1 or 2). CL = 2: the pair walks the same (sample, n-block, k-block) sequence on
                      // neighbouring m-groups, each CTA samples half of every W k-block and stores it into both CTAs' rings
   int NR, NAr;       // A rings (one per active MMA issuer) and slots per ring; NA = NR * NAr
@@ -471,7 +474,12 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   // streamed: then the NB passes over one group of A tiles follow each other on the same SM and
   // all but the first are L2 hits (measured before: every pass re-read A from HBM).
   int s0, nb0, mg0;
-  if (a.nb_inner) {
+  if (a.nb_inner == 2) {
+    const int64_t key0 = i0 / a.S;
+    s0 = (int)(i0 - key0 * a.S);
+    mg0 = (int)(key0 / a.NB);
+    nb0 = (int)(key0 - (int64_t)mg0 * a.NB);
+  } else if (a.nb_inner) {
     const int64_t key0 = i0 / a.NB;
     nb0 = (int)(i0 - key0 * a.NB);
     s0 = (int)(key0 / a.num_mg);
@@ -484,6 +492,10 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   }
   // advances (s, nb, mg) to the next item; true when a new (sample, n-block) panel starts (stationary order only)
   auto walk = [&](int& ws, int& wnb, int& wmg) -> bool {
+    if (a.nb_inner == 2) {
+      if (++ws == a.S) { ws = 0; if (++wnb == a.NB) { wnb = 0; ++wmg; } }
+      return false;
+    }
     if (a.nb_inner) {
       if (++wnb == a.NB) { wnb = 0; if (++wmg == a.num_mg) { wmg = 0; ++ws; } }
       return false;
@@ -678,8 +690,13 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     int rslot[N_MMA_WARPS] = {0, 0};
     uint32_t rphase[N_MMA_WARPS] = {0, 0};
     const int Cin = a.CB * BK;
+    int prev_mg = -1;
     for (int it = 0; it < n_items; ++it) {
       const int mtv = tiles_of(mg);
+      // x shared by the samples, sample-fastest order, ring == one full item: the previous item left
+      // exactly these tiles in exactly these slots
+      const bool keep = a.a_keep && mg == prev_mg && mtv == a.MT;
+      prev_mg = mg;
       int cw[MAX_MT], chh[MAX_MT], cn[MAX_MT];
 #pragma unroll
       for (int t = 0; t < MAX_MT; ++t) {
@@ -705,7 +722,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             PW(0, mbar_wait(smem_u32(&ctrl->a_empty[slot]), (a.NR == 2 ? rphase[r] : rphase[0]) ^ 1u));
             if (leader) {
               const uint32_t bar = smem_u32(&ctrl->a_full[slot]);
-              if (PROF && (a.debug & 8)) {
+              if (keep || (PROF && (a.debug & 8))) {
                 mbar_arrive(bar);
               } else if (FLIP && a.a2_tma) {  // patch-matrix Flipout: the tile and its sign-flipped twin, two loads on one barrier
                 mbar_expect_tx(bar, 2 * A_SLOT);
@@ -1604,6 +1621,14 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   if (a.stationary && a.NB >= 4 && a.nkb >= 2 && a.num_mt >= 4) a.stationary = 0;
   if (force_stat == 0) a.stationary = 0;
   if (force_stat == 1 && panel_fits(BN)) a.stationary = 1;
+  // x shared by all samples (the first layer of an MC-batched model), BT_TC2_SINNER=1: samples are walked like
+  // n-blocks of one wide GEMM -- (m-group, n-block, sample) order, W streamed -- so an m-group's A tiles are
+  // fetched once and, when the reduction is short enough for the ring to hold a whole item, never leave shared
+  // memory.  OFF by default: the order re-samples W for every (m-group, sample) item, and on the ResNet stem
+  // (3->64 7x7, 32 samples x 128 images) that costs more than the A traffic it saves (7.1 ms against 3.3 ms
+  // with one stationary panel per sample; profiles/r1_experiments.txt).
+  const bool s_inner = x_shared && !flipout && a.nkb <= MAX_NA / 2 && env_int("BT_TC2_SINNER", 0) != 0;
+  if (s_inner) a.stationary = 0;
   const int NSLOTS = 512 / (NSUBW * BN);
   if (a.stationary) {
     a.RW = a.nkb;
@@ -1617,6 +1642,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
     }
     // short reductions: two accumulator sets of two tiles, so the epilogue of one item overlaps the MMAs of the next
     if (a.nkb <= 8 && a.MT > 2) a.MT = 2;
+    if (s_inner) a.MT = a.num_mt >= 2 ? 2 : 1;
     if (force_mt >= 1 && force_mt <= MAX_MT && force_mt <= NSLOTS) a.MT = force_mt;
     a.RW = (ring_bytes(2, res_min) - 4 * A_SLOT_T) / WB;
     if (a.RW > 4) a.RW = 4;  // deeper W rings measured no faster; the space goes to the A ring
@@ -1635,6 +1661,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   a.num_mg = (a.num_mg + a.CL - 1) / a.CL;
   a.nb_inner = (!a.stationary && a.NB > 1) ? 1 : 0;
   if (env_int("BT_TC2_NBINNER", -1) == 0) a.nb_inner = 0;
+  if (s_inner) a.nb_inner = 2;
   a.stage_bufs = 2;
   a.res_bufs = res_min;
   a.NA = (ring_bytes(2, res_min) - a.RW * WB) / A_SLOT_T;
@@ -1657,6 +1684,11 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   a.NR = a.MT >= 2 ? N_MMA_WARPS : 1;
   a.NAr = a.NA / a.NR;
   a.NA = a.NAr * a.NR;
+  if (s_inner && a.NAr >= a.nkb && a.NR * a.nkb >= 2 && (a.MT == 1 || a.MT == a.NR)) {  // one tile per ring: slot kb <-> k-block kb
+    a.NAr = a.nkb;
+    a.NA = a.NR * a.NAr;
+    a.a_keep = 1;
+  }
   BT_REQUIRE(a.NA >= 2 && a.RW >= 1 && a.RW <= MAX_RW, BT_ERR_UNSUPPORTED, "tensor-core forward: no room for the pipelines");
   a.total_items = (int64_t)a.S * a.NB * a.num_mg;
   const int ncl = sms / a.CL;
@@ -1664,9 +1696,9 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   const int smem_bytes = 1024 + CTRL_BYTES + (flipout ? SHIFT_BYTES : 0) + (a.stage_bufs + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT_T + a.RW * WB;
   BT_REQUIRE(smem_bytes <= SMEM_LIMIT, BT_ERR_UNSUPPORTED, "tensor-core forward: shared memory plan %d exceeds %d", smem_bytes, SMEM_LIMIT);
   if (env_int("BT_TC2_LOG", 0))
-    fprintf(stderr, "tc2: flip=%d mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d\n",
+    fprintf(stderr, "tc2: flip=%d mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d order=%d keep=%d\n",
             (int)flipout, (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,
-            (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs, a.CL);
+            (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs, a.CL, a.nb_inner, a.a_keep);
   const bool o32 = g->out_dtype == BT_F32;
   if (BN == 64)
     return o32 ? tc2_launch<64, float>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream)

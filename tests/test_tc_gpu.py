@@ -173,6 +173,35 @@ def test_tc_mc_batched_equals_sample_loop(cuda_device):
     assert torch.equal(again, folded)
 
 
+@pytest.mark.parametrize("cin,cout,k,stride,pad,batch,hw,S", [
+    (3, 64, 7, 2, 3, 3, 36, 40),      # RGB stem through the patch matrix: 3 k-blocks, ragged last tile
+    (64, 96, 1, 1, 0, 5, 20, 24),     # 1x1 (plain GEMM map), one k-block, two tiles kept per item
+    (128, 64, 3, 2, 1, 2, 30, 8),     # K = 1152: too long for the kept ring -> the usual order
+])
+def test_tc_shared_input_sample_fastest_order(cuda_device, cin, cout, k, stride, pad, batch, hw, S, monkeypatch):
+    """x shared by all samples: the (m-group, n-block, sample) order with the A tiles kept in shared
+    memory gives bit-identical outputs to the per-sample loop and to the (sample, ...) order."""
+    torch.manual_seed(21)
+    layer = L.Conv2dReparameterization(cin, cout, k, stride=stride, padding=pad, bias=True, prior_type="normal").to(cuda_device)
+    layer.path = "tc"
+    layer.dnn_to_bnn_flag = True
+    x = torch.randn(batch, cin, hw, hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    with torch.no_grad():
+        loop = []
+        for s in range(S):
+            with bt.mc_sample(11 + s):
+                loop.append(layer(x))
+        monkeypatch.setenv("BT_TC2_SINNER", "1")
+        with bt.mc_batched(S, 11, shared_batch=batch):
+            folded = layer(x)
+        monkeypatch.setenv("BT_TC2_SINNER", "0")
+        with bt.mc_batched(S, 11, shared_batch=batch):
+            usual = layer(x)
+    torch.cuda.synchronize()
+    assert torch.equal(folded, torch.cat(loop))
+    assert torch.equal(folded, usual)
+
+
 def test_conv3d_tc_matches_oracle(cuda_device):
     torch.manual_seed(12)
     layer = L.Conv3dReparameterization(16, 24, 3, 0, 1, 0, -3.0, stride=1, padding=1).to(cuda_device)

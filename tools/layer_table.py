@@ -53,7 +53,14 @@ for (path, flops, nbytes, a, b), (lid, (name, m)) in zip(ops.PROFILE.records, so
     r["n"] += 1
     r["ms"] += a.elapsed_time(b)
 print(f"mc_batch={mc_batch} whole forward {total:.2f} ms; sum of Bayesian layer calls {sum(r['ms'] for r in rows.values()):.2f} ms")
-print(f"{'first layer':28s} {'weight':22s} {'cnt':>3s} {'ms/call':>8s} {'TFLOP/s':>8s} {'GB/s':>7s} path")
+PEAK_TF, PEAK_GB = float(os.environ.get("BT_PEAK_TF", "1372.6")), float(os.environ.get("BT_PEAK_GB", "6541.5"))
+print(f"{'first layer':28s} {'weight':22s} {'cnt':>3s} {'ms/call':>8s} {'TFLOP/s':>8s} {'GB/s':>7s} {'t_tc':>6s} {'t_hbm':>6s} {'gap ms':>7s} path")
+gap_total = ideal_total = 0.0
 for key, r in rows.items():
     ms = r["ms"] / r["n"]
-    print(f"{r['name']:28s} {str(key[0]):22s} {r['n']:3d} {ms:8.3f} {r['flops'] / ms / 1e9:8.1f} {r['bytes'] / ms / 1e6:7.0f} {'tc' if r['path'] == 2 else 'simt'}")
+    t_tc, t_hbm = r["flops"] / PEAK_TF / 1e9, r["bytes"] / PEAK_GB / 1e6
+    gap = (ms - max(t_tc, t_hbm)) * r["n"]
+    gap_total += gap; ideal_total += max(t_tc, t_hbm) * r["n"]
+    print(f"{r['name']:28s} {str(key[0]):22s} {r['n']:3d} {ms:8.3f} {r['flops'] / ms / 1e9:8.1f} {r['bytes'] / ms / 1e6:7.0f} "
+          f"{t_tc:6.3f} {t_hbm:6.3f} {gap:7.3f} {'tc' if r['path'] == 2 else 'simt'}")
+print(f"sum of per-layer max(t_tc, t_hbm) = {ideal_total:.2f} ms; gap to it {gap_total:.2f} ms (peaks {PEAK_TF} TFLOP/s, {PEAK_GB} GB/s)")
