@@ -441,7 +441,10 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     for (int i = 0; i < a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), NPW); mbar_init(smem_u32(&ctrl->w_empty[i]), N_MMA_WARPS * CL); }
     mbar_init(smem_u32(&ctrl->w_full[a.RW]), NPW);  // the shift tile stays CTA-local
     mbar_init(smem_u32(&ctrl->w_empty[a.RW]), N_MMA_WARPS);
-    for (int i = 0; i < a.NSETS; ++i) { mbar_init(smem_u32(&ctrl->acc_full[i]), N_MMA_WARPS); mbar_init(smem_u32(&ctrl->acc_empty[i]), 128); }
+    for (int i = 0; i < a.NSETS; ++i) mbar_init(smem_u32(&ctrl->acc_full[i]), N_MMA_WARPS);
+    // acc_empty is per accumulator TILE (set * MT + t): the MMAs of the next item restart on tile t as soon as the
+    // epilogue has drained it, instead of waiting for the whole set
+    for (int i = 0; i < a.NSETS * a.MT; ++i) mbar_init(smem_u32(&ctrl->acc_empty[i]), 128);
     for (int i = 0; i < 4; ++i) { mbar_init(smem_u32(&ctrl->res_full[i]), 1); mbar_init(smem_u32(&ctrl->res_empty[i]), 4); }
     mbar_fence_init();
   }
@@ -549,6 +552,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               if (++rslot == a.res_bufs) { rslot = 0; rphase ^= 1u; }
             }
           }
+          mbar_arrive(smem_u32(&ctrl->acc_empty[set * a.MT + t]));
           continue;
         }
         const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)((set * a.MT + t) * ACC_COLS);
@@ -663,9 +667,10 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             if (++rslot == a.res_bufs) { rslot = 0; rphase ^= 1u; }
           }
         }
+        // this thread's TMEM reads of tile t have completed (tcgen05.wait::ld above): hand the tile back
+        tc_fence_before();
+        mbar_arrive(smem_u32(&ctrl->acc_empty[set * a.MT + t]));
       }
-      tc_fence_before();
-      mbar_arrive(smem_u32(&ctrl->acc_empty[set]));
       if (++set == a.NSETS) { set = 0; set_phase ^= 1u; }
       walk(s, nb, mg);
     }
@@ -758,6 +763,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
     int mg = mg0, nb_unused = nb0, s_unused = s0, set = 0, aslot = 0, wslot_r = 0;
     uint32_t set_phase = 0, aphase = 0, wphase = 0, sphase = 0;
+    uint32_t emp_bits = 0;  // phase of every acc_empty barrier (one per accumulator tile) as seen by this issuer
     const uint32_t acc0 = a.has_shift ? 1u : 0u;  // accumulators start from the shift, not from zero
     const uint64_t ones_desc = umma_desc_sw32(ones_base), shift_desc = umma_desc_sw32(shift_base);
     const uint64_t shift2_desc = umma_desc_sw32(shift_base + SHIFT_BYTES);  // Flipout: perturbation bias
@@ -766,29 +772,10 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     for (int it = 0; it < n_items; ++it) {
       const bool last = !a.stationary || it + 1 == n_items || mg + 1 == a.num_mg;
       const int mtv = tiles_of(mg);  // 0 for the odd tail of a CTA pair: W slots are still consumed, nothing is issued
-      if (mtv > 0) {
-        PW(0, mbar_wait(smem_u32(&ctrl->acc_empty[set]), set_phase ^ 1u));
-        tc_fence_after();
-      }
       const uint32_t dbase = tmem + (uint32_t)(set * a.MT * ACC_COLS);
-      if (a.has_shift) {
-        // D = ones[128 x 16] * shift[BN x 16]^T: every row of the accumulator starts as the
-        // per-channel shift (bias * scale + BatchNorm shift, split into three bf16 terms)
-        if (first) {
-          PW(1, mbar_wait(smem_u32(&ctrl->w_full[a.RW]), sphase));
-          tc_fence_after();
-        }
-        if (leader && !(PROF && (a.debug & 4))) {
-#pragma unroll
-          for (int t = 0; t < MAX_MT; ++t)
-            if (t < mtv && (a.NR == 2 ? (t % N_MMA_WARPS) : 0) == j) {
-              umma_bf16(dbase + (uint32_t)(t * ACC_COLS), ones_desc, shift_desc, idesc, 0u);
-              if constexpr (FLIP) umma_bf16(dbase + (uint32_t)(t * ACC_COLS + BN), ones_desc, shift2_desc, idesc, 0u);
-            }
-        }
-        if (last && leader) umma_commit(smem_u32(&ctrl->w_empty[a.RW]));
-        __syncwarp();
-        if (last) sphase ^= 1u;
+      if (a.has_shift && first) {
+        PW(1, mbar_wait(smem_u32(&ctrl->w_full[a.RW]), sphase));
+        tc_fence_after();
       }
       for (int kb = 0; kb < a.nkb; ++kb) {
         const int wslot = a.stationary ? kb : wslot_r;
@@ -802,6 +789,19 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         for (int t = 0; t < MAX_MT; ++t) {
           if (t < mtv) {
             if ((a.NR == 2 ? (t % N_MMA_WARPS) : 0) == j) {
+              if (kb == 0) {
+                // first touch of accumulator tile t in this item: the epilogue must have drained it
+                const int ti = set * a.MT + t;
+                PW(0, mbar_wait(smem_u32(&ctrl->acc_empty[ti]), ((emp_bits >> ti) & 1u) ^ 1u));
+                emp_bits ^= 1u << ti;
+                tc_fence_after();
+                // D = ones[128 x 16] * shift[BN x 16]^T: every row of the accumulator starts as the
+                // per-channel shift (bias * scale + BatchNorm shift, split into three bf16 terms)
+                if (a.has_shift && leader && !(PROF && (a.debug & 4))) {
+                  umma_bf16(dbase + (uint32_t)(t * ACC_COLS), ones_desc, shift_desc, idesc, 0u);
+                  if constexpr (FLIP) umma_bf16(dbase + (uint32_t)(t * ACC_COLS + BN), ones_desc, shift2_desc, idesc, 0u);
+                }
+              }
               const int slot = ring0 + aslot;
               PW(2, mbar_wait(smem_u32(&ctrl->a_full[slot]), aphase));
               if constexpr (FLIP) {  // the flipped copy is in place too
@@ -829,6 +829,11 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               if (++aslot == a.NAr) { aslot = 0; aphase ^= 1u; }
             }
           }
+        }
+        if (kb == 0 && a.has_shift) {  // the shift tile has been read by this issuer's rank-1 MMAs of the item
+          if (last && leader) umma_commit(smem_u32(&ctrl->w_empty[a.RW]));
+          __syncwarp();
+          if (last) sphase ^= 1u;
         }
         if (last && leader) {  // the slot is free once BOTH CTAs' tensor cores have read it: its producers sit in both
           if constexpr (CL > 1) umma_commit_multicast(smem_u32(&ctrl->w_empty[wslot]), (uint16_t)3);
