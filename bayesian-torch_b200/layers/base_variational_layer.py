@@ -73,20 +73,21 @@ class _BayesLayer(BaseVariationalLayer_):
 
     _rank = 0
     _flipout = False
+    _transpose = False  # ConvTransposeNd: weight [c_in, c_out / groups, *k], the layer is the data-gradient of a conv
     _wname = "weight"  # parameter suffix: mu_weight / mu_kernel
 
     # per-layer overrides of the process-wide settings in ops (None = follow the global)
     sample_mode: Optional[str] = None
     path: Optional[str] = None
 
-    def _setup(self, w_shape, bias: bool, prior_mean, prior_variance, mu_init, rho_init):
+    def _setup(self, w_shape, bias: bool, prior_mean, prior_variance, mu_init, rho_init, bias_n=None):
         w = self._wname
         self.register_parameter("mu_" + w, Parameter(torch.empty(w_shape)))
         self.register_parameter("rho_" + w, Parameter(torch.empty(w_shape)))
         self.register_buffer("eps_" + w, torch.empty(w_shape), persistent=False)
         self.register_buffer("prior_weight_mu", torch.empty(w_shape), persistent=False)
         self.register_buffer("prior_weight_sigma", torch.empty(w_shape), persistent=False)
-        n = w_shape[0]
+        n = w_shape[0] if bias_n is None else bias_n
         if bias:
             self.mu_bias = Parameter(torch.empty(n))
             self.rho_bias = Parameter(torch.empty(n))
@@ -188,6 +189,10 @@ class _BayesLayer(BaseVariationalLayer_):
         BatchNorm and before the folded ReLU: the identity branch of a residual block."""
         if self.dnn_to_bnn_flag:
             return_kl = False
+        if self._transpose:
+            if residual is not None:
+                raise RuntimeError("residual epilogue is not available on ConvTranspose layers")
+            return self._forward_transpose(input, return_kl)
         mu_w, rho_w = self._w()
         r = self._rank
         mode = self.sample_mode or ops.get_sample_mode()
@@ -237,6 +242,74 @@ class _BayesLayer(BaseVariationalLayer_):
             out = out.reshape(-1, *lead[1:], out.shape[-1])   # leading axis may be folded S*B
         if return_kl:
             return out, kl
+        return out
+
+    def _forward_transpose(self, x, return_kl):
+        """ConvTranspose{1,2,3}d{Reparameterization,Flipout}.forward (conv_variational.py:941-989,
+        conv_flipout.py:757-831): out = conv_transpose(x, mu + sigma * eps) + (mu_b + sigma_b * eps_b), Flipout
+        likewise with the two paths.  The contraction is the DATA GRADIENT of the convolution whose weight has
+        this layer's [c_in, c_out / groups, *k] shape, so it runs on the backward-data kernel of that
+        convolution (ops.bayes_transpose_layer); the sampled bias is added by torch ops (autograd
+        differentiates it); KL is the shared multi-tensor kernel."""
+        r = self._rank
+        if x.dim() != r + 2:
+            raise RuntimeError(f"{type(self).__name__} expects a {r + 2}-d input, got {tuple(x.shape)}")
+        if ops.current_n_samples() != 1:
+            raise RuntimeError("ConvTranspose layers do not fold samples (mc_batched): loop over mc_sample(s)")
+        mu_w, rho_w = self._w()
+        mode = self.sample_mode or ops.get_sample_mode()
+        call = ops.LayerCall(rank=r, flipout=self._flipout)
+        call.stride, call.padding, call.dilation, call.groups = self._conv_args()
+        call.output_padding = _ntuple(self.output_padding, r)
+        call.seed, call.layer_id = ops.get_seed(), self._layer_id
+        call.want_kl = False
+        call.path = ops._PATHS[self.path or ops.get_path()]
+        if ops._STATE.sample_override is not None:
+            call.sample_id = ops._STATE.sample_override
+        else:
+            call.sample_id = self._calls & 0xFFFFFFFF
+            self._calls += 1
+        eps_w = getattr(self, "eps_" + self._wname)
+        eps_b = None
+        ops._require_cuda(x)
+        out_sp = [(x.shape[2 + i] - 1) * call.stride[i] - 2 * call.padding[i] + call.dilation[i] * (mu_w.shape[2 + i] - 1)
+                  + call.output_padding[i] + 1 for i in range(r)]
+        oshape = (x.shape[0], mu_w.shape[1] * call.groups, *out_sp)
+        s_in = s_out = None
+        if mode == "torch":
+            if self._flipout:   # conv_flipout.py:776-777 then :781,:791 draw order
+                s_in = torch.empty_like(x, dtype=torch.float32, memory_format=torch.contiguous_format).uniform_(-1, 1).sign()
+                s_out = torch.empty(oshape, dtype=torch.float32, device=x.device).uniform_(-1, 1).sign()
+            call.eps_w = eps_w.normal_()
+            if self.mu_bias is not None:
+                eps_b = self.eps_bias.normal_()
+        elif mode == "buffer":
+            call.eps_w = eps_w
+            eps_b = self.eps_bias
+            if self._flipout:
+                if self.sign_input is None or self.sign_output is None:
+                    raise RuntimeError("sample mode 'buffer' on a Flipout layer needs layer.sign_input / layer.sign_output")
+                s_in, s_out = self.sign_input, self.sign_output
+        else:
+            # in-kernel Philox: weights and signs are generated by the kernels; the bias draw and (Flipout) the
+            # output signs the bias perturbation needs are the exported streams of the same keys.  The equivalent
+            # convolution reads THIS layer's output as its input, so our sign_output is its SIGN_IN stream.
+            if self.mu_bias is not None:
+                eps_b = ops.philox_normal(self.mu_bias.numel(), call.seed, call.sample_id, self._layer_id, _lib.KIND_EPS_B, x.device)
+                if self._flipout:
+                    s_out = ops.philox_sign_shape(oshape, x.device, call.seed, call.sample_id, self._layer_id, _lib.KIND_SIGN_IN)
+        if self._flipout and mode != "philox":
+            call.sign_in, call.sign_out = s_out, s_in   # (equivalent convolution's view, see above)
+        out = ops.bayes_transpose_layer(call, x, mu_w, rho_w, oshape)
+        if self.mu_bias is not None:
+            bshape = (1, -1) + (1,) * r
+            db = torch.nn.functional.softplus(self.rho_bias) * eps_b.detach()
+            if self._flipout:
+                out = out + (self.mu_bias.view(bshape) + db.view(bshape) * s_out.reshape(oshape)).to(out.dtype)
+            else:
+                out = out + (self.mu_bias + db).view(bshape).to(out.dtype)
+        if return_kl:
+            return out, self.kl_loss()
         return out
 
     def _draw_signs(self, x, mu_w):

@@ -7,10 +7,15 @@ positional prior/posterior arguments of Conv3d -- same parameter names (mu_kerne
 rho_kernel, mu_bias, rho_bias) and the same ValueError on bad groups.  `prior_type`
 None is read as 'normal' (SURVEY.md section 0).  The convolution is an implicit GEMM
 whose weight tile is sampled in shared memory.
+
+ConvTranspose{1,2,3}dReparameterization (conv_variational.py:822-1340; weight
+[in_channels, out_channels / groups, *k], `output_padding` after `groups`) run on the backward-data
+kernel of the convolution with the same weight (base_variational_layer._forward_transpose).
 """
 from ..base_variational_layer import _BayesLayer, get_kernel_size
 
-__all__ = ["Conv1dReparameterization", "Conv2dReparameterization", "Conv3dReparameterization"]
+__all__ = ["Conv1dReparameterization", "Conv2dReparameterization", "Conv3dReparameterization",
+           "ConvTranspose1dReparameterization", "ConvTranspose2dReparameterization", "ConvTranspose3dReparameterization"]
 
 
 class _ConvReparam(_BayesLayer):
@@ -35,8 +40,12 @@ class _ConvReparam(_BayesLayer):
         self.posterior_rho_init = (posterior_rho_init,) if tuple_inits else posterior_rho_init
         self.bias = bias
         k = get_kernel_size(kernel_size, self._rank)
-        self._setup((out_channels, in_channels // groups, *k), bias, prior_mean, prior_variance, posterior_mu_init,
-                    posterior_rho_init)
+        if self._transpose:
+            self._setup((in_channels, out_channels // groups, *k), bias, prior_mean, prior_variance, posterior_mu_init,
+                        posterior_rho_init, bias_n=out_channels)
+        else:
+            self._setup((out_channels, in_channels // groups, *k), bias, prior_mean, prior_variance, posterior_mu_init,
+                        posterior_rho_init)
 
 
 class Conv1dReparameterization(_ConvReparam):
@@ -69,3 +78,27 @@ class Conv3dReparameterization(_ConvReparam):
         super().__init__()
         self._init_conv(in_channels, out_channels, kernel_size, stride, padding, dilation, groups, prior_mean,
                         prior_variance, posterior_mu_init, posterior_rho_init, bias)
+
+
+class _ConvTransposeReparam(_ConvReparam):
+    _transpose = True
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1,
+                 output_padding=0, prior_mean=0, prior_variance=1, posterior_mu_init=0, posterior_rho_init=-3.0,
+                 bias=True):
+        super().__init__()
+        self.output_padding = output_padding
+        self._init_conv(in_channels, out_channels, kernel_size, stride, padding, dilation, groups, prior_mean,
+                        prior_variance, posterior_mu_init, posterior_rho_init, bias)
+
+
+class ConvTranspose1dReparameterization(_ConvTransposeReparam):
+    _rank = 1
+
+
+class ConvTranspose2dReparameterization(_ConvTransposeReparam):
+    _rank = 2
+
+
+class ConvTranspose3dReparameterization(_ConvTransposeReparam):
+    _rank = 3

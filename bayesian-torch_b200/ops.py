@@ -301,6 +301,7 @@ class LayerCall:
     out_shift: Optional[torch.Tensor] = None
     out_relu: bool = False
     residual: Optional[torch.Tensor] = None     # added after the affine, before the ReLU (inference only)
+    output_padding: Tuple[int, ...] = ()        # ConvTranspose layers only
 
 
 def _conv_out_size(i, k, s, p, d):
@@ -514,6 +515,87 @@ class _BayesLayerFn(torch.autograd.Function):
         return None, gx, gmu, grho, gmb, grb
 
 
+class _BayesTransposeFn(torch.autograd.Function):
+    """conv_transpose(x, W) with W = mu + softplus(rho) * eps sampled in the kernels (Flipout: the mean path plus
+    the sign-flipped perturbation path), bias excluded.  With E the convolution whose weight has W's shape
+    [c_in, c_out / groups, *k] (E maps this layer's OUTPUT space to its INPUT space):
+        forward      = E's backward-data  on grad_out := x            (bt_conv_*_bwd, grad_x only)
+        grad_x       = E's forward        on x_E := grad_out           (bt_conv_*_fwd, no bias)
+        grad_mu/rho  = E's backward-weights with x_E := grad_out, grad_out_E := x
+    all three regenerate the same eps (and signs) from the (seed, sample, layer) key or read the same buffers."""
+
+    @staticmethod
+    def forward(ctx, call: LayerCall, x, mu_w, rho_w, oshape):
+        dev = _require_cuda(x, mu_w, rho_w)
+        if x.dtype not in _DT:
+            raise RuntimeError(f"activations must be float32 or bfloat16, got {x.dtype}")
+        mu_wc, rho_wc = _f32c(mu_w.detach(), "mu"), _f32c(rho_w.detach(), "rho")
+        xd = _dense(x.detach())
+        if xd.shape[1] != mu_wc.shape[0]:
+            raise RuntimeError(f"input has {xd.shape[1]} channels, layer expects {mu_wc.shape[0]}")
+        if min(oshape[2:]) <= 0:
+            raise RuntimeError(f"conv_transpose output size {tuple(oshape[2:])} is not positive for input {tuple(xd.shape)}")
+        for i in range(call.rank):  # E's forward arithmetic must map the output back onto x exactly
+            if _conv_out_size(oshape[2 + i], mu_wc.shape[2 + i], call.stride[i], call.padding[i], call.dilation[i]) != xd.shape[2 + i]:
+                raise RuntimeError("output_padding must be smaller than either stride or dilation")
+        out = _like_x_format(xd, tuple(oshape))
+        if call.sign_in is not None:    # E's input is our output, E's output is our input
+            call.sign_in = _match_strides(call.sign_in, out)
+        if call.sign_out is not None:
+            call.sign_out = _match_strides(call.sign_out, xd)
+        geom = _build_geom(call, out, mu_wc.shape, xd)
+        p, keep = _build_params(call, mu_wc, rho_wc, None, None)
+        grads = LayerGrads()
+        grads.grad_x = _ptr(out)
+        op = b"flipout_bwd" if call.flipout else b"reparam_bwd"
+        ws = torch.empty(max(int(_lib.lib().bt_workspace_bytes(op, C.byref(geom), 2)), 256), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = _entry(call, True)(C.byref(geom), C.byref(p), _ptr(out), _ptr(xd), None, C.byref(grads), _ptr(ws),
+                                    call.path, _stream())
+        _lib.check(rc, "conv_transpose forward")
+        ctx.call = call
+        ctx.save_for_backward(x, mu_w, rho_w)
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        call: LayerCall = ctx.call
+        x, mu_w, rho_w = ctx.saved_tensors
+        dev = x.device
+        mu_wc, rho_wc = _f32c(mu_w.detach(), "mu"), _f32c(rho_w.detach(), "rho")
+        xd = _dense(x.detach())
+        go = _dense(g_out.detach().to(x.dtype))
+        p, keep = _build_params(call, mu_wc, rho_wc, None, None)
+        L = _lib.lib()
+        gx = gmu = grho = None
+        with torch.cuda.device(dev):
+            if ctx.needs_input_grad[1]:
+                gx = torch.empty_like(xd)
+                geom = _build_geom(call, go, mu_wc.shape, gx)
+                op = b"flipout_fwd" if call.flipout else b"reparam_fwd"
+                ws = torch.empty(max(int(L.bt_workspace_bytes(op, C.byref(geom), 2)), 256), dtype=torch.uint8, device=dev)
+                rc = _entry(call, False)(C.byref(geom), C.byref(p), _ptr(go), _ptr(gx), None, _ptr(ws), call.path, _stream())
+                _lib.check(rc, "conv_transpose backward (data)")
+            if ctx.needs_input_grad[2] or ctx.needs_input_grad[3]:
+                gmu, grho = torch.empty_like(mu_wc), torch.empty_like(rho_wc)
+                geom = _build_geom(call, go, mu_wc.shape, xd)
+                grads = LayerGrads()
+                grads.grad_mu_w, grads.grad_rho_w = _ptr(gmu), _ptr(grho)
+                op = b"flipout_bwd" if call.flipout else b"reparam_bwd"
+                ws = torch.empty(max(int(L.bt_workspace_bytes(op, C.byref(geom), 2)), 256), dtype=torch.uint8, device=dev)
+                rc = _entry(call, True)(C.byref(geom), C.byref(p), _ptr(go), _ptr(xd), None, C.byref(grads), _ptr(ws),
+                                        call.path, _stream())
+                _lib.check(rc, "conv_transpose backward (weights)")
+        if gx is not None and gx.shape != x.shape:
+            gx = gx.view_as(x)
+        return None, gx, gmu, grho, None
+
+
+def bayes_transpose_layer(call: LayerCall, x, mu_w, rho_w, oshape):
+    """conv_transpose(x, sampled W) of a ConvTranspose{1,2,3}d Bayesian layer, bias excluded."""
+    return _BayesTransposeFn.apply(call, x, mu_w, rho_w, tuple(int(v) for v in oshape))
+
+
 def bayes_layer(call: LayerCall, x, mu_w, rho_w, mu_b, rho_b):
     """(out, kl) of one Bayesian layer call; kl is a zero constant when call.want_kl is False."""
     return _BayesLayerFn.apply(call, x, mu_w, rho_w, mu_b, rho_b)
@@ -537,15 +619,22 @@ def philox_sign(n: int, seed: int, sample_id: int, layer_id: int, kind: int, dev
     return out
 
 
-def philox_sign_like(t: torch.Tensor, seed: int, sample_id: int, layer_id: int, kind: int) -> torch.Tensor:
-    """+-1 tensor shaped like t ([B, C, *spatial]) holding the signs the kernels generate for each
+def philox_sign_shape(shape, device, seed: int, sample_id: int, layer_id: int, kind: int) -> torch.Tensor:
+    """+-1 tensor of logical shape [B, C, *spatial] holding the signs the kernels generate for each
     element: the sign streams run over an activation tensor in CHANNELS-LAST order ((b, spatial...), c),
     whatever its memory layout (csrc/bt_common.cuh: bt_sign_index)."""
-    flat = philox_sign(t.numel(), seed, sample_id, layer_id, kind, t.device)
-    if t.dim() <= 2:
-        return flat.view(t.shape)
-    shape = tuple(t.shape)
+    shape = tuple(int(v) for v in shape)
+    n = 1
+    for v in shape:
+        n *= v
+    flat = philox_sign(n, seed, sample_id, layer_id, kind, device)
+    if len(shape) <= 2:
+        return flat.view(shape)
     return flat.view((shape[0],) + shape[2:] + (shape[1],)).movedim(-1, 1)
+
+
+def philox_sign_like(t: torch.Tensor, seed: int, sample_id: int, layer_id: int, kind: int) -> torch.Tensor:
+    return philox_sign_shape(t.shape, t.device, seed, sample_id, layer_id, kind)
 
 
 def philox_eps_weight(w_shape, seed: int, sample_id: int, layer_id: int, device="cuda") -> torch.Tensor:

@@ -17,6 +17,7 @@ import torch.nn.functional as F
 __all__ = [
     "softplus_ref", "kl_normal", "kl_normal_from_rho", "sample_weight",
     "linear_reparam", "conv_reparam", "linear_flipout", "conv_flipout",
+    "conv_transpose_reparam", "conv_transpose_flipout",
     "get_rho", "mc_moments", "predictive_entropy", "mutual_information",
 ]
 
@@ -112,6 +113,39 @@ def conv_flipout(x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b, sign_in, sign_out,
     delta_b = None if mu_b is None else softplus_ref(rho_b) * eps_b
     mean_path = conv(x, mu_k, mu_b, stride, padding, dilation, groups)
     pert = conv(x * sign_in, delta_k, delta_b, stride, padding, dilation, groups)
+    out = mean_path + pert * sign_out
+    return out, kl_normal_from_rho(mu_k, rho_k, mu_b, rho_b, prior_mu, prior_sigma, dtype)
+
+
+def _conv_transpose(rank: int):
+    return {1: F.conv_transpose1d, 2: F.conv_transpose2d, 3: F.conv_transpose3d}[rank]
+
+
+def conv_transpose_reparam(x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b, stride=1, padding=0,
+                           output_padding=0, dilation=1, groups=1, prior_mu=0.0, prior_sigma=1.0,
+                           dtype=torch.float32) -> Tuple[torch.Tensor, torch.Tensor]:
+    """ConvTranspose{1,2,3}dReparameterization.forward (conv_variational.py:941-989,
+    1116-1164, 1292-1340); kernel [c_in, c_out / groups, *k]."""
+    x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b = (
+        _c(t, dtype) for t in (x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b))
+    w = sample_weight(mu_k, rho_k, eps_k)
+    b = None if mu_b is None else sample_weight(mu_b, rho_b, eps_b)
+    out = _conv_transpose(mu_k.dim() - 2)(x, w, b, stride, padding, output_padding, groups, dilation)
+    return out, kl_normal_from_rho(mu_k, rho_k, mu_b, rho_b, prior_mu, prior_sigma, dtype)
+
+
+def conv_transpose_flipout(x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b, sign_in, sign_out,
+                           stride=1, padding=0, output_padding=0, dilation=1, groups=1,
+                           prior_mu=0.0, prior_sigma=1.0, dtype=torch.float32):
+    """ConvTranspose{1,2,3}dFlipout.forward (flipout_layers/conv_flipout.py:757-831,
+    956-1030, 1155-1228)."""
+    x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b, sign_in, sign_out = (
+        _c(t, dtype) for t in (x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b, sign_in, sign_out))
+    convt = _conv_transpose(mu_k.dim() - 2)
+    delta_k = softplus_ref(rho_k) * eps_k
+    delta_b = None if mu_b is None else softplus_ref(rho_b) * eps_b
+    mean_path = convt(x, mu_k, mu_b, stride, padding, output_padding, groups, dilation)
+    pert = convt(x * sign_in, delta_k, delta_b, stride, padding, output_padding, groups, dilation)
     out = mean_path + pert * sign_out
     return out, kl_normal_from_rho(mu_k, rho_k, mu_b, rho_b, prior_mu, prior_sigma, dtype)
 

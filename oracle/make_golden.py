@@ -10,6 +10,9 @@ Harness-side shims, no edits to the reference:
     Linear/Conv2d Reparameterization; for the other layers the forward is run
     with return_kl=False and KL is computed with the reference's own
     kl_div(..., 'normal') on the same tensors (= upstream behaviour).
+  * ConvTranspose1dFlipout / ConvTranspose2dFlipout allocate prior_weight_sigma with the
+    un-transposed kernel shape; the harness substitutes the same constant in the right shape
+    (see ref_kl).
 Each fixture stores inputs (x, mu/rho, eps, signs), outputs (out, kl) and the
 autograd gradients of  L = sum(out*g) + c*kl  w.r.t. x and every parameter.
 """
@@ -43,15 +46,26 @@ def ref_kl(layer):
     """kl_loss() with 'normal' semantics for every layer class."""
     w = "mu_weight" if hasattr(layer, "mu_weight") else "mu_kernel"
     r = w.replace("mu", "rho")
+    ps = layer.prior_weight_sigma
+    if ps.shape != getattr(layer, w).shape:
+        # ConvTranspose1dFlipout / ConvTranspose2dFlipout register prior_weight_sigma as [c_out, c_in/g, *k]
+        # although the kernel is [c_in, c_out/g, *k] (conv_flipout.py:706-709, :904-908): kl_div cannot
+        # broadcast it unless c_in == c_out.  The buffer is a constant fill, so the shape-correct constant is used.
+        ps = torch.full_like(getattr(layer, w), float(layer.prior_variance))
     kl = layer.kl_div(getattr(layer, w), torch.log1p(torch.exp(getattr(layer, r))),
-                      layer.prior_weight_mu, layer.prior_weight_sigma, "normal")
+                      layer.prior_weight_mu, ps, "normal")
     if layer.mu_bias is not None:
         kl = kl + layer.kl_div(layer.mu_bias, torch.log1p(torch.exp(layer.rho_bias)),
                                layer.prior_bias_mu, layer.prior_bias_sigma, "normal")
     return kl
 
 
+ONLY = None  # `python oracle/make_golden.py <prefix> ...`: write only the fixtures whose name starts with a prefix
+
+
 def run_case(name, layer, x, flipout=False, seed=0, extra=None):
+    if ONLY and not any(name.startswith(p) for p in ONLY):
+        return
     torch.manual_seed(1000 + seed)
     x = x.clone().requires_grad_(True)
     torch.manual_seed(2000 + seed)
@@ -144,6 +158,34 @@ def main():
     run_case("conv2d_fo_s2_nobias", L.Conv2dFlipout(6, 8, 3, stride=2, padding=1, bias=False), R(2, 6, 11, 11),
              flipout=True, seed=33, extra=cfg(stride=2, padding=1, dilation=1, groups=1))
 
+    # ---- Conv1d / Conv3d Flipout (conv_flipout.py:57, :443) ----
+    run_case("conv1d_fo_k3_s2", L.Conv1dFlipout(6, 10, 3, stride=2, padding=1), R(3, 6, 25), flipout=True, seed=34,
+             extra=cfg(stride=2, padding=1, dilation=1, groups=1))
+    run_case("conv3d_fo_k3", L.Conv3dFlipout(4, 6, 3, padding=1, bias=False), R(2, 4, 5, 6, 4), flipout=True, seed=35,
+             extra=cfg(stride=1, padding=1, dilation=1, groups=1))
+
+    # ---- ConvTranspose{1,2,3}d Reparameterization (conv_variational.py:822, :992, :1167) and Flipout
+    #      (conv_flipout.py:640, :834, :1033); kernel [c_in, c_out / groups, *k] ----
+    def ct(**kw):
+        return cfg(stride=kw.get("stride", 1), padding=kw.get("padding", 0), dilation=kw.get("dilation", 1),
+                   groups=kw.get("groups", 1), output_padding=kw.get("output_padding", 0))
+    kw = dict(stride=2, padding=1, output_padding=1)
+    run_case("convT1d_rp_k3_s2", L.ConvTranspose1dReparameterization(6, 10, 3, **kw), R(3, 6, 9), seed=60, extra=ct(**kw))
+    kw = dict(stride=2, padding=1, output_padding=1)
+    run_case("convT2d_rp_k3_s2", L.ConvTranspose2dReparameterization(8, 12, (3, 3), **kw), R(2, 8, 7, 6), seed=61, extra=ct(**kw))
+    kw = dict(stride=1, padding=2, dilation=2, groups=2)
+    run_case("convT2d_rp_dil2_groups2_nobias", L.ConvTranspose2dReparameterization(8, 12, (3, 3), bias=False, **kw),
+             R(2, 8, 6, 6), seed=62, extra=ct(**kw))
+    kw = dict(stride=2, padding=0)
+    run_case("convT3d_rp_k2_s2", L.ConvTranspose3dReparameterization(4, 6, (2, 2, 2), **kw), R(2, 4, 3, 4, 3), seed=63, extra=ct(**kw))
+    kw = dict(stride=2, padding=1, output_padding=1)
+    run_case("convT1d_fo_k3_s2", L.ConvTranspose1dFlipout(6, 10, 3, **kw), R(3, 6, 9), flipout=True, seed=64, extra=ct(**kw))
+    kw = dict(stride=2, padding=1, output_padding=1)
+    run_case("convT2d_fo_k3_s2", L.ConvTranspose2dFlipout(8, 12, (3, 3), **kw), R(2, 8, 5, 6), flipout=True, seed=65, extra=ct(**kw))
+    kw = dict(stride=1, padding=1)
+    run_case("convT3d_fo_k3_nobias", L.ConvTranspose3dFlipout(4, 6, (3, 3, 3), bias=False, **kw), R(2, 4, 3, 4, 3), flipout=True,
+             seed=66, extra=ct(**kw))
+
     # ---- MOPED rho (utils/util.py:63-69) and tensor-valued priors (utils/util.py:101-104) ----
     w = R(40, 30) * 0.05
     lay = L.LinearReparameterization(30, 40)
@@ -155,6 +197,8 @@ def main():
              extra={"moped_w": w, "moped_delta": np.asarray(0.5), "moped_rho": U.get_rho(w, 0.5),
                     "prior_w_mu": lay.prior_weight_mu, "prior_w_sigma": lay.prior_weight_sigma})
 
+    if ONLY and not any("dnn_to_bnn_small".startswith(p) for p in ONLY):
+        return
     # ---- dnn_to_bnn + get_kl_loss on a small torch model (models/dnn_to_bnn.py:127-165) ----
     torch.manual_seed(50)
     net = torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3, padding=1), torch.nn.ReLU(), torch.nn.Conv2d(8, 8, 3, stride=2, bias=False),
@@ -185,4 +229,5 @@ def main():
 
 
 if __name__ == "__main__":
+    ONLY = sys.argv[1:] or None
     main()

@@ -36,7 +36,7 @@ def cfg_of(d):
         v = np.asarray(v)
         return int(v) if v.ndim == 0 else tuple(int(i) for i in v)
     c = {k[4:]: d[k] for k in d if k.startswith("cfg_")}
-    out = {k: conv(c[k]) for k in ("stride", "padding", "dilation", "groups") if k in c}
+    out = {k: conv(c[k]) for k in ("stride", "padding", "dilation", "groups", "output_padding") if k in c}
     out["prior_mu"] = float(c.get("prior_mean", 0.0))
     out["prior_sigma"] = float(c.get("prior_variance", 1.0))
     return out

@@ -26,6 +26,14 @@ SIGS = {
     "Conv2dFlipout": ["in_channels", "out_channels", "kernel_size", "stride", "padding", "dilation", "groups",
                       "prior_mean", "prior_variance", "posterior_mu_init", "posterior_rho_init", "bias"],
 }
+_CONV_FO = SIGS["Conv2dFlipout"]
+SIGS["Conv1dFlipout"] = SIGS["Conv3dFlipout"] = _CONV_FO                                  # conv_flipout.py:58-70, :444-456
+_CT_A = _CONV_FO[:7] + ["output_padding"] + _CONV_FO[7:]                                     # output_padding after groups
+_CT_B = _CONV_FO[:5] + ["output_padding"] + _CONV_FO[5:]                                     # output_padding after padding
+for _r in "123":                                                                             # conv_variational.py:822-1340
+    SIGS[f"ConvTranspose{_r}dReparameterization"] = _CT_A
+SIGS["ConvTranspose1dFlipout"] = _CT_A                                                       # conv_flipout.py:641-654
+SIGS["ConvTranspose2dFlipout"] = SIGS["ConvTranspose3dFlipout"] = _CT_B                      # conv_flipout.py:835-848, :1034-1047
 
 
 @pytest.mark.parametrize("name", sorted(SIGS))
@@ -53,6 +61,28 @@ def test_names_shapes_and_state_dict():
         L.Conv2dReparameterization(6, 8, 3, groups=4)
     lin.dnn_to_bnn_flag = True
     assert lin.dnn_to_bnn_flag is True
+
+
+def test_transposed_and_flipout_conv_shapes():
+    """ConvTranspose kernels are [c_in, c_out / groups, *k] with a c_out-sized bias (conv_variational.py:876-905)."""
+    for r, k in ((1, (3,)), (2, (3, 2)), (3, (2, 3, 2))):
+        for kind in ("Reparameterization", "Flipout"):
+            t = getattr(L, f"ConvTranspose{r}d{kind}")(8, 12, k, groups=2)
+            assert t.mu_kernel.shape == t.eps_kernel.shape == t.prior_weight_sigma.shape == (8, 6, *k)
+            assert t.mu_bias.shape == t.prior_bias_mu.shape == (12,)
+            assert t.output_padding == 0 and repr(t) == f"ConvTranspose{r}d{kind}()"
+            assert sorted(t.state_dict()) == ["mu_bias", "mu_kernel", "rho_bias", "rho_kernel"]
+    assert L.Conv1dFlipout(4, 6, 3).mu_kernel.shape == (6, 4, 3)
+    assert L.Conv3dFlipout(4, 6, (3, 2, 1), bias=False).mu_kernel.shape == (6, 4, 3, 2, 1)
+    with pytest.raises(ValueError, match="invalid in_channels size"):
+        L.ConvTranspose2dFlipout(6, 8, 3, groups=4)
+    net = torch.nn.Sequential(torch.nn.ConvTranspose2d(4, 6, 3, stride=2), torch.nn.Conv1d(3, 5, 3), torch.nn.Conv3d(2, 4, 3))
+    params = {"prior_mu": 0.0, "prior_sigma": 1.0, "posterior_mu_init": 0.0, "posterior_rho_init": -3.0,
+              "type": "Flipout", "moped_enable": True, "moped_delta": 0.5}
+    w = net[0].weight.detach().clone()
+    bt.dnn_to_bnn(net, params)   # dispatches on any class name containing "Conv" (dnn_to_bnn.py:131-139)
+    assert [type(m).__name__ for m in net] == ["ConvTranspose2dFlipout", "Conv1dFlipout", "Conv3dFlipout"]
+    torch.testing.assert_close(net[0].mu_kernel.detach(), w)   # MOPED copies the [c_in, c_out, k, k] weight as is
 
 
 def test_dtype_casts_keep_fp32_masters():

@@ -16,13 +16,19 @@ def run_oracle(name, d, dtype=torch.float32):
     prior = dict(prior_mu=c["prior_mu"], prior_sigma=c["prior_sigma"])
     if "prior_w_mu" in d:  # tensor-valued prior (utils/util.py:101-104)
         prior = None
-    conv_kw = {k: c[k] for k in ("stride", "padding", "dilation", "groups") if k in c}
+    conv_kw = {k: c[k] for k in ("stride", "padding", "dilation", "groups", "output_padding") if k in c}
     leaves = {k: d[k].clone().to(dtype).requires_grad_(True) for k in ("x", "mu_w", "rho_w", "mu_b", "rho_b") if k in d}
     g = lambda k: leaves.get(k)
     eps_b = d.get("eps_b")
     if name.startswith("linear_rp"):
         out, kl = oracle.linear_reparam(g("x"), g("mu_w"), g("rho_w"), g("mu_b"), g("rho_b"), d["eps_w"], eps_b,
                                         dtype=dtype, **(prior or {}))
+    elif name.startswith("convT") and "_rp_" in name:
+        out, kl = oracle.conv_transpose_reparam(g("x"), g("mu_w"), g("rho_w"), g("mu_b"), g("rho_b"), d["eps_w"], eps_b,
+                                                dtype=dtype, **conv_kw, **prior)
+    elif name.startswith("convT"):
+        out, kl = oracle.conv_transpose_flipout(g("x"), g("mu_w"), g("rho_w"), g("mu_b"), g("rho_b"), d["eps_w"], eps_b,
+                                                d["sign_in"], d["sign_out"], dtype=dtype, **conv_kw, **prior)
     elif "_rp_" in name:
         out, kl = oracle.conv_reparam(g("x"), g("mu_w"), g("rho_w"), g("mu_b"), g("rho_b"), d["eps_w"], eps_b,
                                       dtype=dtype, **conv_kw, **prior)

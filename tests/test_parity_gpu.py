@@ -30,8 +30,14 @@ def build_layer(name, d, dev):
     w = d["mu_w"]
     bias = "mu_b" in d
     pm, ps = c["prior_mu"], c["prior_sigma"]
-    conv_kw = {k: c[k] for k in ("stride", "padding", "dilation", "groups") if k in c}
-    if name.startswith("linear_rp"):
+    conv_kw = {k: c[k] for k in ("stride", "padding", "dilation", "groups", "output_padding") if k in c}
+    if name.startswith("convT"):   # kernel [c_in, c_out / groups, *k]
+        cls = getattr(L, f"ConvTranspose{name[5]}d" + ("Reparameterization" if "_rp_" in name else "Flipout"))
+        layer = cls(w.shape[0], w.shape[1] * conv_kw["groups"], tuple(w.shape[2:]), bias=bias, **conv_kw)
+    elif name.startswith("conv1d_fo") or name.startswith("conv3d_fo"):
+        cls = L.Conv1dFlipout if name.startswith("conv1d") else L.Conv3dFlipout
+        layer = cls(w.shape[1] * conv_kw["groups"], w.shape[0], tuple(w.shape[2:]), bias=bias, **conv_kw)
+    elif name.startswith("linear_rp"):
         layer = L.LinearReparameterization(w.shape[1], w.shape[0], prior_mean=pm, prior_variance=ps, bias=bias)
     elif name.startswith("linear_fo"):
         layer = L.LinearFlipout(w.shape[1], w.shape[0], bias=bias)
