@@ -62,6 +62,9 @@ SIGNATURES = {
                                      C.c_int, C.c_float, C.c_float, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                      C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                      C.c_void_p, C.c_void_p, C.c_void_p]),
+    "bt_kl_laplace_multi": (C.c_int, [C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int64),
+                                      C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                      C.c_void_p, C.c_void_p, C.c_void_p]),
     "bt_linear_reparam_fwd": (C.c_int, _FWD),
     "bt_conv_reparam_fwd": (C.c_int, _FWD),
     "bt_linear_flipout_fwd": (C.c_int, _FWD),
@@ -99,7 +102,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
-        if handle.bt_abi_version() != 3:
+        if handle.bt_abi_version() != 4:
             raise RuntimeError("libbt_b200.so ABI version mismatch")
         _lib = handle
     return _lib

@@ -31,6 +31,7 @@ struct KlTable {
   int32_t n;
   int32_t total_chunks;
   int32_t q_is_sigma;
+  int32_t laplace;  // the fork's 'laplace' prior: KL(N(mu, sigma) || Laplace(0, 1)), analytic (base_variational_layer.py:74-97)
   float prior_mu, prior_sigma;
 };
 
@@ -82,7 +83,33 @@ __device__ __forceinline__ KlElem kl_elem(float mu, float rho, float pm, const K
   return e;
 }
 
-template <bool kGrad, bool kTensorPrior>
+// KL(N(mu, sigma) || Laplace(mu_p = 0, b = 1)) as the fork's kl_div('laplace') writes it
+// (base_variational_layer.py:74-97; location and scale are hard-coded there):
+//   log(2b) - 0.5 log(2 pi sigma^2) - 0.5 + E|w| / b,   E|w| = sigma sqrt(2/pi) exp(-mu^2 / 2 sigma^2) + mu erf(mu / (sigma sqrt 2))
+// (1 - 2 Phi(-z) = erf(z / sqrt 2)).  d/dmu = erf(mu / (sigma sqrt 2)),  d/dsigma = -1/sigma + sqrt(2/pi) exp(-mu^2 / 2 sigma^2).
+template <bool kGrad>
+__device__ __forceinline__ KlElem kl_elem_laplace(float mu, float rho, bool q_is_sigma) {
+  float sig, dsig_drho;
+  if (q_is_sigma) {
+    sig = rho;
+    dsig_drho = 1.f;
+  } else {
+    const float t = expf(fminf(rho, 30.f));
+    sig = rho > 20.f ? rho : log1pf(t);
+    dsig_drho = rho > 20.f ? 1.f : t / (1.f + t);
+  }
+  const float inv = 1.f / sig;
+  const float z = mu * inv;
+  const float g = 0.7978845608028654f * expf(-0.5f * z * z);  // sqrt(2/pi) exp(-mu^2 / 2 sigma^2)
+  const float er = erff(z * 0.7071067811865476f);
+  KlElem e;
+  e.kl = (0.6931471805599453f - 0.9189385332046727f - logf(sig) - 0.5f) + (sig * g + mu * er);
+  e.dmu = kGrad ? er : 0.f;
+  e.drho = kGrad ? (g - inv) * dsig_drho : 0.f;
+  return e;
+}
+
+template <bool kGrad, bool kTensorPrior, bool kLaplace = false>
 __global__ void __launch_bounds__(KL_THREADS) kl_normal_multi_kernel(const __grid_constant__ KlTable tab,
                                                                       double* __restrict__ acc,
                                                                       unsigned int* __restrict__ done_counter,
@@ -137,10 +164,18 @@ __global__ void __launch_bounds__(KL_THREADS) kl_normal_multi_kernel(const __gri
           if (psig) ps4 = __ldcs(reinterpret_cast<const float4*>(psig + off));
         }
         const bool tp = kTensorPrior && psig != nullptr;
-        const KlElem e0 = kl_elem<kGrad>(m4[i].x, r4[i].x, pm4.x, tp ? kl_prior(ps4.x) : prior_c, qsig);
-        const KlElem e1 = kl_elem<kGrad>(m4[i].y, r4[i].y, pm4.y, tp ? kl_prior(ps4.y) : prior_c, qsig);
-        const KlElem e2 = kl_elem<kGrad>(m4[i].z, r4[i].z, pm4.z, tp ? kl_prior(ps4.z) : prior_c, qsig);
-        const KlElem e3 = kl_elem<kGrad>(m4[i].w, r4[i].w, pm4.w, tp ? kl_prior(ps4.w) : prior_c, qsig);
+        KlElem e0, e1, e2, e3;
+        if constexpr (kLaplace) {
+          e0 = kl_elem_laplace<kGrad>(m4[i].x, r4[i].x, qsig);
+          e1 = kl_elem_laplace<kGrad>(m4[i].y, r4[i].y, qsig);
+          e2 = kl_elem_laplace<kGrad>(m4[i].z, r4[i].z, qsig);
+          e3 = kl_elem_laplace<kGrad>(m4[i].w, r4[i].w, qsig);
+        } else {
+          e0 = kl_elem<kGrad>(m4[i].x, r4[i].x, pm4.x, tp ? kl_prior(ps4.x) : prior_c, qsig);
+          e1 = kl_elem<kGrad>(m4[i].y, r4[i].y, pm4.y, tp ? kl_prior(ps4.y) : prior_c, qsig);
+          e2 = kl_elem<kGrad>(m4[i].z, r4[i].z, pm4.z, tp ? kl_prior(ps4.z) : prior_c, qsig);
+          e3 = kl_elem<kGrad>(m4[i].w, r4[i].w, pm4.w, tp ? kl_prior(ps4.w) : prior_c, qsig);
+        }
         part += (e0.kl + e1.kl) + (e2.kl + e3.kl);
         if (kGrad) {
           if (dmu) __stcs(reinterpret_cast<float4*>(dmu + off), make_float4(e0.dmu * gs, e1.dmu * gs, e2.dmu * gs, e3.dmu * gs));
@@ -151,7 +186,8 @@ __global__ void __launch_bounds__(KL_THREADS) kl_normal_multi_kernel(const __gri
       for (int64_t i = base + tid; i < end; i += KL_THREADS) {
         const float pm = (kTensorPrior && pmu) ? pmu[i] : tab.prior_mu;
         const float ps = (kTensorPrior && psig) ? psig[i] : tab.prior_sigma;
-        const KlElem e = kl_elem<kGrad>(mu[i], rho[i], pm, (kTensorPrior && psig) ? kl_prior(ps) : prior_c, qsig);
+        const KlElem e = kLaplace ? kl_elem_laplace<kGrad>(mu[i], rho[i], qsig)
+                                  : kl_elem<kGrad>(mu[i], rho[i], pm, (kTensorPrior && psig) ? kl_prior(ps) : prior_c, qsig);
         part += e.kl;
         if (kGrad) {
           if (dmu) dmu[i] = e.dmu * gs;
@@ -205,11 +241,11 @@ int64_t bt_kl_workspace_bytes_internal(int n) { return kl_workspace_bytes(n < 1 
 static int kl_launch(int n, const float* const* mu, const float* const* rho, const int64_t* numel, int q_is_sigma,
                      float prior_mu, float prior_sigma, const float* const* pmu_t, const float* const* psig_t,
                      float* kl_each, float* kl_total, float* const* d_mu, float* const* d_rho,
-                     const float* grad_scale, void* workspace, cudaStream_t stream) {
+                     const float* grad_scale, void* workspace, cudaStream_t stream, bool laplace = false) {
   BT_REQUIRE(n >= 1 && n <= KL_MAX_TENSORS, BT_ERR_INVALID, "bt_kl_normal_multi: n=%d outside [1,%d]", n,
              KL_MAX_TENSORS);
   BT_REQUIRE(mu && rho && numel && workspace, BT_ERR_INVALID, "bt_kl_normal_multi: null table or workspace");
-  BT_REQUIRE(prior_sigma > 0.f || psig_t, BT_ERR_INVALID, "bt_kl_normal_multi: prior_sigma must be > 0");
+  BT_REQUIRE(laplace || prior_sigma > 0.f || psig_t, BT_ERR_INVALID, "bt_kl_normal_multi: prior_sigma must be > 0");
   KlTable tab;
   bool any_tensor_prior = false;
   const bool grad = (d_mu != nullptr) || (d_rho != nullptr);
@@ -231,6 +267,7 @@ static int kl_launch(int n, const float* const* mu, const float* const* rho, con
   tab.n = n;
   tab.total_chunks = (int32_t)chunks;
   tab.q_is_sigma = q_is_sigma;
+  tab.laplace = laplace ? 1 : 0;
   tab.prior_mu = prior_mu;
   tab.prior_sigma = prior_sigma;
 
@@ -243,7 +280,10 @@ static int kl_launch(int n, const float* const* mu, const float* const* rho, con
   if (grid < 1) grid = 1;
 #define KL_GO(G, T)                                                                                         \
   kl_normal_multi_kernel<G, T><<<grid, KL_THREADS, 0, stream>>>(tab, acc, counter, kl_each, kl_total, grad_scale)
-  if (grad) {
+  if (laplace) {
+    if (grad) kl_normal_multi_kernel<true, false, true><<<grid, KL_THREADS, 0, stream>>>(tab, acc, counter, kl_each, kl_total, grad_scale);
+    else kl_normal_multi_kernel<false, false, true><<<grid, KL_THREADS, 0, stream>>>(tab, acc, counter, kl_each, kl_total, grad_scale);
+  } else if (grad) {
     if (any_tensor_prior) KL_GO(true, true); else KL_GO(true, false);
   } else {
     if (any_tensor_prior) KL_GO(false, true); else KL_GO(false, false);
@@ -260,6 +300,13 @@ extern "C" int bt_kl_normal_multi(int n, const float* const* mu, const float* co
                                   void* workspace, bt_stream_t stream) {
   return kl_launch(n, mu, rho, numel, q_is_sigma, prior_mu, prior_sigma, prior_mu_t, prior_sigma_t, kl_each, kl_total,
                    d_mu, d_rho, grad_scale, workspace, (cudaStream_t)stream);
+}
+
+extern "C" int bt_kl_laplace_multi(int n, const float* const* mu, const float* const* rho, const int64_t* numel,
+                                   int q_is_sigma, float* kl_each, float* kl_total, float* const* d_mu, float* const* d_rho,
+                                   const float* grad_scale, void* workspace, bt_stream_t stream) {
+  return kl_launch(n, mu, rho, numel, q_is_sigma, 0.f, 1.f, nullptr, nullptr, kl_each, kl_total, d_mu, d_rho, grad_scale,
+                   workspace, (cudaStream_t)stream, true);
 }
 
 // kl(weight) + kl(bias) of one layer, as forward(return_kl=True) returns it.

@@ -54,10 +54,10 @@ class BaseVariationalLayer_(nn.Module):
         Conv2d default of None raises there)."""
         if prior_type is None:
             prior_type = "normal"
-        if prior_type == "laplace":
-            raise NotImplementedError("the fork's 'laplace' prior is outside this build's hot path (SURVEY.md 8f)")
-        if prior_type != "normal":
+        if prior_type not in ("normal", "laplace"):
             raise ValueError(f"Unknown prior_type: {prior_type}")
+        if prior_type == "laplace":   # location 0 / scale 1 hard-coded by the fork (base_variational_layer.py:80-81)
+            return ops.kl_normal_multi([mu_q], [sigma_q], q_is_sigma=True, prior_type="laplace")
 
         def split(p):
             if torch.is_tensor(p) and p.numel() > 1:
@@ -176,7 +176,19 @@ class _BayesLayer(BaseVariationalLayer_):
         mus, rhos, pm, ps = [mu_w], [rho_w], [pt[0]], [pt[1]]
         if self.mu_bias is not None:
             mus.append(self.mu_bias); rhos.append(self.rho_bias); pm.append(pt[2]); ps.append(pt[3])
+        if self._prior_kind() == "laplace":
+            return ops.kl_normal_multi(mus, rhos, prior_type="laplace")
         return ops.kl_normal_multi(mus, rhos, float(self.prior_mean), float(self.prior_variance), pm, ps)
+
+    def _prior_kind(self):
+        """'normal' or 'laplace': the fork's prior_type argument (Linear / Conv2d Reparameterization only;
+        None reads as 'normal')."""
+        pt = getattr(self, "prior_type", None)
+        if pt is None:
+            return "normal"
+        if pt not in ("normal", "laplace"):
+            raise ValueError(f"Unknown prior_type: {pt}")
+        return pt
 
     # -- forward ----------------------------------------------------------------------------
     def _conv_args(self):
@@ -211,7 +223,8 @@ class _BayesLayer(BaseVariationalLayer_):
         call.seed, call.layer_id = ops.get_seed(), self._layer_id
         call.n_samples = ops.current_n_samples()
         call.x_shared = call.n_samples > 1 and ops._STATE.shared_batch is not None and x.shape[0] == ops._STATE.shared_batch
-        call.want_kl = bool(return_kl)
+        laplace = self._prior_kind() == "laplace"   # its KL is a separate launch (kl_loss), not the fused normal-prior one
+        call.want_kl = bool(return_kl) and not laplace
         call.path = ops._PATHS[self.path or ops.get_path()]
         call.out_scale, call.out_shift, call.out_relu = self._ep_scale, self._ep_shift, self._ep_relu
         call.residual = residual
@@ -241,7 +254,7 @@ class _BayesLayer(BaseVariationalLayer_):
         if lead is not None:
             out = out.reshape(-1, *lead[1:], out.shape[-1])   # leading axis may be folded S*B
         if return_kl:
-            return out, kl
+            return out, (self.kl_loss() if laplace else kl)
         return out
 
     def _forward_transpose(self, x, return_kl):

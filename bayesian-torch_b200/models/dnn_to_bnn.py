@@ -72,14 +72,14 @@ def dnn_to_bnn(m, bnn_prior_parameters):
 
 def get_kl_loss(m):
     """Sum over modules having kl_loss() of weight-KL-mean + bias-KL-mean (dnn_to_bnn.py:157-165).
-    Native layers are batched into one launch per distinct (prior_mu, prior_sigma)."""
+    Native layers are batched into one launch per distinct (prior_mu, prior_sigma, prior_type)."""
     groups = {}
     other = None
     for layer in m.modules():
         if not hasattr(layer, "kl_loss"):
             continue
         if isinstance(layer, bayesian_layers.base_variational_layer._BayesLayer):
-            key = (float(layer.prior_mean), float(layer.prior_variance))
+            key = (float(layer.prior_mean), float(layer.prior_variance), layer._prior_kind())
             g = groups.setdefault(key, ([], [], [], []))
             mu_w, rho_w = layer._w()
             pt = layer._prior_tensors()
@@ -90,7 +90,7 @@ def get_kl_loss(m):
             kl = layer.kl_loss()
             other = kl if other is None else other + kl
     total = other
-    for (pm, ps), (mus, rhos, pmt, pst) in groups.items():
-        kl = ops.kl_normal_multi(mus, rhos, pm, ps, pmt, pst)
+    for (pm, ps, kind), (mus, rhos, pmt, pst) in groups.items():
+        kl = ops.kl_normal_multi(mus, rhos, pm, ps, pmt, pst, prior_type=kind)
         total = kl if total is None else total + kl
     return total

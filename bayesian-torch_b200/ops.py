@@ -202,7 +202,7 @@ def kl_workspace(n: int, device) -> torch.Tensor:
 
 
 def _kl_call(mus, rhos, q_is_sigma, prior_mu, prior_sigma, pmu_t, psig_t, want_each, d_mu=None, d_rho=None,
-             grad_scale=None):
+             grad_scale=None, prior_type="normal"):
     dev = _require_cuda(*mus, *rhos)
     n = len(mus)
     numel = (C.c_int64 * n)(*[m.numel() for m in mus])
@@ -210,6 +210,14 @@ def _kl_call(mus, rhos, q_is_sigma, prior_mu, prior_sigma, pmu_t, psig_t, want_e
     total = torch.empty((), dtype=torch.float32, device=dev)
     ws = kl_workspace(n, dev)
     any_pt = any(t is not None for t in pmu_t) or any(t is not None for t in psig_t)
+    if prior_type == "laplace":
+        with torch.cuda.device(dev):
+            rc = _lib.lib().bt_kl_laplace_multi(
+                n, _ptr_array(mus), _ptr_array(rhos), numel, int(q_is_sigma), _ptr(each), _ptr(total),
+                _ptr_array(d_mu) if d_mu is not None else None, _ptr_array(d_rho) if d_rho is not None else None,
+                _ptr(grad_scale), _ptr(ws), _stream())
+        _lib.check(rc, "bt_kl_laplace_multi")
+        return total, each
     with torch.cuda.device(dev):
         rc = _lib.lib().bt_kl_normal_multi(
             n, _ptr_array(mus), _ptr_array(rhos), numel, int(q_is_sigma), float(prior_mu), float(prior_sigma),
@@ -229,7 +237,7 @@ class _KLMulti(torch.autograd.Function):
         mus = [_f32c(p.detach(), "mu") for p in params[:n]]
         rhos = [_f32c(p.detach(), "rho") for p in params[n:]]
         total, _ = _kl_call(mus, rhos, cfg["q_is_sigma"], cfg["prior_mu"], cfg["prior_sigma"], cfg["pmu_t"],
-                            cfg["psig_t"], False)
+                            cfg["psig_t"], False, prior_type=cfg.get("prior_type", "normal"))
         ctx.cfg = cfg
         ctx.save_for_backward(*params)
         return total
@@ -245,20 +253,26 @@ class _KLMulti(torch.autograd.Function):
         d_rho = [torch.empty_like(r) for r in rhos]
         gs = g.detach().to(torch.float32).contiguous()
         _kl_call(mus, rhos, cfg["q_is_sigma"], cfg["prior_mu"], cfg["prior_sigma"], cfg["pmu_t"], cfg["psig_t"], False,
-                 d_mu, d_rho, gs)
+                 d_mu, d_rho, gs, prior_type=cfg.get("prior_type", "normal"))
         grads = [d.view_as(p) for d, p in zip(d_mu + d_rho, params)]
         return (None, *grads)
 
 
 def kl_normal_multi(mus: Sequence[torch.Tensor], rhos: Sequence[torch.Tensor], prior_mu: float = 0.0,
                     prior_sigma: float = 1.0, prior_mu_t: Optional[Sequence] = None,
-                    prior_sigma_t: Optional[Sequence] = None, q_is_sigma: bool = False) -> torch.Tensor:
+                    prior_sigma_t: Optional[Sequence] = None, q_is_sigma: bool = False,
+                    prior_type: str = "normal") -> torch.Tensor:
     """Sum over tensors of the mean element-wise Gaussian KL (base_variational_layer.py:70-72).
-    One kernel launch for the whole table; differentiable w.r.t. every mu and rho."""
+    One kernel launch for the whole table; differentiable w.r.t. every mu and rho.
+    prior_type 'laplace': the fork's KL(N || Laplace(0, 1)) (base_variational_layer.py:74-97), which
+    ignores the prior arguments."""
     n = len(mus)
     if n == 0:
         raise ValueError("kl_normal_multi: empty tensor list")
+    if prior_type not in ("normal", "laplace"):
+        raise ValueError(f"Unknown prior_type: {prior_type}")
     cfg = {
+        "prior_type": prior_type,
         "q_is_sigma": bool(q_is_sigma), "prior_mu": float(prior_mu), "prior_sigma": float(prior_sigma),
         "pmu_t": [None if t is None else _f32c(t.detach(), "prior_mu") for t in (prior_mu_t or [None] * n)],
         "psig_t": [None if t is None else _f32c(t.detach(), "prior_sigma") for t in (prior_sigma_t or [None] * n)],

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define BT_ABI_VERSION 3
+#define BT_ABI_VERSION 4
 
 typedef void* bt_stream_t; /* cudaStream_t */
 
@@ -157,6 +157,15 @@ int bt_kl_normal_multi(int n, const float* const* mu, const float* const* rho, c
                        const float* const* prior_mu_t, const float* const* prior_sigma_t,
                        float* kl_each, float* kl_total, float* const* d_mu, float* const* d_rho,
                        const float* grad_scale, void* workspace, bt_stream_t stream);
+
+/* ---- KL(N(mu, sigma) || Laplace(0, 1)): replaces the 'laplace' branch the fork added to
+ *      BaseVariationalLayer_.kl_div (base_variational_layer.py:74-97; location 0 and scale 1
+ *      are hard-coded there, whatever mu_p / sigma_p the caller passes), analytic form
+ *      log 2 - 0.5 log(2 pi sigma^2) - 0.5 + E|w|, mean over elements.  Arguments as
+ *      bt_kl_normal_multi without the prior. */
+int bt_kl_laplace_multi(int n, const float* const* mu, const float* const* rho, const int64_t* numel,
+                        int q_is_sigma, float* kl_each, float* kl_total, float* const* d_mu, float* const* d_rho,
+                        const float* grad_scale, void* workspace, bt_stream_t stream);
 
 /* ---- Reparameterization forward: replaces LinearReparameterization.forward
  *      (linear_variational.py:160-204) and Conv{1,2,3}dReparameterization.forward

@@ -15,7 +15,7 @@ import torch
 import torch.nn.functional as F
 
 __all__ = [
-    "softplus_ref", "kl_normal", "kl_normal_from_rho", "sample_weight",
+    "softplus_ref", "kl_normal", "kl_laplace", "kl_normal_from_rho", "sample_weight",
     "linear_reparam", "conv_reparam", "linear_flipout", "conv_flipout",
     "conv_transpose_reparam", "conv_transpose_flipout",
     "get_rho", "mc_moments", "predictive_entropy", "mutual_information",
@@ -40,6 +40,19 @@ def kl_normal(mu_q, sigma_q, mu_p, sigma_p) -> torch.Tensor:
     sigma_p = torch.as_tensor(sigma_p, dtype=mu_q.dtype)
     kl = (torch.log(sigma_p) - torch.log(sigma_q)
           + (sigma_q ** 2 + (mu_q - mu_p) ** 2) / (2 * (sigma_p ** 2)) - 0.5)
+    return kl.mean()
+
+
+def kl_laplace(mu_q, sigma_q) -> torch.Tensor:
+    """The fork's analytic KL(N(mu_q, sigma_q) || Laplace(0, 1)) then .mean()
+    (layers/base_variational_layer.py:74-97: b_p = 1 and mu_p = 0 are hard-coded, the
+    caller's prior arguments are ignored).  E|w| is the folded-normal mean."""
+    std_normal = torch.distributions.Normal(torch.zeros((), dtype=mu_q.dtype), torch.ones((), dtype=mu_q.dtype))
+    b_p = torch.tensor(1.0, dtype=mu_q.dtype)
+    off = mu_q - torch.tensor(0.0, dtype=mu_q.dtype)
+    exp_abs = (sigma_q * math.sqrt(2.0 / math.pi) * torch.exp(-off ** 2 / (2 * sigma_q ** 2))
+               + off * (1 - 2 * std_normal.cdf(-off / sigma_q)))
+    kl = torch.log(2 * b_p) - 0.5 * torch.log(2 * math.pi * sigma_q ** 2) - 0.5 + (1 / b_p) * exp_abs
     return kl.mean()
 
 

@@ -63,14 +63,20 @@ def ref_kl(layer):
 ONLY = None  # `python oracle/make_golden.py <prefix> ...`: write only the fixtures whose name starts with a prefix
 
 
-def run_case(name, layer, x, flipout=False, seed=0, extra=None):
+def run_case(name, layer, x, flipout=False, seed=0, extra=None, laplace=False):
     if ONLY and not any(name.startswith(p) for p in ONLY):
         return
     torch.manual_seed(1000 + seed)
     x = x.clone().requires_grad_(True)
     torch.manual_seed(2000 + seed)
     out = layer(x, return_kl=False)
-    kl = ref_kl(layer)
+    if laplace:   # the fork's own kl_loss() with prior_type='laplace' (it prints on every call)
+        import contextlib
+        import io
+        with contextlib.redirect_stdout(io.StringIO()):
+            kl = layer.kl_loss()
+    else:
+        kl = ref_kl(layer)
     g = torch.randn(out.shape, generator=torch.Generator().manual_seed(3000 + seed))
     loss = (out * g).sum() + KL_COEF * kl
     params = [p for p in layer.parameters()]
@@ -157,6 +163,12 @@ def main():
              extra=cfg(stride=1, padding=1, dilation=1, groups=1))
     run_case("conv2d_fo_s2_nobias", L.Conv2dFlipout(6, 8, 3, stride=2, padding=1, bias=False), R(2, 6, 11, 11),
              flipout=True, seed=33, extra=cfg(stride=2, padding=1, dilation=1, groups=1))
+
+    # ---- the fork's Laplace prior (base_variational_layer.py:74-97): Linear / Conv2d Reparameterization only ----
+    run_case("linear_rp_laplace_24x40", L.LinearReparameterization(40, 24, prior_type="laplace", posterior_rho_init=-1.0), R(6, 40),
+             seed=45, extra={"cfg_prior_type": np.asarray(1)}, laplace=True)
+    run_case("conv2d_rp_laplace_3x3", L.Conv2dReparameterization(6, 8, 3, padding=1, prior_type="laplace"), R(2, 6, 9, 9), seed=46,
+             extra=dict(cfg(stride=1, padding=1, dilation=1, groups=1), cfg_prior_type=np.asarray(1)), laplace=True)
 
     # ---- Conv1d / Conv3d Flipout (conv_flipout.py:57, :443) ----
     run_case("conv1d_fo_k3_s2", L.Conv1dFlipout(6, 10, 3, stride=2, padding=1), R(3, 6, 25), flipout=True, seed=34,

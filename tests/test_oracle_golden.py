@@ -38,6 +38,10 @@ def run_oracle(name, d, dtype=torch.float32):
     else:
         out, kl = oracle.conv_flipout(g("x"), g("mu_w"), g("rho_w"), g("mu_b"), g("rho_b"), d["eps_w"], eps_b,
                                       d["sign_in"], d["sign_out"], dtype=dtype, **conv_kw, **prior)
+    if "cfg_prior_type" in d:  # the fork's Laplace(0, 1) prior (base_variational_layer.py:74-97)
+        kl = oracle.kl_laplace(g("mu_w"), oracle.softplus_ref(g("rho_w")))
+        if g("mu_b") is not None:
+            kl = kl + oracle.kl_laplace(g("mu_b"), oracle.softplus_ref(g("rho_b")))
     if prior is None:
         kl = oracle.kl_normal(g("mu_w"), oracle.softplus_ref(g("rho_w")), d["prior_w_mu"].to(dtype), d["prior_w_sigma"].to(dtype))
         kl = kl + oracle.kl_normal(g("mu_b"), oracle.softplus_ref(g("rho_b")), 0.0, 1.0)

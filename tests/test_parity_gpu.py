@@ -38,7 +38,8 @@ def build_layer(name, d, dev):
         cls = L.Conv1dFlipout if name.startswith("conv1d") else L.Conv3dFlipout
         layer = cls(w.shape[1] * conv_kw["groups"], w.shape[0], tuple(w.shape[2:]), bias=bias, **conv_kw)
     elif name.startswith("linear_rp"):
-        layer = L.LinearReparameterization(w.shape[1], w.shape[0], prior_mean=pm, prior_variance=ps, bias=bias)
+        layer = L.LinearReparameterization(w.shape[1], w.shape[0], prior_mean=pm, prior_variance=ps, bias=bias,
+                                           prior_type="laplace" if "cfg_prior_type" in d else "normal")
     elif name.startswith("linear_fo"):
         layer = L.LinearFlipout(w.shape[1], w.shape[0], bias=bias)
     elif name.startswith("conv1d_rp"):
@@ -47,7 +48,8 @@ def build_layer(name, d, dev):
         layer = L.Conv3dReparameterization(w.shape[1], w.shape[0], tuple(w.shape[2:]), pm, ps, 0, -3.0, bias=bias, **conv_kw)
     elif name.startswith("conv2d_rp"):
         layer = L.Conv2dReparameterization(w.shape[1] * conv_kw["groups"], w.shape[0], tuple(w.shape[2:]), prior_mean=pm,
-                                           prior_variance=ps, prior_type="normal", bias=bias, **conv_kw)
+                                           prior_variance=ps, prior_type="laplace" if "cfg_prior_type" in d else "normal",
+                                           bias=bias, **conv_kw)
     else:
         layer = L.Conv2dFlipout(w.shape[1], w.shape[0], tuple(w.shape[2:]), bias=bias, **conv_kw)
     layer = layer.to(dev)
@@ -204,3 +206,36 @@ def test_dnn_to_bnn_small_model_matches_reference(cuda_device):
     # MOPED on device uses the bt_moped_rho kernel
     w = d["dnn_0.weight"].to(cuda_device)
     close(bt.utils.get_rho(w, 0.5), oracle.get_rho(d["dnn_0.weight"], 0.5), rtol=1e-5, scale_atol=1e-6, msg="moped rho")
+
+
+def test_laplace_prior_kl_div_and_get_kl_loss(cuda_device):
+    """The fork's 'laplace' prior (base_variational_layer.py:74-97): kl_div called directly, kl_loss(),
+    forward(return_kl=True) and get_kl_loss over a model mixing both priors; gradients against autograd
+    through the oracle restatement."""
+    torch.manual_seed(31)
+    lin = L.LinearReparameterization(300, 70, prior_type="laplace", posterior_rho_init=-1.5).to(cuda_device)
+    conv = L.Conv2dReparameterization(8, 16, 3, prior_type="normal").to(cuda_device)
+    with torch.no_grad():
+        lin.mu_weight.mul_(8.0)      # spread mu / sigma over both tails of the erf term
+    mu, rho = lin.mu_weight.detach().cpu(), lin.rho_weight.detach().cpu()
+    want = oracle.kl_laplace(mu.double(), oracle.softplus_ref(rho.double()))
+    got = lin.kl_div(lin.mu_weight, torch.log1p(torch.exp(lin.rho_weight)), 0.3, 2.0, "laplace")   # prior args are ignored
+    close(got, want.float(), rtol=RTOL, scale_atol=1e-6, msg="kl_div laplace")
+    want_l = want + oracle.kl_laplace(lin.mu_bias.detach().cpu().double(), oracle.softplus_ref(lin.rho_bias.detach().cpu().double()))
+    close(lin.kl_loss(), want_l.float(), rtol=RTOL, scale_atol=1e-6, msg="kl_loss laplace")
+    lin.sample_mode, lin.path = "torch", "simt"
+    out, kl = lin(torch.randn(5, 300, device=cuda_device))
+    close(kl, want_l.float(), rtol=RTOL, scale_atol=1e-6, msg="forward kl laplace")
+    net = torch.nn.Sequential(conv, lin)
+    want_n = oracle.kl_normal_from_rho(conv.mu_kernel.detach().cpu(), conv.rho_kernel.detach().cpu(),
+                                       conv.mu_bias.detach().cpu(), conv.rho_bias.detach().cpu())
+    total = bt.get_kl_loss(net)
+    close(total, (want_l + want_n).float(), rtol=RTOL, scale_atol=1e-6, msg="get_kl_loss mixed priors")
+    total.backward()
+    m = lin.mu_weight.detach().cpu().double().requires_grad_(True)
+    r = lin.rho_weight.detach().cpu().double().requires_grad_(True)
+    oracle.kl_laplace(m, oracle.softplus_ref(r)).backward()
+    close(lin.mu_weight.grad, m.grad.float(), rtol=1e-4, scale_atol=1e-5, msg="d kl / d mu (laplace)")
+    close(lin.rho_weight.grad, r.grad.float(), rtol=1e-4, scale_atol=1e-5, msg="d kl / d rho (laplace)")
+    with pytest.raises(ValueError, match="Unknown prior_type"):
+        lin.kl_div(lin.mu_weight, lin.mu_weight.abs() + 1, 0.0, 1.0, "cauchy")
