@@ -11,7 +11,7 @@ from .mc import (MCAccumulator, MCResult, allreduce_gradients, allreduce_moments
                  shard_samples)  # noqa: F401
 from .models.dnn_to_bnn import dnn_to_bnn, get_kl_loss  # noqa: F401
 from .models.fuse import fold_batchnorm  # noqa: F401
-from .ops import (manual_seed, mc_batched, mc_sample, path, sample_mode, set_path,  # noqa: F401
+from .ops import (invalidate_packed, manual_seed, mc_batched, mc_sample, path, sample_mode, set_path,  # noqa: F401
                   set_sample_mode)
 
 __version__ = "0.1.0"

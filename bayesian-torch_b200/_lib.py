@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libbt_b200.so")
 BT_F32, BT_BF16 = 0, 1
 PATH_AUTO, PATH_SIMT_F32, PATH_TC_BF16 = 0, 1, 2
 KIND_EPS_W, KIND_EPS_B, KIND_SIGN_IN, KIND_SIGN_OUT = 0, 1, 2, 3
+FLAG_PACKED_VALID = 1
 
 _i64x3 = C.c_int64 * 3
 
@@ -38,7 +39,7 @@ class LayerParams(C.Structure):
         "prior_mu_w_t", "prior_sigma_w_t", "prior_mu_b_t", "prior_sigma_b_t")] + [
         ("prior_mu", C.c_float), ("prior_sigma", C.c_float),
         ("seed", C.c_uint64), ("sample_id", C.c_uint32), ("layer_id", C.c_uint32),
-        ("out_scale", C.c_void_p), ("out_shift", C.c_void_p), ("out_relu", C.c_int32), ("reserved", C.c_int32),
+        ("out_scale", C.c_void_p), ("out_shift", C.c_void_p), ("out_relu", C.c_int32), ("flags", C.c_int32),
         ("residual", C.c_void_p)]
 
 

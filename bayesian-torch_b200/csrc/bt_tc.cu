@@ -1511,6 +1511,8 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
       tc2_pack_dgrad_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, wn, opt.cin_w, opt.cout_w, pl.T,
                                                              a.K, bt_rng_key(p->seed, p->sample_id, p->layer_id, BT_KIND_EPS_W));
       BT_LAUNCH_OK("tc2_pack_dgrad_kernel");
+    } else if ((p->flags & BT_FLAG_PACKED_VALID) && !p->eps_w) {
+      // frozen inference model: the workspace still holds this layer's packed parameters
     } else {
       tc2_pack_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, p->out_scale, wn, (int)g->c_in, pl.T,
                                                        a.K);

@@ -155,6 +155,10 @@ class _BayesLayer(BaseVariationalLayer_):
             r = fn(t)
             if t.dtype == torch.float32 and r.is_floating_point() and r.dtype != torch.float32:
                 r = r.to(torch.float32)
+            # .to(memory_format=channels_last) would re-stride the 4-d / 5-d kernels; the CUDA path reads them
+            # in the reference's [c_out, c_in/g, *k] order, so a re-strided kernel cost a copy on every call
+            if r.dim() >= 4 and not r.is_contiguous():
+                r = r.contiguous()
             return r
         const = {n: b is not None and self._prior_marks.get(n) == (id(b), b._version)
                  for n, b in self._prior_buffers().items()} if hasattr(self, "_prior_marks") else {}
@@ -228,6 +232,7 @@ class _BayesLayer(BaseVariationalLayer_):
         call.path = ops._PATHS[self.path or ops.get_path()]
         call.out_scale, call.out_shift, call.out_relu = self._ep_scale, self._ep_shift, self._ep_relu
         call.residual = residual
+        call.frozen = bool(getattr(self, "_frozen", False)) and not torch.is_grad_enabled()
         if ops._STATE.sample_override is not None:
             call.sample_id = ops._STATE.sample_override
         else:

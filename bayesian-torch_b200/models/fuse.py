@@ -98,6 +98,7 @@ def fold_batchnorm(model: nn.Module, inplace: bool = False, join_in_epilogue: bo
         layer = modules[node.target]
         if calls[node.target] != 1 or not layer.dnn_to_bnn_flag or layer._flipout:
             continue  # shared module, (out, kl) tuple output, or Flipout (its epilogue has the sign product)
+        layer._frozen = True   # inference-only from here on: the packed parameters are kept between calls (ops._PACKED)
         users = list(node.users)
         if len(users) == 1 and users[0].op == "call_module" and isinstance(modules[users[0].target], _BN) \
                 and calls[users[0].target] == 1 and layer._ep_scale is None:

@@ -7,6 +7,7 @@ is no CPU / eager fallback (BASELINE.json north_star).
 from __future__ import annotations
 
 import contextlib
+import os
 import ctypes as C
 import threading
 from dataclasses import dataclass, field
@@ -316,6 +317,7 @@ class LayerCall:
     out_relu: bool = False
     residual: Optional[torch.Tensor] = None     # added after the affine, before the ReLU (inference only)
     output_padding: Tuple[int, ...] = ()        # ConvTranspose layers only
+    frozen: bool = False                        # inference-only layer (fold_batchnorm): keep the packed parameters
 
 
 def _conv_out_size(i, k, s, p, d):
@@ -374,6 +376,7 @@ def _build_params(call: LayerCall, mu_w, rho_w, mu_b, rho_b) -> Tuple[LayerParam
     p.out_scale, p.out_shift, p.out_relu = _ptr(sc), _ptr(sh), int(bool(call.out_relu))
     p.residual = _ptr(call.residual)
     keep.append(call.residual)
+    p.flags = 0
     return p, keep
 
 
@@ -421,6 +424,31 @@ def _match_strides(t: torch.Tensor, ref: torch.Tensor) -> torch.Tensor:
     return torch.empty_like(ref, dtype=torch.float32).copy_(t)
 
 
+_ZERO = {}
+_PACK_CACHE_ON = os.environ.get("BT_PACK_CACHE", "1") != "0"
+_PACKED = {}   # layer_id -> (key, workspace) of frozen layers (see _BayesLayerFn.forward)
+
+
+def invalidate_packed(model=None) -> None:
+    """Drop the cached packed parameters of every layer of `model` (all layers when None).  Needed only after
+    writing a frozen (fold_batchnorm'd) model's parameters through `.data`, which no version counter sees."""
+    if model is None:
+        _PACKED.clear()
+        return
+    for m in model.modules():
+        _PACKED.pop(getattr(m, "_layer_id", None), None)
+
+
+
+def _zero_scalar(dev) -> torch.Tensor:
+    """fp32 zero on `dev`, created once: what a layer returns for kl when return_kl is off."""
+    key = (dev.type, dev.index)
+    z = _ZERO.get(key)
+    if z is None:
+        z = _ZERO[key] = torch.zeros((), dtype=torch.float32, device=dev)
+    return z
+
+
 class _BayesLayerFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, call: LayerCall, x, mu_w, rho_w, mu_b, rho_b):
@@ -459,7 +487,24 @@ class _BayesLayerFn(torch.autograd.Function):
         p, keep = _build_params(call, mu_wc, rho_wc, mu_bc, rho_bc)
         L = _lib.lib()
         op = b"flipout_fwd" if call.flipout else b"reparam_fwd"
-        ws = torch.empty(max(int(L.bt_workspace_bytes(op, C.byref(g), 2)), 256), dtype=torch.uint8, device=dev)
+        ws_bytes = max(int(L.bt_workspace_bytes(op, C.byref(g), 2)), 256)
+        ws = None
+        if call.frozen and call.eps_w is None and _PACK_CACHE_ON:
+            # The tensor-core forward packs (mu, softplus(rho)) * out_scale into the workspace before its main
+            # launch.  A frozen layer keeps its workspace between calls and skips that launch while the
+            # parameters (storage and version), the epilogue scale and the geometry are what they were.
+            key = (mu_wc.data_ptr(), mu_w._version, rho_wc.data_ptr(), rho_w._version,
+                   _ptr(call.out_scale), None if call.out_scale is None else call.out_scale._version,
+                   bytes(g), ws_bytes, dev.index, _stream(), call.path, call.residual is None)
+            hit = _PACKED.get(call.layer_id)
+            if hit is not None and hit[0] == key:
+                ws = hit[1]
+                p.flags |= _lib.FLAG_PACKED_VALID
+            else:
+                ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+                _PACKED[call.layer_id] = (key, ws)
+        if ws is None:
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         kl = torch.empty((), dtype=torch.float32, device=dev) if call.want_kl else None
         with torch.cuda.device(dev):
             used = L.bt_select_path(C.byref(g), C.byref(p), int(call.flipout), call.path)
@@ -481,7 +526,7 @@ class _BayesLayerFn(torch.autograd.Function):
         ctx.out_meta = (tuple(out.shape), tuple(out.stride()))
         ctx.save_for_backward(x, mu_w, rho_w, mu_b, rho_b)
         if kl is None:
-            kl = torch.zeros((), dtype=torch.float32, device=dev)
+            kl = _zero_scalar(dev)   # a cached constant: no fill kernel per layer call
             ctx.mark_non_differentiable(kl)
         return out, kl
 

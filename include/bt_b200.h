@@ -25,6 +25,7 @@ extern "C" {
 #endif
 
 #define BT_ABI_VERSION 4
+#define BT_FLAG_PACKED_VALID 1
 
 typedef void* bt_stream_t; /* cudaStream_t */
 
@@ -108,7 +109,10 @@ typedef struct bt_layer_params {
   const float* out_scale;
   const float* out_shift;
   int32_t out_relu;
-  int32_t reserved;
+  /* bit 0 (BT_FLAG_PACKED_VALID): the caller's workspace still holds the packed (mu, sigma) copy the
+   * tensor-core forward made on an earlier call with the same parameters, out_scale and geometry
+   * (frozen inference models): the packing launch is skipped.  Ignored with tensor-fed eps. */
+  int32_t flags;
   const void* residual;
 } bt_layer_params;
 

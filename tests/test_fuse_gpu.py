@@ -108,3 +108,34 @@ def test_maxpool_nhwc_matches_torch(cuda_device):
         want = torch.nn.functional.max_pool2d(x, k, st, pd)
         assert got.is_contiguous(memory_format=torch.channels_last)
         torch.testing.assert_close(got, want, rtol=0, atol=0)
+
+
+def test_frozen_layers_keep_packed_parameters_until_they_change(cuda_device):
+    """fold_batchnorm marks its layers inference-only: the tensor-core forward packs (mu, sigma) once and later
+    calls skip that launch; an in-place parameter update (version counter) or invalidate_packed() re-packs."""
+    from bayesian_torch_b200 import ops
+    m = make(cuda_device).to(memory_format=torch.channels_last).to(torch.bfloat16)
+    f = bt.fold_batchnorm(m)
+    x = torch.randn(4, 64, 14, 14, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+
+    def run():
+        ops.PROFILE.reset()
+        with torch.no_grad(), bt.mc_sample(5):
+            y = f(x).float()
+        return y, ops.PROFILE.launches
+    y0, n0 = run()
+    y1, n1 = run()
+    layers = [mod for mod in f.modules() if getattr(mod, "_frozen", False)]
+    assert len(layers) == 7 and n1 == n0 - len(layers)      # one packing launch per layer saved
+    assert torch.equal(y1, y0)
+    with torch.no_grad():
+        layers[0].mu_kernel.mul_(1.5)                        # in-place update: version counter moves
+    y2, n2 = run()
+    assert n2 == n1 + 1 and not torch.equal(y2, y0)
+    bt.invalidate_packed(f)
+    y3, n3 = run()
+    assert n3 == n0 and torch.equal(y3, y2)
+    with bt.mc_sample(5):                                     # grad mode: never cached
+        ops.PROFILE.reset()
+        f(x)
+        assert ops.PROFILE.launches == n0

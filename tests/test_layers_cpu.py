@@ -90,6 +90,8 @@ def test_dtype_casts_keep_fp32_masters():
     assert m[0].mu_kernel.dtype == torch.float32 and m[0].eps_kernel.dtype == torch.float32
     assert m[1].weight.dtype == torch.bfloat16
     assert m[0]._prior_tensors() == (None, None, None, None)      # constants stay scalars after _apply
+    m = m.to(memory_format=torch.channels_last)                    # kernels keep the reference's [c_out, c_in, kh, kw] order
+    assert m[0].mu_kernel.is_contiguous() and m[0].rho_kernel.is_contiguous() and m[0].eps_kernel.is_contiguous()
     m[0].prior_weight_mu = torch.zeros_like(m[0].mu_kernel)        # utils.util.MOPED style assignment
     assert m[0]._prior_tensors()[0] is m[0].prior_weight_mu
 
