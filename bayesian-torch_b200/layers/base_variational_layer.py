@@ -255,6 +255,12 @@ class _BayesLayer(BaseVariationalLayer_):
                 if self.sign_input is None or self.sign_output is None:
                     raise RuntimeError("sample mode 'buffer' on a Flipout layer needs layer.sign_input / layer.sign_output")
                 call.sign_in, call.sign_out = self.sign_input, self.sign_output
+        if torch.is_grad_enabled() and mode != "philox":
+            # backward regenerates W (and the rho gradient) from eps: keep THIS call's draw, not the buffer a later
+            # call of the same layer (weight sharing, LSTM steps) overwrites -- the reference's autograd saves the
+            # buffer itself and reads the last draw there (oracle.lstm_unrolled, alias_eps)
+            call.eps_w = None if call.eps_w is None else call.eps_w.clone()
+            call.eps_b = None if call.eps_b is None else call.eps_b.clone()
         out, kl = ops.bayes_layer(call, x, mu_w, rho_w, self.mu_bias, self.rho_bias)
         if lead is not None:
             out = out.reshape(-1, *lead[1:], out.shape[-1])   # leading axis may be folded S*B

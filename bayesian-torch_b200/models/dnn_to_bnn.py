@@ -53,6 +53,19 @@ def bnn_conv_layer(params, d):
     return bnn_layer
 
 
+def bnn_lstm_layer(params, d):
+    """nn.LSTM -> LSTM<type> (dnn_to_bnn.py:103-121): input_size / hidden_size only; MOPED is not applied
+    to LSTM layers there either."""
+    bnn_layer = _layer_class(d, params)(
+        in_features=d.input_size, out_features=d.hidden_size, prior_mean=params["prior_mu"],
+        prior_variance=params["prior_sigma"], posterior_mu_init=params["posterior_mu_init"],
+        posterior_rho_init=params["posterior_rho_init"], bias=d.bias is not None)
+    if params.get("moped_enable", False):
+        print("WARNING: MOPED method is not supported for LSTM layers!!!")
+    bnn_layer.dnn_to_bnn_flag = True
+    return bnn_layer
+
+
 def dnn_to_bnn(m, bnn_prior_parameters):
     """In-place recursive swap (dnn_to_bnn.py:127-154)."""
     for name, child in list(m._modules.items()):
@@ -66,7 +79,7 @@ def dnn_to_bnn(m, bnn_prior_parameters):
         elif "Linear" in cls:
             setattr(m, name, bnn_linear_layer(bnn_prior_parameters, child))
         elif "LSTM" in cls:
-            raise NotImplementedError("LSTM layers are outside this build's hot path (SURVEY.md row 6)")
+            setattr(m, name, bnn_lstm_layer(bnn_prior_parameters, child))
     return
 
 

@@ -17,7 +17,7 @@ import torch.nn.functional as F
 __all__ = [
     "softplus_ref", "kl_normal", "kl_laplace", "kl_normal_from_rho", "sample_weight",
     "linear_reparam", "conv_reparam", "linear_flipout", "conv_flipout",
-    "conv_transpose_reparam", "conv_transpose_flipout",
+    "conv_transpose_reparam", "conv_transpose_flipout", "lstm_unrolled",
     "get_rho", "mc_moments", "predictive_entropy", "mutual_information",
 ]
 
@@ -161,6 +161,51 @@ def conv_transpose_flipout(x, mu_k, rho_k, mu_b, rho_b, eps_k, eps_b, sign_in, s
     pert = convt(x * sign_in, delta_k, delta_b, stride, padding, output_padding, groups, dilation)
     out = mean_path + pert * sign_out
     return out, kl_normal_from_rho(mu_k, rho_k, mu_b, rho_b, prior_mu, prior_sigma, dtype)
+
+
+def lstm_unrolled(x, p, draws, flipout=False, hidden_states=None, dtype=torch.float32, alias_eps=False):
+    """LSTMReparameterization / LSTMFlipout.forward (rnn_variational.py:112-153, rnn_flipout.py:102-155).
+    p: {"ih.mu_weight": ..., "hh.rho_bias": ...}; draws(tag, t) -> (eps_w, eps_b[, sign_in, sign_out]) of
+    sub-layer `tag` at step t (a fresh draw per step and sub-layer).  Returns (hidden_seq, c_seq, kl) with
+    kl summed over the steps as the reference does.
+
+    alias_eps=True reproduces one more property of the reference: every sub-layer draws into ONE eps buffer
+    through `.data.normal_()` (linear_variational.py:164,176; linear_flipout.py:150,162), the multiplication
+    `sigma * eps` saves that buffer for backward, and the version counter does not see `.data` writes -- so after
+    a multi-step forward the backward of EVERY step reads the LAST step's eps.  Outputs, KL, dx and the mu
+    gradients are unaffected; the rho gradients are those of the wrong draw.  The CUDA path regenerates each
+    call's own draw (the mathematically correct gradient, alias_eps=False); the aliasing mode exists so the
+    restatement can be pinned against the reference's autograd output."""
+    if alias_eps:
+        bufs, inner = {}, draws
+
+        def draws(tag, t):  # noqa: F811
+            vals = inner(tag, t)
+            if tag not in bufs:
+                bufs[tag] = [torch.empty_like(vals[0]), torch.empty_like(vals[1])]
+            bufs[tag][0].data.copy_(vals[0]); bufs[tag][1].data.copy_(vals[1])
+            return [bufs[tag][0].data, bufs[tag][1].data] + list(vals[2:])
+    B, T, _ = x.shape
+    HS = p["hh.mu_weight"].shape[1]
+    h_t = torch.zeros(B, HS, dtype=dtype) if hidden_states is None else hidden_states[0]
+    c_t = torch.zeros(B, HS, dtype=dtype) if hidden_states is None else hidden_states[1]
+    fn = linear_flipout if flipout else linear_reparam
+    hs, cs, kl = [], [], 0
+    for t in range(T):
+        ff = []
+        for tag, inp in (("ih", x[:, t, :]), ("hh", h_t)):
+            out, k = fn(inp, p[tag + ".mu_weight"], p[tag + ".rho_weight"], p.get(tag + ".mu_bias"), p.get(tag + ".rho_bias"),
+                        *draws(tag, t), dtype=dtype)
+            ff.append(out)
+            kl = kl + k
+        gates = ff[0] + ff[1]
+        i_t, f_t = torch.sigmoid(gates[:, :HS]), torch.sigmoid(gates[:, HS:HS * 2])
+        g_t, o_t = torch.tanh(gates[:, HS * 2:HS * 3]), torch.sigmoid(gates[:, HS * 3:])
+        c_t = f_t * c_t + i_t * g_t
+        h_t = o_t * torch.tanh(c_t)
+        hs.append(h_t.unsqueeze(0))
+        cs.append(c_t.unsqueeze(0))
+    return (torch.cat(hs, 0).transpose(0, 1).contiguous(), torch.cat(cs, 0).transpose(0, 1).contiguous(), kl)
 
 
 def get_rho(w: torch.Tensor, delta: float) -> torch.Tensor:

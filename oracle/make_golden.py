@@ -209,6 +209,48 @@ def main():
              extra={"moped_w": w, "moped_delta": np.asarray(0.5), "moped_rho": U.get_rho(w, 0.5),
                     "prior_w_mu": lay.prior_weight_mu, "prior_w_sigma": lay.prior_weight_sigma})
 
+    # ---- LSTMReparameterization / LSTMFlipout (rnn_variational.py:46-153, rnn_flipout.py:46-155): a fresh draw per
+    #      time step and per sub-layer; the draws are recovered by replaying torch's generator from the state
+    #      recorded before each ih / hh call.  Harness shim: the fork's kl_div has no default prior_type and the
+    #      Flipout linears call it without one -> default it to 'normal' (upstream behaviour).
+    from bayesian_torch.layers.base_variational_layer import BaseVariationalLayer_ as RefBase
+    RefBase.kl_div.__defaults__ = ("normal",)
+    for name, cls, T, seed in (("lstm_rp_T5", L.LSTMReparameterization, 5, 70), ("lstm_fo_T4", L.LSTMFlipout, 4, 71)):
+        if ONLY and not any(name.startswith(p) for p in ONLY):
+            continue
+        torch.manual_seed(1000 + seed)
+        lstm = cls(6, 5)
+        x = R(3, T, 6).requires_grad_(True)
+        states = []
+        hooks = [m.register_forward_pre_hook(lambda mod, inp, tag=tag: states.append((tag, torch.get_rng_state(), tuple(inp[0].shape))))
+                 for tag, m in (("ih", lstm.ih), ("hh", lstm.hh))]
+        torch.manual_seed(2000 + seed)
+        hs, (_, cs), kl = lstm(x)
+        for h in hooks:
+            h.remove()
+        g = torch.randn(hs.shape, generator=torch.Generator().manual_seed(3000 + seed))
+        gc = torch.randn(cs.shape, generator=torch.Generator().manual_seed(3001 + seed))
+        loss = (hs * g).sum() + (cs * gc).sum() + KL_COEF * kl
+        names = [n for n, _ in lstm.named_parameters()]
+        grads = torch.autograd.grad(loss, [x] + list(lstm.parameters()))
+        d = {"x": x.detach(), "g": g, "gc": gc, "hs": hs.detach(), "cs": cs.detach(), "kl": kl.detach(), "dx": grads[0]}
+        d.update({"p_" + n: p.detach() for n, p in lstm.named_parameters()})
+        d.update({"d_" + n: gr for n, gr in zip(names, grads[1:])})
+        keep = torch.get_rng_state()
+        flip = cls is L.LSTMFlipout
+        for i, (tag, st, xs) in enumerate(states):   # call i: step i // 2, layer ih / hh
+            torch.set_rng_state(st)
+            lay = getattr(lstm, tag)
+            t = i // 2
+            d[f"eps_{tag}_w_{t}"] = torch.empty_like(lay.eps_weight).normal_()     # linear_variational.py:164 / linear_flipout.py:150
+            d[f"eps_{tag}_b_{t}"] = torch.empty_like(lay.eps_bias).normal_()       # :176 / :162
+            if flip:                                                               # linear_flipout.py:169-170
+                d[f"sin_{tag}_{t}"] = torch.empty(xs).uniform_(-1, 1).sign()
+                d[f"sout_{tag}_{t}"] = torch.empty(xs[0], 20).uniform_(-1, 1).sign()
+        torch.set_rng_state(keep)
+        np.savez_compressed(os.path.join(OUT, name + ".npz"), **{k: v.numpy() for k, v in d.items()})
+        print(f"{name:34s} hs{tuple(hs.shape)} kl={float(kl):.6f}")
+
     if ONLY and not any("dnn_to_bnn_small".startswith(p) for p in ONLY):
         return
     # ---- dnn_to_bnn + get_kl_loss on a small torch model (models/dnn_to_bnn.py:127-165) ----

@@ -8,7 +8,7 @@ import oracle
 from oracle.make_golden import KL_COEF
 from conftest import cfg_of, golden_names, load_golden
 
-LAYER_CASES = [n for n in golden_names() if not n.startswith("dnn_to_bnn")]
+LAYER_CASES = [n for n in golden_names() if not n.startswith(("dnn_to_bnn", "lstm_"))]
 
 
 def run_oracle(name, d, dtype=torch.float32):
@@ -82,6 +82,48 @@ def test_oracle_fp64_agrees(name):
     scale = float(d["out"].abs().max())
     assert float((out.detach().float() - d["out"]).abs().max()) <= 2e-6 * max(scale, 1.0) * 8
     assert abs(float(kl) - float(d["kl"])) <= 1e-5 * abs(float(d["kl"]))
+
+
+def lstm_draws(d, flip):
+    def draws(tag, t):
+        out = [d[f"eps_{tag}_w_{t}"], d[f"eps_{tag}_b_{t}"]]
+        if flip:
+            out += [d[f"sin_{tag}_{t}"], d[f"sout_{tag}_{t}"]]
+        return out
+    return draws
+
+
+@pytest.mark.parametrize("name", ["lstm_rp_T5", "lstm_fo_T4"])
+def test_oracle_lstm_matches_reference(name):
+    """The unrolled cell with the per-step draws recovered from the reference run reproduces its hidden /
+    cell sequences, the summed KL and the gradients."""
+    d = load_golden(name)
+    flip = name.startswith("lstm_fo")
+    p = {k[2:]: v.clone().requires_grad_(True) for k, v in d.items() if k.startswith("p_")}
+    x = d["x"].clone().requires_grad_(True)
+    # alias_eps: the reference's backward reads the LAST step's eps for every step (see oracle.lstm_unrolled)
+    hs, cs, kl = oracle.lstm_unrolled(x, p, lstm_draws(d, flip), flipout=flip, alias_eps=True)
+    torch.testing.assert_close(hs.detach(), d["hs"], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(cs.detach(), d["cs"], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(kl.detach(), d["kl"], rtol=1e-6, atol=1e-6)
+    loss = (hs * d["g"]).sum() + (cs * d["gc"]).sum() + KL_COEF * kl
+    keys = sorted(p)
+    grads = torch.autograd.grad(loss, [x] + [p[k] for k in keys])
+    torch.testing.assert_close(grads[0], d["dx"], rtol=1e-4, atol=1e-5)
+    for k, gr in zip(keys, grads[1:]):
+        torch.testing.assert_close(gr, d["d_" + k], rtol=1e-4, atol=1e-5, msg=lambda m: f"{name}:{k}: {m}")
+    # per-step draws kept apart (what the CUDA path differentiates): same outputs, dx and mu gradients; the
+    # rho gradients are the ones that change
+    p2 = {k: v.detach().clone().requires_grad_(True) for k, v in p.items()}
+    x2 = d["x"].clone().requires_grad_(True)
+    hs2, cs2, kl2 = oracle.lstm_unrolled(x2, p2, lstm_draws(d, flip), flipout=flip)
+    assert torch.equal(hs2, hs) and torch.equal(cs2, cs)
+    g2 = torch.autograd.grad((hs2 * d["g"]).sum() + (cs2 * d["gc"]).sum() + KL_COEF * kl2, [x2] + [p2[k] for k in keys])
+    torch.testing.assert_close(g2[0], d["dx"], rtol=1e-4, atol=1e-5)
+    for k, gr in zip(keys, g2[1:]):
+        if ".mu_" in k:
+            torch.testing.assert_close(gr, d["d_" + k], rtol=1e-4, atol=1e-5)
+    assert not torch.allclose(g2[1 + keys.index("hh.rho_weight")], d["d_hh.rho_weight"], rtol=1e-2, atol=1e-4)
 
 
 def test_moped_rho_and_closed_form_kl():

@@ -14,7 +14,7 @@ from conftest import cfg_of, golden_names, load_golden
 from oracle.make_golden import KL_COEF
 
 pytestmark = pytest.mark.gpu
-LAYER_CASES = [n for n in golden_names() if not n.startswith("dnn_to_bnn")]
+LAYER_CASES = [n for n in golden_names() if not n.startswith(("dnn_to_bnn", "lstm_"))]
 RTOL = 1e-5
 
 
@@ -239,3 +239,49 @@ def test_laplace_prior_kl_div_and_get_kl_loss(cuda_device):
     close(lin.rho_weight.grad, r.grad.float(), rtol=1e-4, scale_atol=1e-5, msg="d kl / d rho (laplace)")
     with pytest.raises(ValueError, match="Unknown prior_type"):
         lin.kl_div(lin.mu_weight, lin.mu_weight.abs() + 1, 0.0, 1.0, "cauchy")
+
+
+@pytest.mark.parametrize("name", ["lstm_rp_T5", "lstm_fo_T4"])
+def test_lstm_matches_reference_fixture(name, cuda_device):
+    """LSTMReparameterization / LSTMFlipout against the reference run: the per-step draws of the fixture are
+    loaded into the sub-layers' buffers by a pre-hook before every ih / hh call."""
+    d = load_golden(name)
+    flip = name.startswith("lstm_fo")
+    lstm = (L.LSTMFlipout if flip else L.LSTMReparameterization)(6, 5).to(cuda_device)
+    with torch.no_grad():
+        for n, p in lstm.named_parameters():
+            p.copy_(d["p_" + n])
+    step = {"ih": 0, "hh": 0}
+
+    def load(tag):
+        def hook(mod, inp):
+            t = step[tag]; step[tag] += 1
+            mod.eps_weight.copy_(d[f"eps_{tag}_w_{t}"]); mod.eps_bias.copy_(d[f"eps_{tag}_b_{t}"])
+            if flip:
+                mod.sign_input, mod.sign_output = d[f"sin_{tag}_{t}"].to(cuda_device), d[f"sout_{tag}_{t}"].to(cuda_device)
+        return hook
+    for tag in ("ih", "hh"):
+        sub = getattr(lstm, tag)
+        sub.sample_mode, sub.path = "buffer", "simt"
+        sub.register_forward_pre_hook(load(tag))
+    x = d["x"].to(cuda_device).requires_grad_(True)
+    hs, (hs2, cs), kl = lstm(x)
+    assert hs2 is hs and hs.shape == d["hs"].shape
+    close(hs, d["hs"], msg=f"{name} hidden"); close(cs, d["cs"], msg=f"{name} cell")
+    close(kl, d["kl"], rtol=RTOL, scale_atol=1e-6, msg=f"{name} kl")
+    ((hs * d["g"].to(cuda_device)).sum() + (cs * d["gc"].to(cuda_device)).sum() + KL_COEF * kl).backward()
+    close(x.grad, d["dx"], rtol=1e-4, msg=f"{name} dx")
+    # rho gradients: the reference's autograd reads the last step's eps for every step (oracle.lstm_unrolled,
+    # alias_eps); this path differentiates each step's own draw -> checked against the oracle without aliasing
+    po = {k[2:]: v.clone().requires_grad_(True) for k, v in d.items() if k.startswith("p_")}
+    from test_oracle_golden import lstm_draws
+    ohs, ocs, okl = oracle.lstm_unrolled(d["x"], po, lstm_draws(d, flip), flipout=flip)
+    names = sorted(po)
+    og = dict(zip(names, torch.autograd.grad((ohs * d["g"]).sum() + (ocs * d["gc"]).sum() + KL_COEF * okl, [po[k] for k in names])))
+    for n, p in lstm.named_parameters():
+        want = d["d_" + n] if ".mu_" in n else og[n]
+        close(p.grad, want, rtol=1e-4, scale_atol=2e-5, msg=f"{name} d_{n}")
+    lstm.dnn_to_bnn_flag = True
+    step.update(ih=0, hh=0)
+    assert len(lstm(d["x"].to(cuda_device))) == 2      # (hidden_seq, (hidden_seq, c_ts)) without kl
+    assert float(bt.get_kl_loss(lstm)) == pytest.approx(2 * float(d["kl"]) / d["x"].shape[1], rel=1e-5)  # parent + children (reference double count)
