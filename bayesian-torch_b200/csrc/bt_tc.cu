@@ -82,6 +82,9 @@ struct Tc2Args {
   int num_mt, num_mg, MT, NSETS, nkb, NA, RW, stationary;  // num_mg: m-groups per key as walked by one cluster
   int nb_inner;      // item order: 1 = (sample, m-group, n-block), n-block fastest (streaming only); 0 = m-group fastest;
                      // 2 = (m-group, n-block, sample), sample fastest: layers whose x is shared by all samples
+  int spn;           // 1, or 2: x is shared by all samples and N == 64 -> two samples ride side by side on the N axis of one
+                     // BN = 128 tile (virtual row v = 64 * (sample within the pair) + channel): every A tile is read once per
+                     // PAIR of samples and feeds a full-width MMA.  S then counts sample pairs.
   int a_keep;        // order 2 with an A ring of exactly one item's tiles: the tiles stay in shared memory while
                      // the samples of an m-group go by (the loader re-arms the slots instead of re-loading them)
   int CL;            // CTAs per cluster (1 or 2). CL = 2: the pair walks the same (sample, n-block, k-block) sequence on
@@ -460,6 +463,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   tc_fence_after();
   const uint32_t tmem = ctrl->tmem_base;
 
+  const int vN = a.N * a.spn;  // width of the (virtual) N axis the tiles are cut from
   const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
   const int cid = blockIdx.x / CL, ncl = gridDim.x / CL;
   const int64_t i0 = a.total_items * cid / ncl;
@@ -540,7 +544,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       }
       PW(0, mbar_wait(smem_u32(&ctrl->acc_full[set]), set_phase));
       tc_fence_after();
-      const int ncols = min(BN, a.N - nb * BN);
+      const int ncols = min(BN, vN - nb * BN);
       const int nsub = (ncols + SUBN - 1) / SUBN;  // staged sub-tiles with at least one real column
       for (int t = 0; t < mtv; ++t) {
         const int m0 = (tile0(mg) + t) * BM + q * 32;  // first row of this warp's 32-row slab
@@ -656,7 +660,9 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             fence_proxy_async();
             __syncwarp();
             if (lane == 0 && !(PROF && (a.debug & 1))) {
-              tma_store_3d(&tm_out, buf, nb * BN + c0, m0, s);  // rows >= Ms and columns >= N are clipped by the map
+              // rows >= Ms and columns >= N are clipped by the map; a stacked pair: column 64 * j + c is channel c of sample 2 s + j
+              if (a.spn == 2) tma_store_3d(&tm_out, buf, (nb * BN + c0) & 63, m0, 2 * s + ((nb * BN + c0) >> 6));
+              else tma_store_3d(&tm_out, buf, nb * BN + c0, m0, s);
               tma_store_commit();
             }
           });
@@ -861,7 +867,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     uint32_t phase = 0;
     for (int it = 0; it < n_items; ++it) {
       const int mtv = tiles_of(mg);
-      const int nsub = (min(BN, a.N - nb * BN) + SUBN - 1) / SUBN;
+      const int nsub = (min(BN, vN - nb * BN) + SUBN - 1) / SUBN;
       for (int t = 0; t < mtv; ++t) {
         for (int sub = 0; sub < nsub; ++sub) {
           mbar_wait(smem_u32(&ctrl->res_empty[slot]), phase ^ 1u);
@@ -1008,12 +1014,14 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             // Flipout: threads [BN, 2 BN) fill the second tile, the bias perturbation sigma_b * eps_b of the
             // perturbation accumulator (inside the s_out product, linear_flipout.py:162,172-173)
             const bool pert = FLIP && p >= BN;
-            const int n = nb * BN + (pert ? p - BN : p);
+            const int vn = nb * BN + (pert ? p - BN : p);
+            const int n = a.spn == 2 ? (vn & 63) : vn;                      // channel
+            const uint32_t smp = a.spn == 2 ? 2u * s + (vn >> 6) : (uint32_t)s;  // sample of this row
             float sh = 0.f;
-            if (n < a.N) {
+            if (vn < vN) {
               if (a.mu_b) {
                 const float e = a.eps_b ? a.eps_b[n]
-                                        : bt_normal1((uint64_t)n, bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_B));
+                                        : bt_normal1((uint64_t)n, bt_rng_key(a.seed, a.sample_id + smp, a.layer_id, BT_KIND_EPS_B));
                 const float db = bt_softplus(a.rho_b[n]) * e;
                 sh = FLIP ? (pert ? db : a.mu_b[n]) : a.mu_b[n] + db;
               }
@@ -1040,7 +1048,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           if (lane == 0) mbar_arrive(smem_u32(&ctrl->w_full[a.RW]));
           sphase ^= 1u;
         }
-        const BtRngKey rk = bt_rng_key(a.seed, a.sample_id + s, a.layer_id, BT_KIND_EPS_W);
+        const BtRngKey rk0 = bt_rng_key(a.seed, a.sample_id + (uint32_t)(s * a.spn), a.layer_id, BT_KIND_EPS_W);
         // packed bf16 (mu, sigma) of this thread's chunk of k-block kb2, eight weights per row
         uint4 nmu8[ROWS_PER_THREAD], nsg8[ROWS_PER_THREAD];
         auto load_params = [&](int kb2) {
@@ -1048,9 +1056,10 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 #pragma unroll
           for (int i = 0; i < ROWS_PER_THREAD; ++i) {
             const int lrow = row_base + RPP * i;
-            const int n = nb * BN + row_first + lrow;
+            const int vn = nb * BN + row_first + lrow;
+            const int n = a.spn == 2 ? (vn & 63) : vn;
             nmu8[i] = nsg8[i] = make_uint4(0u, 0u, 0u, 0u);
-            if (lrow < rows_cta && k2 < a.K && n < a.N && !(PROF && (a.debug & 32))) {
+            if (lrow < rows_cta && k2 < a.K && vn < vN && !(PROF && (a.debug & 32))) {
               const int64_t e = (int64_t)n * a.K + k2;
               nmu8[i] = __ldg(reinterpret_cast<const uint4*>(a.mu_p + e));
               nsg8[i] = __ldg(reinterpret_cast<const uint4*>(a.sig_p + e));
@@ -1076,11 +1085,14 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             const int lrow = row_base + RPP * i;
             if (lrow >= rows_cta) break;
             const int row = row_first + lrow;
-            const int n = nb * BN + row;
+            const int vn = nb * BN + row;
+            const int n = a.spn == 2 ? (vn & 63) : vn;
+            BtRngKey rk = rk0;
+            if (a.spn == 2) rk.sample_id += (uint32_t)(vn >> 6);  // second sample of the stacked pair
             float z[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) z[e] = 0.f;
-            if (kin && n < a.N && !(PROF && (a.debug & 16))) {
+            if (kin && vn < vN && !(PROF && (a.debug & 16))) {
               const int64_t e = (int64_t)n * a.K + k;
               if (a.eps_p) {
                 const float4 e0 = __ldg(reinterpret_cast<const float4*>(a.eps_p + e));
@@ -1600,7 +1612,13 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   const int sms = bt_num_sms();
   a.num_mt = (a.Ms + BM - 1) / BM;
   a.nkb = (a.K + BK - 1) / BK;
-  int BN = a.N <= 64 ? 64 : 128;
+  // x shared by all samples and exactly 64 output channels (the ResNet stem under mc_batched): two samples ride side by
+  // side on the N axis of a BN = 128 tile, so an A tile is fetched once per pair and feeds a full-width MMA (at N = 64
+  // the tensor core reads 128 B of A per cycle at full rate: the layer was bound by that read)
+  a.spn = (x_shared && a.N == 64 && S % 2 == 0 && !flipout && !p->residual && !p->eps_w && !p->eps_b && !opt.dgrad &&
+           env_int("BT_TC2_SPN", 1) != 0) ? 2 : 1;
+  if (a.spn == 2) a.S = S / 2;
+  int BN = a.N * a.spn <= 64 ? 64 : 128;
   // shared-memory budget: staging (1, 2 or 4 buffers per epilogue warp) + residual ring (0, 2 or 4)
   // + A ring + W ring / panel
   const int res_min = p->residual ? 2 : 0;
@@ -1620,7 +1638,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   // (1024 -> 256 1x1 at 14x14: 0.34 ms stationary/64, 0.23 ms streaming/128).
   if (force_bn == 64 || force_bn == 128) BN = force_bn;
   const int WB = NSUBW * BN * BK * 2;
-  a.NB = (a.N + BN - 1) / BN;
+  a.NB = (a.N * a.spn + BN - 1) / BN;
   a.stationary = panel_fits(BN) ? 1 : 0;
   // Wide layers with a short reduction (the 1x1 expansions, N >= 4 n-blocks) stream instead: with
   // the n-block innermost in the item order every group of A tiles is fetched from HBM once rather
@@ -1703,9 +1721,9 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   const int smem_bytes = 1024 + CTRL_BYTES + (flipout ? SHIFT_BYTES : 0) + (a.stage_bufs + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT_T + a.RW * WB;
   BT_REQUIRE(smem_bytes <= SMEM_LIMIT, BT_ERR_UNSUPPORTED, "tensor-core forward: shared memory plan %d exceeds %d", smem_bytes, SMEM_LIMIT);
   if (env_int("BT_TC2_LOG", 0))
-    fprintf(stderr, "tc2: flip=%d mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d order=%d keep=%d\n",
+    fprintf(stderr, "tc2: flip=%d mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d order=%d keep=%d spn=%d\n",
             (int)flipout, (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,
-            (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs, a.CL, a.nb_inner, a.a_keep);
+            (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs, a.CL, a.nb_inner, a.a_keep, a.spn);
   const bool o32 = g->out_dtype == BT_F32;
   if (BN == 64)
     return o32 ? tc2_launch<64, float>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream)

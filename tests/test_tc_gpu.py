@@ -176,6 +176,8 @@ def test_tc_mc_batched_equals_sample_loop(cuda_device):
 @pytest.mark.parametrize("cin,cout,k,stride,pad,batch,hw,S", [
     (3, 64, 7, 2, 3, 3, 36, 40),      # RGB stem through the patch matrix: 3 k-blocks, ragged last tile
     (64, 96, 1, 1, 0, 5, 20, 24),     # 1x1 (plain GEMM map), one k-block, two tiles kept per item
+    (64, 64, 1, 1, 0, 5, 20, 6),      # 64 output channels: two samples stacked on the N axis of one tile (sampled bias per sample)
+    (64, 64, 3, 1, 1, 3, 17, 7),      # odd sample count: no stacking
     (128, 64, 3, 2, 1, 2, 30, 8),     # K = 1152: too long for the kept ring -> the usual order
 ])
 def test_tc_shared_input_sample_fastest_order(cuda_device, cin, cout, k, stride, pad, batch, hw, S, monkeypatch):
