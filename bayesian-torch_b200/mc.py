@@ -160,3 +160,50 @@ def mc_predict(model, x: torch.Tensor, num_mc: int, *, softmax: bool = True, gro
         acc = MCAccumulator(x.shape[0], probe.reshape(probe.shape[0], -1).shape[1], x.device, softmax)
     allreduce_moments(acc.buf, group)
     return acc.finalize(num_mc, uncertainty)
+
+
+class HostBatchPrefetcher:
+    """Double-buffered host -> device input pipeline for MC inference over a stream of batches.
+
+    The reference's evaluate() loops copy every batch synchronously before its S forwards
+    (examples/main_bayesian_cifar_dnn2bnn.py:537-541: `data.cuda()`).  Here the copy of batch i+1 (pinned host
+    memory, a side stream, converted to the model's dtype / memory format on that stream) runs while batch i
+    computes, so the PCIe time (77 MB per 128 fp32 ImageNet-size images) leaves the step's critical path.
+
+        pf = HostBatchPrefetcher(device, dtype=torch.bfloat16, memory_format=torch.channels_last)
+        pf.submit(first_batch)
+        for nxt in rest:            # pinned host tensors
+            x = pf.take()           # device tensor of the batch submitted earlier
+            pf.submit(nxt)          # its copy overlaps the forwards of x
+            res = mc_predict(model, x, S)
+    """
+
+    def __init__(self, device, dtype=None, memory_format=torch.contiguous_format):
+        self.device = torch.device(device)
+        self.dtype, self.memory_format = dtype, memory_format
+        self.stream = torch.cuda.Stream(self.device)
+        self._pending = None
+
+    def submit(self, host_batch: torch.Tensor) -> None:
+        if self._pending is not None:
+            raise RuntimeError("HostBatchPrefetcher: take() the pending batch before submitting another")
+        if host_batch.is_cuda:
+            raise RuntimeError("HostBatchPrefetcher.submit expects a host tensor (pin it for an asynchronous copy)")
+        with torch.cuda.stream(self.stream):
+            x = host_batch.to(self.device, non_blocking=True)
+            if self.dtype is not None:
+                x = x.to(self.dtype)
+            x = x.contiguous(memory_format=self.memory_format)
+            done = torch.cuda.Event()
+            done.record(self.stream)
+        self._pending = (x, done)
+
+    def take(self) -> torch.Tensor:
+        if self._pending is None:
+            raise RuntimeError("HostBatchPrefetcher: nothing submitted")
+        x, done = self._pending
+        self._pending = None
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(done)
+        x.record_stream(cur)     # allocated on the side stream, consumed on the compute stream
+        return x

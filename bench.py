@@ -214,9 +214,17 @@ def run_b200(args):
     def step_resident():
         return bt.mc_predict(model, x_dev, S, batch_samples=args.mc_batch)
 
+    # end to end through the public API: every step copies its own batch from pinned host memory (bt.HostBatchPrefetcher:
+    # the copy of the NEXT step's batch is issued right after this step's forwards are enqueued and overlaps them) and
+    # reads the predictive mean / variance back to the host
+    prefetch = bt.HostBatchPrefetcher(dev, dtype=torch.bfloat16, memory_format=torch.channels_last)
+
     def step_e2e():
-        xd = x_host.to(dev, non_blocking=True).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        if prefetch._pending is None:          # first step of a timed run: nothing to overlap with, the copy is exposed
+            prefetch.submit(x_host)
+        xd = prefetch.take()
         res = bt.mc_predict(model, xd, S, batch_samples=args.mc_batch)
+        prefetch.submit(x_host)                # next step's batch (same synthetic images): H2D on the side stream
         return res.mean.cpu(), res.var.cpu()
 
     def barrier():
@@ -265,7 +273,8 @@ def run_b200(args):
     tc_ms, tc_flops = sum(t for _, _, t in tc), sum(f for f, _, _ in tc)
     other_ms = sum(t for _, _, t in other)
 
-    ms_e2e, _ = timed(step_e2e, max(1, min(args.steps, 3)))
+    ms_e2e, _ = timed(step_e2e, args.steps)
+    prefetch.take()                            # the batch submitted by the last step (one copy more than steps timed)
 
     if rank == 0:
         pk = peaks()

@@ -196,3 +196,22 @@ def test_full_size_mc_batching_is_consistent(cuda_device):
     torch.testing.assert_close(b.mean, a.mean, rtol=1e-4, atol=1e-6)
     torch.testing.assert_close(b.var, a.var, rtol=1e-3, atol=1e-7)
     torch.testing.assert_close(b.entropy, a.entropy, rtol=1e-4, atol=1e-5)
+
+
+def test_host_batch_prefetcher(cuda_device):
+    """Double-buffered pinned-host -> device input pipeline: values, dtype, memory format, ordering."""
+    pf = bt.HostBatchPrefetcher(cuda_device, dtype=torch.bfloat16, memory_format=torch.channels_last)
+    batches = [torch.randn(4, 3, 16, 16).pin_memory() for _ in range(3)]
+    pf.submit(batches[0])
+    with pytest.raises(RuntimeError, match="take"):
+        pf.submit(batches[1])
+    for i in range(3):
+        x = pf.take()
+        if i + 1 < 3:
+            pf.submit(batches[i + 1])
+        assert x.dtype == torch.bfloat16 and x.is_contiguous(memory_format=torch.channels_last)
+        assert torch.equal(x.float().cpu(), batches[i].bfloat16().float())
+    with pytest.raises(RuntimeError, match="nothing submitted"):
+        pf.take()
+    with pytest.raises(RuntimeError, match="host tensor"):
+        pf.submit(torch.zeros(1, device=cuda_device))
