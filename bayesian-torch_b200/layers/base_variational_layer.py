@@ -232,7 +232,10 @@ class _BayesLayer(BaseVariationalLayer_):
         call.path = ops._PATHS[self.path or ops.get_path()]
         call.out_scale, call.out_shift, call.out_relu = self._ep_scale, self._ep_shift, self._ep_relu
         call.residual = residual
-        call.frozen = bool(getattr(self, "_frozen", False)) and not torch.is_grad_enabled()
+        if getattr(self, "_frozen", False) and not torch.is_grad_enabled():
+            if getattr(self, "_pack_cache", None) is None:
+                self._pack_cache = {}
+            call.pack_cache = self._pack_cache
         if ops._STATE.sample_override is not None:
             call.sample_id = ops._STATE.sample_override
         else:

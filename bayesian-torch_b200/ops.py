@@ -317,7 +317,7 @@ class LayerCall:
     out_relu: bool = False
     residual: Optional[torch.Tensor] = None     # added after the affine, before the ReLU (inference only)
     output_padding: Tuple[int, ...] = ()        # ConvTranspose layers only
-    frozen: bool = False                        # inference-only layer (fold_batchnorm): keep the packed parameters
+    pack_cache: Optional[dict] = None           # inference-only layer (fold_batchnorm): where its packed parameters live
 
 
 def _conv_out_size(i, k, s, p, d):
@@ -426,17 +426,15 @@ def _match_strides(t: torch.Tensor, ref: torch.Tensor) -> torch.Tensor:
 
 _ZERO = {}
 _PACK_CACHE_ON = os.environ.get("BT_PACK_CACHE", "1") != "0"
-_PACKED = {}   # layer_id -> (key, workspace) of frozen layers (see _BayesLayerFn.forward)
 
 
-def invalidate_packed(model=None) -> None:
-    """Drop the cached packed parameters of every layer of `model` (all layers when None).  Needed only after
-    writing a frozen (fold_batchnorm'd) model's parameters through `.data`, which no version counter sees."""
-    if model is None:
-        _PACKED.clear()
-        return
+def invalidate_packed(model) -> None:
+    """Drop the cached packed parameters of every frozen layer of `model` (see _BayesLayerFn.forward).  Needed only
+    after writing a fold_batchnorm'd model's parameters through `.data`, which no version counter sees."""
     for m in model.modules():
-        _PACKED.pop(getattr(m, "_layer_id", None), None)
+        cache = getattr(m, "_pack_cache", None)
+        if cache is not None:
+            cache.clear()
 
 
 
@@ -489,20 +487,20 @@ class _BayesLayerFn(torch.autograd.Function):
         op = b"flipout_fwd" if call.flipout else b"reparam_fwd"
         ws_bytes = max(int(L.bt_workspace_bytes(op, C.byref(g), 2)), 256)
         ws = None
-        if call.frozen and call.eps_w is None and _PACK_CACHE_ON:
+        if call.pack_cache is not None and call.eps_w is None and _PACK_CACHE_ON:
             # The tensor-core forward packs (mu, softplus(rho)) * out_scale into the workspace before its main
             # launch.  A frozen layer keeps its workspace between calls and skips that launch while the
             # parameters (storage and version), the epilogue scale and the geometry are what they were.
             key = (mu_wc.data_ptr(), mu_w._version, rho_wc.data_ptr(), rho_w._version,
                    _ptr(call.out_scale), None if call.out_scale is None else call.out_scale._version,
                    bytes(g), ws_bytes, dev.index, _stream(), call.path, call.residual is None)
-            hit = _PACKED.get(call.layer_id)
+            hit = call.pack_cache.get("ws")
             if hit is not None and hit[0] == key:
                 ws = hit[1]
                 p.flags |= _lib.FLAG_PACKED_VALID
             else:
                 ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-                _PACKED[call.layer_id] = (key, ws)
+                call.pack_cache["ws"] = (key, ws)   # lives and dies with the layer object
         if ws is None:
             ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         kl = torch.empty((), dtype=torch.float32, device=dev) if call.want_kl else None

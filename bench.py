@@ -299,7 +299,7 @@ def run_b200(args):
                          "ms_per_step_other_bt_kernels": other_ms,
                          "share_of_step": tc_ms / ms_step if ms_step > 0 else None},
         }
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:   # the CPU baseline is a rank-0, N = 1 figure (torchrun pins OMP threads to 1)
             line["cpu_baseline"] = {k: v for k, v in cpu_reference_images_per_s(B, S, 16, repeats=5).items()
                                     if k != "seconds_per_forward"}
         print(json.dumps(line))
