@@ -125,6 +125,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; the reference arm is ONE process that should use every host
+    # core, so the thread pools are sized before torch is imported (nothing above this line imports it)
+    for var in ("OMP_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[var] = str(os.cpu_count() or 1)
     t_all = time.perf_counter()
     per_step = []
     base = None
