@@ -1,6 +1,3 @@
 mkdir -p gpurun_out
-export BT_AFF=1 BT_XS=1 BT_TC2_LOG=1
-for mt in 0 2; do echo "MT=$mt"
-for a in "256 256 3 1 1 128 14" "1024 256 1 1 0 128 14" "512 512 3 1 1 128 7" "2048 512 1 1 0 128 7" "128 128 3 1 1 128 28" "512 128 1 1 0 128 28"; do
-BT_TC2_MT=$mt timeout 120 python tools/one_layer.py $a 32 3 2>&1 | tail -2 | cut -c1-230
-done; done
+timeout 420 compute-sanitizer --tool memcheck --launch-timeout 120 --error-exitcode 7 python -m pytest tests/test_tc_gpu.py -q -x -k "shared_input or mc_batched or matches_oracle" > gpurun_out/memcheck.log 2>&1
+echo "rc=$?"; grep -E "ERROR SUMMARY|passed|failed|Invalid|error" gpurun_out/memcheck.log | head -12
