@@ -327,6 +327,9 @@ class _BayesLayer(BaseVariationalLayer_):
                     s_out = ops.philox_sign_shape(oshape, x.device, call.seed, call.sample_id, self._layer_id, _lib.KIND_SIGN_IN)
         if self._flipout and mode != "philox":
             call.sign_in, call.sign_out = s_out, s_in   # (equivalent convolution's view, see above)
+        if torch.is_grad_enabled() and mode != "philox":   # this call's draw, not the buffer a later call overwrites
+            call.eps_w = call.eps_w.clone()
+            eps_b = None if eps_b is None else eps_b.clone()
         out = ops.bayes_transpose_layer(call, x, mu_w, rho_w, oshape)
         if self.mu_bias is not None:
             bshape = (1, -1) + (1,) * r
