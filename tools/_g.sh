@@ -1,3 +1,5 @@
 mkdir -p gpurun_out
-timeout 420 compute-sanitizer --tool memcheck --launch-timeout 120 --error-exitcode 7 python -m pytest tests/test_tc_gpu.py -q -x -k "shared_input or mc_batched or matches_oracle" > gpurun_out/memcheck.log 2>&1
-echo "rc=$?"; grep -E "ERROR SUMMARY|passed|failed|Invalid|error" gpurun_out/memcheck.log | head -12
+( timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4 ) > gpurun_out/t.log; cat gpurun_out/t.log
+timeout 200 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; tail -2 gpurun_out/smoke.log
+timeout 400 python bench.py > gpurun_out/bench1.json 2> gpurun_out/bench1.err; cut -c1-220 gpurun_out/bench1.json; tail -2 gpurun_out/bench1.err
+timeout 200 python tools/linear_sweep.py 4096 1 > gpurun_out/linear_sweep.txt 2>&1; timeout 300 python tools/linear_sweep.py 4096 8 >> gpurun_out/linear_sweep.txt 2>&1; cat gpurun_out/linear_sweep.txt
