@@ -1,5 +1,13 @@
 mkdir -p gpurun_out
-( timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4 ) > gpurun_out/t.log; cat gpurun_out/t.log
-timeout 200 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; tail -2 gpurun_out/smoke.log
-timeout 400 python bench.py > gpurun_out/bench1.json 2> gpurun_out/bench1.err; cut -c1-220 gpurun_out/bench1.json; tail -2 gpurun_out/bench1.err
-timeout 200 python tools/linear_sweep.py 4096 1 > gpurun_out/linear_sweep.txt 2>&1; timeout 300 python tools/linear_sweep.py 4096 8 >> gpurun_out/linear_sweep.txt 2>&1; cat gpurun_out/linear_sweep.txt
+export BT_AFF=1 BT_XS=1
+cd bayesian-torch_b200/csrc
+for v in default wide default wide; do
+cp libbt_$v.so libbt_b200.so; cd ../..
+echo "== $v"
+for a in "256 256 3 1 1 128 14" "512 2048 1 1 0 128 7"; do
+timeout 120 python tools/one_layer.py $a 32 3 2>&1 | tail -1 | cut -c1-120
+done
+cd bayesian-torch_b200/csrc
+done
+cd ../..
+timeout 300 python -m pytest tests/test_rng_mc_gpu.py -x -q 2>&1 | tail -2
