@@ -15,6 +15,7 @@ BT_F32, BT_BF16 = 0, 1
 PATH_AUTO, PATH_SIMT_F32, PATH_TC_BF16 = 0, 1, 2
 KIND_EPS_W, KIND_EPS_B, KIND_SIGN_IN, KIND_SIGN_OUT = 0, 1, 2, 3
 FLAG_PACKED_VALID = 1
+ABI_VERSION = 5
 
 _i64x3 = C.c_int64 * 3
 
@@ -40,7 +41,7 @@ class LayerParams(C.Structure):
         ("prior_mu", C.c_float), ("prior_sigma", C.c_float),
         ("seed", C.c_uint64), ("sample_id", C.c_uint32), ("layer_id", C.c_uint32),
         ("out_scale", C.c_void_p), ("out_shift", C.c_void_p), ("out_relu", C.c_int32), ("flags", C.c_int32),
-        ("residual", C.c_void_p)]
+        ("residual", C.c_void_p), ("workspace_bytes", C.c_int64)]
 
 
 class LayerGrads(C.Structure):
@@ -103,7 +104,7 @@ def lib() -> C.CDLL:
             fn = getattr(handle, name)
             fn.restype = res
             fn.argtypes = args
-        if handle.bt_abi_version() != 4:
+        if handle.bt_abi_version() != ABI_VERSION:
             raise RuntimeError("libbt_b200.so ABI version mismatch")
         _lib = handle
     return _lib

@@ -96,14 +96,17 @@ static int forward_common(const bt_geom* g, const bt_layer_params* p, const void
     if (rc != BT_OK) return rc;
   }
   void* tc_ws = workspace ? (char*)workspace + KL_SCRATCH : nullptr;
+  BT_REQUIRE(p->workspace_bytes == 0 || p->workspace_bytes >= KL_SCRATCH, BT_ERR_INVALID, "%s: workspace_bytes %lld is smaller than the KL scratch",
+             who, (long long)p->workspace_bytes);
+  const int64_t tc_ws_bytes = p->workspace_bytes > 0 ? p->workspace_bytes - KL_SCRATCH : 0;
   const char* why = "";
   if (path == BT_PATH_TC_BF16) {
     BT_REQUIRE(bt_tc_supported(g, p, flipout, &why), BT_ERR_UNSUPPORTED, "%s: tensor-core path unavailable: %s", who,
                why);
-    return bt_tc_forward(g, p, x, out, tc_ws, flipout, st);
+    return bt_tc_forward(g, p, x, out, tc_ws, tc_ws_bytes, flipout, st);
   }
   if (path == BT_PATH_AUTO && bt_tc_supported(g, p, flipout, &why) && tc_ws)
-    return bt_tc_forward(g, p, x, out, tc_ws, flipout, st);
+    return bt_tc_forward(g, p, x, out, tc_ws, tc_ws_bytes, flipout, st);
   BT_REQUIRE(path == BT_PATH_AUTO || path == BT_PATH_SIMT_F32, BT_ERR_INVALID, "%s: unknown path %d", who, path);
   return bt_simt_forward(g, p, x, out, flipout, st);
 }
@@ -117,13 +120,16 @@ static int backward_common(const bt_geom* g, const bt_layer_params* p, const voi
   BT_REQUIRE(!p->out_scale && !p->out_shift && !p->out_relu && !p->residual, BT_ERR_UNSUPPORTED,
              "%s: the folded BatchNorm / ReLU / residual epilogue is inference-only", who);
   cudaStream_t st = (cudaStream_t)stream;
+  BT_REQUIRE(p->workspace_bytes == 0 || p->workspace_bytes >= KL_SCRATCH, BT_ERR_INVALID, "%s: workspace_bytes %lld is smaller than the KL scratch",
+             who, (long long)p->workspace_bytes);
+  const int64_t tc_ws_bytes = p->workspace_bytes > 0 ? p->workspace_bytes - KL_SCRATCH : 0;
   bt_layer_grads rest = *grads;
   // grad_x on the tensor-core kernel when the problem qualifies (bf16 channels-last activations): the forward
   // kernel run on grad_out with the transposed, regenerated weights
   if (grads->grad_x && path != BT_PATH_SIMT_F32 && workspace) {
     const char* why = "";
     if (bt_tc_dgrad_supported(g, p, flipout, &why)) {
-      rc = bt_tc_dgrad(g, p, grad_out, grads->grad_x, (char*)workspace + KL_SCRATCH, flipout, st);
+      rc = bt_tc_dgrad(g, p, grad_out, grads->grad_x, (char*)workspace + KL_SCRATCH, tc_ws_bytes, flipout, st);
       if (rc != BT_OK) return rc;
       rest.grad_x = nullptr;
     } else {
@@ -134,7 +140,7 @@ static int backward_common(const bt_geom* g, const bt_layer_params* p, const voi
   if (grads->grad_mu_w && grads->grad_rho_w && path != BT_PATH_SIMT_F32 && workspace) {
     const char* why = "";
     if (bt_tc_wgrad_supported(g, p, flipout, &why)) {
-      rc = bt_tc_wgrad(g, p, x, grad_out, grad_kl, grads->grad_mu_w, grads->grad_rho_w, (char*)workspace + KL_SCRATCH, flipout, st);
+      rc = bt_tc_wgrad(g, p, x, grad_out, grad_kl, grads->grad_mu_w, grads->grad_rho_w, (char*)workspace + KL_SCRATCH, tc_ws_bytes, flipout, st);
       if (rc != BT_OK) return rc;
       rest.grad_mu_w = rest.grad_rho_w = nullptr;
     } else {

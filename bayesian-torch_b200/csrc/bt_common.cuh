@@ -196,7 +196,7 @@ int bt_simt_backward(const bt_geom* g, const bt_layer_params* p, const void* x, 
                      cudaStream_t stream);
 bool bt_tc_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why);
 
-int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
+int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace, int64_t ws_bytes,
                   bool flipout, cudaStream_t stream);
 int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout);
 // backward data on the tensor-core kernel (grad_out convolved with the transposed, regenerated weights)
@@ -206,6 +206,6 @@ int64_t bt_tc_dgrad_workspace_bytes(const bt_geom* g, bool flipout);
 bool bt_tc_wgrad_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why);
 int64_t bt_tc_wgrad_workspace_bytes(const bt_geom* g, bool flipout);
 int bt_tc_wgrad(const bt_geom* g, const bt_layer_params* p, const void* x, const void* grad_out, const float* grad_kl,
-                float* grad_mu_w, float* grad_rho_w, void* workspace, bool flipout, cudaStream_t stream);
-int bt_tc_dgrad(const bt_geom* g, const bt_layer_params* p, const void* grad_out, void* grad_x, void* workspace, bool flipout,
-                cudaStream_t stream);
+                float* grad_mu_w, float* grad_rho_w, void* workspace, int64_t ws_bytes, bool flipout, cudaStream_t stream);
+int bt_tc_dgrad(const bt_geom* g, const bt_layer_params* p, const void* grad_out, void* grad_x, void* workspace, int64_t ws_bytes,
+                bool flipout, cudaStream_t stream);

@@ -1342,18 +1342,26 @@ static int64_t x_span_elems(const bt_geom* g) {
 }
 
 // bytes of the caller's workspace the forward needs: packed (mu, sigma, eps) + the patch matrix
-// (Flipout: two patch matrices and the sign-flipped copy of x they are built from)
+// (Flipout: two patch matrices and the sign-flipped copy of x they are built from).  The operand mode is
+// decided by the SAME tc2_plan the launch uses (with the most permissive parameters: no tensor-fed draws),
+// so the size and the carve-up of tc2_run cannot disagree; a geometry the plan rejects never reaches the
+// tensor-core kernels and needs the packed area only.
+static int64_t packed_bytes(int64_t n, int64_t kp) { return ((3 * n * kp * 4 + 255) / 256) * 256; }
+static int64_t patch_bytes(const bt_geom* g, int64_t rows_per_s, int64_t Kp) {
+  const bool x_shared = g->n_samples > 1 && g->x_sample_stride == 0;
+  return ((rows_per_s * (x_shared ? 1 : g->n_samples) * Kp * 2 + 255) / 256) * 256;
+}
 int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout) {
   int64_t taps = 1;
   for (int i = 0; i < g->rank; ++i) taps *= g->k_size[i];
   const int64_t Kp = (g->c_in / (g->groups > 0 ? g->groups : 1) * taps + 7) & ~7ll;
-  int64_t bytes = ((3 * g->c_out * Kp * 4 + 255) / 256) * 256;
-  const bool gemm_like = g->rank == 0 && g->x_chan_stride == 1 && g->c_in % 8 == 0 && g->x_batch_stride % 8 == 0 &&
-                         (!flipout || g->c_in % 64 == 0);
-  const bool im2col_like = g->rank >= 1 && g->rank <= 2 && g->x_chan_stride == 1 && g->c_in % 64 == 0;
-  if ((!gemm_like && !im2col_like) || env_int("BT_TC2_AMODE", 0) == A_PATCH) {
-    const bool x_shared = g->n_samples > 1 && g->x_sample_stride == 0;
-    const int64_t pm = ((g->batch * prod_out(g) * (x_shared ? 1 : g->n_samples) * Kp * 2 + 255) / 256) * 256;
+  int64_t bytes = packed_bytes(g->c_out, Kp);
+  bt_layer_params none;
+  memset(&none, 0, sizeof(none));
+  Plan pl;
+  const char* why = "";
+  if (tc2_plan(g, &none, flipout, &pl, &why) && pl.mode == A_PATCH) {
+    const int64_t pm = patch_bytes(g, pl.rows_per_s, pl.Kp);
     bytes += pm;
     if (flipout) bytes += pm + ((x_span_elems(g) * 2 + 255) / 256) * 256;
   }
@@ -1472,6 +1480,7 @@ struct RunOpt {
   int cin_w = 0, cout_w = 0; // the layer's own (C_in, C_out) when dgrad
   int a_dil_h = 1, a_dil_w = 1, SH = 0, SW = 0;
   int64_t s_bs = 0, s_hs = 0, s_ws = 0;  // strides of the un-inserted grad_out (tensor-fed signs)
+  int64_t ws_bytes = 0;      // bytes the caller says `workspace` holds (0: not stated, unchecked)
 };
 
 static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
@@ -1515,6 +1524,15 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   __nv_bfloat16* sig_p = mu_p + wn;
   float* eps_p = (p->eps_w || opt.dgrad) ? (float*)(sig_p + wn) : nullptr;
   __nv_bfloat16* patches = (__nv_bfloat16*)((char*)workspace + ((3 * wn * 4 + 255) / 256) * 256);
+  if (opt.ws_bytes > 0) {  // the carve-up below must fit what the caller allocated (bt_workspace_bytes)
+    int64_t need = ((3 * wn * 4 + 255) / 256) * 256;
+    if (pl.mode == A_PATCH) {
+      const int64_t pm = patch_bytes(g, pl.rows_per_s, pl.Kp);
+      need += pm + (flipout ? pm + ((x_span_elems(g) * 2 + 255) / 256) * 256 : 0);
+    }
+    BT_REQUIRE(need <= opt.ws_bytes, BT_ERR_INVALID, "tensor-core %s: workspace of %lld bytes, %lld needed (bt_workspace_bytes)",
+               opt.dgrad ? "dgrad" : "forward", (long long)opt.ws_bytes, (long long)need);
+  }
   {
     int64_t blocks = (wn + 255) / 256;
     const int64_t cap = (int64_t)bt_num_sms() * 8;
@@ -1732,9 +1750,11 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
              : tc2_launch<128, __nv_bfloat16>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream);
 }
 
-int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
+int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace, int64_t ws_bytes,
                   bool flipout, cudaStream_t stream) {
-  return tc2_run(g, p, x, out, workspace, flipout, RunOpt(), stream);
+  RunOpt opt;
+  opt.ws_bytes = ws_bytes;
+  return tc2_run(g, p, x, out, workspace, flipout, opt, stream);
 }
 
 // ------------------------------------------------------------------ backward data ----
@@ -1810,8 +1830,8 @@ int64_t bt_tc_dgrad_workspace_bytes(const bt_geom* g, bool flipout) {
   return bt_tc_workspace_bytes(&t, flipout) + (inserted ? dgrad_insert_bytes(&t) : 0);
 }
 
-int bt_tc_dgrad(const bt_geom* g, const bt_layer_params* p, const void* grad_out, void* grad_x, void* workspace, bool flipout,
-                cudaStream_t stream) {
+int bt_tc_dgrad(const bt_geom* g, const bt_layer_params* p, const void* grad_out, void* grad_x, void* workspace, int64_t ws_bytes,
+                bool flipout, cudaStream_t stream) {
   bt_geom t;
   bool inserted;
   const char* why = "";
@@ -1842,9 +1862,15 @@ int bt_tc_dgrad(const bt_geom* g, const bt_layer_params* p, const void* grad_out
     BT_LAUNCH_OK("tc2_zero_insert_kernel");
     a_src = workspace;
     ws = (char*)workspace + bytes;
+    if (ws_bytes > 0) {
+      BT_REQUIRE(ws_bytes > bytes, BT_ERR_INVALID, "tensor-core dgrad: workspace of %lld bytes cannot hold the zero-inserted grad_out (%lld)",
+                 (long long)ws_bytes, (long long)bytes);
+      ws_bytes -= bytes;
+    }
     opt.a_dil_h = sh; opt.a_dil_w = sw; opt.SH = (int)OH; opt.SW = (int)OW;
     opt.s_bs = g->out_batch_stride; opt.s_hs = ohs; opt.s_ws = ows;
   }
+  opt.ws_bytes = ws_bytes;
   return tc2_run(&t, &q, a_src, grad_x, ws, flipout, opt, stream);
 }
 
@@ -2208,7 +2234,7 @@ int64_t bt_tc_wgrad_workspace_bytes(const bt_geom* g, bool flipout) {
 }
 
 int bt_tc_wgrad(const bt_geom* g, const bt_layer_params* p, const void* x, const void* grad_out, const float* grad_kl,
-                float* grad_mu_w, float* grad_rho_w, void* workspace, bool flipout, cudaStream_t stream) {
+                float* grad_mu_w, float* grad_rho_w, void* workspace, int64_t ws_bytes, bool flipout, cudaStream_t stream) {
   const char* why = "";
   Plan pl;
   BT_REQUIRE(wgrad_plan(g, p, flipout, &pl, &why), BT_ERR_UNSUPPORTED, "tensor-core wgrad: %s", why);
@@ -2229,6 +2255,9 @@ int bt_tc_wgrad(const bt_geom* g, const bt_layer_params* p, const void* x, const
   a.dW = (float*)workspace;
   a.dD = (float*)((char*)workspace + acc_bytes);
   void* rest = (char*)workspace + 2 * acc_bytes;
+  BT_REQUIRE(ws_bytes <= 0 || ws_bytes >= bt_tc_wgrad_workspace_bytes(g, flipout), BT_ERR_INVALID,
+             "tensor-core wgrad: workspace of %lld bytes, %lld needed (bt_workspace_bytes)", (long long)ws_bytes,
+             (long long)bt_tc_wgrad_workspace_bytes(g, flipout));
   BT_CUDA_OK(cudaMemsetAsync(workspace, 0, (size_t)(flipout ? 2 : 1) * acc_bytes, stream));
 
   alignas(64) CUtensorMap tm_a, tm_b, tm_a2;

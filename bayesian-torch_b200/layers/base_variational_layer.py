@@ -131,8 +131,36 @@ class _BayesLayer(BaseVariationalLayer_):
     def prepare(self):
         raise NotImplementedError("INT8 post-training quantisation stubs are outside this build's scope (SURVEY.md row 9)")
 
+    @staticmethod
+    def _mark_of(b):
+        # `layer.prior_bias_mu.data = t` (utils/util.py:MOPED, Linear branch) changes neither id() nor _version,
+        # only the storage: the mark carries data_ptr and shape too
+        return (id(b), b._version, b.data_ptr(), tuple(b.shape))
+
     def _mark_constant_priors(self):
-        self._prior_marks = {n: (id(b), b._version) for n, b in self._prior_buffers().items() if b is not None}
+        self._prior_marks = {n: self._mark_of(b) for n, b in self._prior_buffers().items() if b is not None}
+
+    def __getstate__(self):
+        # (runs on the SOURCE of a deepcopy / pickle) remember which priors are still the constant fill: the
+        # marks hold id() / data_ptr() of this object's buffers and mean nothing for the clone's
+        state = self.__dict__.copy()
+        marks = state.get("_prior_marks")
+        if marks is not None:
+            state["_prior_const_at_copy"] = [n for n, b in self._prior_buffers().items()
+                                             if b is not None and marks.get(n) == self._mark_of(b)]
+        return state
+
+    def __setstate__(self, state):
+        # copy.deepcopy / pickle: the clone is a NEW layer with its own Philox stream (clones sharing a
+        # layer id would draw bit-identical eps, e.g. ModuleList([deepcopy(block) for ...]))
+        const = state.pop("_prior_const_at_copy", None)
+        super().__setstate__(state)
+        if "_layer_id" in self.__dict__:
+            self._layer_id = ops.next_layer_id()
+            self._calls = 0
+            self._pack_cache = None
+        if const is not None:
+            self._prior_marks = {n: self._mark_of(getattr(self, n)) for n in const}
 
     def _prior_buffers(self):
         return {n: getattr(self, n) for n in ("prior_weight_mu", "prior_weight_sigma", "prior_bias_mu", "prior_bias_sigma")}
@@ -144,7 +172,7 @@ class _BayesLayer(BaseVariationalLayer_):
         out = []
         for n, b in self._prior_buffers().items():
             mark = self._prior_marks.get(n)
-            changed = b is not None and (mark is None or mark != (id(b), b._version))
+            changed = b is not None and (mark is None or mark != self._mark_of(b))
             out.append(b if changed else None)
         return tuple(out)
 
@@ -160,13 +188,13 @@ class _BayesLayer(BaseVariationalLayer_):
             if r.dim() >= 4 and not r.is_contiguous():
                 r = r.contiguous()
             return r
-        const = {n: b is not None and self._prior_marks.get(n) == (id(b), b._version)
+        const = {n: b is not None and self._prior_marks.get(n) == self._mark_of(b)
                  for n, b in self._prior_buffers().items()} if hasattr(self, "_prior_marks") else {}
         super()._apply(keep_fp32, *args, **kwargs)
         for n, was_const in const.items():  # moving devices re-creates buffers; constants stay constants
             if was_const:
                 b = getattr(self, n)
-                self._prior_marks[n] = (id(b), b._version)
+                self._prior_marks[n] = self._mark_of(b)
         return self
 
     def _w(self):
@@ -226,7 +254,8 @@ class _BayesLayer(BaseVariationalLayer_):
         call.prior_t = self._prior_tensors()
         call.seed, call.layer_id = ops.get_seed(), self._layer_id
         call.n_samples = ops.current_n_samples()
-        call.x_shared = call.n_samples > 1 and ops._STATE.shared_batch is not None and x.shape[0] == ops._STATE.shared_batch
+        # the leading dim BEFORE Linear flattens [B, T, F] -> [B*T, F]: a shared model input keeps batch B there
+        call.x_shared = call.n_samples > 1 and ops._STATE.shared_batch is not None and input.shape[0] == ops._STATE.shared_batch
         laplace = self._prior_kind() == "laplace"   # its KL is a separate launch (kl_loss), not the fused normal-prior one
         call.want_kl = bool(return_kl) and not laplace
         call.path = ops._PATHS[self.path or ops.get_path()]
@@ -238,6 +267,7 @@ class _BayesLayer(BaseVariationalLayer_):
             call.pack_cache = self._pack_cache
         if ops._STATE.sample_override is not None:
             call.sample_id = ops._STATE.sample_override
+            call.seed = ops.call_seed(call.seed, self._layer_id)   # repeated calls inside the block: fresh streams
         else:
             call.sample_id = self._calls & 0xFFFFFFFF
             self._calls += call.n_samples
@@ -293,6 +323,7 @@ class _BayesLayer(BaseVariationalLayer_):
         call.path = ops._PATHS[self.path or ops.get_path()]
         if ops._STATE.sample_override is not None:
             call.sample_id = ops._STATE.sample_override
+            call.seed = ops.call_seed(call.seed, self._layer_id)
         else:
             call.sample_id = self._calls & 0xFFFFFFFF
             self._calls += 1

@@ -72,7 +72,13 @@ def fold_batchnorm(model: nn.Module, inplace: bool = False, join_in_epilogue: bo
     if model.training:
         raise RuntimeError("fold_batchnorm is an inference-time rewrite: call model.eval() first")
     if not inplace:
+        src = model
         model = copy.deepcopy(model)
+        # the folded model REPLACES the original (same weights, same draws): its layers keep the Philox
+        # stream ids a plain deepcopy would renew (_BayesLayer.__setstate__)
+        for a, b in zip(model.modules(), src.modules()):
+            if isinstance(a, _BayesLayer):
+                a._layer_id, a._calls = b._layer_id, b._calls
     graph = _Tracer().trace(model)
     gm = fx.GraphModule(model, graph)
     modules = dict(gm.named_modules())

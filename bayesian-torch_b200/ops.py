@@ -29,6 +29,7 @@ class _State(threading.local):
         self.path = "auto"                           # "auto" | "simt" | "tc"
         self.n_samples = 1                           # >1 inside mc_batched()
         self.shared_batch: Optional[int] = None      # batch of the un-folded model input
+        self.call_counts: Optional[dict] = None      # layer_id -> calls so far inside this mc_sample()/mc_batched() block
 
 
 _STATE = _State()
@@ -123,12 +124,32 @@ def path(p: str):
 def mc_sample(sample_id: int):
     """Pin the Monte-Carlo sample index used by every layer inside the block: sample s
     of a model is the same weight draw on any rank / any GPU count."""
-    old = _STATE.sample_override
+    old = (_STATE.sample_override, _STATE.call_counts)
     _STATE.sample_override = int(sample_id) & 0xFFFFFFFF
+    _STATE.call_counts = {}
     try:
         yield
     finally:
-        _STATE.sample_override = old
+        _STATE.sample_override, _STATE.call_counts = old
+
+
+def call_seed(seed: int, layer_id: int) -> int:
+    """Seed of this call of layer `layer_id`.  Inside mc_sample() / mc_batched() the sample id is pinned, so a
+    layer that runs several times in one forward (LSTM steps, weight sharing) would repeat its draw; the
+    reference redraws on every call (linear_variational.py:164).  The k-th call (k >= 1) of a layer inside the
+    block therefore uses seed + k * 0x9E3779B97F4A7C15 (mod 2^64): a different Philox key, i.e. an independent
+    stream; the first call uses the seed itself.  Outside such a block the per-layer call counter already
+    advances the sample id."""
+    counts = _STATE.call_counts
+    if counts is None:
+        return seed
+    k = counts.get(layer_id, 0)
+    counts[layer_id] = k + 1
+    return derive_seed(seed, k)
+
+
+def derive_seed(seed: int, k: int) -> int:
+    return (int(seed) + int(k) * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
 
 
 @contextlib.contextmanager
@@ -138,14 +159,15 @@ def mc_batched(n_samples: int, first_sample: int = 0, shared_batch: Optional[int
     uses weight draw first_sample + s.  Deterministic torch layers (BN, ReLU, pooling)
     work unchanged on the folded batch.  shared_batch=B: a layer input whose batch is B
     (the model input) is shared by all samples and only its OUTPUT is folded to [S*B, ...]."""
-    old = (_STATE.n_samples, _STATE.sample_override, _STATE.shared_batch)
+    old = (_STATE.n_samples, _STATE.sample_override, _STATE.shared_batch, _STATE.call_counts)
     _STATE.n_samples = int(n_samples)
     _STATE.sample_override = int(first_sample) & 0xFFFFFFFF
     _STATE.shared_batch = shared_batch
+    _STATE.call_counts = {}
     try:
         yield
     finally:
-        _STATE.n_samples, _STATE.sample_override, _STATE.shared_batch = old
+        _STATE.n_samples, _STATE.sample_override, _STATE.shared_batch, _STATE.call_counts = old
 
 
 def current_n_samples() -> int:
@@ -503,6 +525,7 @@ class _BayesLayerFn(torch.autograd.Function):
                 call.pack_cache["ws"] = (key, ws)   # lives and dies with the layer object
         if ws is None:
             ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        p.workspace_bytes = ws.numel()
         kl = torch.empty((), dtype=torch.float32, device=dev) if call.want_kl else None
         with torch.cuda.device(dev):
             used = L.bt_select_path(C.byref(g), C.byref(p), int(call.flipout), call.path)
@@ -563,6 +586,7 @@ class _BayesLayerFn(torch.autograd.Function):
             gk = g_kl.detach().to(torch.float32).contiguous()
         op = b"flipout_bwd" if call.flipout else b"reparam_bwd"
         ws = torch.empty(max(int(_lib.lib().bt_workspace_bytes(op, C.byref(geom), 2)), 256), dtype=torch.uint8, device=dev)
+        p.workspace_bytes = ws.numel()
         with torch.cuda.device(dev):
             rc = _entry(call, True)(C.byref(geom), C.byref(p), _ptr(xd), _ptr(go), _ptr(gk), C.byref(grads), _ptr(ws),
                                     call.path, _stream())
@@ -606,6 +630,7 @@ class _BayesTransposeFn(torch.autograd.Function):
         grads.grad_x = _ptr(out)
         op = b"flipout_bwd" if call.flipout else b"reparam_bwd"
         ws = torch.empty(max(int(_lib.lib().bt_workspace_bytes(op, C.byref(geom), 2)), 256), dtype=torch.uint8, device=dev)
+        p.workspace_bytes = ws.numel()
         with torch.cuda.device(dev):
             rc = _entry(call, True)(C.byref(geom), C.byref(p), _ptr(out), _ptr(xd), None, C.byref(grads), _ptr(ws),
                                     call.path, _stream())
@@ -631,6 +656,7 @@ class _BayesTransposeFn(torch.autograd.Function):
                 geom = _build_geom(call, go, mu_wc.shape, gx)
                 op = b"flipout_fwd" if call.flipout else b"reparam_fwd"
                 ws = torch.empty(max(int(L.bt_workspace_bytes(op, C.byref(geom), 2)), 256), dtype=torch.uint8, device=dev)
+                p.workspace_bytes = ws.numel()
                 rc = _entry(call, False)(C.byref(geom), C.byref(p), _ptr(go), _ptr(gx), None, _ptr(ws), call.path, _stream())
                 _lib.check(rc, "conv_transpose backward (data)")
             if ctx.needs_input_grad[2] or ctx.needs_input_grad[3]:
@@ -640,6 +666,7 @@ class _BayesTransposeFn(torch.autograd.Function):
                 grads.grad_mu_w, grads.grad_rho_w = _ptr(gmu), _ptr(grho)
                 op = b"flipout_bwd" if call.flipout else b"reparam_bwd"
                 ws = torch.empty(max(int(L.bt_workspace_bytes(op, C.byref(geom), 2)), 256), dtype=torch.uint8, device=dev)
+                p.workspace_bytes = ws.numel()
                 rc = _entry(call, True)(C.byref(geom), C.byref(p), _ptr(go), _ptr(xd), None, C.byref(grads), _ptr(ws),
                                         call.path, _stream())
                 _lib.check(rc, "conv_transpose backward (weights)")
@@ -709,6 +736,8 @@ def philox_eps_weight(w_shape, seed: int, sample_id: int, layer_id: int, device=
 def add_relu_(y: torch.Tensor, r: torch.Tensor) -> torch.Tensor:
     """y <- relu(y + r) in one pass (the residual join of a ResNet block), in place."""
     _require_cuda(y, r)
+    if torch.is_grad_enabled() and (y.requires_grad or r.requires_grad):
+        return torch.relu(y + r)   # the raw kernel has no autograd node: differentiable graphs go through torch
     if y.shape != r.shape or y.dtype != r.dtype or y.stride() != r.stride() or y.dtype not in _DT:
         return torch.relu_(y.add_(r))
     if not (y.is_contiguous() or (y.dim() == 4 and y.is_contiguous(memory_format=torch.channels_last))):
@@ -722,7 +751,8 @@ def maxpool2d(x: torch.Tensor, kernel_size: int, stride: int, padding: int) -> t
     """MaxPool2d (floor mode, square window) on a bf16 channels-last tensor in one 16-byte-per-thread
     pass; anything else goes to torch."""
     if not (x.is_cuda and x.dim() == 4 and x.dtype == torch.bfloat16 and x.shape[1] % 8 == 0
-            and x.is_contiguous(memory_format=torch.channels_last) and 2 * padding <= kernel_size):
+            and x.is_contiguous(memory_format=torch.channels_last) and 2 * padding <= kernel_size) \
+            or (torch.is_grad_enabled() and x.requires_grad):   # no autograd node on the raw kernel
         return torch.nn.functional.max_pool2d(x, kernel_size, stride, padding)
     B, Cc, H, W = x.shape
     oh, ow = (H + 2 * padding - kernel_size) // stride + 1, (W + 2 * padding - kernel_size) // stride + 1

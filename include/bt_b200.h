@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define BT_ABI_VERSION 4
+#define BT_ABI_VERSION 5
 #define BT_FLAG_PACKED_VALID 1
 
 typedef void* bt_stream_t; /* cudaStream_t */
@@ -114,6 +114,10 @@ typedef struct bt_layer_params {
    * (frozen inference models): the packing launch is skipped.  Ignored with tensor-fed eps. */
   int32_t flags;
   const void* residual;
+  /* Size in bytes of the `workspace` passed with this call (what the caller allocated from
+   * bt_workspace_bytes).  0 = not stated.  When stated, every entry point checks its carve-up of the
+   * workspace against it and returns BT_ERR_INVALID instead of writing past the end. */
+  int64_t workspace_bytes;
 } bt_layer_params;
 
 /* Gradient outputs of a backward call (all fp32 device buffers shaped like the

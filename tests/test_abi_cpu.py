@@ -31,10 +31,10 @@ def test_header_symbols_all_exported_and_bound():
 
 def test_abi_version_and_struct_layout():
     L = _lib.lib()
-    assert L.bt_abi_version() == 4
+    assert L.bt_abi_version() == 5
     # struct sizes the header implies (LP64): catches field drift between header and ctypes
     assert ctypes.sizeof(_lib.Geom) == 6 * 4 + 3 * 8 + 6 * 24 + 3 * 8 + 24 + 3 * 8 + 24
-    assert ctypes.sizeof(_lib.LayerParams) == 12 * 8 + 2 * 4 + 8 + 2 * 4 + 2 * 8 + 2 * 4 + 8
+    assert ctypes.sizeof(_lib.LayerParams) == 12 * 8 + 2 * 4 + 8 + 2 * 4 + 2 * 8 + 2 * 4 + 8 + 8
     assert ctypes.sizeof(_lib.LayerGrads) == 5 * 8
     assert L.bt_workspace_bytes(b"kl", None, 3) >= 3 * 8 + 8
 
