@@ -174,16 +174,27 @@ def tc_traffic(launches_per_step):
     return None
 
 
-def build_model(device, fold_bn=True):
+def build_model(device, fold_bn=True, prepare=None):
+    """The model every arm of this benchmark (and tests/test_config3_gpu.py) runs.  `prepare(model)` is called on
+    the fp32 eval-mode model on `device` before the bf16 / channels-last conversion and the BatchNorm fold (the
+    parity test builds its CPU oracle twin there)."""
     import torch
     import torchvision
     import bayesian_torch_b200 as bt
     torch.manual_seed(0)
     model = torchvision.models.resnet50()          # random init: no checkpoints offline
+    # gamma of the last BatchNorm of every block: 0.5 keeps the random-init residual stack (weight noise sigma =
+    # 0.5 |w| on top) in a regime where the logits are O(1) and the softmax is not saturated, so the predictive
+    # mean / variance the step returns (and the checksum printed with it) mean something.  No effect on the work done.
+    for name, mod in model.named_modules():
+        if name.endswith("bn3"):
+            mod.weight.data.fill_(0.5)
     params = {"prior_mu": 0.0, "prior_sigma": 1.0, "posterior_mu_init": 0.0, "posterior_rho_init": -3.0,
               "type": "Reparameterization", "moped_enable": True, "moped_delta": 0.5}
     bt.dnn_to_bnn(model, params)                   # MOPED: mu <- DNN init, rho <- get_rho (ImageNet examples force it)
     model = model.to(device).eval()
+    if prepare is not None:
+        prepare(model)
     # bf16 activations, channels-last; variational parameters stay fp32 masters (layers/_apply)
     model = model.to(memory_format=torch.channels_last).to(torch.bfloat16)
     if fold_bn:   # eval-mode BatchNorm / ReLU / residual join folded into the layer kernels (exact up to rounding)
