@@ -123,7 +123,9 @@ def path(p: str):
 @contextlib.contextmanager
 def mc_sample(sample_id: int):
     """Pin the Monte-Carlo sample index used by every layer inside the block: sample s
-    of a model is the same weight draw on any rank / any GPU count."""
+    of a model is the same weight draw on any rank / any GPU count.  One model forward per
+    block: a layer called AGAIN inside the same block (LSTM time steps, weight sharing, a
+    second forward) draws afresh, as the reference does on every call (call_seed below)."""
     old = (_STATE.sample_override, _STATE.call_counts)
     _STATE.sample_override = int(sample_id) & 0xFFFFFFFF
     _STATE.call_counts = {}

@@ -4,7 +4,8 @@ batch 128 x 3 x 224 x 224 synthetic images (BASELINE.json configs[3]; the metric
 on it and it fits one B200).  torchvision.resnet50 + dnn_to_bnn(Reparameterization), eval.
 
     python bench.py --gpus N --steps K --warmup W            # this repo (CUDA, sm_100a)
-    python bench.py --impl reference --gpus N ...            # reference CPU path (oracle port)
+    python bench.py --impl reference --gpus N ...            # the reference's own eager code on the host cores
+    python bench.py --workload train --gpus N ...            # configs[2] extended to N GPUs (ResNet-18 Flipout training step)
 
 One step = one MC prediction of one batch: S weight samples sharded over the N ranks (S/N
 full-batch forwards each), predictive mean/variance/entropy/MI joined by one NCCL
@@ -29,6 +30,8 @@ if ROOT not in sys.path:
 METRIC = "bayesian_resnet50_mc_images_per_s_S32"
 UNIT = "images/s"
 GFLOP_PER_IMAGE_SAMPLE = 8.178368512  # 2 * 4 089 184 256 MACs, Bayesian layers only
+BNN_PARAMS = {"prior_mu": 0.0, "prior_sigma": 1.0, "posterior_mu_init": 0.0, "posterior_rho_init": -3.0,
+              "type": "Reparameterization", "moped_enable": True, "moped_delta": 0.5}
 
 
 def parse():
@@ -37,13 +40,16 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="mc_inference", choices=["mc_inference", "train"])
     ap.add_argument("--batch", type=int, default=128)
     ap.add_argument("--samples", type=int, default=32)
     ap.add_argument("--mc-batch", type=int, default=int(os.environ.get("BT_MC_BATCH", "32")),
                     help="weight samples folded into one model pass (ops.mc_batched)")
-    ap.add_argument("--cpu-batch", type=int, default=8, help="images in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-eager", action="store_true", help="skip the reference-eager-on-this-GPU comparison")
+    ap.add_argument("--no-extras", action="store_true", help="skip the configs[2] / configs[4] / KL side measurements")
     ap.add_argument("--no-fold-bn", action="store_true", help="keep BatchNorm / ReLU as separate torch ops")
+    ap.add_argument("--no-graph", action="store_true", help="enqueue every step from Python instead of replaying a CUDA graph")
     return ap.parse_args()
 
 
@@ -90,35 +96,67 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-# ------------------------------------------------------------------------------------------
-# reference arm / cpu baseline: the oracle port of the reference's CPU path on host cores
-# ------------------------------------------------------------------------------------------
-def cpu_reference_images_per_s(batch: int, samples: int, cpu_batch: int, repeats: int = 1):
-    """Time the oracle port (oracle/layers.py) of the reference's eager path on this host's
-    cores: torchvision.resnet50 with every Conv2d/Linear swapped for the CPU restatement of
-    the Reparameterization layers, fp32, all threads.  Bounded sample: `cpu_batch` images x 1
-    weight sample per timed forward; one image needs `samples` forwards, so
-    images/s = cpu_batch / (t_forward * samples)."""
+def seed_resnet50():
+    """The deterministic network both arms convert: torchvision ResNet-50, random init (no checkpoints offline).
+    gamma of the last BatchNorm of every block is 0.5: that keeps the random-init residual stack (weight noise
+    sigma = 0.5 |w| on top) in a regime where the logits are O(1) and the softmax is not saturated, so the
+    predictive mean / variance a step returns (and the checksum printed with it) mean something.  No effect on
+    the work done."""
     import torch
     import torchvision
-    from oracle.layers import oracle_dnn_to_bnn
+    torch.manual_seed(0)
+    model = torchvision.models.resnet50()
+    for name, mod in model.named_modules():
+        if name.endswith("bn3"):
+            mod.weight.data.fill_(0.5)
+    return model
+
+
+# ------------------------------------------------------------------------------------------
+# reference arm / cpu baseline / eager-on-this-GPU: the reference's OWN code (oracle/_ref, staged by
+# oracle/build_ref.py), never this repo's kernels
+# ------------------------------------------------------------------------------------------
+def reference_model(device):
+    """torchvision ResNet-50 converted by the reference's dnn_to_bnn (models/dnn_to_bnn.py:127-154, MOPED on),
+    eval mode -- the model examples/main_bayesian_imagenet_dnn2bnn.py builds."""
+    from oracle.build_ref import import_reference
+    L, D, U, where = import_reference()
+    model = seed_resnet50()
+    D.dnn_to_bnn(model, dict(BNN_PARAMS))
+    return model.to(device).eval(), where
+
+
+def cpu_reference_images_per_s(batch: int, samples: int, forwards: int, warm: int = 1, budget_s: float = 120.0):
+    """Time the reference's eager CPU path on this host's cores: `forwards` Monte-Carlo forwards of the FULL batch
+    (fp32, all threads).  One step of the metric is `samples` such forwards (the evaluate() loop,
+    examples/main_bayesian_cifar_dnn2bnn.py:542-556), so images/s = batch / (t_forward * samples)."""
+    import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    torch.manual_seed(0)
-    model = oracle_dnn_to_bnn(torchvision.models.resnet50()).eval()
-    x = torch.randn(cpu_batch, 3, 224, 224)
+    try:
+        model, where = reference_model("cpu")
+        kind = "reference"
+    except ImportError:   # oracle/_ref not staged (a clone that never saw /root/reference): the oracle port
+        from oracle.layers import oracle_dnn_to_bnn
+        model, where, kind = oracle_dnn_to_bnn(seed_resnet50()).eval(), "oracle/layers.py", "port"
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(batch, 3, 224, 224, generator=g)
+    times = []
+    t_all = time.perf_counter()
     with torch.no_grad():
-        model(x)  # warm-up
-        best = float("inf")
-        for _ in range(max(1, repeats)):
+        for i in range(warm + forwards):
             t0 = time.perf_counter()
             model(x)
-            best = min(best, time.perf_counter() - t0)
-    ips = cpu_batch / (best * samples)
-    return {"value": ips, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{cpu_batch} images x 1 weight sample per timed forward (fp32, torch CPU, {cores} threads), "
-                      f"best of {max(1, repeats)}; scaled to S={samples} forwards per image",
-            "seconds_per_forward": best}
+            dt = time.perf_counter() - t0
+            if i >= warm:
+                times.append(dt)
+            if time.perf_counter() - t_all > budget_s and times:
+                break
+    t = sum(times) / len(times)
+    return {"value": batch / (t * samples), "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{len(times)} Monte-Carlo forward(s) of the full batch ({batch} images, fp32, torch CPU, {cores} threads, "
+                      f"{warm} warm-up) of the {samples} a step needs: {t:.2f} s each; the step time is {samples} x that",
+            "source": where, "seconds_per_forward": t, "forwards_timed": len(times)}
 
 
 def run_reference(args):
@@ -129,46 +167,72 @@ def run_reference(args):
     # core, so the thread pools are sized before torch is imported (nothing above this line imports it)
     for var in ("OMP_NUM_THREADS", "MKL_NUM_THREADS"):
         os.environ[var] = str(os.cpu_count() or 1)
-    t_all = time.perf_counter()
-    per_step = []
-    base = None
-    for i in range(args.warmup + args.steps):
-        base = cpu_reference_images_per_s(args.batch, args.samples, args.cpu_batch)
-        if i >= args.warmup:
-            per_step.append(base["seconds_per_forward"])
-        if time.perf_counter() - t_all > 240:   # keep the whole run within a few minutes
-            break
-    if not per_step:
-        per_step = [base["seconds_per_forward"]]
-    t = sum(per_step) / len(per_step)
-    value = args.cpu_batch / (t * args.samples)
-    ms_full = 1e3 * t * args.samples * args.batch / args.cpu_batch
-    base["value"] = value
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": len(per_step),
-            "warmup": args.warmup, "ms_per_step": ms_full, "higher_is_better": True, "scaling": "strong",
+    warm = max(1, min(args.warmup, 2))
+    base = cpu_reference_images_per_s(args.batch, args.samples, forwards=args.steps, warm=warm, budget_s=200.0)
+    t = base.pop("seconds_per_forward")
+    n = base.pop("forwards_timed")
+    line = {"impl": "reference", "metric": METRIC, "value": base["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": n,
+            "warmup": warm, "ms_per_step": 1e3 * t * args.samples, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "resnet50_dnn_to_bnn_reparam_mc_inference", "batch": args.batch, "samples": args.samples,
-                       "image": "3x224x224", "note": "reference CPU path (oracle port); each step is a bounded sample, "
-                                                     "ms_per_step extrapolated to the full batch x S"},
-            "cpu_baseline": {k: v for k, v in base.items() if k != "seconds_per_forward"},
-            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                       "image": "3x224x224", "note": "the reference's own eager code on the host cores; each timed step is ONE of the "
+                                                     f"{args.samples} full-batch Monte-Carlo forwards of a step (bounded sample), "
+                                                     f"ms_per_step = {args.samples} x the measured forward"},
+            "cpu_baseline": base,
+            "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+
+
+def eager_on_gpu(dev, batch: int, samples: int, timed_forwards: int = 2):
+    """SURVEY.md section 2's bar: the reference's eager op sequence ON THIS GPU (`.cuda()`, what a user of the
+    reference gets today): softplus, normal_(), mul, add, F.conv2d per layer (conv_variational.py:362-385) x 54
+    layers x S sequential forwards (main_bayesian_cifar_dnn2bnn.py:542-556), CUDA-event timed."""
+    import torch
+    out = {}
+    g = torch.Generator().manual_seed(0)
+    x32 = torch.randn(batch, 3, 224, 224, generator=g).to(dev)
+    for tag in ("fp32_nchw", "bf16_channels_last"):
+        try:
+            model, where = reference_model(dev)
+            x = x32
+            if tag == "bf16_channels_last":   # the reference's --half analogue on this hardware
+                model = model.to(torch.bfloat16).to(memory_format=torch.channels_last)
+                x = x32.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+            with torch.no_grad():
+                for _ in range(2):
+                    model(x)
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                outs = [model(x) for _ in range(timed_forwards)]
+                torch.softmax(torch.stack(outs).float(), dim=-1).mean(0)
+                e1.record()
+                torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / timed_forwards
+            out[tag] = {"value": batch * 1e3 / (ms * samples), "unit": UNIT, "ms_per_forward": ms,
+                        "sample": f"{timed_forwards} of the {samples} full-batch forwards of a step, scaled",
+                        "tf32_conv": bool(torch.backends.cudnn.allow_tf32)}
+            del model
+        except Exception as e:   # the reference's own limits (e.g. dtype handling) are reported, not hidden
+            out[tag] = {"error": f"{type(e).__name__}: {e}"[:300]}
+        torch.cuda.empty_cache()
+    out["source"] = "oracle/_ref (the unmodified reference), torch eager on this GPU"
+    return out
 
 
 # ------------------------------------------------------------------------------------------
 # this repo's arm
 # ------------------------------------------------------------------------------------------
-def tc_traffic(launches_per_step):
-    """DRAM bytes per launch of the dominant kernel from the committed ncu pass over one timed step
-    of this same command (profiles/r1_tc2_traffic.json, tools/summarize_launches.py); None when the
-    capture does not match the launch count of this run."""
-    path = os.path.join(ROOT, "profiles", "r1_tc2_traffic.json")
+def measured_traffic(n_gpus, launches_per_step, samples_per_gpu):
+    """DRAM bytes per launch of the dominant kernel from an ncu pass over one timed step of THIS command at THIS
+    GPU count (profiles/r2_tc2_traffic.json, tools/summarize_launches.py); None when no capture matches."""
+    path = os.path.join(ROOT, "profiles", "r2_tc2_traffic.json")
     try:
         with open(path) as f:
-            t = json.load(f)
-        if t.get("launches") == launches_per_step:
-            return t["dram_bytes_per_launch"]
+            for t in json.load(f).get("captures", []):
+                if t.get("n_gpus") == n_gpus and t.get("launches") == launches_per_step and t.get("samples_per_gpu") == samples_per_gpu:
+                    return t["dram_bytes_per_launch"]
     except (OSError, ValueError, KeyError):
         pass
     return None
@@ -179,19 +243,9 @@ def build_model(device, fold_bn=True, prepare=None):
     the fp32 eval-mode model on `device` before the bf16 / channels-last conversion and the BatchNorm fold (the
     parity test builds its CPU oracle twin there)."""
     import torch
-    import torchvision
     import bayesian_torch_b200 as bt
-    torch.manual_seed(0)
-    model = torchvision.models.resnet50()          # random init: no checkpoints offline
-    # gamma of the last BatchNorm of every block: 0.5 keeps the random-init residual stack (weight noise sigma =
-    # 0.5 |w| on top) in a regime where the logits are O(1) and the softmax is not saturated, so the predictive
-    # mean / variance the step returns (and the checksum printed with it) mean something.  No effect on the work done.
-    for name, mod in model.named_modules():
-        if name.endswith("bn3"):
-            mod.weight.data.fill_(0.5)
-    params = {"prior_mu": 0.0, "prior_sigma": 1.0, "posterior_mu_init": 0.0, "posterior_rho_init": -3.0,
-              "type": "Reparameterization", "moped_enable": True, "moped_delta": 0.5}
-    bt.dnn_to_bnn(model, params)                   # MOPED: mu <- DNN init, rho <- get_rho (ImageNet examples force it)
+    model = seed_resnet50()
+    bt.dnn_to_bnn(model, dict(BNN_PARAMS))         # MOPED: mu <- DNN init, rho <- get_rho (ImageNet examples force it)
     model = model.to(device).eval()
     if prepare is not None:
         prepare(model)
@@ -200,6 +254,110 @@ def build_model(device, fold_bn=True, prepare=None):
     if fold_bn:   # eval-mode BatchNorm / ReLU / residual join folded into the layer kernels (exact up to rounding)
         model = bt.fold_batchnorm(model, inplace=True)
     return model
+
+
+def roofline_of(records, ms_step, pk, tc_path, n_gpus, samples_per_gpu):
+    tc = [(f, b, e0.elapsed_time(e1)) for path, f, b, e0, e1 in records if path == tc_path]
+    other_ms = sum(e0.elapsed_time(e1) for path, f, b, e0, e1 in records if path != tc_path)
+    tc_ms, tc_flops = sum(t for _, _, t in tc), sum(f for f, _, _ in tc)
+    achieved = tc_flops / (tc_ms * 1e-3) / 1e12 if tc_ms > 0 else 0.0
+    # every layer against ITS OWN binding bound: tensor pipe or HBM, whichever takes longer
+    t_tc = [f / (pk["tflops"] * 1e12) * 1e3 for f, _, _ in tc]
+    t_hbm = [b / (pk["gbs"] * 1e9) * 1e3 for _, b, _ in tc]
+    comp = [i for i in range(len(tc)) if t_tc[i] >= t_hbm[i]]
+    mem = [i for i in range(len(tc)) if t_tc[i] < t_hbm[i]]
+    mixed = sum(max(a, b) for a, b in zip(t_tc, t_hbm))
+
+    def frac(idx, bound):
+        return (sum(bound[i] for i in idx) / sum(tc[i][2] for i in idx)) if idx else None
+    return {"bound": "tensor", "kernel": "tc2_fwd_kernel (all launches of one step)", "achieved": achieved,
+            "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"],
+            "traffic": measured_traffic(n_gpus, len(tc), samples_per_gpu),
+            "algorithmic_bytes_per_launch": (sum(b for _, b, _ in tc) / len(tc)) if tc else None,
+            "peak_source": pk["source"], "launches_per_step": len(tc), "ms_per_step_in_kernel": tc_ms,
+            "ms_per_step_other_bt_kernels": other_ms, "share_of_step": tc_ms / ms_step if ms_step > 0 else None,
+            "mixed_bound_ms": mixed, "mixed_bound_frac": mixed / tc_ms if tc_ms > 0 else None,
+            "compute_bound_layers": {"count": len(comp), "ms": sum(tc[i][2] for i in comp), "frac_of_tensor_peak": frac(comp, t_tc)},
+            "hbm_bound_layers": {"count": len(mem), "ms": sum(tc[i][2] for i in mem), "frac_of_hbm_peak": frac(mem, t_hbm),
+                                 "hbm_peak_gbs": pk["gbs"]}}
+
+
+def cuda_time(fn, iters, warm=2):
+    import torch
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def extras(dev, model, pk):
+    """Side measurements on the same box, N = 1: BASELINE.json configs[4] (LinearReparameterization sweep, one weight
+    sample per call, bf16 tensor-core path and fp32 activations, fused KL on), the KL kernel over ResNet-50's table,
+    configs[2] (ResNet-18 Flipout training step).  Reported under `extra`; none of it is in the timed region."""
+    import torch
+    import bayesian_torch_b200 as bt
+    from bayesian_torch_b200 import layers as L
+    out = {}
+    sweep = []
+    for n in (1024, 2048, 4096, 8192, 16384):
+        torch.manual_seed(0)
+        layer = L.LinearReparameterization(n, n, bias=True).to(dev)
+        row = {"n": n, "batch": 4096}
+        xb = torch.randn(4096, n, device=dev).bfloat16()
+        with torch.no_grad():
+            for tag, x, iters in (("bf16", xb, 10), ("fp32", xb.float(), 10 if n <= 4096 else 2)):
+                ms = cuda_time(lambda: layer(x, return_kl=True), iters)
+                tf = 2.0 * 4096 * n * n / ms / 1e9
+                row[tag] = {"ms_fwd_plus_kl": ms, "tflops": tf, "frac_of_tensor_peak": tf / pk["tflops"]}
+            kms = cuda_time(lambda: layer.kl_loss(), 10, warm=3)
+            row["kl"] = {"ms": kms, "gbs": 8.0 * (n * n + n) / kms / 1e6, "frac_of_hbm_peak": 8.0 * (n * n + n) / kms / 1e6 / pk["gbs"]}
+        sweep.append(row)
+        del layer, xb, x
+        torch.cuda.empty_cache()
+    out["cfg4_linear_sweep_S1"] = sweep
+    with torch.no_grad():
+        nbytes = 8 * sum(p.numel() for n_, p in model.named_parameters() if n_.rsplit(".", 1)[-1].startswith("mu_"))
+        kms = cuda_time(lambda: bt.get_kl_loss(model), 20, warm=3)
+    out["kl_resnet50_table"] = {"ms": kms, "gbs": nbytes / kms / 1e6, "frac_of_hbm_peak": nbytes / kms / 1e6 / pk["gbs"], "bytes": nbytes}
+    out["cfg2_resnet18_flipout_train_step"] = train_step_time(dev, 128, "Flipout", iters=5)
+    return out
+
+
+def make_train_step(dev, batch, typ="Flipout", arch="resnet18"):
+    """BASELINE.json configs[2]: torchvision ResNet-18 + dnn_to_bnn(type=Flipout), synthetic 3x224x224, one step =
+    forward, get_kl_loss, CE + kl / batch, backward, SGD (examples/main_bayesian_cifar_dnn2bnn.py:374-449, num_mc 1)."""
+    import torch
+    import torchvision
+    import bayesian_torch_b200 as bt
+    torch.manual_seed(0)
+    model = getattr(torchvision.models, arch)()
+    bt.dnn_to_bnn(model, dict(BNN_PARAMS, type=typ, moped_enable=False))
+    model = model.to(dev).bfloat16().to(memory_format=torch.channels_last).train()
+    opt = torch.optim.SGD(model.parameters(), lr=1e-3, momentum=0.9)
+    return model, opt
+
+
+def train_step_time(dev, batch, typ, iters):
+    import torch
+    import bayesian_torch_b200 as bt
+    model, opt = make_train_step(dev, batch, typ)
+    x = torch.randn(batch, 3, 224, 224, device=dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    y = torch.randint(0, 1000, (batch,), device=dev)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        out = model(x)
+        loss = torch.nn.functional.cross_entropy(out.float(), y) + bt.get_kl_loss(model) / batch
+        loss.backward()
+        opt.step()
+    ms = cuda_time(step, iters)
+    return {"ms": ms, "images_per_s": batch * 1e3 / ms, "batch": batch, "dtype": "bf16 activations, fp32 parameters"}
 
 
 def run_b200(args):
@@ -218,6 +376,8 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+    if args.workload == "train":
+        return run_train(args, dev, rank, world)
 
     model = build_model(dev, fold_bn=not args.no_fold_bn)
     B, S = args.batch, args.samples
@@ -226,19 +386,25 @@ def run_b200(args):
     x_dev = x_host.to(dev).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
     bt.manual_seed(1234)
 
-    def step_resident():
-        return bt.mc_predict(model, x_dev, S, batch_samples=args.mc_batch)
+    # One step through the public API.  bt.MCPredictor captures the step's launches (the S/N folded forwards, the
+    # accumulate / finalize kernels) into a CUDA graph on first use and replays it: at 8 GPUs a step is ~9 ms of
+    # device time and enqueueing its 58 launches from Python took 4.5 ms of host time.
+    predictor = bt.MCPredictor(model, S, batch_samples=args.mc_batch, use_graph=not args.no_graph)
 
-    # end to end through the public API: every step copies its own batch from pinned host memory (bt.HostBatchPrefetcher:
-    # the copy of the NEXT step's batch is issued right after this step's forwards are enqueued and overlaps them) and
-    # reads the predictive mean / variance back to the host
-    prefetch = bt.HostBatchPrefetcher(dev, dtype=torch.bfloat16, memory_format=torch.channels_last)
+    def step_resident():
+        return predictor(x_dev)
+
+    # end to end through the public API: every step brings its batch in from pinned host memory -- each rank copies
+    # its 1/N of the images over PCIe and an all-gather over NVLink assembles the batch on every GPU
+    # (bt.HostBatchPrefetcher: the copy of the NEXT step's batch overlaps this step's forwards) -- and reads the
+    # predictive mean / variance back to the host
+    prefetch = bt.HostBatchPrefetcher(dev, dtype=torch.bfloat16, memory_format=torch.channels_last, shard=world > 1)
 
     def step_e2e():
         if prefetch._pending is None:          # first step of a timed run: nothing to overlap with, the copy is exposed
             prefetch.submit(x_host)
         xd = prefetch.take()
-        res = bt.mc_predict(model, xd, S, batch_samples=args.mc_batch)
+        res = predictor(xd)
         prefetch.submit(x_host)                # next step's batch (same synthetic images): H2D on the side stream
         return res.mean.cpu(), res.var.cpu()
 
@@ -272,28 +438,30 @@ def run_b200(args):
     ms_step, res = timed(step_resident, args.steps)
     if ncu_range:
         torch.cuda.cudart().cudaProfilerStop()
-    launches = ops.PROFILE.launches
+    launches = predictor.launches_per_step * args.steps if predictor.graphed else ops.PROFILE.launches
     clocks = sampler.stop() if rank == 0 else None
+    # what the step returned, as numbers the N = 1 / 2 / 4 / 8 lines can be compared by (sample s is the same draw on
+    # any rank: the sums differ only by the order of the fp32 additions)
+    checksum = {"sum_mean_sq": float((res.mean.double() ** 2).sum()), "sum_var": float(res.var.double().sum()),
+                "sum_entropy": float(res.entropy.double().sum()), "sum_mutual_info": float(res.mutual_info.double().sum()),
+                "max_mean": float(res.mean.max()), "argmax_sum": int(res.mean.argmax(-1).sum())}
 
-    # roofline of the dominant kernel (tc_fwd_kernel): CUDA events around every layer call of
-    # one more timed step, on the launching stream
+    # roofline of the dominant kernel (tc2_fwd_kernel): CUDA events around every layer call of one more step
+    # enqueued eagerly on the launching stream (the same launches the graph replays)
     ops.PROFILE.reset()
     ops.PROFILE.timing = True
     barrier()
-    step_resident()
+    with torch.no_grad():
+        bt.mc_predict(model, x_dev, S, batch_samples=args.mc_batch)
     torch.cuda.synchronize()
     ops.PROFILE.timing = False
-    tc = [(f, b, e0.elapsed_time(e1)) for path, f, b, e0, e1 in ops.PROFILE.records if path == _lib.PATH_TC_BF16]
-    other = [(f, b, e0.elapsed_time(e1)) for path, f, b, e0, e1 in ops.PROFILE.records if path != _lib.PATH_TC_BF16]
-    tc_ms, tc_flops = sum(t for _, _, t in tc), sum(f for f, _, _ in tc)
-    other_ms = sum(t for _, _, t in other)
+    records = ops.PROFILE.records
 
     ms_e2e, _ = timed(step_e2e, args.steps)
     prefetch.take()                            # the batch submitted by the last step (one copy more than steps timed)
 
     if rank == 0:
         pk = peaks()
-        achieved = tc_flops / (tc_ms * 1e-3) / 1e12 if tc_ms > 0 else 0.0
         value = B * 1e3 / ms_step
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
@@ -301,23 +469,114 @@ def run_b200(args):
             "data": "synthetic",
             "config": {"workload": "resnet50_dnn_to_bnn_reparam_mc_inference", "batch": B, "samples": S, "image": "3x224x224",
                        "samples_per_gpu": S / world, "mc_batch": args.mc_batch, "bn_folded": not args.no_fold_bn, "parallelism": f"mc_samples_sharded_x{world}",
+                       "cuda_graph": predictor.graphed,
                        "l2": "activations per step (GBs) far exceed the 126 MB L2; no flush needed",
                        "image_samples_per_s": value * S,
                        "tflops_bayesian_layers": value * S * GFLOP_PER_IMAGE_SAMPLE / 1e3},
             "clocks": clocks,
             "e2e": {"value": B * 1e3 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": x_host.numel() * 4,
-                    "d2h_bytes_per_step": 2 * res.mean.numel() * 4},
+                    "d2h_bytes_per_step": 2 * res.mean.numel() * 4 * world,
+                    "note": "whole-job bytes: each rank copies batch/N images H2D (an NVLink all-gather assembles the batch) "
+                            "and reads mean + variance back"},
             "gpu_launches": launches,
-            "roofline": {"bound": "tensor", "kernel": "tc2_fwd_kernel (all launches of one step)", "achieved": achieved,
-                         "peak": pk["tflops"], "unit": "TFLOP/s", "frac": achieved / pk["tflops"], "traffic": tc_traffic(len(tc)), "algorithmic_bytes_per_launch": (sum(b for _, b, _ in tc) / len(tc)) if tc else None,
-                         "peak_source": pk["source"], "launches_per_step": len(tc), "ms_per_step_in_kernel": tc_ms,
-                         "ms_per_step_other_bt_kernels": other_ms,
-                         "share_of_step": tc_ms / ms_step if ms_step > 0 else None},
+            "checksum": checksum,
+            "roofline": roofline_of(records, ms_step, pk, _lib.PATH_TC_BF16, world, S / world),
         }
-        if not args.no_cpu_baseline and world == 1:   # the CPU baseline is a rank-0, N = 1 figure (torchrun pins OMP threads to 1)
-            line["cpu_baseline"] = {k: v for k, v in cpu_reference_images_per_s(B, S, 16, repeats=5).items()
-                                    if k != "seconds_per_forward"}
+        if world == 1:   # rank-0, N = 1 side figures (torchrun pins OMP threads to 1, and they need a free GPU)
+            torch.cuda.empty_cache()
+            if not args.no_cpu_baseline:
+                base = cpu_reference_images_per_s(B, S, forwards=2, warm=1, budget_s=60.0)
+                line["cpu_baseline"] = {k: v for k, v in base.items() if k not in ("seconds_per_forward", "forwards_timed")}
+            if not args.no_eager:
+                try:
+                    line["eager_b200"] = eager_on_gpu(dev, B, S)
+                except ImportError as e:
+                    line["eager_b200"] = {"error": str(e)}
+            if not args.no_extras:
+                line["extra"] = extras(dev, model, pk)
         print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def run_train(args, dev, rank, world):
+    """configs[2] extended to N GPUs (training): data-parallel ResNet-18 Flipout, batch 128 PER GPU
+    (weak scaling), the mu / rho gradients summed by NCCL in fixed fp32 buckets issued from inside backward
+    (bt.GradientBuckets) so the all-reduce overlaps the remaining dgrad / wgrad kernels."""
+    import torch
+    import torch.distributed as dist
+    import bayesian_torch_b200 as bt
+    from bayesian_torch_b200 import ops
+    B = args.batch
+    model, opt = make_train_step(dev, B)
+    bt.manual_seed(1234 + rank)        # each rank draws its own weight noise, like the reference's DDP ranks
+    buckets = bt.GradientBuckets(model, bucket_mb=25.0) if world > 1 else None
+    g = torch.Generator().manual_seed(rank)
+    x_host = torch.randn(B, 3, 224, 224, generator=g).pin_memory()
+    y = torch.randint(0, 1000, (B,), generator=g).to(dev)
+    x_dev = x_host.to(dev).bfloat16().contiguous(memory_format=torch.channels_last)
+    prefetch = bt.HostBatchPrefetcher(dev, dtype=torch.bfloat16, memory_format=torch.channels_last)
+
+    def step(x):
+        opt.zero_grad(set_to_none=True)
+        out = model(x)
+        loss = torch.nn.functional.cross_entropy(out.float(), y) + bt.get_kl_loss(model) / (B * world)
+        loss.backward()
+        if buckets is not None:
+            buckets.finish()           # the last buckets' all-reduces + the copy-back of the averaged gradients
+        opt.step()
+        return loss
+
+    def step_e2e():
+        if prefetch._pending is None:
+            prefetch.submit(x_host)
+        xd = prefetch.take()
+        loss = step(xd)
+        prefetch.submit(x_host)
+        return loss.cpu()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms) / steps, out
+
+    for _ in range(max(args.warmup, 3)):
+        step(x_dev)
+    sampler = ClockSampler(dev.index)
+    if rank == 0:
+        sampler.start()
+    ops.PROFILE.reset()
+    ms_step, loss = timed(lambda: step(x_dev), args.steps)
+    launches = ops.PROFILE.launches
+    clocks = sampler.stop() if rank == 0 else None
+    ms_e2e, _ = timed(step_e2e, args.steps)
+    prefetch.take()
+    if rank == 0:
+        value = B * world * 1e3 / ms_step
+        print(json.dumps({
+            "metric": "bayesian_resnet18_flipout_train_images_per_s", "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "resnet18_dnn_to_bnn_flipout_training_step", "batch_per_gpu": B, "global_batch": B * world,
+                       "image": "3x224x224", "parallelism": f"dp{world}", "grad_allreduce": "bucketed fp32, issued inside backward" if world > 1 else "none",
+                       "l2": "activations per step far exceed the 126 MB L2; no flush needed"},
+            "clocks": clocks, "loss": float(loss),
+            "e2e": {"value": B * world * 1e3 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": x_host.numel() * 4 * world, "d2h_bytes_per_step": 4 * world},
+            "gpu_launches": launches}))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

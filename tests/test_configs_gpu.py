@@ -81,6 +81,17 @@ def oracle_twin(model, dev):
     return twin
 
 
+def pin_layer_ids(model, base):
+    """Give the model's Bayesian layers fixed Philox stream ids.  The ids come from a process-wide counter, so the
+    draws (and with them the whole numeric instance) would depend on which tests ran before.  That matters for the
+    GRADIENT checks below: ReLU / max-pool route gradients discontinuously, an activation within ~1e-7 of a tie
+    routes differently on the two sides, and one re-routed element moves a weight gradient (a random-sign sum over
+    ~1e5 positions) by ~1/sqrt(N) ~ 3e-3 of its size.  Pinned ids make the instance -- and its absence of ties --
+    reproducible."""
+    for i, m in enumerate(mod for mod in model.modules() if isinstance(mod, _BayesLayer)):
+        m._layer_id = base + i
+
+
 def set_sample(twin, s):
     for m in twin.modules():
         if isinstance(m, OracleFed):
@@ -118,6 +129,7 @@ def test_config0_scnn_forward_kl_backward(cuda_device):
     torch.manual_seed(0)
     bt.manual_seed(77)
     model = SCNN().to(cuda_device)
+    pin_layer_ids(model, 1)
     twin = oracle_twin(model, cuda_device)
     x = torch.randn(128, 1, 28, 28)
     y = torch.randint(0, 10, (128,))
@@ -186,6 +198,7 @@ def test_config1_resnet20_mc_inference(cuda_device):
     torch.manual_seed(1)
     bt.manual_seed(78)
     model = ResNet20().to(cuda_device).eval()
+    pin_layer_ids(model, 1)
     for m in model.modules():
         if isinstance(m, nn.BatchNorm2d):
             m.running_mean.normal_(0, 0.1); m.running_var.uniform_(0.8, 1.2)
@@ -238,6 +251,7 @@ def test_config2_resnet18_flipout_training_step(cuda_device):
     bt.dnn_to_bnn(model, {"prior_mu": 0.0, "prior_sigma": 1.0, "posterior_mu_init": 0.0, "posterior_rho_init": -3.0,
                           "type": "Flipout", "moped_enable": True, "moped_delta": 0.5})
     model = model.to(cuda_device).eval()    # eval: BatchNorm uses running statistics on both sides (batch 6 is too small for batch stats parity)
+    pin_layer_ids(model, 1)
     twin = oracle_twin(model, cuda_device).eval()
     assert sum(isinstance(m, _BayesLayer) for m in model.modules()) == 21
     B = 6

@@ -88,3 +88,63 @@ def test_two_rank_gradient_allreduce_matches_full_batch():
     torch.nn.functional.mse_loss(model(x), y).backward()
     for g, p in zip(grads, model.parameters()):
         torch.testing.assert_close(g, p.grad, rtol=1e-5, atol=1e-6)
+
+
+def _bucket_worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import bayesian_torch_b200 as bt
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.Tanh(), torch.nn.Linear(5, 3), torch.nn.Linear(3, 3))
+    model[3].weight.requires_grad_(True)
+    unused = torch.nn.Parameter(torch.zeros(4))           # a parameter that never gets a gradient: its bucket must still flush
+    model.register_parameter("unused", unused)
+    buckets = bt.GradientBuckets(model, bucket_mb=1e-4)   # tiny buckets: several collectives, issued from inside backward
+    opt = torch.optim.SGD(model.parameters(), lr=0.1)
+    x, y = torch.randn(8, 6), torch.randn(8, 3)
+    lo, hi = rank * 4, rank * 4 + 4
+    fired_during_backward = []
+    for step in range(2):                                 # two steps: the buckets re-arm
+        opt.zero_grad(set_to_none=True)
+        torch.nn.functional.mse_loss(model(x[lo:hi]), y[lo:hi]).backward()
+        fired_during_backward.append(sum(b["fired"] for b in buckets.buckets))
+        n = buckets.finish()
+        if step == 0:
+            grads = [None if p.grad is None else p.grad.clone().numpy() for p in model.parameters()]   # numpy: pickled by value
+        opt.step()
+    if rank == 0:
+        ret.put((n, fired_during_backward, len(buckets.buckets), grads, [p.detach().clone().numpy() for p in model.parameters()]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_gradient_buckets_fire_inside_backward_and_match_full_batch():
+    """GradientBuckets: all-reduces are issued by the post-accumulate hooks (before backward() returns), the averaged
+    gradients the optimizer sees equal the full-batch ones, and two SGD steps track the single-process run."""
+    ctx = mp.get_context("spawn")
+    ret = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_bucket_worker, args=(r, 2, port, ret)) for r in range(2)]
+    [p.start() for p in procs]
+    n, fired, nb, grads, params = ret.get(timeout=120)
+    [p.join(timeout=120) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    assert nb >= 3 and n >= 3
+    assert fired[0] >= nb - 1 and fired[1] >= nb - 1      # every complete bucket went out from inside backward
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.Tanh(), torch.nn.Linear(5, 3), torch.nn.Linear(3, 3))
+    model.register_parameter("unused", torch.nn.Parameter(torch.zeros(4)))
+    opt = torch.optim.SGD(model.parameters(), lr=0.1)
+    x, y = torch.randn(8, 6), torch.randn(8, 3)
+    for step in range(2):
+        opt.zero_grad(set_to_none=True)
+        torch.nn.functional.mse_loss(model(x), y).backward()
+        if step == 0:
+            for g, p in zip(grads, model.parameters()):
+                if p.grad is None:
+                    assert g is None
+                else:
+                    torch.testing.assert_close(torch.from_numpy(g), p.grad, rtol=1e-5, atol=1e-6)
+        opt.step()
+    for a, p in zip(params, model.parameters()):
+        torch.testing.assert_close(torch.from_numpy(a), p.detach(), rtol=1e-5, atol=1e-6)

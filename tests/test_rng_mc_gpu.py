@@ -215,3 +215,39 @@ def test_host_batch_prefetcher(cuda_device):
         pf.take()
     with pytest.raises(RuntimeError, match="host tensor"):
         pf.submit(torch.zeros(1, device=cuda_device))
+
+
+def test_mc_predictor_graph_replay_equals_eager(cuda_device):
+    """bt.MCPredictor: the step captured into a CUDA graph (the C ABI allocates nothing, synchronises nothing and
+    launches on the caller's stream) returns bit-for-bit what the eager mc_predict returns, also for a NEW input of
+    the same shape on replay, and re-captures when a parameter changes."""
+    import torch.nn as nn
+    torch.manual_seed(11)
+    bt.manual_seed(31)
+    net = nn.Sequential(nn.Conv2d(64, 64, 3, padding=1, bias=False), nn.BatchNorm2d(64), nn.ReLU(), nn.Conv2d(64, 128, 1),
+                        nn.ReLU(), nn.AdaptiveAvgPool2d(1), nn.Flatten(), nn.Linear(128, 16))
+    bt.dnn_to_bnn(net, {"prior_mu": 0.0, "prior_sigma": 1.0, "posterior_mu_init": 0.0, "posterior_rho_init": -3.0,
+                        "type": "Reparameterization", "moped_enable": True, "moped_delta": 0.5})
+    net = net.to(cuda_device).eval().to(memory_format=torch.channels_last).to(torch.bfloat16)
+    net = bt.fold_batchnorm(net, inplace=True)
+    x1 = torch.randn(8, 64, 12, 12, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    x2 = torch.randn(8, 64, 12, 12, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    pred = bt.MCPredictor(net, 6, batch_samples=3)
+    with torch.no_grad():
+        want1 = bt.mc_predict(net, x1, 6, batch_samples=3)
+        want2 = bt.mc_predict(net, x2, 6, batch_samples=3)
+    got1 = pred(x1)
+    assert pred.graphed and pred.launches_per_step >= 2 * 3 + 2 + 1
+    n0 = ops.PROFILE.launches
+    got2 = pred(x2)
+    assert ops.PROFILE.launches - n0 == 1          # replay: only the finalize kernel is launched from the host
+    got1b = pred(x1)
+    for got, want in ((got1, want1), (got2, want2), (got1b, want1)):
+        for a, b in zip(got, want):
+            torch.testing.assert_close(a, b, rtol=0, atol=0)
+    with torch.no_grad():
+        net.get_submodule("0").mu_kernel.mul_(1.5)     # parameter version changes -> new capture with re-packed weights
+        want3 = bt.mc_predict(net, x1, 6, batch_samples=3)
+    got3 = pred(x1)
+    torch.testing.assert_close(got3.mean, want3.mean, rtol=0, atol=0)
+    assert float((got3.mean - got1.mean).abs().max()) > 0

@@ -262,8 +262,9 @@ def test_conv2d_tc_residual_epilogue(cin, cout, k, pad, batch, hw, S, relu, cuda
         with bt.mc_batched(S, 5):
             plain = layer(x)
         layer._ep_relu = relu
-        with bt.mc_batched(S, 5):
+        with bt.mc_batched(S, 5):      # (one call per block: a second call inside a block draws afresh, ops.call_seed)
             fused = layer(x, residual=res)
+        with bt.mc_batched(S, 5):
             fused_nchw = layer(x, residual=res.contiguous())      # another layout: copied to out's strides
     want = plain + res
     if relu:

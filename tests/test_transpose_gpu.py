@@ -88,6 +88,7 @@ def test_transpose_bf16_channels_last_route(cuda_device):
     with bt.mc_sample(2), torch.no_grad():
         layer.path = "simt"
         want, _ = layer(x)
+    with bt.mc_sample(2), torch.no_grad():   # a new block: a second call inside the first would draw afresh
         layer.path = "auto"
         got, _ = layer(x.bfloat16().contiguous(memory_format=torch.channels_last))
     assert got.dtype == torch.bfloat16 and got.shape == want.shape == (4, 64, 28, 28)
