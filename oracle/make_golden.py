@@ -31,14 +31,11 @@ KL_COEF = 0.37
 
 
 def import_reference():
-    stub = types.ModuleType("termcolor")
-    stub.colored = lambda s, *a, **k: s
-    sys.modules.setdefault("termcolor", stub)
-    if "/root/reference" not in sys.path:
-        sys.path.insert(0, "/root/reference")
-    import bayesian_torch.layers as L  # noqa
-    from bayesian_torch.models import dnn_to_bnn as D  # noqa
-    from bayesian_torch.utils import util as U  # noqa
+    """The reference itself: the staged archive (oracle/build_ref.py) or /root/reference, with the termcolor stub."""
+    if ROOT not in sys.path:
+        sys.path.insert(0, ROOT)
+    from oracle.build_ref import import_reference as imp
+    L, D, U, _ = imp()
     return L, D, U
 
 
@@ -66,6 +63,13 @@ ONLY = None  # `python oracle/make_golden.py <prefix> ...`: write only the fixtu
 def run_case(name, layer, x, flipout=False, seed=0, extra=None, laplace=False):
     if ONLY and not any(name.startswith(p) for p in ONLY):
         return
+    # layer and input are built HERE under a per-case seed (callables), so a fixture depends on its own case only,
+    # not on which cases ran before it
+    torch.manual_seed(500 + seed)
+    if isinstance(layer, types.FunctionType):
+        layer = layer()
+    if isinstance(x, types.FunctionType):
+        x = x()
     torch.manual_seed(1000 + seed)
     x = x.clone().requires_grad_(True)
     torch.manual_seed(2000 + seed)
@@ -120,60 +124,63 @@ def cfg(**kw):
     return {"cfg_" + k: np.asarray(v) for k, v in kw.items()}
 
 
-def main():
+def main(out_dir=None):
+    global OUT
+    if out_dir is not None:
+        OUT = out_dir
     os.makedirs(OUT, exist_ok=True)
     L, D, U = import_reference()
     torch.manual_seed(0)
     R = torch.randn
 
     # ---- LinearReparameterization (linear_variational.py:54) ----
-    run_case("linear_rp_8x5x7_bias", L.LinearReparameterization(5, 7), R(8, 5), seed=1)
-    run_case("linear_rp_33x70x37_nobias", L.LinearReparameterization(70, 37, bias=False), R(33, 70), seed=2)
-    run_case("linear_rp_lead_2x3x16x24", L.LinearReparameterization(16, 24), R(2, 3, 16), seed=3)
-    run_case("linear_rp_128x256x192_prior", L.LinearReparameterization(
-        256, 192, prior_mean=0.3, prior_variance=0.5, posterior_rho_init=-2.0), R(128, 256), seed=4,
+    run_case("linear_rp_8x5x7_bias", lambda: L.LinearReparameterization(5, 7), lambda: R(8, 5), seed=1)
+    run_case("linear_rp_33x70x37_nobias", lambda: L.LinearReparameterization(70, 37, bias=False), lambda: R(33, 70), seed=2)
+    run_case("linear_rp_lead_2x3x16x24", lambda: L.LinearReparameterization(16, 24), lambda: R(2, 3, 16), seed=3)
+    run_case("linear_rp_128x256x192_prior", lambda: L.LinearReparameterization(
+        256, 192, prior_mean=0.3, prior_variance=0.5, posterior_rho_init=-2.0), lambda: R(128, 256), seed=4,
         extra=cfg(prior_mean=0.3, prior_variance=0.5))
 
     # ---- Conv2dReparameterization (conv_variational.py:234) ----
     def c2(name, x, seed, **kw):
-        layer = L.Conv2dReparameterization(prior_type="normal", **kw)
+        layer = lambda: L.Conv2dReparameterization(prior_type="normal", **kw)  # noqa: E731
         ex = cfg(stride=kw.get("stride", 1), padding=kw.get("padding", 0), dilation=kw.get("dilation", 1),
                  groups=kw.get("groups", 1), prior_mean=kw.get("prior_mean", 0), prior_variance=kw.get("prior_variance", 1))
         run_case(name, layer, x, seed=seed, extra=ex)
-    c2("conv2d_rp_1x1", R(2, 16, 9, 9), 10, in_channels=16, out_channels=24, kernel_size=1)
-    c2("conv2d_rp_3x3_p1", R(3, 8, 12, 12), 11, in_channels=8, out_channels=16, kernel_size=3, padding=1)
-    c2("conv2d_rp_3x3_s2_p1", R(2, 8, 13, 11), 12, in_channels=8, out_channels=12, kernel_size=3, stride=2, padding=1)
-    c2("conv2d_rp_7x7_s2_p3_c3", R(2, 3, 32, 32), 13, in_channels=3, out_channels=16, kernel_size=7, stride=2, padding=3, bias=False)
-    c2("conv2d_rp_groups2", R(2, 8, 10, 10), 14, in_channels=8, out_channels=12, kernel_size=3, padding=1, groups=2)
-    c2("conv2d_rp_dil2", R(2, 4, 14, 14), 15, in_channels=4, out_channels=6, kernel_size=3, padding=2, dilation=2)
-    c2("conv2d_rp_prior", R(2, 4, 8, 8), 16, in_channels=4, out_channels=8, kernel_size=(3, 2), padding=(1, 0),
+    c2("conv2d_rp_1x1", lambda: R(2, 16, 9, 9), 10, in_channels=16, out_channels=24, kernel_size=1)
+    c2("conv2d_rp_3x3_p1", lambda: R(3, 8, 12, 12), 11, in_channels=8, out_channels=16, kernel_size=3, padding=1)
+    c2("conv2d_rp_3x3_s2_p1", lambda: R(2, 8, 13, 11), 12, in_channels=8, out_channels=12, kernel_size=3, stride=2, padding=1)
+    c2("conv2d_rp_7x7_s2_p3_c3", lambda: R(2, 3, 32, 32), 13, in_channels=3, out_channels=16, kernel_size=7, stride=2, padding=3, bias=False)
+    c2("conv2d_rp_groups2", lambda: R(2, 8, 10, 10), 14, in_channels=8, out_channels=12, kernel_size=3, padding=1, groups=2)
+    c2("conv2d_rp_dil2", lambda: R(2, 4, 14, 14), 15, in_channels=4, out_channels=6, kernel_size=3, padding=2, dilation=2)
+    c2("conv2d_rp_prior", lambda: R(2, 4, 8, 8), 16, in_channels=4, out_channels=8, kernel_size=(3, 2), padding=(1, 0),
        stride=(1, 2), prior_mean=-0.2, prior_variance=2.0)
-    c2("conv2d_rp_64ch", R(2, 64, 14, 14), 17, in_channels=64, out_channels=64, kernel_size=3, padding=1, bias=False)
+    c2("conv2d_rp_64ch", lambda: R(2, 64, 14, 14), 17, in_channels=64, out_channels=64, kernel_size=3, padding=1, bias=False)
 
     # ---- Conv1d / Conv3d Reparameterization (conv_variational.py:68, :650) ----
-    run_case("conv1d_rp_k3", L.Conv1dReparameterization(6, 10, 3, stride=2, padding=1), R(3, 6, 25), seed=20,
+    run_case("conv1d_rp_k3", lambda: L.Conv1dReparameterization(6, 10, 3, stride=2, padding=1), lambda: R(3, 6, 25), seed=20,
              extra=cfg(stride=2, padding=1, dilation=1, groups=1))
-    run_case("conv3d_rp_k3", L.Conv3dReparameterization(4, 6, 3, 0, 1, 0, -3.0, stride=1, padding=1), R(2, 4, 6, 7, 5),
+    run_case("conv3d_rp_k3", lambda: L.Conv3dReparameterization(4, 6, 3, 0, 1, 0, -3.0, stride=1, padding=1), lambda: R(2, 4, 6, 7, 5),
              seed=21, extra=cfg(stride=1, padding=1, dilation=1, groups=1))
 
     # ---- Flipout (linear_flipout.py:49, conv_flipout.py:247) ----
-    run_case("linear_fo_16x20x12", L.LinearFlipout(20, 12), R(16, 20), flipout=True, seed=30)
-    run_case("linear_fo_nobias", L.LinearFlipout(33, 9, bias=False), R(5, 33), flipout=True, seed=31)
-    run_case("conv2d_fo_3x3", L.Conv2dFlipout(8, 12, 3, padding=1), R(2, 8, 10, 10), flipout=True, seed=32,
+    run_case("linear_fo_16x20x12", lambda: L.LinearFlipout(20, 12), lambda: R(16, 20), flipout=True, seed=30)
+    run_case("linear_fo_nobias", lambda: L.LinearFlipout(33, 9, bias=False), lambda: R(5, 33), flipout=True, seed=31)
+    run_case("conv2d_fo_3x3", lambda: L.Conv2dFlipout(8, 12, 3, padding=1), lambda: R(2, 8, 10, 10), flipout=True, seed=32,
              extra=cfg(stride=1, padding=1, dilation=1, groups=1))
-    run_case("conv2d_fo_s2_nobias", L.Conv2dFlipout(6, 8, 3, stride=2, padding=1, bias=False), R(2, 6, 11, 11),
+    run_case("conv2d_fo_s2_nobias", lambda: L.Conv2dFlipout(6, 8, 3, stride=2, padding=1, bias=False), lambda: R(2, 6, 11, 11),
              flipout=True, seed=33, extra=cfg(stride=2, padding=1, dilation=1, groups=1))
 
     # ---- the fork's Laplace prior (base_variational_layer.py:74-97): Linear / Conv2d Reparameterization only ----
-    run_case("linear_rp_laplace_24x40", L.LinearReparameterization(40, 24, prior_type="laplace", posterior_rho_init=-1.0), R(6, 40),
+    run_case("linear_rp_laplace_24x40", lambda: L.LinearReparameterization(40, 24, prior_type="laplace", posterior_rho_init=-1.0), lambda: R(6, 40),
              seed=45, extra={"cfg_prior_type": np.asarray(1)}, laplace=True)
-    run_case("conv2d_rp_laplace_3x3", L.Conv2dReparameterization(6, 8, 3, padding=1, prior_type="laplace"), R(2, 6, 9, 9), seed=46,
+    run_case("conv2d_rp_laplace_3x3", lambda: L.Conv2dReparameterization(6, 8, 3, padding=1, prior_type="laplace"), lambda: R(2, 6, 9, 9), seed=46,
              extra=dict(cfg(stride=1, padding=1, dilation=1, groups=1), cfg_prior_type=np.asarray(1)), laplace=True)
 
     # ---- Conv1d / Conv3d Flipout (conv_flipout.py:57, :443) ----
-    run_case("conv1d_fo_k3_s2", L.Conv1dFlipout(6, 10, 3, stride=2, padding=1), R(3, 6, 25), flipout=True, seed=34,
+    run_case("conv1d_fo_k3_s2", lambda: L.Conv1dFlipout(6, 10, 3, stride=2, padding=1), lambda: R(3, 6, 25), flipout=True, seed=34,
              extra=cfg(stride=2, padding=1, dilation=1, groups=1))
-    run_case("conv3d_fo_k3", L.Conv3dFlipout(4, 6, 3, padding=1, bias=False), R(2, 4, 5, 6, 4), flipout=True, seed=35,
+    run_case("conv3d_fo_k3", lambda: L.Conv3dFlipout(4, 6, 3, padding=1, bias=False), lambda: R(2, 4, 5, 6, 4), flipout=True, seed=35,
              extra=cfg(stride=1, padding=1, dilation=1, groups=1))
 
     # ---- ConvTranspose{1,2,3}d Reparameterization (conv_variational.py:822, :992, :1167) and Flipout
@@ -182,30 +189,31 @@ def main():
         return cfg(stride=kw.get("stride", 1), padding=kw.get("padding", 0), dilation=kw.get("dilation", 1),
                    groups=kw.get("groups", 1), output_padding=kw.get("output_padding", 0))
     kw = dict(stride=2, padding=1, output_padding=1)
-    run_case("convT1d_rp_k3_s2", L.ConvTranspose1dReparameterization(6, 10, 3, **kw), R(3, 6, 9), seed=60, extra=ct(**kw))
+    run_case("convT1d_rp_k3_s2", lambda: L.ConvTranspose1dReparameterization(6, 10, 3, **kw), lambda: R(3, 6, 9), seed=60, extra=ct(**kw))
     kw = dict(stride=2, padding=1, output_padding=1)
-    run_case("convT2d_rp_k3_s2", L.ConvTranspose2dReparameterization(8, 12, (3, 3), **kw), R(2, 8, 7, 6), seed=61, extra=ct(**kw))
+    run_case("convT2d_rp_k3_s2", lambda: L.ConvTranspose2dReparameterization(8, 12, (3, 3), **kw), lambda: R(2, 8, 7, 6), seed=61, extra=ct(**kw))
     kw = dict(stride=1, padding=2, dilation=2, groups=2)
-    run_case("convT2d_rp_dil2_groups2_nobias", L.ConvTranspose2dReparameterization(8, 12, (3, 3), bias=False, **kw),
-             R(2, 8, 6, 6), seed=62, extra=ct(**kw))
+    run_case("convT2d_rp_dil2_groups2_nobias", lambda: L.ConvTranspose2dReparameterization(8, 12, (3, 3), bias=False, **kw),
+             lambda: R(2, 8, 6, 6), seed=62, extra=ct(**kw))
     kw = dict(stride=2, padding=0)
-    run_case("convT3d_rp_k2_s2", L.ConvTranspose3dReparameterization(4, 6, (2, 2, 2), **kw), R(2, 4, 3, 4, 3), seed=63, extra=ct(**kw))
+    run_case("convT3d_rp_k2_s2", lambda: L.ConvTranspose3dReparameterization(4, 6, (2, 2, 2), **kw), lambda: R(2, 4, 3, 4, 3), seed=63, extra=ct(**kw))
     kw = dict(stride=2, padding=1, output_padding=1)
-    run_case("convT1d_fo_k3_s2", L.ConvTranspose1dFlipout(6, 10, 3, **kw), R(3, 6, 9), flipout=True, seed=64, extra=ct(**kw))
+    run_case("convT1d_fo_k3_s2", lambda: L.ConvTranspose1dFlipout(6, 10, 3, **kw), lambda: R(3, 6, 9), flipout=True, seed=64, extra=ct(**kw))
     kw = dict(stride=2, padding=1, output_padding=1)
-    run_case("convT2d_fo_k3_s2", L.ConvTranspose2dFlipout(8, 12, (3, 3), **kw), R(2, 8, 5, 6), flipout=True, seed=65, extra=ct(**kw))
+    run_case("convT2d_fo_k3_s2", lambda: L.ConvTranspose2dFlipout(8, 12, (3, 3), **kw), lambda: R(2, 8, 5, 6), flipout=True, seed=65, extra=ct(**kw))
     kw = dict(stride=1, padding=1)
-    run_case("convT3d_fo_k3_nobias", L.ConvTranspose3dFlipout(4, 6, (3, 3, 3), bias=False, **kw), R(2, 4, 3, 4, 3), flipout=True,
+    run_case("convT3d_fo_k3_nobias", lambda: L.ConvTranspose3dFlipout(4, 6, (3, 3, 3), bias=False, **kw), lambda: R(2, 4, 3, 4, 3), flipout=True,
              seed=66, extra=ct(**kw))
 
     # ---- MOPED rho (utils/util.py:63-69) and tensor-valued priors (utils/util.py:101-104) ----
+    torch.manual_seed(540)   # (every case seeds its own construction: fixtures do not depend on the case order)
     w = R(40, 30) * 0.05
     lay = L.LinearReparameterization(30, 40)
     lay.mu_weight.data.copy_(w)
     lay.rho_weight.data.copy_(U.get_rho(w, 0.5))
     lay.prior_weight_mu = w.clone() * 0.9
     lay.prior_weight_sigma = torch.rand(40, 30) + 0.5
-    run_case("linear_rp_moped_tensorprior", lay, R(4, 30), seed=40,
+    run_case("linear_rp_moped_tensorprior", lay, lambda: R(4, 30), seed=40,
              extra={"moped_w": w, "moped_delta": np.asarray(0.5), "moped_rho": U.get_rho(w, 0.5),
                     "prior_w_mu": lay.prior_weight_mu, "prior_w_sigma": lay.prior_weight_sigma})
 
@@ -264,6 +272,7 @@ def main():
     for m in net.modules():
         if hasattr(m, "prior_type"):
             m.prior_type = "normal"
+    torch.manual_seed(52)
     x = R(4, 3, 8, 8)
     torch.manual_seed(51)
     y = net(x)
@@ -282,6 +291,42 @@ def main():
     print("dnn_to_bnn_small", tuple(y.shape), float(kl), sorted(net.state_dict().keys()))
 
 
+def check(tol=1e-6):
+    """Regenerate every fixture into a scratch directory and compare with the committed files.  Returns the list of
+    (fixture, key, max|delta|) that differ by more than `tol` * max(1, max|committed|)."""
+    import tempfile
+    committed = os.path.join(ROOT, "tests", "golden")
+    bad = []
+    with tempfile.TemporaryDirectory() as tmp:
+        import contextlib
+        import io
+        with contextlib.redirect_stdout(io.StringIO()):
+            main(tmp)
+        names = sorted(f for f in os.listdir(tmp) if f.endswith(".npz"))
+        have = sorted(f for f in os.listdir(committed) if f.endswith(".npz"))
+        for f in sorted(set(names) ^ set(have)):
+            bad.append((f, "<file>", float("inf")))
+        for f in names:
+            if f not in have:
+                continue
+            a, b = np.load(os.path.join(tmp, f)), np.load(os.path.join(committed, f))
+            for k in sorted(set(a.files) | set(b.files)):
+                if k not in a.files or k not in b.files or a[k].shape != b[k].shape:
+                    bad.append((f, k, float("inf")))
+                    continue
+                d = float(np.max(np.abs(a[k].astype(np.float64) - b[k].astype(np.float64)))) if a[k].size else 0.0
+                if d > tol * max(1.0, float(np.max(np.abs(b[k]))) if b[k].size else 1.0):
+                    bad.append((f, k, d))
+    return bad
+
+
 if __name__ == "__main__":
-    ONLY = sys.argv[1:] or None
+    args = sys.argv[1:]
+    if "--check" in args:
+        diffs = check()
+        for f, k, d in diffs:
+            print(f"DIFF {f}:{k} max|delta| {d:.3e}")
+        print("fixtures reproduce from the committed recipe" if not diffs else f"{len(diffs)} entries differ")
+        sys.exit(1 if diffs else 0)
+    ONLY = args or None
     main()

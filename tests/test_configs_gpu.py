@@ -10,6 +10,15 @@ every Bayesian layer replaced by the oracle restatement fed with the EXPORTED st
               bf16 tensor-core path at the documented bf16 bound
   configs[2]  torchvision ResNet-18 + dnn_to_bnn(type="Flipout"), one training step (forward, get_kl_loss,
               CE + kl / batch, backward) at a reduced batch / image size the CPU twin finishes in seconds
+
+Gradients through ReLU / max-pool: both route gradients DISCONTINUOUSLY.  The two sides agree to ~1e-6 on every
+activation, so an activation within ~1e-6 of zero (or of a pooling tie) routes differently, and one re-routed element
+moves a weight gradient -- a random-sign sum over ~1e5 positions -- by ~1/sqrt(N) ~ 3e-3 of its size, on every layer
+upstream.  With millions of activations a few such elements exist in most draws, so an element-wise 1e-4 check of the
+true architecture passes or fails by luck.  Each training-step config is therefore checked twice: the TRUE
+architecture with outputs / KL / loss at rtol 1e-5 and gradients by relative L2 error (<= 2e-2, a few re-routings),
+and a SMOOTH twin of it (softplus for ReLU, average for max pooling: same layers, same shapes, same kernels) with
+gradients element-wise at rtol 1e-4 (configs[0]) / 2e-3 (configs[2], 21 layers of fp32 re-association).
 """
 import copy
 
@@ -107,8 +116,10 @@ def close(a, b, rtol, scale_atol, msg):
 class SCNN(nn.Module):
     """simple_cnn_variational.py:13-89 on the drop-in layers (dropout left out: its mask is torch's RNG)."""
 
-    def __init__(self):
+    def __init__(self, smooth=False):
         super().__init__()
+        self.act = F.softplus if smooth else F.relu
+        self.pool = F.avg_pool2d if smooth else F.max_pool2d
         kw = dict(prior_mean=0.0, prior_variance=1.0, posterior_mu_init=0.0, posterior_rho_init=-3.0)
         self.conv1 = L.Conv2dReparameterization(1, 32, 3, stride=1, prior_type="normal", **kw)
         self.conv2 = L.Conv2dReparameterization(32, 64, 3, stride=1, prior_type="normal", **kw)
@@ -118,17 +129,36 @@ class SCNN(nn.Module):
     def forward(self, x):
         kl_sum = 0
         x, kl = self.conv1(x); kl_sum = kl_sum + kl
-        x, kl = self.conv2(F.relu(x)); kl_sum = kl_sum + kl
-        x = torch.flatten(F.max_pool2d(F.relu(x), 2), 1)
+        x, kl = self.conv2(self.act(x)); kl_sum = kl_sum + kl
+        x = torch.flatten(self.pool(self.act(x), 2), 1)
         x, kl = self.fc1(x); kl_sum = kl_sum + kl
-        x, kl = self.fc2(F.relu(x)); kl_sum = kl_sum + kl
+        x, kl = self.fc2(self.act(x)); kl_sum = kl_sum + kl
         return F.log_softmax(x, dim=1), kl_sum
 
 
-def test_config0_scnn_forward_kl_backward(cuda_device):
+def compare_grads(model, twin, smooth, rtol, scale_atol):
+    names = {"mu_kernel": "mu_w", "rho_kernel": "rho_w", "mu_weight": "mu_w", "rho_weight": "rho_w", "mu_bias": "mu_b", "rho_bias": "rho_b"}
+    tw = dict(twin.named_parameters())
+    checked = 0
+    for n, p in model.named_parameters():
+        lay, leaf = n.rsplit(".", 1)
+        if leaf not in names:
+            continue
+        want = tw[f"{lay}.{names[leaf]}"].grad
+        if smooth:
+            close(p.grad, want, rtol, scale_atol, f"grad {n}")
+        else:   # a few re-routed ReLU / max-pool elements (module docstring): relative L2 error
+            err = float((p.grad.detach().cpu().double() - want.double()).norm() / want.double().norm().clamp_min(1e-30))
+            assert err <= 2e-2, f"grad {n}: relative L2 error {err}"
+        checked += 1
+    return checked
+
+
+@pytest.mark.parametrize("smooth", [False, True])
+def test_config0_scnn_forward_kl_backward(cuda_device, smooth):
     torch.manual_seed(0)
     bt.manual_seed(77)
-    model = SCNN().to(cuda_device)
+    model = SCNN(smooth).to(cuda_device)
     pin_layer_ids(model, 1)
     twin = oracle_twin(model, cuda_device)
     x = torch.randn(128, 1, 28, 28)
@@ -144,11 +174,7 @@ def test_config0_scnn_forward_kl_backward(cuda_device):
     close(out, wout, 1e-5, 1e-5, "log-probabilities")
     close(kl, wkl, 1e-5, 1e-6, "kl")
     close(loss, wloss, 1e-5, 1e-6, "loss")
-    names = {"mu_kernel": "mu_w", "rho_kernel": "rho_w", "mu_weight": "mu_w", "rho_weight": "rho_w", "mu_bias": "mu_b", "rho_bias": "rho_b"}
-    tw = dict(twin.named_parameters())
-    for n, p in model.named_parameters():
-        lay, leaf = n.rsplit(".", 1)
-        close(p.grad, tw[f"{lay}.{names[leaf]}"].grad, 1e-4, 2e-5, f"grad {n}")
+    assert compare_grads(model, twin, smooth, 1e-4, 2e-5) == 8
 
 
 # ---------------------------------------------------------------------------------- configs[1]
@@ -243,11 +269,25 @@ def test_config1_resnet20_mc_inference(cuda_device):
 
 
 # ---------------------------------------------------------------------------------- configs[2]
-def test_config2_resnet18_flipout_training_step(cuda_device):
+def smoothen(model):
+    """ReLU -> Softplus, MaxPool2d -> AvgPool2d in place (same layers, shapes and kernels; smooth gradients)."""
+    for m in list(model.modules()):
+        for name, child in list(m._modules.items()):
+            if isinstance(child, nn.ReLU):
+                setattr(m, name, nn.Softplus())
+            elif isinstance(child, nn.MaxPool2d):
+                setattr(m, name, nn.AvgPool2d(child.kernel_size, child.stride, child.padding))
+    return model
+
+
+@pytest.mark.parametrize("smooth", [False, True])
+def test_config2_resnet18_flipout_training_step(cuda_device, smooth):
     import torchvision
     torch.manual_seed(2)
     bt.manual_seed(79)
     model = torchvision.models.resnet18(num_classes=20)
+    if smooth:
+        smoothen(model)
     bt.dnn_to_bnn(model, {"prior_mu": 0.0, "prior_sigma": 1.0, "posterior_mu_init": 0.0, "posterior_rho_init": -3.0,
                           "type": "Flipout", "moped_enable": True, "moped_delta": 0.5})
     model = model.to(cuda_device).eval()    # eval: BatchNorm uses running statistics on both sides (batch 6 is too small for batch stats parity)
@@ -268,12 +308,4 @@ def test_config2_resnet18_flipout_training_step(cuda_device):
     wloss.backward()
     close(out, wout, 1e-4, 1e-4, "logits")
     close(kl, wkl, 1e-5, 1e-6, "get_kl_loss")
-    names = {"mu_kernel": "mu_w", "rho_kernel": "rho_w", "mu_weight": "mu_w", "rho_weight": "rho_w", "mu_bias": "mu_b", "rho_bias": "rho_b"}
-    tw = dict(twin.named_parameters())
-    checked = 0
-    for n, p in model.named_parameters():
-        lay, leaf = n.rsplit(".", 1)
-        if leaf in names:
-            close(p.grad, tw[f"{lay}.{names[leaf]}"].grad, 2e-3, 2e-4, f"grad {n}")   # 21 layers of fp32 re-association
-            checked += 1
-    assert checked == 2 * 21 + 2
+    assert compare_grads(model, twin, smooth, 2e-3, 2e-4) == 2 * 21 + 2   # (element-wise: 21 layers of fp32 re-association)

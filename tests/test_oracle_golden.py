@@ -1,5 +1,7 @@
 """Pin the CPU oracle (oracle/bt_oracle.py) against fixtures produced by the
 reference itself (oracle/make_golden.py): outputs, KL and autograd gradients."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -159,3 +161,15 @@ def test_mc_moments_and_uncertainty():
     ent = -(p.mean(0) * torch.log(p.mean(0) + 1e-15)).sum(-1)
     torch.testing.assert_close(oracle.predictive_entropy(p), ent)
     assert (oracle.mutual_information(p) > -1e-9).all()
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="needs the reference checkout (build container only)")
+def test_fixtures_regenerate_from_the_committed_recipe():
+    """`python oracle/make_golden.py --check`: running the reference again reproduces every committed fixture
+    (each case seeds its own layer construction and input, so fixtures do not depend on the case order)."""
+    import importlib.util
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bt_make_golden", os.path.join(root, "oracle", "make_golden.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    assert mod.check() == []
