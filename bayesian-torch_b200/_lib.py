@@ -15,6 +15,8 @@ BT_F32, BT_BF16 = 0, 1
 PATH_AUTO, PATH_SIMT_F32, PATH_TC_BF16 = 0, 1, 2
 KIND_EPS_W, KIND_EPS_B, KIND_SIGN_IN, KIND_SIGN_OUT = 0, 1, 2, 3
 FLAG_PACKED_VALID = 1
+FLAG_TRANSPOSE_BIAS = 2
+FLAG_BIAS_GRAD_X_SIDE = 4
 ABI_VERSION = 5
 
 _i64x3 = C.c_int64 * 3

@@ -90,8 +90,12 @@ static int forward_common(const bt_geom* g, const bt_layer_params* p, const void
   int rc = check_common(g, p, x, out, who);
   if (rc != BT_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  if (kl_out) {
-    BT_REQUIRE(workspace, BT_ERR_INVALID, "%s: kl_out needs a workspace (bt_workspace_bytes)", who);
+  BT_REQUIRE(!kl_out || workspace, BT_ERR_INVALID, "%s: kl_out needs a workspace (bt_workspace_bytes)", who);
+  // the tensor-core forward evaluates the KL term inside its parameter-packing pass (mu / rho read once); the
+  // fp32 kernels read the parameters tile by tile, many times: there the KL is its own HBM-bound launch
+  const char* why0 = "";
+  const bool on_tc = workspace && (path == BT_PATH_TC_BF16 || path == BT_PATH_AUTO) && bt_tc_supported(g, p, flipout, &why0);
+  if (kl_out && !on_tc) {
     rc = bt_kl_layer(p, weight_numel(g), p->mu_b ? g->c_out : 0, kl_out, workspace, st);
     if (rc != BT_OK) return rc;
   }
@@ -103,10 +107,10 @@ static int forward_common(const bt_geom* g, const bt_layer_params* p, const void
   if (path == BT_PATH_TC_BF16) {
     BT_REQUIRE(bt_tc_supported(g, p, flipout, &why), BT_ERR_UNSUPPORTED, "%s: tensor-core path unavailable: %s", who,
                why);
-    return bt_tc_forward(g, p, x, out, tc_ws, tc_ws_bytes, flipout, st);
+    return bt_tc_forward(g, p, x, out, tc_ws, tc_ws_bytes, flipout, kl_out, workspace, st);
   }
   if (path == BT_PATH_AUTO && bt_tc_supported(g, p, flipout, &why) && tc_ws)
-    return bt_tc_forward(g, p, x, out, tc_ws, tc_ws_bytes, flipout, st);
+    return bt_tc_forward(g, p, x, out, tc_ws, tc_ws_bytes, flipout, kl_out, workspace, st);
   BT_REQUIRE(path == BT_PATH_AUTO || path == BT_PATH_SIMT_F32, BT_ERR_INVALID, "%s: unknown path %d", who, path);
   return bt_simt_forward(g, p, x, out, flipout, st);
 }

@@ -196,8 +196,10 @@ int bt_simt_backward(const bt_geom* g, const bt_layer_params* p, const void* x, 
                      cudaStream_t stream);
 bool bt_tc_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why);
 
+// kl_out non-null: forward(return_kl=True) -- the KL term is evaluated by the parameter-packing pass (kl_scratch: >= 32
+// bytes of the caller's workspace)
 int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace, int64_t ws_bytes,
-                  bool flipout, cudaStream_t stream);
+                  bool flipout, float* kl_out, void* kl_scratch, cudaStream_t stream);
 int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout);
 // backward data on the tensor-core kernel (grad_out convolved with the transposed, regenerated weights)
 bool bt_tc_dgrad_supported(const bt_geom* g, const bt_layer_params* p, bool flipout, const char** why);

@@ -13,6 +13,7 @@
 // ONE fp64 atomicAdd per chunk into the tensor's accumulator; the last block to finish
 // turns the fp64 sums into the fp32 means kl_div returns and their total.
 #include "bt_common.cuh"
+#include "bt_kl.cuh"
 
 #define KL_MAX_TENSORS 192
 #define KL_THREADS 256
@@ -34,54 +35,6 @@ struct KlTable {
   int32_t laplace;  // the fork's 'laplace' prior: KL(N(mu, sigma) || Laplace(0, 1)), analytic (base_variational_layer.py:74-97)
   float prior_mu, prior_sigma;
 };
-
-struct KlElem {
-  float kl, dmu, drho;
-};
-
-// Per-prior constants of the KL term: log(sigma_p) and 1 / sigma_p^2.  With the reference's
-// constant-filled priors they are loop invariants (computed once per thread, not per element).
-struct KlPrior {
-  float log_ps, inv2;
-};
-__device__ __forceinline__ KlPrior kl_prior(float ps) {
-  KlPrior p;
-  p.log_ps = logf(ps);
-  p.inv2 = __frcp_rn(ps * ps);
-  return p;
-}
-
-// The pass is HBM-bound only if an element costs ~20 issue slots: softplus and the two logs use
-// the MUFU approximations (ex2 / lg2, relative error ~2^-22) with a series for small exp(rho),
-// where log(1 + t) computed as such would lose the low bits of t.  Checked against the fp64
-// oracle at rtol 1e-5 on the mean (tests/test_parity_gpu.py).
-template <bool kGrad>
-__device__ __forceinline__ KlElem kl_elem(float mu, float rho, float pm, const KlPrior pr, bool q_is_sigma) {
-  // sigma = log1p(exp(rho)) (linear_variational.py:163); sigmoid(rho) = t/(1+t) with t = exp(rho)
-  float sig, dsig_drho;
-  if (q_is_sigma) {
-    sig = rho;
-    dsig_drho = 1.f;
-  } else {
-    const float t = __expf(fminf(rho, 30.f));
-    const float series = t * (1.f - t * (0.5f - t * (0.33333334f - 0.25f * t)));  // log1p(t), t < 2^-5: error < t^5/5
-    const float big = __logf(1.f + t);
-    sig = rho > 20.f ? rho : (t < 0.03125f ? series : big);
-    dsig_drho = kGrad ? (rho > 20.f ? 1.f : __fdividef(t, 1.f + t)) : 0.f;
-  }
-  const float d = mu - pm;
-  KlElem e;
-  // log(sigma_p) - log(sigma_q) + (sigma_q^2 + (mu_q-mu_p)^2) / (2 sigma_p^2) - 0.5
-  e.kl = (pr.log_ps - __logf(sig)) + 0.5f * (sig * sig + d * d) * pr.inv2 - 0.5f;
-  if (kGrad) {
-    e.dmu = d * pr.inv2;
-    e.drho = (sig * pr.inv2 - __frcp_rn(sig)) * dsig_drho;
-  } else {
-    e.dmu = 0.f;
-    e.drho = 0.f;
-  }
-  return e;
-}
 
 // KL(N(mu, sigma) || Laplace(mu_p = 0, b = 1)) as the fork's kl_div('laplace') writes it
 // (base_variational_layer.py:74-97; location and scale are hard-coded there):

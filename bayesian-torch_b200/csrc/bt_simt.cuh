@@ -21,6 +21,7 @@ struct SParams {
   const float *out_scale, *out_shift;  // folded BatchNorm epilogue (forward only)
   int out_relu;
   const void* residual;  // out-shaped, out dtype (forward only)
+  int dgrad_bias;        // backward-data run as the FORWARD of a ConvTranspose layer: add the sampled bias to grad_x
   uint64_t seed;
   uint32_t sample_id, layer_id;
 };
@@ -76,6 +77,7 @@ static inline SParams bt_sparams_from(const bt_layer_params* p) {
   s.mu_w = p->mu_w; s.rho_w = p->rho_w; s.mu_b = p->mu_b; s.rho_b = p->rho_b;
   s.eps_w = p->eps_w; s.eps_b = p->eps_b; s.sign_in = p->sign_in; s.sign_out = p->sign_out;
   s.out_scale = p->out_scale; s.out_shift = p->out_shift; s.out_relu = p->out_relu; s.residual = p->residual;
+  s.dgrad_bias = (p->flags & BT_FLAG_TRANSPOSE_BIAS) && p->mu_b ? 1 : 0;
   s.seed = p->seed; s.sample_id = p->sample_id; s.layer_id = p->layer_id;
   return s;
 }

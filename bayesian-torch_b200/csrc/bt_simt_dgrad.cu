@@ -148,6 +148,22 @@ __global__ void __launch_bounds__(NT) simt_dgrad_kernel(const SGeo g, const SPar
     __syncthreads();
   }
 
+  // ConvTranspose forward (this kernel's grad_x IS that layer's output): the layer's sampled bias per output
+  // channel, mu_b + softplus(rho_b) eps_b (conv_variational.py:941-989); Flipout keeps the perturbation apart,
+  // it is multiplied by the output sign below (conv_flipout.py:757-831)
+  float b_mean[4] = {0.f, 0.f, 0.f, 0.f}, b_pert[4] = {0.f, 0.f, 0.f, 0.f};
+  if (p.dgrad_bias) {
+    const BtRngKey key_b = bt_rng_key(p.seed, p.sample_id, p.layer_id, BT_KIND_EPS_B);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int c = c0 + ty * 4 + j;
+      if (c >= g.Cg) continue;
+      const int64_t cg = (int64_t)grp * g.Cg + c;
+      const float e = p.eps_b ? p.eps_b[cg] : bt_normal1((uint64_t)cg, key_b);
+      b_mean[j] = p.mu_b[cg];
+      b_pert[j] = bt_softplus(p.rho_b[cg]) * e;
+    }
+  }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int64_t m = m0 + (i < 4 ? tx * 4 + i : 64 + tx * 4 + (i - 4));
@@ -173,7 +189,9 @@ __global__ void __launch_bounds__(NT) simt_dgrad_kernel(const SGeo g, const SPar
           const uint64_t li = bt_sign_index((uint64_t)b, Cin, cg, g.ID, id, g.IH, ih, g.IW, iw);
           sg = bt_sign1(li, key_si);
         }
-        v += acc[NA - 1][i][j] * sg;
+        v += (acc[NA - 1][i][j] + b_pert[j]) * sg + b_mean[j];
+      } else {
+        v += b_mean[j] + b_pert[j];
       }
       gx[off] = bt_from_float<TX>(v);
     }

@@ -185,29 +185,35 @@ __global__ void param_grad_finalize_kernel(float* __restrict__ gmu, float* __res
   }
 }
 
-// One CTA per output channel: s1 = sum grad_out, s2 = sum grad_out*s_out (Flipout), then the
-// bias (mu_b, rho_b) gradients including the KL term.
-template <typename TO, bool kFlip>
+// One CTA per channel: s1 = sum grad_out, s2 = sum grad_out*s_out (Flipout), then the
+// bias (mu_b, rho_b) gradients including the KL term.  XSIDE: the reduced tensor is the one passed as `x`
+// (the backward of a ConvTranspose layer, whose output gradient sits on the x side of the equivalent convolution;
+// its output signs are that convolution's SIGN_IN stream).
+template <typename TO, bool kFlip, bool XSIDE>
 __global__ void __launch_bounds__(256) bias_grad_kernel(const SGeo g, const SParams p, const TO* __restrict__ gout,
                                                         float* __restrict__ gmu_b, float* __restrict__ grho_b,
                                                         KlGradArgs kl) {
   __shared__ float red[2][8];
   const int n = blockIdx.x;
-  const int64_t Cout = (int64_t)g.Ng * g.groups;
-  const BtRngKey key_so = bt_rng_key(p.seed, p.sample_id, p.layer_id, BT_KIND_SIGN_OUT);
+  const int64_t Cout = XSIDE ? (int64_t)g.Cg * g.groups : (int64_t)g.Ng * g.groups;
+  const BtRngKey key_so = bt_rng_key(p.seed, p.sample_id, p.layer_id, XSIDE ? BT_KIND_SIGN_IN : BT_KIND_SIGN_OUT);
+  const float* __restrict__ sign_t = XSIDE ? p.sign_in : p.sign_out;
+  const int D = XSIDE ? g.ID : g.OD, H = XSIDE ? g.IH : g.OH, W = XSIDE ? g.IW : g.OW;
+  const int64_t bs = XSIDE ? g.xbs : g.obs, cs = XSIDE ? g.xcs : g.ocs, s0 = XSIDE ? g.xs0 : g.os0, s1s = XSIDE ? g.xs1 : g.os1,
+                s2s = XSIDE ? g.xs2 : g.os2;
+  const int64_t M = g.batch * D * H * W;
   float s1 = 0.f, s2 = 0.f;
-  for (int64_t m = threadIdx.x; m < g.M; m += blockDim.x) {
+  for (int64_t m = threadIdx.x; m < M; m += blockDim.x) {
     int64_t t = m;
-    const int ow = (int)(t % g.OW); t /= g.OW;
-    const int oh = (int)(t % g.OH); t /= g.OH;
-    const int od = (int)(t % g.OD); t /= g.OD;
+    const int ow = (int)(t % W); t /= W;
+    const int oh = (int)(t % H); t /= H;
+    const int od = (int)(t % D); t /= D;
     const int64_t b = t;
-    const int64_t off = b * g.obs + (int64_t)n * g.ocs + (int64_t)od * g.os0 + (int64_t)oh * g.os1 + (int64_t)ow * g.os2;
+    const int64_t off = b * bs + (int64_t)n * cs + (int64_t)od * s0 + (int64_t)oh * s1s + (int64_t)ow * s2s;
     const float v = bt_to_float<TO>(gout[off]);
     s1 += v;
     if (kFlip) {
-      const float sg = p.sign_out ? p.sign_out[off]
-                                  : bt_sign1(bt_sign_index((uint64_t)b, Cout, n, g.OD, od, g.OH, oh, g.OW, ow), key_so);
+      const float sg = sign_t ? sign_t[off] : bt_sign1(bt_sign_index((uint64_t)b, Cout, n, D, od, H, oh, W, ow), key_so);
       s2 += v * sg;
     }
   }
@@ -284,11 +290,19 @@ int backward_typed(const SGeo& g, const SParams& p, const bt_layer_params* lp, c
   }
   if (p.mu_b && (gr->grad_mu_b || gr->grad_rho_b)) {
     KlGradArgs kl = {grad_kl, lp->prior_mu_b_t, lp->prior_sigma_b_t, lp->prior_mu, lp->prior_sigma};
-    const int cout = g.Ng * g.groups;
-    if (flip)
-      bias_grad_kernel<TO, true><<<cout, 256, 0, stream>>>(g, p, (const TO*)gout, gr->grad_mu_b, gr->grad_rho_b, kl);
-    else
-      bias_grad_kernel<TO, false><<<cout, 256, 0, stream>>>(g, p, (const TO*)gout, gr->grad_mu_b, gr->grad_rho_b, kl);
+    if (lp->flags & BT_FLAG_BIAS_GRAD_X_SIDE) {   // backward of a ConvTranspose layer: its output gradient is `x` here
+      const int cin = g.Cg * g.groups;
+      if (flip)
+        bias_grad_kernel<TX, true, true><<<cin, 256, 0, stream>>>(g, p, (const TX*)x, gr->grad_mu_b, gr->grad_rho_b, kl);
+      else
+        bias_grad_kernel<TX, false, true><<<cin, 256, 0, stream>>>(g, p, (const TX*)x, gr->grad_mu_b, gr->grad_rho_b, kl);
+    } else {
+      const int cout = g.Ng * g.groups;
+      if (flip)
+        bias_grad_kernel<TO, true, false><<<cout, 256, 0, stream>>>(g, p, (const TO*)gout, gr->grad_mu_b, gr->grad_rho_b, kl);
+      else
+        bias_grad_kernel<TO, false, false><<<cout, 256, 0, stream>>>(g, p, (const TO*)gout, gr->grad_mu_b, gr->grad_rho_b, kl);
+    }
     BT_LAUNCH_OK("bias_grad_kernel");
   }
   return BT_OK;

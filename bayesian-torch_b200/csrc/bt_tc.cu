@@ -32,6 +32,7 @@
 #include <type_traits>
 
 #include "bt_common.cuh"
+#include "bt_kl.cuh"
 #include "bt_tc.cuh"
 
 using namespace btc;
@@ -181,11 +182,31 @@ __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
 // ---------------------------------------------------------------- parameter packing ----
 // mu[n][c][tap] -> mu_p[n][tap*Cin + c] with row pitch Kp (zero beyond K), sigma_p = softplus(rho)
 // likewise (sigma does not depend on the sample: hoisted out of the per-sample work), eps likewise.
-__global__ void tc2_pack_kernel(const float* __restrict__ mu, const float* __restrict__ rho,
+// With KL = true the same pass also evaluates the layer's KL term, kl(weight) + kl(bias) as forward(return_kl=True)
+// returns it (linear_variational.py:183-198): mu and rho are read ONCE for sampling and KL (8 B per weight; the
+// separate KL launch read them a second time).  Per-thread fp32 partial sums are flushed into fp64 every 16
+// elements, blocks add one fp64 atomic each, the last block to finish writes the two means' sum.
+struct PackKl {
+  double* acc;                   // [2]: sum over the weight, sum over the bias (zeroed by the caller)
+  unsigned int* counter;         // blocks done (zeroed by the caller)
+  float* kl_out;
+  const float *pmu_t, *psig_t;   // tensor-valued weight priors in the parameter's own layout, or null
+  const float *mu_b, *rho_b, *pmu_b_t, *psig_b_t;
+  float prior_mu, prior_sigma;
+  int64_t w_numel;
+  int b_numel;
+};
+
+template <bool KL>
+__global__ void __launch_bounds__(256) tc2_pack_kernel(const float* __restrict__ mu, const float* __restrict__ rho,
                                 const float* __restrict__ eps, __nv_bfloat16* __restrict__ mu_p, __nv_bfloat16* __restrict__ sig_p,
                                 float* __restrict__ eps_p, const float* __restrict__ scale, int64_t total, int Cin, int T,
-                                int Kp) {
+                                int Kp, const PackKl kf) {
   const int K = Cin * T;
+  const KlPrior prior_c = kl_prior(KL ? kf.prior_sigma : 1.f);
+  float part = 0.f;
+  double dsum = 0.0;
+  int since = 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t n = i / Kp;
     const int k = (int)(i - n * Kp);
@@ -194,8 +215,14 @@ __global__ void tc2_pack_kernel(const float* __restrict__ mu, const float* __res
       const int tap = k / Cin, c = k - tap * Cin;
       const int64_t src = n * K + (int64_t)c * T + tap;
       m = mu[src];
-      sg = bt_softplus(rho[src]);
+      const float r = rho[src];
+      sg = bt_softplus(r);
       if (eps_p) e = eps[src];
+      if constexpr (KL) {
+        const float pm = kf.pmu_t ? kf.pmu_t[src] : kf.prior_mu;
+        part += kl_elem<false>(m, r, pm, kf.psig_t ? kl_prior(kf.psig_t[src]) : prior_c, false).kl;
+        if (++since == 16) { dsum += (double)part; part = 0.f; since = 0; }
+      }
       if (scale) {  // folded BatchNorm scale of output channel n rides on the sampled weight row
         const float sc = scale[n];
         m *= sc;
@@ -205,6 +232,37 @@ __global__ void tc2_pack_kernel(const float* __restrict__ mu, const float* __res
     mu_p[i] = __float2bfloat16_rn(m);
     sig_p[i] = __float2bfloat16_rn(sg);
     if (eps_p) eps_p[i] = e;
+  }
+  if constexpr (KL) {
+    __shared__ double red[2][8];
+    __shared__ bool is_last;
+    dsum += (double)part;
+    double bsum = 0.0;
+    if (blockIdx.x == 0 && kf.mu_b) {   // the bias term: a few hundred elements, one block
+      for (int i = threadIdx.x; i < kf.b_numel; i += blockDim.x) {
+        const float pm = kf.pmu_b_t ? kf.pmu_b_t[i] : kf.prior_mu;
+        bsum += (double)kl_elem<false>(kf.mu_b[i], kf.rho_b[i], pm, kf.psig_b_t ? kl_prior(kf.psig_b_t[i]) : prior_c, false).kl;
+      }
+    }
+    dsum = bt_warp_sum(dsum);
+    bsum = bt_warp_sum(bsum);
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = dsum; red[1][threadIdx.x >> 5] = bsum; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double a = 0.0, b = 0.0;
+      for (int w = 0; w < 8; ++w) { a += red[0][w]; b += red[1][w]; }
+      atomicAdd(&kf.acc[0], a);
+      if (blockIdx.x == 0) atomicAdd(&kf.acc[1], b);
+      __threadfence();
+      is_last = atomicAdd(kf.counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (is_last && threadIdx.x == 0) {
+      __threadfence();
+      double kl = __ldcg(&kf.acc[0]) / (double)kf.w_numel;
+      if (kf.mu_b && kf.b_numel > 0) kl += __ldcg(&kf.acc[1]) / (double)kf.b_numel;
+      *kf.kl_out = (float)kl;
+    }
   }
 }
 
@@ -1481,6 +1539,8 @@ struct RunOpt {
   int a_dil_h = 1, a_dil_w = 1, SH = 0, SW = 0;
   int64_t s_bs = 0, s_hs = 0, s_ws = 0;  // strides of the un-inserted grad_out (tensor-fed signs)
   int64_t ws_bytes = 0;      // bytes the caller says `workspace` holds (0: not stated, unchecked)
+  float* kl_out = nullptr;   // forward(return_kl=True): kl(weight) + kl(bias) <- evaluated by the packing pass
+  void* kl_scratch = nullptr;  // >= 32 bytes of the caller's workspace for the fp64 accumulators
 };
 
 static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace,
@@ -1524,6 +1584,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   __nv_bfloat16* sig_p = mu_p + wn;
   float* eps_p = (p->eps_w || opt.dgrad) ? (float*)(sig_p + wn) : nullptr;
   __nv_bfloat16* patches = (__nv_bfloat16*)((char*)workspace + ((3 * wn * 4 + 255) / 256) * 256);
+  bool kl_done = false;
   if (opt.ws_bytes > 0) {  // the carve-up below must fit what the caller allocated (bt_workspace_bytes)
     int64_t need = ((3 * wn * 4 + 255) / 256) * 256;
     if (pl.mode == A_PATCH) {
@@ -1543,11 +1604,34 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
       BT_LAUNCH_OK("tc2_pack_dgrad_kernel");
     } else if ((p->flags & BT_FLAG_PACKED_VALID) && !p->eps_w) {
       // frozen inference model: the workspace still holds this layer's packed parameters
+    } else if (opt.kl_out) {
+      BT_REQUIRE(opt.kl_scratch, BT_ERR_INVALID, "tensor-core forward: kl_out needs the workspace's KL scratch");
+      PackKl kf;
+      memset(&kf, 0, sizeof(kf));
+      kf.acc = (double*)opt.kl_scratch;
+      kf.counter = (unsigned int*)(kf.acc + 2);
+      kf.kl_out = opt.kl_out;
+      kf.pmu_t = p->prior_mu_w_t; kf.psig_t = p->prior_sigma_w_t;
+      kf.mu_b = p->mu_b; kf.rho_b = p->rho_b; kf.pmu_b_t = p->prior_mu_b_t; kf.psig_b_t = p->prior_sigma_b_t;
+      kf.prior_mu = p->prior_mu; kf.prior_sigma = p->prior_sigma;
+      kf.w_numel = (int64_t)a.N * pl.K;
+      kf.b_numel = p->mu_b ? a.N : 0;
+      BT_CUDA_OK(cudaMemsetAsync(opt.kl_scratch, 0, 32, stream));
+      tc2_pack_kernel<true><<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, p->out_scale, wn, (int)g->c_in,
+                                                             pl.T, a.K, kf);
+      BT_LAUNCH_OK("tc2_pack_kernel(kl)");
+      kl_done = true;
     } else {
-      tc2_pack_kernel<<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, p->out_scale, wn, (int)g->c_in, pl.T,
-                                                       a.K);
+      PackKl kf;
+      memset(&kf, 0, sizeof(kf));
+      tc2_pack_kernel<false><<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, p->out_scale, wn, (int)g->c_in,
+                                                              pl.T, a.K, kf);
       BT_LAUNCH_OK("tc2_pack_kernel");
     }
+  }
+  if (opt.kl_out && !kl_done) {   // packing skipped (frozen layer) or a backward-data run: the stand-alone KL launch
+    const int rc = bt_kl_layer(p, (int64_t)a.N * pl.K, p->mu_b ? a.N : 0, opt.kl_out, opt.kl_scratch, stream);
+    if (rc != BT_OK) return rc;
   }
   a.mu_p = mu_p; a.sig_p = sig_p; a.eps_p = eps_p;
   a.has_shift = (p->mu_b || p->out_shift) ? 1 : 0;
@@ -1716,6 +1800,11 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   {
     int left = ring_bytes(a.stage_bufs, a.res_bufs) - a.RW * WB - a.NA * A_SLOT_T;
     if (a.res_bufs == 2) {
+      // Two residual sub-tiles in flight (32 KB per SM) cap the residual stream at ~32 KB per HBM round trip
+      // (~2 000 cycles): about half of an SM's share of the HBM bandwidth, and the wide expansions read as many
+      // residual bytes as they write outputs (512<-128 at 28x28 ran at 58 % of the HBM bound with two, the
+      // 256<-64 layers at 87 % with four).  A streaming layer gives up one of its four W slots for the space.
+      if (left < 2 * STAGE_UNIT && !a.stationary && a.RW >= 3 && env_int("BT_TC2_RES4", 1) != 0) { a.RW -= 1; left += WB; }
       if (left >= 2 * STAGE_UNIT) { a.res_bufs = 4; left -= 2 * STAGE_UNIT; }
       else if (a.stationary && a.NA >= 6) { a.res_bufs = 4; a.NA -= 2; left += 2 * A_SLOT_T - 2 * STAGE_UNIT; }
     }
@@ -1751,9 +1840,11 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
 }
 
 int bt_tc_forward(const bt_geom* g, const bt_layer_params* p, const void* x, void* out, void* workspace, int64_t ws_bytes,
-                  bool flipout, cudaStream_t stream) {
+                  bool flipout, float* kl_out, void* kl_scratch, cudaStream_t stream) {
   RunOpt opt;
   opt.ws_bytes = ws_bytes;
+  opt.kl_out = kl_out;
+  opt.kl_scratch = kl_scratch;
   return tc2_run(g, p, x, out, workspace, flipout, opt, stream);
 }
 
@@ -1802,7 +1893,8 @@ static bool dgrad_geom(const bt_geom* g, bt_geom* t, bool* inserted, const char*
 
 static bt_layer_params dgrad_params(const bt_layer_params* p) {
   bt_layer_params q = *p;
-  q.mu_b = q.rho_b = q.eps_b = nullptr;
+  // (a ConvTranspose forward keeps its bias: the rank-1 shift MMA adds it per output channel of this run)
+  if (!(p->flags & BT_FLAG_TRANSPOSE_BIAS)) q.mu_b = q.rho_b = q.eps_b = nullptr;
   q.out_scale = q.out_shift = nullptr; q.out_relu = 0; q.residual = nullptr;
   q.sign_in = p->sign_out;   // the A operand (grad_out) is flipped by s_out, the result by s_in
   q.sign_out = p->sign_in;

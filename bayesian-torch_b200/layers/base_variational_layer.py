@@ -306,8 +306,8 @@ class _BayesLayer(BaseVariationalLayer_):
         conv_flipout.py:757-831): out = conv_transpose(x, mu + sigma * eps) + (mu_b + sigma_b * eps_b), Flipout
         likewise with the two paths.  The contraction is the DATA GRADIENT of the convolution whose weight has
         this layer's [c_in, c_out / groups, *k] shape, so it runs on the backward-data kernel of that
-        convolution (ops.bayes_transpose_layer); the sampled bias is added by torch ops (autograd
-        differentiates it); KL is the shared multi-tensor kernel."""
+        convolution, which also adds the sampled bias in its epilogue (ops.bayes_transpose_layer); KL is the shared
+        multi-tensor kernel."""
         r = self._rank
         if x.dim() != r + 2:
             raise RuntimeError(f"{type(self).__name__} expects a {r + 2}-d input, got {tuple(x.shape)}")
@@ -328,7 +328,6 @@ class _BayesLayer(BaseVariationalLayer_):
             call.sample_id = self._calls & 0xFFFFFFFF
             self._calls += 1
         eps_w = getattr(self, "eps_" + self._wname)
-        eps_b = None
         ops._require_cuda(x)
         out_sp = [(x.shape[2 + i] - 1) * call.stride[i] - 2 * call.padding[i] + call.dilation[i] * (mu_w.shape[2 + i] - 1)
                   + call.output_padding[i] + 1 for i in range(r)]
@@ -340,35 +339,22 @@ class _BayesLayer(BaseVariationalLayer_):
                 s_out = torch.empty(oshape, dtype=torch.float32, device=x.device).uniform_(-1, 1).sign()
             call.eps_w = eps_w.normal_()
             if self.mu_bias is not None:
-                eps_b = self.eps_bias.normal_()
+                call.eps_b = self.eps_bias.normal_()
         elif mode == "buffer":
             call.eps_w = eps_w
-            eps_b = self.eps_bias
+            call.eps_b = self.eps_bias
             if self._flipout:
                 if self.sign_input is None or self.sign_output is None:
                     raise RuntimeError("sample mode 'buffer' on a Flipout layer needs layer.sign_input / layer.sign_output")
                 s_in, s_out = self.sign_input, self.sign_output
-        else:
-            # in-kernel Philox: weights and signs are generated by the kernels; the bias draw and (Flipout) the
-            # output signs the bias perturbation needs are the exported streams of the same keys.  The equivalent
-            # convolution reads THIS layer's output as its input, so our sign_output is its SIGN_IN stream.
-            if self.mu_bias is not None:
-                eps_b = ops.philox_normal(self.mu_bias.numel(), call.seed, call.sample_id, self._layer_id, _lib.KIND_EPS_B, x.device)
-                if self._flipout:
-                    s_out = ops.philox_sign_shape(oshape, x.device, call.seed, call.sample_id, self._layer_id, _lib.KIND_SIGN_IN)
+        # (in-kernel Philox: weights, bias draw and signs are all generated by the kernels; the equivalent convolution
+        # reads THIS layer's output as its input, so our output signs are its SIGN_IN stream)
         if self._flipout and mode != "philox":
             call.sign_in, call.sign_out = s_out, s_in   # (equivalent convolution's view, see above)
         if torch.is_grad_enabled() and mode != "philox":   # this call's draw, not the buffer a later call overwrites
             call.eps_w = call.eps_w.clone()
-            eps_b = None if eps_b is None else eps_b.clone()
-        out = ops.bayes_transpose_layer(call, x, mu_w, rho_w, oshape)
-        if self.mu_bias is not None:
-            bshape = (1, -1) + (1,) * r
-            db = torch.nn.functional.softplus(self.rho_bias) * eps_b.detach()
-            if self._flipout:
-                out = out + (self.mu_bias.view(bshape) + db.view(bshape) * s_out.reshape(oshape)).to(out.dtype)
-            else:
-                out = out + (self.mu_bias + db).view(bshape).to(out.dtype)
+            call.eps_b = None if call.eps_b is None else call.eps_b.clone()
+        out = ops.bayes_transpose_layer(call, x, mu_w, rho_w, self.mu_bias, self.rho_bias, oshape)
         if return_kl:
             return out, self.kl_loss()
         return out

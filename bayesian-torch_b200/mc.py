@@ -268,7 +268,7 @@ class MCPredictor:
 
 
 class GradientBuckets:
-    """Data-parallel gradient exchange of the training path: fixed, pre-allocated flat fp32 buckets
+    """Data-parallel gradient exchange of the training path: fixed, pre-allocated flat buckets
     filled from inside backward; a bucket's NCCL all-reduce (average) is issued the moment its last gradient has
     been produced, so it overlaps the dgrad / wgrad kernels of the layers still to come.  Replaces the
     DistributedDataParallel wrapper of the reference's training drivers (utils/utils.py:482-495) around the loop
@@ -293,7 +293,9 @@ class GradientBuckets:
         self.buckets = []        # dicts: flat, params [(p, off, n)], pending, work
         cur, cur_n = [], 0
         for p in reversed(params):
-            if cur and (cur_n + p.numel() > limit or p.device != cur[0].device):
+            # a bucket is one flat buffer of ONE dtype on one device: fp32 for the variational parameters (the
+            # kernels' masters), the model's own dtype for what .bfloat16() converted (BatchNorm affine terms)
+            if cur and (cur_n + p.numel() > limit or p.device != cur[0].device or p.dtype != cur[0].dtype):
                 self._close(cur, cur_n); cur, cur_n = [], 0
             cur.append(p); cur_n += p.numel()
         if cur:
@@ -307,7 +309,7 @@ class GradientBuckets:
         self.collectives = 0
 
     def _close(self, ps, n):
-        flat = torch.zeros(n, dtype=torch.float32, device=ps[0].device)
+        flat = torch.zeros(n, dtype=ps[0].dtype, device=ps[0].device)
         offs, off = [], 0
         for p in ps:
             offs.append((p, off, p.numel())); off += p.numel()

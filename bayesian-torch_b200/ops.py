@@ -569,8 +569,13 @@ class _BayesLayerFn(torch.autograd.Function):
         S = call.n_samples
         if S != 1:
             raise RuntimeError("backward through mc_batched() is not supported; loop over mc_sample(s) for training")
-        # grad_out must share dtype with x and have a dense layout
-        go = _dense(g_out.detach().to(x.dtype))
+        # grad_out must share dtype with x and have a dense layout; a gradient that arrives in another memory format
+        # than the forward output had (autograd materialises unused outputs as contiguous zeros; some torch ops drop
+        # channels-last) is re-laid out like the output, so the tensor-core backward still applies
+        go = g_out.detach().to(x.dtype)
+        if tuple(go.shape) == ctx.out_meta[0] and tuple(go.stride()) != ctx.out_meta[1]:
+            go = torch.empty_strided(ctx.out_meta[0], ctx.out_meta[1], dtype=x.dtype, device=dev).copy_(go)
+        go = _dense(go)
         geom = _build_geom(call, xd, mu_wc.shape, go)
         p, keep = _build_params(call, mu_wc, rho_wc, mu_bc, rho_bc)
         grads = LayerGrads()
@@ -599,20 +604,25 @@ class _BayesLayerFn(torch.autograd.Function):
 
 
 class _BayesTransposeFn(torch.autograd.Function):
-    """conv_transpose(x, W) with W = mu + softplus(rho) * eps sampled in the kernels (Flipout: the mean path plus
-    the sign-flipped perturbation path), bias excluded.  With E the convolution whose weight has W's shape
-    [c_in, c_out / groups, *k] (E maps this layer's OUTPUT space to its INPUT space):
-        forward      = E's backward-data  on grad_out := x            (bt_conv_*_bwd, grad_x only)
+    """conv_transpose(x, W) + b with W = mu + softplus(rho) * eps and b = mu_b + softplus(rho_b) * eps_b sampled in
+    the kernels (Flipout: the mean path plus the sign-flipped perturbation path, bias perturbation inside the sign
+    product).  With E the convolution whose weight has W's shape [c_in, c_out / groups, *k] (E maps this layer's
+    OUTPUT space to its INPUT space):
+        forward      = E's backward-data  on grad_out := x, the sampled bias added in its epilogue
+                       (bt_conv_*_bwd, grad_x only, BT_FLAG_TRANSPOSE_BIAS)
         grad_x       = E's forward        on x_E := grad_out           (bt_conv_*_fwd, no bias)
-        grad_mu/rho  = E's backward-weights with x_E := grad_out, grad_out_E := x
+        grad_mu/rho  = E's backward-weights with x_E := grad_out, grad_out_E := x; the bias gradients reduce x_E
+                       (BT_FLAG_BIAS_GRAD_X_SIDE)
     all three regenerate the same eps (and signs) from the (seed, sample, layer) key or read the same buffers."""
 
     @staticmethod
-    def forward(ctx, call: LayerCall, x, mu_w, rho_w, oshape):
-        dev = _require_cuda(x, mu_w, rho_w)
+    def forward(ctx, call: LayerCall, x, mu_w, rho_w, mu_b, rho_b, oshape):
+        dev = _require_cuda(x, mu_w, rho_w, mu_b, rho_b)
         if x.dtype not in _DT:
             raise RuntimeError(f"activations must be float32 or bfloat16, got {x.dtype}")
         mu_wc, rho_wc = _f32c(mu_w.detach(), "mu"), _f32c(rho_w.detach(), "rho")
+        mu_bc = None if mu_b is None else _f32c(mu_b.detach(), "mu_bias")
+        rho_bc = None if rho_b is None else _f32c(rho_b.detach(), "rho_bias")
         xd = _dense(x.detach())
         if xd.shape[1] != mu_wc.shape[0]:
             raise RuntimeError(f"input has {xd.shape[1]} channels, layer expects {mu_wc.shape[0]}")
@@ -627,7 +637,8 @@ class _BayesTransposeFn(torch.autograd.Function):
         if call.sign_out is not None:
             call.sign_out = _match_strides(call.sign_out, xd)
         geom = _build_geom(call, out, mu_wc.shape, xd)
-        p, keep = _build_params(call, mu_wc, rho_wc, None, None)
+        p, keep = _build_params(call, mu_wc, rho_wc, mu_bc, rho_bc)
+        p.flags |= _lib.FLAG_TRANSPOSE_BIAS
         grads = LayerGrads()
         grads.grad_x = _ptr(out)
         op = b"flipout_bwd" if call.flipout else b"reparam_bwd"
@@ -638,22 +649,24 @@ class _BayesTransposeFn(torch.autograd.Function):
                                     call.path, _stream())
         _lib.check(rc, "conv_transpose forward")
         ctx.call = call
-        ctx.save_for_backward(x, mu_w, rho_w)
+        ctx.save_for_backward(x, mu_w, rho_w, mu_b, rho_b)
         return out
 
     @staticmethod
     def backward(ctx, g_out):
         call: LayerCall = ctx.call
-        x, mu_w, rho_w = ctx.saved_tensors
+        x, mu_w, rho_w, mu_b, rho_b = ctx.saved_tensors
         dev = x.device
         mu_wc, rho_wc = _f32c(mu_w.detach(), "mu"), _f32c(rho_w.detach(), "rho")
+        mu_bc = None if mu_b is None else _f32c(mu_b.detach(), "mu_bias")
+        rho_bc = None if rho_b is None else _f32c(rho_b.detach(), "rho_bias")
         xd = _dense(x.detach())
         go = _dense(g_out.detach().to(x.dtype))
-        p, keep = _build_params(call, mu_wc, rho_wc, None, None)
         L = _lib.lib()
-        gx = gmu = grho = None
+        gx = gmu = grho = gmb = grb = None
         with torch.cuda.device(dev):
             if ctx.needs_input_grad[1]:
+                p, keep = _build_params(call, mu_wc, rho_wc, None, None)
                 gx = torch.empty_like(xd)
                 geom = _build_geom(call, go, mu_wc.shape, gx)
                 op = b"flipout_fwd" if call.flipout else b"reparam_fwd"
@@ -661,11 +674,19 @@ class _BayesTransposeFn(torch.autograd.Function):
                 p.workspace_bytes = ws.numel()
                 rc = _entry(call, False)(C.byref(geom), C.byref(p), _ptr(go), _ptr(gx), None, _ptr(ws), call.path, _stream())
                 _lib.check(rc, "conv_transpose backward (data)")
-            if ctx.needs_input_grad[2] or ctx.needs_input_grad[3]:
-                gmu, grho = torch.empty_like(mu_wc), torch.empty_like(rho_wc)
+            need_w = ctx.needs_input_grad[2] or ctx.needs_input_grad[3]
+            need_b = mu_b is not None and (ctx.needs_input_grad[4] or ctx.needs_input_grad[5])
+            if need_w or need_b:
+                p, keep = _build_params(call, mu_wc, rho_wc, mu_bc, rho_bc)
+                p.flags |= _lib.FLAG_BIAS_GRAD_X_SIDE
                 geom = _build_geom(call, go, mu_wc.shape, xd)
                 grads = LayerGrads()
-                grads.grad_mu_w, grads.grad_rho_w = _ptr(gmu), _ptr(grho)
+                if need_w:
+                    gmu, grho = torch.empty_like(mu_wc), torch.empty_like(rho_wc)
+                    grads.grad_mu_w, grads.grad_rho_w = _ptr(gmu), _ptr(grho)
+                if need_b:
+                    gmb, grb = torch.empty_like(mu_bc), torch.empty_like(rho_bc)
+                    grads.grad_mu_b, grads.grad_rho_b = _ptr(gmb), _ptr(grb)
                 op = b"flipout_bwd" if call.flipout else b"reparam_bwd"
                 ws = torch.empty(max(int(L.bt_workspace_bytes(op, C.byref(geom), 2)), 256), dtype=torch.uint8, device=dev)
                 p.workspace_bytes = ws.numel()
@@ -674,12 +695,12 @@ class _BayesTransposeFn(torch.autograd.Function):
                 _lib.check(rc, "conv_transpose backward (weights)")
         if gx is not None and gx.shape != x.shape:
             gx = gx.view_as(x)
-        return None, gx, gmu, grho, None
+        return None, gx, gmu, grho, gmb, grb, None
 
 
-def bayes_transpose_layer(call: LayerCall, x, mu_w, rho_w, oshape):
-    """conv_transpose(x, sampled W) of a ConvTranspose{1,2,3}d Bayesian layer, bias excluded."""
-    return _BayesTransposeFn.apply(call, x, mu_w, rho_w, tuple(int(v) for v in oshape))
+def bayes_transpose_layer(call: LayerCall, x, mu_w, rho_w, mu_b, rho_b, oshape):
+    """conv_transpose(x, sampled W) + sampled bias of a ConvTranspose{1,2,3}d Bayesian layer, all in the kernels."""
+    return _BayesTransposeFn.apply(call, x, mu_w, rho_w, mu_b, rho_b, tuple(int(v) for v in oshape))
 
 
 def bayes_layer(call: LayerCall, x, mu_w, rho_w, mu_b, rho_b):

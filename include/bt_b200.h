@@ -26,6 +26,13 @@ extern "C" {
 
 #define BT_ABI_VERSION 5
 #define BT_FLAG_PACKED_VALID 1
+/* bt_conv_*_bwd run as the FORWARD of a ConvTranspose layer (grad_x only, see the table in INTEGRATION.md): the layer's
+ * sampled bias -- mu_b + softplus(rho_b) eps_b per output channel; Flipout: mu_b + softplus(rho_b) eps_b s_out -- is
+ * added to grad_x in the kernel epilogue (conv_variational.py:941-989, conv_flipout.py:757-831). */
+#define BT_FLAG_TRANSPOSE_BIAS 2
+/* bt_conv_*_bwd run as the BACKWARD of such a layer: grad_mu_b / grad_rho_b reduce the tensor passed as `x` (the
+ * gradient of the layer's output) instead of `grad_out`. */
+#define BT_FLAG_BIAS_GRAD_X_SIDE 4
 
 typedef void* bt_stream_t; /* cudaStream_t */
 

@@ -174,7 +174,7 @@ def test_config0_scnn_forward_kl_backward(cuda_device, smooth):
     close(out, wout, 1e-5, 1e-5, "log-probabilities")
     close(kl, wkl, 1e-5, 1e-6, "kl")
     close(loss, wloss, 1e-5, 1e-6, "loss")
-    assert compare_grads(model, twin, smooth, 1e-4, 2e-5) == 8
+    assert compare_grads(model, twin, smooth, 1e-4, 2e-5) == 16
 
 
 # ---------------------------------------------------------------------------------- configs[1]

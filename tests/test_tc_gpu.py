@@ -304,3 +304,36 @@ def test_cluster_pair_matches_single_cta(cin, cout, k, pad, batch, hw, S, cuda_d
         torch.cuda.synchronize()
     assert float(outs["1"].float().abs().max()) > 0
     torch.testing.assert_close(outs["2"], outs["1"], rtol=0, atol=0)
+
+
+def test_tc_forward_kl_is_fused_into_the_packing_pass(cuda_device):
+    """forward(return_kl=True) on the tensor-core path: the KL term comes out of the parameter-packing launch (mu / rho
+    read once for sampling and KL), with scalar and with tensor-valued priors, bias included; rtol 1e-5 vs the oracle,
+    and no separate KL kernel is launched."""
+    torch.manual_seed(21)
+    layer = L.Conv2dReparameterization(64, 136, 3, padding=1, bias=True, prior_mean=0.1, prior_variance=0.7, prior_type="normal").to(cuda_device)
+    layer.eps_kernel.normal_(); layer.eps_bias.normal_()
+    x = torch.randn(2, 64, 9, 9, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    n0 = ops.PROFILE.launches
+    out, kl = run_tc(layer, x)
+    assert ops.PROFILE.launches - n0 == 2          # the packing pass (with the KL) and the GEMM, nothing else
+    sig = lambda r: torch.log1p(torch.exp(r))
+    mu, rho, mb, rb = (t.detach().cpu() for t in (layer.mu_kernel, layer.rho_kernel, layer.mu_bias, layer.rho_bias))
+    want = oracle.kl_normal(mu, sig(rho), torch.full_like(mu, 0.1), torch.full_like(mu, 0.7)) + \
+        oracle.kl_normal(mb, sig(rb), torch.full_like(mb, 0.1), torch.full_like(mb, 0.7))
+    torch.testing.assert_close(kl.cpu(), want, rtol=1e-5, atol=1e-6)
+    # tensor-valued priors (utils/util.py:101-104 MOPED): weight prior tensors, bias mean tensor
+    pm, ps = torch.randn_like(mu) * 0.1, torch.rand_like(mu) + 0.5
+    pbm = torch.randn_like(mb) * 0.1
+    layer.prior_weight_mu, layer.prior_weight_sigma = pm.to(cuda_device), ps.to(cuda_device)
+    layer.prior_bias_mu.data = pbm.to(cuda_device)
+    out2, kl2 = run_tc(layer, x)
+    want2 = oracle.kl_normal(mu, sig(rho), pm, ps) + oracle.kl_normal(mb, sig(rb), pbm, torch.full_like(mb, 0.7))
+    torch.testing.assert_close(kl2.cpu(), want2, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(out2, out, rtol=0, atol=0)
+    # gradients of the fused KL flow through the same autograd node as before
+    (kl2 * 3.0).backward()
+    m = mu.double().requires_grad_(True); r = rho.double().requires_grad_(True)
+    (3.0 * oracle.kl_normal(m, torch.log1p(torch.exp(r)), pm.double(), ps.double())).backward()
+    torch.testing.assert_close(layer.mu_kernel.grad.cpu().double(), m.grad, rtol=1e-4, atol=1e-8)
+    torch.testing.assert_close(layer.rho_kernel.grad.cpu().double(), r.grad, rtol=1e-4, atol=1e-8)

@@ -48,7 +48,7 @@ layers = [m for _, m in sorted(names.items())]
 rows = collections.OrderedDict()
 for (path, flops, nbytes, a, b), (lid, (name, m)) in zip(ops.PROFILE.records, sorted(names.items())):
     w = m._w()[0]
-    key = (tuple(w.shape), m.stride if hasattr(m, "stride") else 1, flops)
+    key = (tuple(w.shape), m.stride if hasattr(m, "stride") else 1, flops, nbytes)   # (nbytes: with / without a residual input)
     r = rows.setdefault(key, {"name": name, "n": 0, "ms": 0.0, "flops": flops, "bytes": nbytes, "path": path})
     r["n"] += 1
     r["ms"] += a.elapsed_time(b)
