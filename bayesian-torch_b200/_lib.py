@@ -46,6 +46,19 @@ class LayerParams(C.Structure):
         ("residual", C.c_void_p), ("workspace_bytes", C.c_int64)]
 
 
+class LstmLayer(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("mu_w", "rho_w", "mu_b", "rho_b", "eps_w", "eps_b", "sign_in", "sign_out")] + [
+        ("seed", C.c_uint64), ("sample_id", C.c_uint32), ("layer_id", C.c_uint32)]
+
+
+class LstmStep(C.Structure):
+    _fields_ = [("batch", C.c_int64), ("in_features", C.c_int32), ("hidden", C.c_int32), ("flipout", C.c_int32),
+                ("reserved", C.c_int32), ("ih", LstmLayer), ("hh", LstmLayer),
+                ("x", C.c_void_p), ("x_row_stride", C.c_int64), ("h_prev", C.c_void_p), ("h_row_stride", C.c_int64),
+                ("c_prev", C.c_void_p), ("c_row_stride", C.c_int64), ("h_out", C.c_void_p), ("h_out_row_stride", C.c_int64),
+                ("c_out", C.c_void_p), ("c_out_row_stride", C.c_int64), ("gates_out", C.c_void_p)]
+
+
 class LayerGrads(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("grad_x", "grad_mu_w", "grad_rho_w", "grad_mu_b", "grad_rho_b")]
 
@@ -77,6 +90,9 @@ SIGNATURES = {
     "bt_conv_reparam_bwd": (C.c_int, _BWD),
     "bt_linear_flipout_bwd": (C.c_int, _BWD),
     "bt_conv2d_flipout_bwd": (C.c_int, _BWD),
+    "bt_lstm_step_fwd": (C.c_int, [C.POINTER(LstmStep), C.c_void_p]),
+    "bt_lstm_step_bwd_gates": (C.c_int, [C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                         C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "bt_mc_accumulate": (C.c_int, [C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_int,
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "bt_mc_finalize": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64,

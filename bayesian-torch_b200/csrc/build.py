@@ -10,7 +10,7 @@ import sys
 from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SOURCES = ["bt_api.cu", "bt_kl.cu", "bt_misc.cu", "bt_simt_fwd.cu", "bt_simt_dgrad.cu", "bt_simt_wgrad.cu", "bt_tc.cu"]
+SOURCES = ["bt_api.cu", "bt_kl.cu", "bt_misc.cu", "bt_lstm.cu", "bt_simt_fwd.cu", "bt_simt_dgrad.cu", "bt_simt_wgrad.cu", "bt_tc.cu"]
 HEADERS = ["bt_common.cuh", "bt_kl.cuh", "bt_simt.cuh", "bt_tc.cuh", os.path.join("..", "..", "include", "bt_b200.h")]
 LIB = os.path.join(HERE, "libbt_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

@@ -265,6 +265,21 @@ class _BayesLayer(BaseVariationalLayer_):
             if getattr(self, "_pack_cache", None) is None:
                 self._pack_cache = {}
             call.pack_cache = self._pack_cache
+        self._set_noise(call, x, mode)
+        out, kl = ops.bayes_layer(call, x, mu_w, rho_w, self.mu_bias, self.rho_bias)
+        if lead is not None:
+            out = out.reshape(-1, *lead[1:], out.shape[-1])   # leading axis may be folded S*B
+        if return_kl:
+            return out, (self.kl_loss() if laplace else kl)
+        return out
+
+    def _set_noise(self, call, x, mode):
+        """Fill the call's noise source for THIS call of the layer: Philox keys (sample id from the enclosing
+        mc_sample / mc_batched block or the layer's own call counter) or, in the tensor-fed modes, the eps / sign
+        tensors -- drawn with torch's generator in the reference's order ('torch') or taken from the buffers
+        ('buffer').  x: the (flattened) input of the call."""
+        mu_w, _ = self._w()
+        r = self._rank
         if ops._STATE.sample_override is not None:
             call.sample_id = ops._STATE.sample_override
             call.seed = ops.call_seed(call.seed, self._layer_id)   # repeated calls inside the block: fresh streams
@@ -294,12 +309,6 @@ class _BayesLayer(BaseVariationalLayer_):
             # buffer itself and reads the last draw there (oracle.lstm_unrolled, alias_eps)
             call.eps_w = None if call.eps_w is None else call.eps_w.clone()
             call.eps_b = None if call.eps_b is None else call.eps_b.clone()
-        out, kl = ops.bayes_layer(call, x, mu_w, rho_w, self.mu_bias, self.rho_bias)
-        if lead is not None:
-            out = out.reshape(-1, *lead[1:], out.shape[-1])   # leading axis may be folded S*B
-        if return_kl:
-            return out, (self.kl_loss() if laplace else kl)
-        return out
 
     def _forward_transpose(self, x, return_kl):
         """ConvTranspose{1,2,3}d{Reparameterization,Flipout}.forward (conv_variational.py:941-989,

@@ -708,6 +708,118 @@ def bayes_layer(call: LayerCall, x, mu_w, rho_w, mu_b, rho_b):
     return _BayesLayerFn.apply(call, x, mu_w, rho_w, mu_b, rho_b)
 
 
+# --------------------------------------------------------------------------- fused LSTM step
+
+
+def _fill_lstm_layer(dst, call: LayerCall, mu_w, rho_w, mu_b, rho_b, keep):
+    dst.mu_w, dst.rho_w, dst.mu_b, dst.rho_b = _ptr(mu_w), _ptr(rho_w), _ptr(mu_b), _ptr(rho_b)
+    eps_w, eps_b = _f32c(call.eps_w, "eps_w"), _f32c(call.eps_b, "eps_b")
+    s_in = None if call.sign_in is None else call.sign_in.detach().to(torch.float32).contiguous()
+    s_out = None if call.sign_out is None else call.sign_out.detach().to(torch.float32).contiguous()
+    keep += [eps_w, eps_b, s_in, s_out]
+    dst.eps_w, dst.eps_b, dst.sign_in, dst.sign_out = _ptr(eps_w), _ptr(eps_b), _ptr(s_in), _ptr(s_out)
+    dst.seed, dst.sample_id, dst.layer_id = call.seed, call.sample_id, call.layer_id
+
+
+def _rows(t: torch.Tensor) -> torch.Tensor:
+    """2-d fp32 view with unit column stride (rows may be strided: a time slice of [batch, seq, features])."""
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"the fused LSTM step computes in float32, got {t.dtype}")
+    return t if t.stride(1) == 1 else t.contiguous()
+
+
+class _LSTMStepFn(torch.autograd.Function):
+    """One time step of LSTMReparameterization / LSTMFlipout in ONE kernel (bt_lstm_step_fwd): both sampled
+    contractions, the gate non-linearities and the cell update.  Backward: bt_lstm_step_bwd_gates (element-wise)
+    and the two linear layers' own backward kernels on the pre-activation gate gradient, which regenerate the
+    step's weights from the calls' keys (or read the calls' eps / sign tensors)."""
+
+    @staticmethod
+    def forward(ctx, calls, x, h_prev, c_prev, ih_mu_w, ih_rho_w, ih_mu_b, ih_rho_b, hh_mu_w, hh_rho_w, hh_mu_b, hh_rho_b):
+        ih_call, hh_call = calls
+        dev = _require_cuda(x, h_prev, c_prev, ih_mu_w, ih_rho_w, hh_mu_w, hh_rho_w)
+        xd, hd, cd = _rows(x.detach()), _rows(h_prev.detach()), _rows(c_prev.detach())
+        B, H = hd.shape
+        params = [None if t is None else _f32c(t.detach(), "parameter") for t in
+                  (ih_mu_w, ih_rho_w, ih_mu_b, ih_rho_b, hh_mu_w, hh_rho_w, hh_mu_b, hh_rho_b)]
+        if params[0].shape != (4 * H, xd.shape[1]) or params[4].shape != (4 * H, H):
+            raise RuntimeError(f"LSTM step: weights {tuple(params[0].shape)} / {tuple(params[4].shape)} do not match x "
+                               f"{tuple(xd.shape)} and hidden {H}")
+        h_t = torch.empty(B, H, dtype=torch.float32, device=dev)
+        c_t = torch.empty(B, H, dtype=torch.float32, device=dev)
+        need_grad = any(ctx.needs_input_grad)   # (grad mode is off inside forward; this is what autograd will ask for)
+        gates = torch.empty(B, 4 * H, dtype=torch.float32, device=dev) if need_grad else None
+        st = _lib.LstmStep()
+        keep = []
+        st.batch, st.in_features, st.hidden, st.flipout = B, xd.shape[1], H, int(ih_call.flipout)
+        _fill_lstm_layer(st.ih, ih_call, *params[:4], keep)
+        _fill_lstm_layer(st.hh, hh_call, *params[4:], keep)
+        st.x, st.x_row_stride = _ptr(xd), xd.stride(0)
+        st.h_prev, st.h_row_stride = _ptr(hd), hd.stride(0)
+        st.c_prev, st.c_row_stride = _ptr(cd), cd.stride(0)
+        st.h_out, st.h_out_row_stride, st.c_out, st.c_out_row_stride = _ptr(h_t), H, _ptr(c_t), H
+        st.gates_out = _ptr(gates)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().bt_lstm_step_fwd(C.byref(st), _stream()), "bt_lstm_step_fwd")
+        ctx.calls = calls
+        ctx.gates = gates
+        ctx.save_for_backward(x, h_prev, c_prev, c_t, ih_mu_w, ih_rho_w, ih_mu_b, ih_rho_b, hh_mu_w, hh_rho_w, hh_mu_b, hh_rho_b)
+        return h_t, c_t
+
+    @staticmethod
+    def backward(ctx, g_h, g_c):
+        x, h_prev, c_prev, c_t, *ps = ctx.saved_tensors
+        dev = x.device
+        B, H = c_t.shape
+        gh = None if g_h is None else _rows(g_h.detach().to(torch.float32))
+        gc = None if g_c is None else _rows(g_c.detach().to(torch.float32))
+        cd = _rows(c_prev.detach())
+        g_pre = torch.empty(B, 4 * H, dtype=torch.float32, device=dev)
+        g_cprev = torch.empty(B, H, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = _lib.lib().bt_lstm_step_bwd_gates(B, H, _ptr(ctx.gates), _ptr(cd), cd.stride(0), _ptr(c_t), c_t.stride(0),
+                                                   _ptr(gh), 0 if gh is None else gh.stride(0), _ptr(gc), 0 if gc is None else gc.stride(0),
+                                                   _ptr(g_pre), _ptr(g_cprev), _stream())
+        _lib.check(rc, "bt_lstm_step_bwd_gates")
+        outs = []
+        for li, (call, inp) in enumerate(zip(ctx.calls, (x, h_prev))):
+            mu_w, rho_w, mu_b, rho_b = ps[4 * li:4 * li + 4]
+            mu_wc, rho_wc = _f32c(mu_w.detach(), "mu"), _f32c(rho_w.detach(), "rho")
+            mu_bc = None if mu_b is None else _f32c(mu_b.detach(), "mu_bias")
+            rho_bc = None if rho_b is None else _f32c(rho_b.detach(), "rho_bias")
+            xd = inp.detach().contiguous()   # (grad_x is written with x's strides: a dense copy of the time slice)
+            call = LayerCall(rank=0, flipout=call.flipout, eps_w=call.eps_w, eps_b=call.eps_b, sign_in=call.sign_in, sign_out=call.sign_out,
+                             seed=call.seed, sample_id=call.sample_id, layer_id=call.layer_id, want_kl=False, path=_lib.PATH_SIMT_F32)
+            if call.sign_in is not None:
+                call.sign_in = _match_strides(call.sign_in, xd)
+                call.sign_out = _match_strides(call.sign_out, g_pre)
+            geom = _build_geom(call, xd, mu_wc.shape, g_pre)
+            p, keep = _build_params(call, mu_wc, rho_wc, mu_bc, rho_bc)
+            grads = LayerGrads()
+            base = 1 if li == 0 else 2                       # needs_input_grad index of x / h_prev
+            gx = torch.empty_like(xd) if ctx.needs_input_grad[base] else None
+            gmu, grho = torch.empty_like(mu_wc), torch.empty_like(rho_wc)
+            gmb = None if mu_bc is None else torch.empty_like(mu_bc)
+            grb = None if rho_bc is None else torch.empty_like(rho_bc)
+            grads.grad_x, grads.grad_mu_w, grads.grad_rho_w = _ptr(gx), _ptr(gmu), _ptr(grho)
+            grads.grad_mu_b, grads.grad_rho_b = _ptr(gmb), _ptr(grb)
+            op = b"flipout_bwd" if call.flipout else b"reparam_bwd"
+            ws = torch.empty(max(int(_lib.lib().bt_workspace_bytes(op, C.byref(geom), 2)), 256), dtype=torch.uint8, device=dev)
+            p.workspace_bytes = ws.numel()
+            with torch.cuda.device(dev):
+                rc = _entry(call, True)(C.byref(geom), C.byref(p), _ptr(xd), _ptr(g_pre), None, C.byref(grads), _ptr(ws),
+                                        _lib.PATH_SIMT_F32, _stream())
+            _lib.check(rc, "LSTM step backward")
+            outs.append((gx, gmu, grho, gmb, grb))
+        (gx, *ih_g), (ghp, *hh_g) = outs
+        return (None, gx, ghp, g_cprev, *ih_g, *hh_g)
+
+
+def lstm_step(ih_call: LayerCall, hh_call: LayerCall, x, h_prev, c_prev, ih_params, hh_params):
+    """(h_t, c_t) of one fused LSTM time step; *_params = (mu_w, rho_w, mu_b, rho_b) of the ih / hh sub-layers."""
+    return _LSTMStepFn.apply((ih_call, hh_call), x, h_prev, c_prev, *ih_params, *hh_params)
+
+
 # --------------------------------------------------------------------------- misc exports
 
 

@@ -220,6 +220,56 @@ int bt_conv2d_flipout_bwd(const bt_geom* g, const bt_layer_params* p, const void
                           const float* grad_kl, const bt_layer_grads* grads, void* workspace, int path,
                           bt_stream_t stream);
 
+/* ---- Fused LSTM time step: replaces one iteration of the unrolled cell of LSTMReparameterization.forward
+ *      (variational_layers/rnn_variational.py:112-153) / LSTMFlipout.forward (flipout_layers/rnn_flipout.py:102-155):
+ *      gates = ih(x_t) + hh(h_prev) with both layers' weights (and Flipout signs) freshly sampled in the kernel,
+ *      i, f, o = sigmoid, g = tanh, c_t = f c_prev + i g, h_t = o tanh(c_t) -- ONE launch instead of two linear
+ *      layers and ~12 element-wise launches.  fp32 tensors; rows may be strided (x_t is a slice of [batch, seq, in],
+ *      h_out / c_out are slots of [batch, seq, hidden]).  Per layer the noise source follows bt_layer_params:
+ *      eps / sign pointers non-NULL -> the caller's draws, NULL -> Philox keyed (seed, sample_id, layer_id). */
+typedef struct bt_lstm_layer {
+  const float* mu_w;  /* [4 * hidden, K] */
+  const float* rho_w;
+  const float* mu_b;  /* [4 * hidden] or NULL */
+  const float* rho_b;
+  const float* eps_w;
+  const float* eps_b;
+  const float* sign_in;  /* Flipout: [batch, K] contiguous */
+  const float* sign_out; /* Flipout: [batch, 4 * hidden] contiguous */
+  uint64_t seed;
+  uint32_t sample_id;
+  uint32_t layer_id;
+} bt_lstm_layer;
+
+typedef struct bt_lstm_step {
+  int64_t batch;
+  int32_t in_features;
+  int32_t hidden;
+  int32_t flipout;
+  int32_t reserved;
+  bt_lstm_layer ih, hh;
+  const float* x;       /* x_t [batch, in_features] */
+  int64_t x_row_stride; /* elements */
+  const float* h_prev;  /* [batch, hidden] */
+  int64_t h_row_stride;
+  const float* c_prev;  /* [batch, hidden]; NULL = zeros */
+  int64_t c_row_stride;
+  float* h_out;
+  int64_t h_out_row_stride;
+  float* c_out;
+  int64_t c_out_row_stride;
+  float* gates_out; /* NULL, or [batch, 4 * hidden] contiguous <- the activations i, f, g, o (saved for backward) */
+} bt_lstm_step;
+
+int bt_lstm_step_fwd(const bt_lstm_step* step, bt_stream_t stream);
+/* Element-wise half of the step's backward: grad_pre [batch, 4 * hidden] (gradient w.r.t. the pre-activation gates)
+ * and grad_c_prev [batch, hidden] from grad_h / grad_c (either may be NULL = zero), the saved activations and c_t.
+ * The two contractions of the backward are bt_linear_*_bwd calls with grad_out := grad_pre (same keys). */
+int bt_lstm_step_bwd_gates(int64_t batch, int hidden, const float* gates, const float* c_prev, int64_t c_prev_row_stride,
+                           const float* c_t, int64_t c_t_row_stride, const float* grad_h, int64_t grad_h_row_stride,
+                           const float* grad_c, int64_t grad_c_row_stride, float* grad_pre, float* grad_c_prev,
+                           bt_stream_t stream);
+
 /* ---- Monte-Carlo reduction: replaces torch.stack(output_mc) -> softmax -> mean(dim=0)
  *      (examples/main_bayesian_cifar_dnn2bnn.py:545,554-556) and the numpy
  *      predictive_entropy / mutual_information (utils/util.py:41-60).

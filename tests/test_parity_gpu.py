@@ -285,3 +285,38 @@ def test_lstm_matches_reference_fixture(name, cuda_device):
     step.update(ih=0, hh=0)
     assert len(lstm(d["x"].to(cuda_device))) == 2      # (hidden_seq, (hidden_seq, c_ts)) without kl
     assert float(bt.get_kl_loss(lstm)) == pytest.approx(2 * float(d["kl"]) / d["x"].shape[1], rel=1e-5)  # parent + children (reference double count)
+
+
+@pytest.mark.parametrize("flip", [False, True])
+def test_lstm_fused_step_equals_composed_step(flip, cuda_device):
+    """The one-kernel time step (bt_lstm_step_fwd + its backward) against the same step run as two Bayesian linear
+    launches and torch gate arithmetic, in-kernel Philox draws, ragged sizes, given initial state: outputs and every
+    gradient at rtol 1e-5 / 1e-4."""
+    torch.manual_seed(3)
+    bt.manual_seed(41)
+    lstm = (L.LSTMFlipout if flip else L.LSTMReparameterization)(19, 23).to(cuda_device)
+    for sub in (lstm.ih, lstm.hh):
+        sub.path = "simt"
+    x = torch.randn(70, 3, 19, device=cuda_device)
+    h0, c0 = torch.randn(70, 23, device=cuda_device), torch.randn(70, 23, device=cuda_device)
+    g1, g2 = torch.randn(70, 3, 23, device=cuda_device), torch.randn(70, 3, 23, device=cuda_device)
+    res = []
+    for fused in (True, False):
+        lstm.fused_step = fused
+        for p in lstm.parameters():
+            p.grad = None
+        xi, hi, ci = (t.clone().requires_grad_(True) for t in (x, h0, c0))
+        n0 = ops.PROFILE.launches
+        with bt.mc_sample(5):
+            hs, (_, cs), kl = lstm(xi, (hi, ci))
+        fwd_launches = ops.PROFILE.launches - n0
+        ((hs * g1).sum() + (cs * g2).sum() + 0.3 * kl).backward()
+        res.append((hs, cs, kl, xi.grad, hi.grad, ci.grad, [p.grad.clone() for p in lstm.parameters()], fwd_launches))
+    a, b = res
+    assert a[7] == 3 + 2 and b[7] == 2 * 3 + 2          # one kernel per step (+ the two KL launches) against two per step
+    for i in range(3):
+        close(a[i], b[i], rtol=RTOL, scale_atol=1e-6, msg=f"lstm fused vs composed output {i}")
+    for i in range(3, 6):
+        close(a[i], b[i], rtol=1e-4, scale_atol=1e-5, msg=f"lstm fused vs composed input grad {i}")
+    for ga, gb in zip(a[6], b[6]):
+        close(ga, gb, rtol=1e-4, scale_atol=1e-5, msg="lstm fused vs composed parameter grad")
