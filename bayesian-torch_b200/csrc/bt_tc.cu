@@ -67,7 +67,7 @@ constexpr int SMEM_LIMIT = 232448;
 constexpr int AVAIL_BYTES = SMEM_LIMIT - 1024 - CTRL_BYTES;  // staging + residual ring + A ring + W ring / panel
 
 struct Tc2Args {
-  const __nv_bfloat16 *mu_p, *sig_p;  // packed [N][K], k = tap*Cin + c, scale folded in, rounded to bf16
+  const void *mu_p, *sig_p;           // packed [N][K], k = tap*Cin + c, scale folded in; bf16, or fp32 for the tf32 instantiation
   const float* eps_p;                 // caller's eps in the same order (deterministic mode), else null
   const float *mu_b, *rho_b, *eps_b;
   const float *out_scale, *out_shift;  // folded BatchNorm (nullable)
@@ -94,6 +94,7 @@ struct Tc2Args {
   int has_shift;     // bias and/or folded BatchNorm shift: added by a rank-1 MMA that initialises each accumulator
   int res_bufs;      // residual tiles in flight per epilogue warp (0: no residual input)
   int stage_bufs;    // epilogue staging buffers per warp (2, or 1 when shared memory is tight)
+  int tf32;          // fp32 activations: fp32 A tiles, tf32 MMAs (k-blocks of 32 elements), fp32 packed parameters
   int debug;         // BT_TC2_DEBUG bits, honoured by the BT_TC2_PROF=1 instantiation only: 1 skip output stores, 4 skip MMAs,
                      // 8 skip A loads, 16 skip the normal draws, 32 skip the parameter loads
   uint64_t seed;
@@ -197,9 +198,16 @@ struct PackKl {
   int b_numel;
 };
 
-template <bool KL>
+template <typename TP>
+__device__ __forceinline__ TP pack_cast(float v);
+template <>
+__device__ __forceinline__ __nv_bfloat16 pack_cast<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <>
+__device__ __forceinline__ float pack_cast<float>(float v) { return v; }
+
+template <bool KL, typename TP>
 __global__ void __launch_bounds__(256) tc2_pack_kernel(const float* __restrict__ mu, const float* __restrict__ rho,
-                                const float* __restrict__ eps, __nv_bfloat16* __restrict__ mu_p, __nv_bfloat16* __restrict__ sig_p,
+                                const float* __restrict__ eps, TP* __restrict__ mu_p, TP* __restrict__ sig_p,
                                 float* __restrict__ eps_p, const float* __restrict__ scale, int64_t total, int Cin, int T,
                                 int Kp, const PackKl kf) {
   const int K = Cin * T;
@@ -229,8 +237,8 @@ __global__ void __launch_bounds__(256) tc2_pack_kernel(const float* __restrict__
         sg *= sc;
       }
     }
-    mu_p[i] = __float2bfloat16_rn(m);
-    sig_p[i] = __float2bfloat16_rn(sg);
+    mu_p[i] = pack_cast<TP>(m);
+    sig_p[i] = pack_cast<TP>(sg);
     if (eps_p) eps_p[i] = e;
   }
   if constexpr (KL) {
@@ -323,7 +331,7 @@ struct PatchGeo {
 // consecutive chunks and read neighbouring input elements.  Index arithmetic is 32-bit whenever
 // the chunk count allows (64-bit division is ~10x the cost and was most of this kernel's time).
 template <typename TX, typename IDX>
-__global__ void __launch_bounds__(256) tc2_patch_kernel(const TX* __restrict__ x, __nv_bfloat16* __restrict__ A, const PatchGeo g) {
+__global__ void __launch_bounds__(256) tc2_patch_kernel(const TX* __restrict__ x, TX* __restrict__ A, const PatchGeo g) {
   const IDX C8 = (IDX)(g.Kp >> 3);
   const IDX total = (IDX)g.rows * C8;
   const IDX stride = (IDX)gridDim.x * blockDim.x;
@@ -353,9 +361,15 @@ __global__ void __launch_bounds__(256) tc2_patch_kernel(const TX* __restrict__ x
       }
       if (++c == g.Cin) { c = 0; if (++kw == g.KW) { kw = 0; if (++kh == g.KH) { kh = 0; ++kd; } } }
     }
-    uint4 pk;
-    pk.x = pack_bf16(v[0], v[1]); pk.y = pack_bf16(v[2], v[3]); pk.z = pack_bf16(v[4], v[5]); pk.w = pack_bf16(v[6], v[7]);
-    *reinterpret_cast<uint4*>(A + (int64_t)row * g.Kp + chunk * 8) = pk;
+    if constexpr (sizeof(TX) == 4) {   // fp32 activations (tf32 path): the patch matrix stays fp32, 32 bytes per thread
+      float4* dst = reinterpret_cast<float4*>(A + (int64_t)row * g.Kp + chunk * 8);
+      dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+      dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+    } else {
+      uint4 pk;
+      pk.x = pack_bf16(v[0], v[1]); pk.y = pack_bf16(v[2], v[3]); pk.z = pack_bf16(v[4], v[5]); pk.w = pack_bf16(v[6], v[7]);
+      *reinterpret_cast<uint4*>(A + (int64_t)row * g.Kp + chunk * 8) = pk;
+    }
   }
 }
 
@@ -458,7 +472,12 @@ __device__ unsigned long long g_tc_prof[160 * PROF_ROLES * PROF_SLOTS];
     }                                                           \
   } while (0)
 
-template <int BN, typename TO, bool PROF, int CL, bool FLIP>
+// TF32: fp32 activations and fp32 outputs (the reference's default dtype, linear_variational.py:181 /
+// conv_variational.py:384).  The A tiles are fp32 (a 128-byte swizzled row holds 32 elements: a k-block is 32
+// deep), the sampled weight is fmaf(sigma, eps, mu) in fp32 rounded to tf32 (cvt.rna), the MMAs are
+// tcgen05.mma.kind::tf32 (K = 8 per instruction, fp32 accumulation).  Every byte layout -- slots, swizzle,
+// descriptors, staging -- is the bf16 one; only the element counts per 16 / 128 bytes change.
+template <int BN, typename TO, bool PROF, int CL, bool FLIP, bool TF32 = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_out,
                const __grid_constant__ CUtensorMap tm_res, const __grid_constant__ CUtensorMap tm_a2,
@@ -469,6 +488,9 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   Ctrl* ctrl = reinterpret_cast<Ctrl*>(smem_raw + (base - raw));
   // Flipout: every k-block carries TWO weight sub-tiles (mu, then sigma*eps), every A slot a second,
   // sign-flipped copy of the tile, and every output tile two accumulators (mean path, perturbation path)
+  static_assert(!(TF32 && (FLIP || PROF)) && (!TF32 || sizeof(TO) == 4), "tf32: Reparameterization, fp32 in / fp32 out");
+  constexpr int BKE = TF32 ? 32 : 64;   // elements of one k-block (128 bytes of A per row)
+  constexpr int EPC16 = TF32 ? 4 : 8;   // weights per 16-byte chunk
   constexpr int NSUBW = FLIP ? 2 : 1;
   constexpr int W_SUB = BN * BK * 2;
   constexpr int W_SLOT = NSUBW * W_SUB;
@@ -758,7 +780,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     int s = s0, mg = mg0, nb = nb0;
     int rslot[N_MMA_WARPS] = {0, 0};
     uint32_t rphase[N_MMA_WARPS] = {0, 0};
-    const int Cin = a.CB * BK;
+    const int Cin = a.CB * BKE;
     int prev_mg = -1;
     for (int it = 0; it < n_items; ++it) {
       const int mtv = tiles_of(mg);
@@ -809,7 +831,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             else if (++rslot[0] == a.NAr) { rslot[0] = 0; rphase[0] ^= 1u; }
           }
         }
-        c0 += BK;
+        c0 += BKE;
         if (a.conv && c0 == Cin) {  // next filter tap
           c0 = 0;
           offw += a.dw;
@@ -824,7 +846,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     // =========================== MMA ISSUERS ===========================
     const int j = warp - WARP_MMA;  // this issuer owns tiles t with t % N_MMA_WARPS == j
     const bool leader = elect_one();
-    constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+    constexpr uint32_t idesc = TF32 ? umma_idesc_tf32(BM, BN) : umma_idesc_bf16(BM, BN);
     int mg = mg0, nb_unused = nb0, s_unused = s0, set = 0, aslot = 0, wslot_r = 0;
     uint32_t set_phase = 0, aphase = 0, wphase = 0, sphase = 0;
     uint32_t emp_bits = 0;  // phase of every acc_empty barrier (one per accumulator tile) as seen by this issuer
@@ -862,7 +884,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 // D = ones[128 x 16] * shift[BN x 16]^T: every row of the accumulator starts as the
                 // per-channel shift (bias * scale + BatchNorm shift, split into three bf16 terms)
                 if (a.has_shift && leader && !(PROF && (a.debug & 4))) {
-                  umma_bf16(dbase + (uint32_t)(t * ACC_COLS), ones_desc, shift_desc, idesc, 0u);
+                  umma_any<TF32>(dbase + (uint32_t)(t * ACC_COLS), ones_desc, shift_desc, idesc, 0u);
                   if constexpr (FLIP) umma_bf16(dbase + (uint32_t)(t * ACC_COLS + BN), ones_desc, shift2_desc, idesc, 0u);
                 }
               }
@@ -877,8 +899,8 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 const uint32_t d = dbase + (uint32_t)(t * ACC_COLS);
                 if (!(PROF && (a.debug & 4))) {
 #pragma unroll
-                  for (int k = 0; k < BK / 16; ++k)
-                    umma_bf16(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : acc0);
+                  for (int k = 0; k < BK / 16; ++k)   // 32 bytes of K per MMA: 16 bf16 or 8 tf32
+                    umma_any<TF32>(d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : acc0);
                   if constexpr (FLIP) {  // perturbation path: (x * s_in) tile against the sigma * eps sub-tile
                     const uint64_t adesc2 = umma_desc_sw128(a_base + slot * A_SLOT_T + A_SLOT);
                     const uint64_t bdesc2 = umma_desc_sw128(w_base + wslot * W_SLOT + W_SUB);
@@ -1061,6 +1083,9 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     if (a.has_shift && p < BM) {  // the constant ones tile (made visible by the first w_full[RW] arrival)
       const uint32_t dst = ones_base + (uint32_t)p * 32u;
       const uint32_t sw = (uint32_t)((p >> 2) & 1) << 4;  // 32-byte swizzle: chunk ^= bit 2 of the row
+      if constexpr (TF32)   // [1, 1, 1, 0 | 0 ...] as tf32 words (K = 8 per MMA: the 32-byte row is the whole reduction)
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + sw), "r"(0x3F800000u), "r"(0x3F800000u), "r"(0x3F800000u), "r"(0u) : "memory");
+      else
       asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + sw), "r"(0x3F803F80u), "r"(0x00003F80u), "r"(0u), "r"(0u) : "memory");
       asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (sw ^ 16u)), "r"(0u), "r"(0u), "r"(0u), "r"(0u) : "memory");
     }
@@ -1087,18 +1112,26 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               if (a.out_shift && !pert) sh += a.out_shift[n];
             }
             // three bf16 terms carry 24 bits of the fp32 shift through the bf16 MMA
+            uint32_t w0, w1, w2 = 0u;
+            if constexpr (TF32) {   // three tf32 terms (10-bit mantissas, truncation splits exactly): 30 bits of the shift
+              w0 = __float_as_uint(sh) & 0xFFFFE000u;
+              const float r1 = sh - __uint_as_float(w0);
+              w1 = __float_as_uint(r1) & 0xFFFFE000u;
+              w2 = __float_as_uint(r1 - __uint_as_float(w1)) & 0xFFFFE000u;
+            } else {
             const __nv_bfloat16 h0 = __float2bfloat16_rn(sh);
             const float r1 = sh - __bfloat162float(h0);
             const __nv_bfloat16 h1 = __float2bfloat16_rn(r1);
             const __nv_bfloat16 h2 = __float2bfloat16_rn(r1 - __bfloat162float(h1));
-            const uint32_t w0 = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
-            const uint32_t w1 = (uint32_t)__bfloat16_as_ushort(h2);
+            w0 = (uint32_t)__bfloat16_as_ushort(h0) | ((uint32_t)__bfloat16_as_ushort(h1) << 16);
+            w1 = (uint32_t)__bfloat16_as_ushort(h2);
+            }
             // (tile rows are 32 bytes and BN = 64 / 128 rows keep the 8-row swizzle phase, so the second tile,
             // SHIFT_BYTES further on, is addressed by its own row index)
             const int prow = pert ? p - BN : p;
             const uint32_t dst = shift_base + (pert ? (uint32_t)SHIFT_BYTES : 0u) + (uint32_t)prow * 32u;
             const uint32_t sw = (uint32_t)((prow >> 2) & 1) << 4;
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + sw), "r"(w0), "r"(w1), "r"(0u), "r"(0u) : "memory");
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + sw), "r"(w0), "r"(w1), "r"(w2), "r"(0u) : "memory");
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (sw ^ 16u)), "r"(0u), "r"(0u), "r"(0u), "r"(0u) : "memory");
           }
           fence_proxy_async();
@@ -1110,7 +1143,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         // packed bf16 (mu, sigma) of this thread's chunk of k-block kb2, eight weights per row
         uint4 nmu8[ROWS_PER_THREAD], nsg8[ROWS_PER_THREAD];
         auto load_params = [&](int kb2) {
-          const int k2 = kb2 * BK + chunk * 8;
+          const int k2 = kb2 * BKE + chunk * EPC16;
 #pragma unroll
           for (int i = 0; i < ROWS_PER_THREAD; ++i) {
             const int lrow = row_base + RPP * i;
@@ -1119,15 +1152,16 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             nmu8[i] = nsg8[i] = make_uint4(0u, 0u, 0u, 0u);
             if (lrow < rows_cta && k2 < a.K && vn < vN && !(PROF && (a.debug & 32))) {
               const int64_t e = (int64_t)n * a.K + k2;
-              nmu8[i] = __ldg(reinterpret_cast<const uint4*>(a.mu_p + e));
-              nsg8[i] = __ldg(reinterpret_cast<const uint4*>(a.sig_p + e));
+              // 16 bytes each: eight packed bf16, or four fp32 for the tf32 instantiation
+              nmu8[i] = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(a.mu_p) + e * (TF32 ? 4 : 2)));
+              nsg8[i] = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(a.sig_p) + e * (TF32 ? 4 : 2)));
             }
           }
         };
         load_params(0);
         for (int kb = 0; kb < a.nkb; ++kb) {
           const int slot = a.stationary ? kb : wslot_r;
-          const int k = kb * BK + chunk * 8;
+          const int k = kb * BKE + chunk * EPC16;
           const bool kin = k < a.K;  // K % 8 == 0: a chunk is all in or all out
           // parameters of this k-block were requested one k-block ago (cur <- nxt); the requests for
           // the next one go out now, a whole k-block of Philox / Box-Muller work ahead of their use
@@ -1147,6 +1181,32 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             const int n = a.spn == 2 ? (vn & 63) : vn;
             BtRngKey rk = rk0;
             if (a.spn == 2) rk.sample_id += (uint32_t)(vn >> 6);  // second sample of the stacked pair
+            if constexpr (TF32) {
+              // four fp32 weights per 16-byte chunk: w = tf32(fmaf(sigma, eps, mu)), the same stream positions as the
+              // bf16 path (half a Philox block per chunk)
+              float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (kin && vn < vN) {
+                const int64_t e = (int64_t)n * a.K + k;
+                if (a.eps_p) {
+                  z4 = __ldg(reinterpret_cast<const float4*>(a.eps_p + e));
+                } else if (a.Kt == a.K) {
+                  z4 = bt_normal4((uint64_t)e >> 2, rk);
+                } else {  // padded K (patch matrix): positions of the TRUE stream, element by element (tiny layers only)
+                  const uint64_t e0 = (uint64_t)n * a.Kt + k;
+                  z4.x = k + 0 < a.Kt ? bt_normal1(e0 + 0, rk) : 0.f;
+                  z4.y = k + 1 < a.Kt ? bt_normal1(e0 + 1, rk) : 0.f;
+                  z4.z = k + 2 < a.Kt ? bt_normal1(e0 + 2, rk) : 0.f;
+                  z4.w = k + 3 < a.Kt ? bt_normal1(e0 + 3, rk) : 0.f;
+                }
+              }
+              const uint32_t t0 = to_tf32(fmaf(__uint_as_float(sg8[i].x), z4.x, __uint_as_float(mu8[i].x)));
+              const uint32_t t1 = to_tf32(fmaf(__uint_as_float(sg8[i].y), z4.y, __uint_as_float(mu8[i].y)));
+              const uint32_t t2 = to_tf32(fmaf(__uint_as_float(sg8[i].z), z4.z, __uint_as_float(mu8[i].z)));
+              const uint32_t t3 = to_tf32(fmaf(__uint_as_float(sg8[i].w), z4.w, __uint_as_float(mu8[i].w)));
+              const uint32_t toff = (uint32_t)(slot * W_SLOT) + (uint32_t)row * 128u + (((uint32_t)chunk ^ (uint32_t)(row & 7)) << 4);
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(w_base + toff), "r"(t0), "r"(t1), "r"(t2), "r"(t3) : "memory");
+              continue;
+            }
             float z[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) z[e] = 0.f;
@@ -1309,6 +1369,7 @@ struct Plan {
   int64_t x_rows;      // rows (A_GEMM / A_PATCH) or images (A_IM2COL) per sample in the A source
   int64_t pitch;       // A_GEMM: row pitch of x in elements
   int T, K, Kp;        // taps, true reduction length, padded reduction length
+  int es;              // bytes per activation element: 2 (bf16 operands) or 4 (fp32 activations, tf32 operands)
   Dense d;
   int64_t xh, xw;
 };
@@ -1328,7 +1389,12 @@ static bool tc2_plan(const bt_geom* g, const bt_layer_params* p, bool flipout, P
   TC_NO(flipout && ((p->sign_in == nullptr) != (p->sign_out == nullptr)), "sign_in and sign_out must both be given or both be null");
   TC_NO(flipout && g->rank > 2, "Flipout rank 3");
   TC_NO(g->groups != 1, "groups != 1");
-  TC_NO(g->x_dtype != BT_BF16, "activations are not bf16");
+  TC_NO(g->x_dtype != BT_BF16 && g->x_dtype != BT_F32, "activations are neither bf16 nor fp32");
+  // fp32 activations run the tf32 instantiation: Reparameterization forward, fp32 in / fp32 out
+  TC_NO(g->x_dtype == BT_F32 && (flipout || g->out_dtype != BT_F32), "fp32 activations: Flipout / mixed dtypes run the fp32 kernels");
+  TC_NO(g->x_dtype == BT_F32 && env_int("BT_TF32", 1) == 0, "tf32 tensor-core path switched off (BT_TF32=0)");
+  const int es = g->x_dtype == BT_F32 ? 4 : 2;
+  const int e16 = 16 / es, bke = 128 / es;   // elements per 16 bytes / per k-block
   TC_NO(g->out_chan_stride != 1, "output channels are not the fastest axis (need channels-last)");
   TC_NO(g->c_out % 8 != 0, "c_out is not a multiple of 8");
   TC_NO(g->batch <= 0, "empty batch");
@@ -1354,16 +1420,17 @@ static bool tc2_plan(const bt_geom* g, const bt_layer_params* p, bool flipout, P
   TC_NO(g->c_in * taps >= (1ll << 24), "reduction length too large");
   pl->K = (int)(g->c_in * taps);
   pl->Kp = (pl->K + 7) & ~7;
+  pl->es = es;
   const int pin = env_int("BT_TC2_AMODE", 0);
   if (g->rank == 0) {
-    if (g->x_chan_stride == 1 && g->x_batch_stride % 8 == 0 && g->c_in % 8 == 0 && (!flipout || g->c_in % 64 == 0) && pin != A_PATCH) {
+    if (g->x_chan_stride == 1 && g->x_batch_stride % e16 == 0 && g->c_in % 8 == 0 && (!flipout || g->c_in % 64 == 0) && pin != A_PATCH) {
       pl->mode = A_GEMM; pl->x_rows = g->batch; pl->pitch = g->x_batch_stride;
       return true;
     }
-  } else if (g->rank <= 2 && g->x_chan_stride == 1 && g->c_in % 64 == 0 && pin != A_PATCH) {
+  } else if (g->rank <= 2 && g->x_chan_stride == 1 && g->c_in % bke == 0 && pin != A_PATCH) {
     conv_dims(g, &pl->d, &pl->xh, &pl->xw, &dense, &taps);
     const Dense& d = pl->d;
-    bool ok = pl->xw % 8 == 0 && pl->xh % 8 == 0 && g->x_batch_stride % 8 == 0;
+    bool ok = pl->xw % e16 == 0 && pl->xh % e16 == 0 && g->x_batch_stride % e16 == 0;
     for (int i = 0; i < 2; ++i)
       ok = ok && d.st[i] <= 8 && d.pd[i] <= 127 && (d.k[i] - 1) * d.dl[i] - d.pd[i] <= 128 && (d.k[i] - 1) * d.dl[i] <= 65535;
     if (ok) {
@@ -1407,7 +1474,7 @@ static int64_t x_span_elems(const bt_geom* g) {
 static int64_t packed_bytes(int64_t n, int64_t kp) { return ((3 * n * kp * 4 + 255) / 256) * 256; }
 static int64_t patch_bytes(const bt_geom* g, int64_t rows_per_s, int64_t Kp) {
   const bool x_shared = g->n_samples > 1 && g->x_sample_stride == 0;
-  return ((rows_per_s * (x_shared ? 1 : g->n_samples) * Kp * 2 + 255) / 256) * 256;
+  return ((rows_per_s * (x_shared ? 1 : g->n_samples) * Kp * (g->x_dtype == BT_F32 ? 4 : 2) + 255) / 256) * 256;
 }
 int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout) {
   int64_t taps = 1;
@@ -1426,10 +1493,10 @@ int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout) {
   return bytes;
 }
 
-template <int BN, typename TO, bool PROF, int CL, bool FLIP>
+template <int BN, typename TO, bool PROF, int CL, bool FLIP, bool TF32 = false>
 static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const CUtensorMap& ta2,
                           const Tc2Args& a, int grid, int smem_bytes, cudaStream_t stream) {
-  BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, PROF, CL, FLIP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, PROF, CL, FLIP, TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3((unsigned)grid);
@@ -1443,14 +1510,19 @@ static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CU
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_fwd_kernel<BN, TO, PROF, CL, FLIP>, ta, to, tr, ta2, a));
-  BT_LAUNCH_OK(PROF ? "tc2_fwd_kernel(prof)" : (FLIP ? "tc2_fwd_kernel(flipout)" : "tc2_fwd_kernel"));
+  BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_fwd_kernel<BN, TO, PROF, CL, FLIP, TF32>, ta, to, tr, ta2, a));
+  BT_LAUNCH_OK(PROF ? "tc2_fwd_kernel(prof)" : (FLIP ? "tc2_fwd_kernel(flipout)" : (TF32 ? "tc2_fwd_kernel(tf32)" : "tc2_fwd_kernel")));
   return BT_OK;
 }
 
 template <int BN, typename TO>
 static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const CUtensorMap& ta2, const Tc2Args& a,
                       int grid, int smem_bytes, bool flip, cudaStream_t stream) {
+  if constexpr (sizeof(TO) == 4) {
+    if (a.tf32)
+      return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, false, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream)
+                       : tc2_launch_one<BN, TO, false, 1, false, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream);
+  }
   if (flip)
     return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream)
                      : tc2_launch_one<BN, TO, false, 1, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream);
@@ -1501,10 +1573,15 @@ static int build_patch_matrices(const bt_geom* g, const Plan& pl, const bt_layer
   if (blocks > cap) blocks = cap;
   // (stacked samples of x are just more images: the batch stride walks across them)
   auto build_patches = [&](const __nv_bfloat16* src, __nv_bfloat16* dst) -> int {
-    if (chunks + cap * 256 < 0x7fffffffll)
+    const bool small = chunks + cap * 256 < 0x7fffffffll;
+    if (g->x_dtype == BT_F32) {   // (pointers are typed bf16 for the Flipout bookkeeping below; fp32 never takes that branch)
+      if (small) tc2_patch_kernel<float, uint32_t><<<(int)blocks, 256, 0, stream>>>((const float*)src, (float*)dst, pg);
+      else tc2_patch_kernel<float, int64_t><<<(int)blocks, 256, 0, stream>>>((const float*)src, (float*)dst, pg);
+    } else if (small) {
       tc2_patch_kernel<__nv_bfloat16, uint32_t><<<(int)blocks, 256, 0, stream>>>(src, dst, pg);
-    else
+    } else {
       tc2_patch_kernel<__nv_bfloat16, int64_t><<<(int)blocks, 256, 0, stream>>>(src, dst, pg);
+    }
     BT_LAUNCH_OK("tc2_patch_kernel");
     return BT_OK;
   };
@@ -1574,15 +1651,20 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   a.Ms = (int)pl.rows_per_s;
   a.Kt = pl.K;
   a.K = pl.mode == A_PATCH ? pl.Kp : pl.K;
+  a.tf32 = pl.es == 4 ? 1 : 0;
+  const int bke = 128 / pl.es;   // elements per k-block
+  const CUtensorMapDataType a_dt = a.tf32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  BT_REQUIRE(!a.tf32 || (!opt.dgrad && !flipout), BT_ERR_UNSUPPORTED, "tensor-core forward: fp32 activations support the Reparameterization forward only");
   a.x_rows_per_s = x_shared ? 0 : (int)pl.x_rows;
   alignas(64) CUtensorMap tm_a, tm_out, tm_res, tm_a2;
   const int es_o = g->out_dtype == BT_F32 ? 4 : 2;
 
   // ---- workspace carve-up: packed parameters, then (A_PATCH) the patch matrix
   const int64_t wn = (int64_t)a.N * a.K;
+  // bf16 packing: mu (2 B), sigma (2 B), eps (4 B) per weight; tf32: three fp32 arrays -- both within 12 B per weight
   __nv_bfloat16* mu_p = (__nv_bfloat16*)workspace;
-  __nv_bfloat16* sig_p = mu_p + wn;
-  float* eps_p = (p->eps_w || opt.dgrad) ? (float*)(sig_p + wn) : nullptr;
+  __nv_bfloat16* sig_p = a.tf32 ? (__nv_bfloat16*)((float*)workspace + wn) : mu_p + wn;
+  float* eps_p = (p->eps_w || opt.dgrad) ? (a.tf32 ? (float*)workspace + 2 * wn : (float*)(sig_p + wn)) : nullptr;
   __nv_bfloat16* patches = (__nv_bfloat16*)((char*)workspace + ((3 * wn * 4 + 255) / 256) * 256);
   bool kl_done = false;
   if (opt.ws_bytes > 0) {  // the carve-up below must fit what the caller allocated (bt_workspace_bytes)
@@ -1617,14 +1699,22 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
       kf.w_numel = (int64_t)a.N * pl.K;
       kf.b_numel = p->mu_b ? a.N : 0;
       BT_CUDA_OK(cudaMemsetAsync(opt.kl_scratch, 0, 32, stream));
-      tc2_pack_kernel<true><<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, p->out_scale, wn, (int)g->c_in,
+      if (a.tf32)
+        tc2_pack_kernel<true, float><<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, (float*)mu_p, (float*)sig_p, eps_p, p->out_scale,
+                                                                      wn, (int)g->c_in, pl.T, a.K, kf);
+      else
+      tc2_pack_kernel<true, __nv_bfloat16><<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, p->out_scale, wn, (int)g->c_in,
                                                              pl.T, a.K, kf);
       BT_LAUNCH_OK("tc2_pack_kernel(kl)");
       kl_done = true;
     } else {
       PackKl kf;
       memset(&kf, 0, sizeof(kf));
-      tc2_pack_kernel<false><<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, p->out_scale, wn, (int)g->c_in,
+      if (a.tf32)
+        tc2_pack_kernel<false, float><<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, (float*)mu_p, (float*)sig_p, eps_p, p->out_scale,
+                                                                       wn, (int)g->c_in, pl.T, a.K, kf);
+      else
+      tc2_pack_kernel<false, __nv_bfloat16><<<(int)blocks, 256, 0, stream>>>(p->mu_w, p->rho_w, p->eps_w, mu_p, sig_p, eps_p, p->out_scale, wn, (int)g->c_in,
                                                               pl.T, a.K, kf);
       BT_LAUNCH_OK("tc2_pack_kernel");
     }
@@ -1650,10 +1740,10 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
     a.conv = 0;
     const cuuint64_t rows = (cuuint64_t)pl.x_rows * (x_shared ? 1 : S);
     const cuuint64_t gdim[2] = {(cuuint64_t)a.K, rows};
-    const cuuint64_t gstr[1] = {(cuuint64_t)pl.pitch * 2};
-    const cuuint32_t box[2] = {BK, BM};
+    const cuuint64_t gstr[1] = {(cuuint64_t)pl.pitch * pl.es};
+    const cuuint32_t box[2] = {(cuuint32_t)bke, BM};
     const cuuint32_t estr[2] = {1, 1};
-    const CUresult r = drv.tiled(&tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(a_src), gdim, gstr, box, estr,
+    const CUresult r = drv.tiled(&tm_a, a_dt, 2, const_cast<void*>(a_src), gdim, gstr, box, estr,
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     BT_REQUIRE(r == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeTiled(x) failed with %d", (int)r);
@@ -1667,7 +1757,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   } else {
     const Dense& d = pl.d;
     a.conv = 1;
-    a.CB = (int)g->c_in / BK;
+    a.CB = (int)g->c_in / bke;
     a.OH = (int)d.out[0]; a.OW = (int)d.out[1]; a.KW = (int)d.k[1];
     a.sh = (int)d.st[0]; a.sw = (int)d.st[1]; a.ph = (int)d.pd[0]; a.pw = (int)d.pd[1]; a.dh = (int)d.dl[0]; a.dw = (int)d.dl[1];
     a.IH = (int)d.in[0]; a.IW = (int)d.in[1];
@@ -1676,17 +1766,17 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
     if (opt.a_dil_h > 1 || opt.a_dil_w > 1) { a.SH = opt.SH; a.SW = opt.SW; a.x_bs = opt.s_bs; a.x_hs = opt.s_hs; a.x_ws = opt.s_ws; }
     const cuuint64_t imgs = (cuuint64_t)g->batch * (x_shared ? 1 : S);
     const cuuint64_t gdim[4] = {(cuuint64_t)g->c_in, (cuuint64_t)d.in[1], (cuuint64_t)d.in[0], imgs};
-    const cuuint64_t gstr[3] = {(cuuint64_t)pl.xw * 2, (cuuint64_t)pl.xh * 2, (cuuint64_t)g->x_batch_stride * 2};
+    const cuuint64_t gstr[3] = {(cuuint64_t)pl.xw * pl.es, (cuuint64_t)pl.xh * pl.es, (cuuint64_t)g->x_batch_stride * pl.es};
     // bounding box of the filter's top-left corner, in (W, H) order like the coordinates
     const int lower[2] = {-(int)d.pd[1], -(int)d.pd[0]};
     const int upper[2] = {(int)(d.pd[1] - (d.k[1] - 1) * d.dl[1]), (int)(d.pd[0] - (d.k[0] - 1) * d.dl[0])};
     const cuuint32_t estr[4] = {1, (cuuint32_t)d.st[1], (cuuint32_t)d.st[0], 1};
-    const CUresult r = drv.im2col(&tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(x), gdim, gstr, lower, upper,
-                                  BK, BM, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+    const CUresult r = drv.im2col(&tm_a, a_dt, 4, const_cast<void*>(x), gdim, gstr, lower, upper,
+                                  (cuuint32_t)bke, BM, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     BT_REQUIRE(r == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeIm2col(x) failed with %d", (int)r);
     // Small-tensor workaround of drivers <= 13.1 (same fix-up CUTLASS applies to im2col descriptors).
-    const int64_t span = (int64_t)imgs * g->x_batch_stride * 2;
+    const int64_t span = (int64_t)imgs * g->x_batch_stride * pl.es;
     if (drv.driver_version <= 13010 && span < 131072) reinterpret_cast<uint64_t*>(&tm_a)[1] &= ~(1ull << 21);
     tm_a2 = tm_a;
   }
@@ -1713,7 +1803,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   // ---- tiling / pipeline configuration
   const int sms = bt_num_sms();
   a.num_mt = (a.Ms + BM - 1) / BM;
-  a.nkb = (a.K + BK - 1) / BK;
+  a.nkb = (a.K + bke - 1) / bke;
   // x shared by all samples and exactly 64 output channels (the ResNet stem under mc_batched): two samples ride side by
   // side on the N axis of a BN = 128 tile, so an A tile is fetched once per pair and feeds a full-width MMA (at N = 64
   // the tensor core reads 128 B of A per cycle at full rate: the layer was bound by that read)
@@ -1908,6 +1998,7 @@ bool bt_tc_dgrad_supported(const bt_geom* g, const bt_layer_params* p, bool flip
   const bt_layer_params q = dgrad_params(p);
   Plan pl;
   if (!tc2_plan(&t, &q, flipout, &pl, why, inserted)) return false;
+  if (pl.es != 2) { *why = "fp32 gradients run the fp32 kernels"; return false; }
   if (inserted && pl.mode == A_PATCH && flipout) { *why = "strided Flipout layer through the patch matrix"; return false; }
   return true;
 }

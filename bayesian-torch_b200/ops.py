@@ -440,6 +440,18 @@ def _dense(x: torch.Tensor) -> torch.Tensor:
     return x.contiguous()
 
 
+def _to_channels_last(call: "LayerCall", x: torch.Tensor) -> torch.Tensor:
+    """The reference feeds contiguous NCHW activations (torch's default); the tensor-core kernels read pixels as GEMM
+    rows, i.e. channels-last.  A 4-d NCHW input of a layer that may run on tensor cores is re-laid out ONCE here (one
+    transposing copy); the layer's output is then channels-last, and BatchNorm / ReLU / pooling keep that format, so
+    the layers downstream get channels-last inputs without further copies.  The fp32 kernels (path 'simt') read any
+    strides and are left alone."""
+    if (call.rank == 2 and call.path != _lib.PATH_SIMT_F32 and call.groups == 1 and x.dim() == 4 and x.shape[1] > 1
+            and x.is_contiguous() and not x.is_contiguous(memory_format=torch.channels_last)):
+        return x.contiguous(memory_format=torch.channels_last)
+    return x
+
+
 def _match_strides(t: torch.Tensor, ref: torch.Tensor) -> torch.Tensor:
     """fp32 copy of t laid out exactly like ref (the kernels index signs with x's / out's offsets)."""
     t = t.detach().reshape(ref.shape)
@@ -480,7 +492,7 @@ class _BayesLayerFn(torch.autograd.Function):
         mu_wc, rho_wc = _f32c(mu_w.detach(), "mu"), _f32c(rho_w.detach(), "rho")
         mu_bc = None if mu_b is None else _f32c(mu_b.detach(), "mu_bias")
         rho_bc = None if rho_b is None else _f32c(rho_b.detach(), "rho_bias")
-        xd = _dense(x.detach())
+        xd = _to_channels_last(call, _dense(x.detach()))
         r = call.rank
         nb = xd.shape[0] * (call.n_samples if call.x_shared else 1)
         if r == 0:
@@ -563,7 +575,7 @@ class _BayesLayerFn(torch.autograd.Function):
         mu_wc, rho_wc = _f32c(mu_w.detach(), "mu"), _f32c(rho_w.detach(), "rho")
         mu_bc = None if mu_b is None else _f32c(mu_b.detach(), "mu_bias")
         rho_bc = None if rho_b is None else _f32c(rho_b.detach(), "rho_bias")
-        xd = _dense(x.detach())
+        xd = _to_channels_last(call, _dense(x.detach()))
         if g_out is None:  # only kl was used downstream
             g_out = torch.empty_strided(ctx.out_meta[0], ctx.out_meta[1], dtype=x.dtype, device=dev).zero_()
         S = call.n_samples

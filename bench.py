@@ -326,6 +326,20 @@ def extras(dev, model, pk):
         kms = cuda_time(lambda: bt.get_kl_loss(model), 20, warm=3)
     out["kl_resnet50_table"] = {"ms": kms, "gbs": nbytes / kms / 1e6, "frac_of_hbm_peak": nbytes / kms / 1e6 / pk["gbs"], "bytes": nbytes}
     out["cfg2_resnet18_flipout_train_step"] = train_step_time(dev, 128, "Flipout", iters=5)
+    # the reference's README usage, untouched: dnn_to_bnn(model); model.cuda(); S sequential forwards on fp32 NCHW input
+    # (no bf16 cast, no BatchNorm fold, no sample folding) -- fp32 activations run the tf32 tensor-core instantiation
+    m32 = seed_resnet50()
+    bt.dnn_to_bnn(m32, dict(BNN_PARAMS))
+    m32 = m32.to(dev).eval()
+    x32 = torch.randn(128, 3, 224, 224, device=dev)
+
+    def fwd32():
+        with torch.no_grad(), bt.mc_sample(0):
+            m32(x32)
+    ms = cuda_time(fwd32, 3)
+    out["fp32_nchw_default_path"] = {"value": 128 * 1e3 / (ms * 32), "unit": UNIT, "ms_per_forward": ms,
+                                     "note": "drop-in default: fp32 NCHW input, path auto (tf32 tensor cores), torch BatchNorm / ReLU, "
+                                             "32 sequential forwards per image scaled from 3; compare eager_b200.fp32_nchw"}
     return out
 
 

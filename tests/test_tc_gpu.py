@@ -223,18 +223,13 @@ def test_tc_rejects_what_it_cannot_run(cuda_device):
     layer.path = "tc"
     with pytest.raises(RuntimeError, match="tensor-core path unavailable"):
         layer(torch.randn(1, 16, 8, 8, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last))
-    with pytest.raises(RuntimeError, match="tensor-core path unavailable"):   # fp32 activations stay on the parity path
-        L.Conv2dReparameterization(64, 64, 1, prior_type="normal").to(cuda_device).__setattr__("path", "tc") or \
-            _tc_on_fp32(cuda_device)
+    fo = L.Conv2dFlipout(64, 64, 1).to(cuda_device)     # fp32 activations: tf32 tensor cores for Reparameterization only
+    fo.path = "tc"
+    with pytest.raises(RuntimeError, match="tensor-core path unavailable"):
+        fo(torch.randn(1, 64, 8, 8, device=cuda_device).contiguous(memory_format=torch.channels_last))
     layer.path = "auto"                        # auto falls back to the fp32 kernel, documented in DESIGN.md
     out, _ = layer(torch.randn(1, 16, 8, 8, device=cuda_device))
     assert out.shape == (1, 16, 8, 8)
-
-
-def _tc_on_fp32(cuda_device):
-    layer = L.Conv2dReparameterization(64, 64, 1, prior_type="normal").to(cuda_device)
-    layer.path = "tc"
-    return layer(torch.randn(1, 64, 8, 8, device=cuda_device))
 
 
 RESIDUAL_CASES = [
