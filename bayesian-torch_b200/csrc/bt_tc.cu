@@ -94,6 +94,9 @@ struct Tc2Args {
   int has_shift;     // bias and/or folded BatchNorm shift: added by a rank-1 MMA that initialises each accumulator
   int res_bufs;      // residual tiles in flight per epilogue warp (0: no residual input)
   int stage_bufs;    // epilogue staging buffers per warp (2, or 1 when shared memory is tight)
+  int pdl;           // launched with programmatic stream serialization: 1 = every role waits for the previous kernel after
+                     // its set-up, 2 = the W producers do not (their inputs -- packed parameters of a frozen layer, biases,
+                     // BatchNorm terms -- were complete long before) and sample the first k-blocks during the previous kernel's tail
   int tf32;          // fp32 activations: fp32 A tiles, tf32 MMAs (k-blocks of 32 elements), fp32 packed parameters
   int debug;         // BT_TC2_DEBUG bits, honoured by the BT_TC2_PROF=1 instantiation only: 1 skip output stores, 4 skip MMAs,
                      // 8 skip A loads, 16 skip the normal draws, 32 skip the parameter loads
@@ -215,12 +218,19 @@ __global__ void __launch_bounds__(256) tc2_pack_kernel(const float* __restrict__
   float part = 0.f;
   double dsum = 0.0;
   int since = 0;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t n = i / Kp;
-    const int k = (int)(i - n * Kp);
+  // (n, k) of the packed index advance incrementally: a 64-bit division per element was most of this kernel's time
+  const int64_t step = (int64_t)gridDim.x * blockDim.x;
+  const int64_t dn = step / Kp;
+  const int dk = (int)(step - dn * Kp);
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t n = i / Kp;
+  int k = (int)(i - n * Kp);
+  for (; i < total; i += step, n += dn, k += dk) {
+    if (k >= Kp) { k -= Kp; ++n; }
     float m = 0.f, sg = 0.f, e = 0.f;
     if (k < K) {
-      const int tap = k / Cin, c = k - tap * Cin;
+      int tap = 0, c = k;
+      if (T > 1) { tap = k / Cin; c = k - tap * Cin; }
       const int64_t src = n * K + (int64_t)c * T + tap;
       m = mu[src];
       const float r = rho[src];
@@ -542,6 +552,14 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   if constexpr (CL > 1) cluster_sync_all();  // the peer's mbarriers are initialised before anything arrives on them
   tc_fence_after();
   const uint32_t tmem = ctrl->tmem_base;
+  // Programmatic dependent launch: this grid may have been scheduled while the previous kernel of the stream was still
+  // draining (its CTAs leave their SMs one by one; ours move in, initialise barriers, allocate TMEM, prefetch the tensor
+  // maps above).  Let the NEXT kernel do the same behind us, then wait -- here, before the first byte of global memory
+  // that a previous kernel may have written (activations, residual) is touched or any output is stored.
+  if (a.pdl) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (!(a.pdl == 2 && warp < NPW)) asm volatile("griddepcontrol.wait;" ::: "memory");
+  }
 
   const int vN = a.N * a.spn;  // width of the (virtual) N axis the tiles are cut from
   const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
@@ -1503,13 +1521,15 @@ static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CU
   cfg.blockDim = dim3(NUM_THREADS);
   cfg.dynamicSmemBytes = (size_t)smem_bytes;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = (unsigned)CL;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = a.pdl ? 2 : 1;
   BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_fwd_kernel<BN, TO, PROF, CL, FLIP, TF32>, ta, to, tr, ta2, a));
   BT_LAUNCH_OK(PROF ? "tc2_fwd_kernel(prof)" : (FLIP ? "tc2_fwd_kernel(flipout)" : (TF32 ? "tc2_fwd_kernel(tf32)" : "tc2_fwd_kernel")));
   return BT_OK;
@@ -1641,6 +1661,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   a.out_scale = p->out_scale; a.out_shift = p->out_shift; a.out_relu = p->out_relu;
   a.seed = p->seed; a.sample_id = p->sample_id; a.layer_id = p->layer_id;
   a.debug = env_int("BT_TC2_DEBUG", 0);
+  a.pdl = env_int("BT_PDL", 1) && !env_int("BT_TC2_PROF", 0) ? 1 : 0;
   a.sign_in = flipout ? p->sign_in : nullptr;
   a.sign_out = flipout ? p->sign_out : nullptr;
   a.kind_a = opt.dgrad ? BT_KIND_SIGN_OUT : BT_KIND_SIGN_IN;
@@ -1686,6 +1707,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
       BT_LAUNCH_OK("tc2_pack_dgrad_kernel");
     } else if ((p->flags & BT_FLAG_PACKED_VALID) && !p->eps_w) {
       // frozen inference model: the workspace still holds this layer's packed parameters
+      if (a.pdl && !p->eps_b && pl.mode != A_PATCH) a.pdl = 2;
     } else if (opt.kl_out) {
       BT_REQUIRE(opt.kl_scratch, BT_ERR_INVALID, "tensor-core forward: kl_out needs the workspace's KL scratch");
       PackKl kf;

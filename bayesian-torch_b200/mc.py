@@ -364,9 +364,9 @@ class HostBatchPrefetcher:
     computes, so the PCIe time (77 MB per 128 fp32 ImageNet-size images) leaves the step's critical path.
 
     shard=True (sample-sharded multi-GPU inference: every rank needs the WHOLE batch): rank r copies only rows
-    [r*B/G, (r+1)*B/G) over PCIe, converts them, and one NCCL all-gather over NVLink assembles the batch on every
-    GPU -- G ranks pulling the same 77 MB through one host's PCIe complex was what held the 8-GPU end-to-end
-    number 15 % under the device-resident one.
+    [r*B/G, (r+1)*B/G) over PCIe (overlapped with the previous step), converts them, and one NCCL all-gather over
+    NVLink (in take(), between two steps) assembles the batch on every GPU -- G ranks pulling the same 77 MB through
+    one host's PCIe complex was what held the 8-GPU end-to-end number 15 % under the device-resident one.
 
         pf = HostBatchPrefetcher(device, dtype=torch.bfloat16, memory_format=torch.channels_last)
         pf.submit(first_batch)
@@ -413,7 +413,7 @@ class HostBatchPrefetcher:
                     part = part.to(self.dtype)
                 part = part.contiguous(memory_format=self.memory_format)
                 x = torch.empty((B, *part.shape[1:]), dtype=part.dtype, device=self.device, memory_format=self.memory_format)
-                work = dist.all_gather_into_tensor(self._flat(x), self._flat(part), group=self.group, async_op=True)
+                work = part        # gathered in take(), on the compute stream
             else:
                 x = host_batch.to(self.device, non_blocking=True)
                 if self.dtype is not None:
@@ -431,6 +431,12 @@ class HostBatchPrefetcher:
         cur = torch.cuda.current_stream(self.device)
         cur.wait_event(done)
         if work is not None:
-            work.wait()          # the compute stream waits for the all-gather (no host block)
+            # The all-gather runs ON the compute stream, between two steps: ~0.1 ms over NVLink.  Issued from the side
+            # stream it overlapped the step in principle, but its CTAs then compete with the persistent layer kernels
+            # (one CTA per SM, all of shared memory): a rank whose peers were late kept SMs busy-waiting and every layer
+            # kernel behind it started short of SMs -- 17 % of the step at 4 GPUs.
+            import torch.distributed as dist
+            work.record_stream(cur)
+            dist.all_gather_into_tensor(self._flat(x), self._flat(work), group=self.group)
         x.record_stream(cur)     # allocated on the side stream, consumed on the compute stream
         return x
