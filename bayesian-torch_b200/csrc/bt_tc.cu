@@ -62,6 +62,7 @@ constexpr int NUM_THREADS = (N_PROD_WARPS + 8) * 32;  // 768
 // grow to 120. The pool setmaxnreg draws on is what the CTA was LAUNCHED with
 // (768 x 80 = 61440 registers), not the whole register file: 128*120 + 128*72 + 512*72 = 61440.
 constexpr int REGS_EPI = 120, REGS_CTRL = 72, REGS_PROD = 72;
+constexpr int REGS_EPI8 = 96;  // eight epilogue warps: 256*96 + 128*72 (control) + 384*72 (12 producer warps) = 61440
 constexpr int MAX_NA = 8, MAX_RW = 24, MAX_SETS = 8, MAX_MT = 4;
 constexpr int SMEM_LIMIT = 232448;
 constexpr int AVAIL_BYTES = SMEM_LIMIT - 1024 - CTRL_BYTES;  // staging + residual ring + A ring + W ring / panel
@@ -97,6 +98,7 @@ struct Tc2Args {
   int pdl;           // launched with programmatic stream serialization: 1 = every role waits for the previous kernel after
                      // its set-up, 2 = the W producers do not (their inputs -- packed parameters of a frozen layer, biases,
                      // BatchNorm terms -- were complete long before) and sample the first k-blocks during the previous kernel's tail
+  int epi8;          // eight epilogue warps (EPI8 instantiation): staging holds 2 * stage_bufs buffers per lane quarter
   int tf32;          // fp32 activations: fp32 A tiles, tf32 MMAs (k-blocks of 32 elements), fp32 packed parameters
   int debug;         // BT_TC2_DEBUG bits, honoured by the BT_TC2_PROF=1 instantiation only: 1 skip output stores, 4 skip MMAs,
                      // 8 skip A loads, 16 skip the normal draws, 32 skip the parameter loads
@@ -487,7 +489,12 @@ __device__ unsigned long long g_tc_prof[160 * PROF_ROLES * PROF_SLOTS];
 // deep), the sampled weight is fmaf(sigma, eps, mu) in fp32 rounded to tf32 (cvt.rna), the MMAs are
 // tcgen05.mma.kind::tf32 (K = 8 per instruction, fp32 accumulation).  Every byte layout -- slots, swizzle,
 // descriptors, staging -- is the bf16 one; only the element counts per 16 / 128 bytes change.
-template <int BN, typename TO, bool PROF, int CL, bool FLIP, bool TF32 = false>
+// EPI8: EIGHT epilogue warps.  On the layers whose output (and residual) stream is the bottleneck -- wide 1x1
+// expansions with a short reduction -- four epilogue warps, one per TMEM lane quarter and scheduler, are latency bound
+// (tcgen05.ld -> convert -> st.shared -> proxy fence -> TMA store, ~1 200-1 700 cycles per 32 x 64 slab: 14 B / cycle /
+// SM of output against an HBM share of 25 B / cycle).  Producer warps 12-15 become a second epilogue group: group g
+// drains columns [64 g, 64 g + 64) of every 128-column tile, two warps per lane quarter interleave on each scheduler.
+template <int BN, typename TO, bool PROF, int CL, bool FLIP, bool TF32 = false, bool EPI8 = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_out,
                const __grid_constant__ CUtensorMap tm_res, const __grid_constant__ CUtensorMap tm_a2,
@@ -499,6 +506,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   // Flipout: every k-block carries TWO weight sub-tiles (mu, then sigma*eps), every A slot a second,
   // sign-flipped copy of the tile, and every output tile two accumulators (mean path, perturbation path)
   static_assert(!(TF32 && (FLIP || PROF)) && (!TF32 || sizeof(TO) == 4), "tf32: Reparameterization, fp32 in / fp32 out");
+  static_assert(!EPI8 || (BN == 128 && sizeof(TO) == 2 && !FLIP && !PROF && !TF32), "EPI8: bf16 Reparameterization, BN = 128");
   constexpr int BKE = TF32 ? 32 : 64;   // elements of one k-block (128 bytes of A per row)
   constexpr int EPC16 = TF32 ? 4 : 8;   // weights per 16-byte chunk
   constexpr int NSUBW = FLIP ? 2 : 1;
@@ -506,12 +514,12 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   constexpr int W_SLOT = NSUBW * W_SUB;
   constexpr int A_SLOT_T = NSUBW * A_SLOT;
   constexpr int ACC_COLS = NSUBW * BN;
-  constexpr int NPW = FLIP ? N_PROD_WARPS - N_FLIP_WARPS : N_PROD_WARPS;  // producer warps
+  constexpr int NPW = (FLIP || EPI8) ? N_PROD_WARPS - N_FLIP_WARPS : N_PROD_WARPS;  // producer warps (12 when warps 12-15 have another role)
   constexpr int PT = NPW * 32;
   constexpr int SUBN = 128 / (int)sizeof(TO);  // output columns per 128-byte staging row
   const uint32_t ones_base = base + BAR_BYTES, shift_base = ones_base + ONES_BYTES;
   const uint32_t stage_base = base + CTRL_BYTES + (FLIP ? SHIFT_BYTES : 0);  // Flipout: a second shift tile (perturbation bias)
-  const uint32_t res_base = stage_base + (uint32_t)a.stage_bufs * STAGE_UNIT;
+  const uint32_t res_base = stage_base + (uint32_t)(a.stage_bufs * (EPI8 ? 2 : 1)) * STAGE_UNIT;
   const uint32_t a_base = res_base + (uint32_t)a.res_bufs * STAGE_UNIT;
   const uint32_t w_base = a_base + a.NA * A_SLOT_T;
 
@@ -537,7 +545,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     for (int i = 0; i < a.NSETS; ++i) mbar_init(smem_u32(&ctrl->acc_full[i]), N_MMA_WARPS);
     // acc_empty is per accumulator TILE (set * MT + t): the MMAs of the next item restart on tile t as soon as the
     // epilogue has drained it, instead of waiting for the whole set
-    for (int i = 0; i < a.NSETS * a.MT; ++i) mbar_init(smem_u32(&ctrl->acc_empty[i]), 128);
+    for (int i = 0; i < a.NSETS * a.MT; ++i) mbar_init(smem_u32(&ctrl->acc_empty[i]), EPI8 ? 256 : 128);
     for (int i = 0; i < 4; ++i) { mbar_init(smem_u32(&ctrl->res_full[i]), 1); mbar_init(smem_u32(&ctrl->res_empty[i]), 4); }
     mbar_fence_init();
   }
@@ -609,7 +617,89 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     return false;
   };
 
-  if (warp >= WARP_EPI0 && warp < WARP_EPI0 + 4) {
+  const bool epi_a = warp >= WARP_EPI0 && warp < WARP_EPI0 + 4;
+  const bool epi_b = EPI8 && warp >= NPW && warp < NPW + 4;
+  if (EPI8 && (epi_a || epi_b)) {
+    if constexpr (EPI8) {
+    // =========================== EPILOGUE, two groups of four warps ===========================
+    reg_alloc<REGS_EPI8>();
+    const int grp = epi_a ? 0 : 1;   // columns [64 grp, 64 grp + 64) of every tile
+    const int q = warp & 3;          // TMEM lane quarter (WARP_EPI0 and NPW are multiples of 4)
+    const uint32_t my_stage = stage_base + (uint32_t)((grp * 4 + q) * a.stage_bufs) * 4096u;
+    const uint32_t my_res = res_base + (uint32_t)q * 4096u;
+    const uint32_t row_sw = (uint32_t)(lane & 7);
+    uint32_t nstore = 0, sbuf = 0;
+    int s = s0, nb = nb0, mg = mg0, set = 0;
+    uint32_t set_phase = 0;
+    int rslot = grp;                 // the residual ring alternates sub-tile 0 / 1: group g owns the slots = g (mod 2)
+    uint32_t rphase = 0;
+    auto epi8_loop = [&](auto relu_c, auto res_c) {
+      constexpr bool RELU = decltype(relu_c)::value, RES = decltype(res_c)::value;
+      for (int it = 0; it < n_items; ++it) {
+        const int mtv = tiles_of(mg);
+        if (mtv == 0) { walk(s, nb, mg); continue; }
+        mbar_wait(smem_u32(&ctrl->acc_full[set]), set_phase);
+        tc_fence_after();
+        for (int t = 0; t < mtv; ++t) {
+          const int m0 = (tile0(mg) + t) * BM + q * 32;
+          const uint32_t ebar = smem_u32(&ctrl->acc_empty[set * a.MT + t]);
+          if (m0 >= a.Ms) {   // slab past the sample's last row: only the rings move on
+            if constexpr (RES) {
+              mbar_wait(smem_u32(&ctrl->res_full[rslot]), rphase);
+              if (lane == 0) mbar_arrive(smem_u32(&ctrl->res_empty[rslot]));
+              rslot += 2;
+              if (rslot >= a.res_bufs) { rslot -= a.res_bufs; rphase ^= 1u; }
+            }
+            mbar_arrive(ebar);
+            continue;
+          }
+          const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)((set * a.MT + t) * ACC_COLS + grp * 64);
+          if (nstore >= (uint32_t)a.stage_bufs) {   // the TMA store that last read this staging buffer has drained it
+            if (lane == 0) {
+              if (a.stage_bufs == 4) tma_store_wait_read<3>();
+              else if (a.stage_bufs == 2) tma_store_wait_read<1>();
+              else tma_store_wait_read<0>();
+            }
+            __syncwarp();
+          }
+          const uint32_t buf = my_stage + sbuf * 4096u;
+          const uint32_t rowaddr = buf + (uint32_t)lane * 128u;
+          const uint32_t resaddr = my_res + (uint32_t)rslot * (uint32_t)STAGE_UNIT + (uint32_t)lane * 128u;
+          uint32_t va[32];
+          tmem_ld32(tacc, va);
+          if constexpr (RES) mbar_wait(smem_u32(&ctrl->res_full[rslot]), rphase);
+          tmem_ld_wait();
+          epi_unit<TO, RELU, RES>(va, rowaddr, resaddr, 0, row_sw);
+          tmem_ld32(tacc + 32, va);
+          tmem_ld_wait();
+          tc_fence_before();
+          mbar_arrive(ebar);        // this thread's reads of its half of tile t are complete
+          epi_unit<TO, RELU, RES>(va, rowaddr, resaddr, 4, row_sw);
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_3d(&tm_out, buf, nb * BN + grp * 64, m0, s);
+            tma_store_commit();
+          }
+          ++nstore;
+          if (++sbuf == (uint32_t)a.stage_bufs) sbuf = 0;
+          if constexpr (RES) {
+            if (lane == 0) mbar_arrive(smem_u32(&ctrl->res_empty[rslot]));
+            rslot += 2;
+            if (rslot >= a.res_bufs) { rslot -= a.res_bufs; rphase ^= 1u; }
+          }
+        }
+        if (++set == a.NSETS) { set = 0; set_phase ^= 1u; }
+        walk(s, nb, mg);
+      }
+    };
+    using T8 = std::true_type;
+    using F8 = std::false_type;
+    if (a.res_bufs != 0) { if (a.out_relu) epi8_loop(T8{}, T8{}); else epi8_loop(F8{}, T8{}); }
+    else { if (a.out_relu) epi8_loop(T8{}, F8{}); else epi8_loop(F8{}, F8{}); }
+    if (lane == 0) tma_store_wait_all();
+    }
+  } else if (epi_a) {
     // =========================== EPILOGUE ===========================
     reg_alloc<REGS_EPI>();
     const int q = warp - WARP_EPI0;  // TMEM lane quarter: WARP_EPI0 is a multiple of 4
@@ -1511,10 +1601,10 @@ int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout) {
   return bytes;
 }
 
-template <int BN, typename TO, bool PROF, int CL, bool FLIP, bool TF32 = false>
+template <int BN, typename TO, bool PROF, int CL, bool FLIP, bool TF32 = false, bool EPI8 = false>
 static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const CUtensorMap& ta2,
                           const Tc2Args& a, int grid, int smem_bytes, cudaStream_t stream) {
-  BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, PROF, CL, FLIP, TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  BT_CUDA_OK(cudaFuncSetAttribute(tc2_fwd_kernel<BN, TO, PROF, CL, FLIP, TF32, EPI8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3((unsigned)grid);
@@ -1530,7 +1620,7 @@ static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CU
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = a.pdl ? 2 : 1;
-  BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_fwd_kernel<BN, TO, PROF, CL, FLIP, TF32>, ta, to, tr, ta2, a));
+  BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_fwd_kernel<BN, TO, PROF, CL, FLIP, TF32, EPI8>, ta, to, tr, ta2, a));
   BT_LAUNCH_OK(PROF ? "tc2_fwd_kernel(prof)" : (FLIP ? "tc2_fwd_kernel(flipout)" : (TF32 ? "tc2_fwd_kernel(tf32)" : "tc2_fwd_kernel")));
   return BT_OK;
 }
@@ -1542,6 +1632,11 @@ static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const CUtens
     if (a.tf32)
       return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, false, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream)
                        : tc2_launch_one<BN, TO, false, 1, false, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream);
+  }
+  if constexpr (sizeof(TO) == 2 && BN == 128) {
+    if (a.epi8)
+      return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, false, false, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream)
+                       : tc2_launch_one<BN, TO, false, 1, false, false, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream);
   }
   if (flip)
     return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream)
@@ -1841,7 +1936,8 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   const int NSUBW = flipout ? 2 : 1;
   const int A_SLOT_T = NSUBW * A_SLOT;
   const int avail = AVAIL_BYTES - (flipout ? SHIFT_BYTES : 0);
-  auto ring_bytes = [&](int stage_bufs, int res_bufs) { return avail - (stage_bufs + res_bufs) * STAGE_UNIT; };
+  int SG = 1;   // epilogue groups, each with its own staging buffers (2 with eight epilogue warps)
+  auto ring_bytes = [&](int stage_bufs, int res_bufs) { return avail - (stage_bufs * SG + res_bufs) * STAGE_UNIT; };
   // a [BN x K] panel that fits next to a 4-deep A ring is generated once per (sample, n-block)
   // (single-buffered epilogue staging is accepted for that)
   auto panel_fits = [&](int bn) { return a.nkb <= MAX_RW && (int64_t)a.nkb * NSUBW * bn * BK * 2 + 4 * A_SLOT_T <= ring_bytes(1, res_min); };
@@ -1851,6 +1947,13 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   // (L2 -> shared memory, then shared memory -> tensor core) is the scarcer resource
   // (1024 -> 256 1x1 at 14x14: 0.34 ms stationary/64, 0.23 ms streaming/128).
   if (force_bn == 64 || force_bn == 128) BN = force_bn;
+  // Eight epilogue warps (EPI8 instantiation) where the output stream is the bottleneck: full 128-column tiles,
+  // bf16 outputs and ONE k-block (K <= 64: the 256<-64 expansions of layer1, -3 % on the same box).  Longer
+  // reductions stream W and need all 16 producer warps: 1024<-256 with 12 producers ran 0.95 -> 1.26 ms
+  // (profiles/r2_experiments.txt), so the switch stays where the producers are idle.
+  a.epi8 = (BN == 128 && !flipout && !a.tf32 && g->out_dtype == BT_BF16 && a.spn == 1 && a.N % 128 == 0 && !env_int("BT_TC2_PROF", 0) &&
+            a.nkb <= env_int("BT_TC2_EPI8_NKB", 1) && env_int("BT_TC2_EPI8", 1) != 0) ? 1 : 0;
+  if (a.epi8) SG = 2;
   const int WB = NSUBW * BN * BK * 2;
   a.NB = (a.N * a.spn + BN - 1) / BN;
   a.stationary = panel_fits(BN) ? 1 : 0;
@@ -1879,8 +1982,10 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
       const int64_t items = (int64_t)a.S * a.NB * ((a.num_mt + mt - 1) / mt);
       if (items >= sms || mt == 1 || (mt == 2 && a.num_mt >= 2)) { a.MT = mt; break; }
     }
-    // short reductions: two accumulator sets of two tiles, so the epilogue of one item overlaps the MMAs of the next
-    if (a.nkb <= 8 && a.MT > 2) a.MT = 2;
+    // short reductions WITH a residual input: two accumulator sets of two tiles, so the (long) epilogue of one item
+    // overlaps the MMAs of the next.  Without a residual the epilogue is short and four tiles per sampled k-block win
+    // (512<-256 /2 at 56x56: 1.63 -> 1.40 ms, 1024<-256 at 14x14: 0.84 -> 0.73 ms; profiles/r2_experiments.txt)
+    if (a.nkb <= 8 && a.MT > 2 && (p->residual || env_int("BT_TC2_SHORTK_MT2", 0))) a.MT = 2;
     if (s_inner) a.MT = a.num_mt >= 2 ? 2 : 1;
     if (force_mt >= 1 && force_mt <= MAX_MT && force_mt <= NSLOTS) a.MT = force_mt;
     a.RW = (ring_bytes(2, res_min) - 4 * A_SLOT_T) / WB;
@@ -1920,8 +2025,8 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
       if (left >= 2 * STAGE_UNIT) { a.res_bufs = 4; left -= 2 * STAGE_UNIT; }
       else if (a.stationary && a.NA >= 6) { a.res_bufs = 4; a.NA -= 2; left += 2 * A_SLOT_T - 2 * STAGE_UNIT; }
     }
-    if (a.stage_bufs == 1 && left >= STAGE_UNIT) { a.stage_bufs = 2; left -= STAGE_UNIT; }
-    if (a.stage_bufs == 2 && left >= 2 * STAGE_UNIT) a.stage_bufs = 4;
+    if (a.stage_bufs == 1 && left >= SG * STAGE_UNIT) { a.stage_bufs = 2; left -= SG * STAGE_UNIT; }
+    if (a.stage_bufs == 2 && left >= 2 * SG * STAGE_UNIT) a.stage_bufs = 4;
   }
   if (env_int("BT_TC2_STAGE", 0) == 2 && a.stage_bufs == 4) a.stage_bufs = 2;
   if (env_int("BT_TC2_NA", 0) >= 2 && env_int("BT_TC2_NA", 0) < a.NA) a.NA = env_int("BT_TC2_NA", 0);
@@ -1937,12 +2042,12 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   a.total_items = (int64_t)a.S * a.NB * a.num_mg;
   const int ncl = sms / a.CL;
   const int grid = (int)(a.total_items < ncl ? a.total_items : ncl) * a.CL;
-  const int smem_bytes = 1024 + CTRL_BYTES + (flipout ? SHIFT_BYTES : 0) + (a.stage_bufs + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT_T + a.RW * WB;
+  const int smem_bytes = 1024 + CTRL_BYTES + (flipout ? SHIFT_BYTES : 0) + (a.stage_bufs * SG + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT_T + a.RW * WB;
   BT_REQUIRE(smem_bytes <= SMEM_LIMIT, BT_ERR_UNSUPPORTED, "tensor-core forward: shared memory plan %d exceeds %d", smem_bytes, SMEM_LIMIT);
   if (env_int("BT_TC2_LOG", 0))
-    fprintf(stderr, "tc2: flip=%d mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d order=%d keep=%d spn=%d\n",
+    fprintf(stderr, "tc2: flip=%d mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d order=%d keep=%d spn=%d epi8=%d tf32=%d pdl=%d\n",
             (int)flipout, (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,
-            (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs, a.CL, a.nb_inner, a.a_keep, a.spn);
+            (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs, a.CL, a.nb_inner, a.a_keep, a.spn, a.epi8, a.tf32, a.pdl);
   const bool o32 = g->out_dtype == BT_F32;
   if (BN == 64)
     return o32 ? tc2_launch<64, float>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream)
