@@ -385,6 +385,76 @@ __global__ void __launch_bounds__(256) tc2_patch_kernel(const TX* __restrict__ x
   }
 }
 
+// Table-driven variant for the common case (short reduction, small window: the RGB stem).  The k -> (offset
+// inside the window, tap position) decode is done ONCE per block into shared memory and the row -> (image,
+// od, oh, ow) decode once per 64-row tile, so the inner loop is two shared loads, three compares and one
+// global load per element: the generic kernel above spent most of its time in integer division.
+constexpr int PT_ROWS = 64;     // rows of the patch matrix per tile
+constexpr int PT_MAXK = 2048;   // longest padded reduction the tables hold (16 KB of shared memory)
+
+template <typename TX>
+__global__ void __launch_bounds__(256) tc2_patch_tab_kernel(const TX* __restrict__ x, TX* __restrict__ A, const PatchGeo g) {
+  __shared__ int tab_off[PT_MAXK];        // element offset of k inside the window; INT_MIN for the K padding
+  __shared__ uint32_t tab_pos[PT_MAXK];   // kd*dd << 20 | kh*dh << 10 | kw*dw
+  __shared__ int64_t row_base[PT_ROWS];   // element offset of the window's (possibly out-of-image) origin
+  __shared__ int row_d[PT_ROWS], row_h[PT_ROWS], row_w[PT_ROWS];
+  for (int k = threadIdx.x; k < g.Kp; k += blockDim.x) {
+    if (k < g.K) {
+      const int tap = k / g.Cin, c = k - tap * g.Cin;
+      const int kw = tap % g.KW, t2 = tap / g.KW;
+      const int kh = t2 % g.KH, kd = t2 / g.KH;
+      tab_off[k] = (int)((int64_t)c * g.xcs + (int64_t)kd * g.dd * g.xs0 + (int64_t)kh * g.dh * g.xs1 + (int64_t)kw * g.dw * g.xs2);
+      tab_pos[k] = ((uint32_t)(kd * g.dd) << 20) | ((uint32_t)(kh * g.dh) << 10) | (uint32_t)(kw * g.dw);
+    } else {
+      tab_off[k] = INT_MIN;
+      tab_pos[k] = 0;
+    }
+  }
+  const int C8 = g.Kp >> 3;
+  const int64_t tiles = (g.rows + PT_ROWS - 1) / PT_ROWS;
+  for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+    const int64_t row0 = tile * PT_ROWS;
+    const int nrows = (int)(g.rows - row0 < PT_ROWS ? g.rows - row0 : PT_ROWS);
+    __syncthreads();   // tables written / previous tile's rows consumed
+    if ((int)threadIdx.x < nrows) {
+      int64_t r = row0 + threadIdx.x;
+      const int ow = (int)(r % g.OW); r /= g.OW;
+      const int oh = (int)(r % g.OH); r /= g.OH;
+      const int od = (int)(r % g.OD); r /= g.OD;
+      const int id0 = od * g.sd - g.pd, ih0 = oh * g.sh - g.ph, iw0 = ow * g.sw - g.pw;
+      row_d[threadIdx.x] = id0; row_h[threadIdx.x] = ih0; row_w[threadIdx.x] = iw0;
+      row_base[threadIdx.x] = r * g.xbs + (int64_t)id0 * g.xs0 + (int64_t)ih0 * g.xs1 + (int64_t)iw0 * g.xs2;
+    }
+    __syncthreads();
+    const int chunks = nrows * C8;
+    TX* At = A + row0 * g.Kp;   // the tile's rows are contiguous: chunk j sits at At + 8 j
+    for (int j = threadIdx.x; j < chunks; j += blockDim.x) {
+      const int rl = j / C8;
+      const int k0 = (j - rl * C8) * 8;
+      const TX* xi = x + row_base[rl];
+      const int id0 = row_d[rl], ih0 = row_h[rl], iw0 = row_w[rl];
+      float v[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int off = tab_off[k0 + e];
+        const uint32_t pos = tab_pos[k0 + e];
+        const int id = id0 + (int)(pos >> 20), ih = ih0 + (int)((pos >> 10) & 1023u), iw = iw0 + (int)(pos & 1023u);
+        const bool ok = off != INT_MIN && (unsigned)id < (unsigned)g.ID && (unsigned)ih < (unsigned)g.IH && (unsigned)iw < (unsigned)g.IW;
+        v[e] = ok ? bt_to_float<TX>(xi[off]) : 0.f;
+      }
+      if constexpr (sizeof(TX) == 4) {
+        float4* dst = reinterpret_cast<float4*>(At + (int64_t)j * 8);
+        dst[0] = make_float4(v[0], v[1], v[2], v[3]);
+        dst[1] = make_float4(v[4], v[5], v[6], v[7]);
+      } else {
+        uint4 pk;
+        pk.x = pack_bf16(v[0], v[1]); pk.y = pack_bf16(v[2], v[3]); pk.z = pack_bf16(v[4], v[5]); pk.w = pack_bf16(v[6], v[7]);
+        *reinterpret_cast<uint4*>(At + (int64_t)j * 8) = pk;
+      }
+    }
+  }
+}
+
 // x * s_in as a bf16 tensor with x's strides (patch-matrix Flipout: the RGB stem, odd C_in): one thread per
 // word of the SIGN_IN stream, i.e. 32 consecutive elements of the sample in channels-last order.
 struct FlipGeo {
@@ -1689,6 +1759,19 @@ static int build_patch_matrices(const bt_geom* g, const Plan& pl, const bt_layer
   // (stacked samples of x are just more images: the batch stride walks across them)
   auto build_patches = [&](const __nv_bfloat16* src, __nv_bfloat16* dst) -> int {
     const bool small = chunks + cap * 256 < 0x7fffffffll;
+    // table-driven kernel: the reduction fits its tables, tap positions fit 10 bits, the window fits 31-bit offsets
+    const int64_t win = (g->c_in - 1) * pg.xcs + (k[0] - 1) * dl[0] * pg.xs0 + (k[1] - 1) * dl[1] * pg.xs1 + (k[2] - 1) * dl[2] * pg.xs2;
+    static const bool tab_on = !(getenv("BT_PATCH_TAB") && atoi(getenv("BT_PATCH_TAB")) == 0);
+    const bool tab = tab_on && pg.Kp <= PT_MAXK && pg.Kp >= 8 && win >= 0 && win < (1ll << 30) && pg.xcs >= 0 && pg.xs0 >= 0 && pg.xs1 >= 0 &&
+                     pg.xs2 >= 0 && k[0] * dl[0] < 1024 && k[1] * dl[1] < 1024 && k[2] * dl[2] < 1024;
+    if (tab) {
+      int64_t tb = (pg.rows + PT_ROWS - 1) / PT_ROWS;
+      if (tb > (int64_t)bt_num_sms() * 8) tb = (int64_t)bt_num_sms() * 8;
+      if (g->x_dtype == BT_F32) tc2_patch_tab_kernel<float><<<(int)tb, 256, 0, stream>>>((const float*)src, (float*)dst, pg);
+      else tc2_patch_tab_kernel<__nv_bfloat16><<<(int)tb, 256, 0, stream>>>(src, dst, pg);
+      BT_LAUNCH_OK("tc2_patch_tab_kernel");
+      return BT_OK;
+    }
     if (g->x_dtype == BT_F32) {   // (pointers are typed bf16 for the Flipout bookkeeping below; fp32 never takes that branch)
       if (small) tc2_patch_kernel<float, uint32_t><<<(int)blocks, 256, 0, stream>>>((const float*)src, (float*)dst, pg);
       else tc2_patch_kernel<float, int64_t><<<(int)blocks, 256, 0, stream>>>((const float*)src, (float*)dst, pg);

@@ -9,7 +9,7 @@ cap() {  # name kernel-regex skip
 }
 cap kl kl_normal_multi_kernel 2 kl
 cap stem tc2_fwd_kernel 2 fwd
-cap stem tc2_patch_kernel 2 patch
+cap stem tc2_patch 2 patch
 cap maxpool maxpool2d_nhwc 2 pool
 cap flipout tc2_fwd_kernel 2 flip
 cap tf32 tc2_fwd_kernel 2 tf32
