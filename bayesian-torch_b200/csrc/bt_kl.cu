@@ -274,3 +274,53 @@ int bt_kl_layer(const bt_layer_params* p, int64_t w_numel, int64_t b_numel, floa
   return kl_launch(n, mu, rho, numel, 0, p->prior_mu, p->prior_sigma, pm, ps, nullptr, kl_out, nullptr, nullptr,
                    nullptr, workspace, stream);
 }
+
+// ---------------------------------------------------------------- allocation-free KL ----
+// bt_kl_normal_multi_static: bt_kl_normal_multi for callers that cannot allocate (CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  The fp64 accumulators + done counter the kernel needs live
+// in a file-scope device array instead of a caller workspace; every GPU that loads the library holds these
+// KL_STATIC_BYTES bytes until the process exits.  All calls on one device SHARE the array: it is cleared on the
+// caller's stream before every launch (it still holds the previous call's sums), and two calls that overlap on
+// one GPU (different streams) race on it.
+#define KL_STATIC_MAX_TENSORS 192
+#define KL_STATIC_BYTES (((KL_STATIC_MAX_TENSORS * 8 + 8 + 255) / 256) * 256) /* 1792 bytes */
+#define KL_STATIC_MAX_DEVICES 64
+static_assert(KL_STATIC_MAX_TENSORS <= KL_MAX_TENSORS, "the static variant cannot exceed the kernel's table");
+
+static __device__ __align__(256) unsigned char g_kl_static_scratch[KL_STATIC_BYTES];
+
+// The array's name is only a host-side stand-in in host code: its device address is looked up once per device,
+// with that device current, and cached.
+static int kl_static_scratch_ptr(void** out) {
+  static void* cached[KL_STATIC_MAX_DEVICES] = {nullptr};
+  int dev = -1;
+  BT_CUDA_OK(cudaGetDevice(&dev));
+  BT_REQUIRE(dev >= 0 && dev < KL_STATIC_MAX_DEVICES, BT_ERR_UNSUPPORTED, "bt_kl_normal_multi_static: device %d outside [0,%d)", dev,
+             KL_STATIC_MAX_DEVICES);
+  void* ptr = __atomic_load_n(&cached[dev], __ATOMIC_ACQUIRE);
+  if (ptr == nullptr) {
+    BT_CUDA_OK(cudaGetSymbolAddress(&ptr, g_kl_static_scratch));
+    BT_REQUIRE(ptr != nullptr, BT_ERR_CUDA, "bt_kl_normal_multi_static: cudaGetSymbolAddress returned a null address");
+    __atomic_store_n(&cached[dev], ptr, __ATOMIC_RELEASE);   // every thread looks up the same address: a benign race
+  }
+  *out = ptr;
+  return BT_OK;
+}
+
+extern "C" int bt_kl_normal_multi_static(int n, const float* const* mu, const float* const* rho, const int64_t* numel,
+                                         int q_is_sigma, float prior_mu, float prior_sigma,
+                                         const float* const* prior_mu_t, const float* const* prior_sigma_t, float* kl_each,
+                                         float* kl_total, float* const* d_mu, float* const* d_rho, const float* grad_scale,
+                                         bt_stream_t stream) {
+  BT_REQUIRE(n >= 1 && n <= KL_STATIC_MAX_TENSORS, BT_ERR_INVALID,
+             "bt_kl_normal_multi_static: n=%d outside [1,%d] (the built-in scratch array holds %d accumulators; "
+             "use bt_kl_normal_multi with a caller workspace beyond that)", n, KL_STATIC_MAX_TENSORS, KL_STATIC_MAX_TENSORS);
+  BT_REQUIRE(kl_workspace_bytes(n) <= (int64_t)KL_STATIC_BYTES, BT_ERR_INVALID,
+             "bt_kl_normal_multi_static: %lld scratch bytes needed, %d built in", (long long)kl_workspace_bytes(n), (int)KL_STATIC_BYTES);
+  void* scratch = nullptr;
+  const int rc = kl_static_scratch_ptr(&scratch);
+  if (rc != BT_OK) return rc;
+  // kl_launch clears the n accumulators + counter with a memset on `stream`, then launches: no allocation anywhere
+  return kl_launch(n, mu, rho, numel, q_is_sigma, prior_mu, prior_sigma, prior_mu_t, prior_sigma_t, kl_each, kl_total,
+                   d_mu, d_rho, grad_scale, scratch, (cudaStream_t)stream);
+}

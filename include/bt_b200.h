@@ -173,6 +173,24 @@ int bt_kl_normal_multi(int n, const float* const* mu, const float* const* rho, c
                        float* kl_each, float* kl_total, float* const* d_mu, float* const* d_rho,
                        const float* grad_scale, void* workspace, bt_stream_t stream);
 
+/* ---- bt_kl_normal_multi without a caller workspace and without any allocation.
+ *      NO COUNTERPART IN THE REFERENCE: added for callers
+ *      that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ *      that forbid it).  The fp64 accumulators + done counter live in a file-scope device array
+ *      (bt_kl.cu) that every GPU loading the library holds until exit: 1792 bytes, hence
+ *      n <= BT_KL_STATIC_MAX_TENSORS; larger n is refused with BT_ERR_INVALID (use
+ *      bt_kl_normal_multi).  The entry point calls no cudaMalloc / cudaFree / allocating library
+ *      routine: one memset on `stream` that clears the array (it keeps the last call's sums),
+ *      then the launch.  Every call on a device shares the array: calls that may overlap on one
+ *      GPU (different streams without an ordering between them) race on it -- serialise them.
+ *      Other arguments and results exactly as bt_kl_normal_multi. */
+#define BT_KL_STATIC_MAX_TENSORS 192
+int bt_kl_normal_multi_static(int n, const float* const* mu, const float* const* rho, const int64_t* numel,
+                              int q_is_sigma, float prior_mu, float prior_sigma,
+                              const float* const* prior_mu_t, const float* const* prior_sigma_t,
+                              float* kl_each, float* kl_total, float* const* d_mu, float* const* d_rho,
+                              const float* grad_scale, bt_stream_t stream);
+
 /* ---- KL(N(mu, sigma) || Laplace(0, 1)): replaces the 'laplace' branch the fork added to
  *      BaseVariationalLayer_.kl_div (base_variational_layer.py:74-97; location 0 and scale 1
  *      are hard-coded there, whatever mu_p / sigma_p the caller passes), analytic form
