@@ -99,6 +99,9 @@ struct Tc2Args {
                      // its set-up, 2 = the W producers do not (their inputs -- packed parameters of a frozen layer, biases,
                      // BatchNorm terms -- were complete long before) and sample the first k-blocks during the previous kernel's tail
   int epi8;          // eight epilogue warps (EPI8 instantiation): staging holds 2 * stage_bufs buffers per lane quarter
+  int w_pre;         // the sampled weights were materialised by tc2_presample_kernel ([S][N][K] bf16 behind tm_a2): one thread of
+                     // the producer group streams the W k-blocks in by TMA instead of the 16 warps sampling them per item
+  int rr, rr_dnb, rr_dmg, rr_ds;  // round-robin item assignment (order 1) and the (nb, mg, s) digits of the cluster count
   int tf32;          // fp32 activations: fp32 A tiles, tf32 MMAs (k-blocks of 32 elements), fp32 packed parameters
   int debug;         // BT_TC2_DEBUG bits, honoured by the BT_TC2_PROF=1 instantiation only: 1 skip output stores, 4 skip MMAs,
                      // 8 skip A loads, 16 skip the normal draws, 32 skip the parameter loads
@@ -455,6 +458,33 @@ __global__ void __launch_bounds__(256) tc2_patch_tab_kernel(const TX* __restrict
   }
 }
 
+// ---------------------------------------------------------------- pre-sampled weights ----
+// W[s][n][k] = bf16(sigma * eps(s) + mu) for every sample of a call, written once, in the arithmetic and at the
+// Philox positions of the in-kernel sampling loop (bit-identical weights).  For the layers whose W k-blocks are
+// STREAMED the fused kernel re-samples a [BN x K] panel for every (sample, n-block, m-group) item -- 25 times per
+// weight on the 3x3 layers at 14x14 -- and its 16 producer warps, not the tensor core, set the pace (65 % of all
+// issue slots, tensor pipe 46 %; profiles/r2_conv3x3_fwd_ncu_metrics.txt).  Materialising S x |W| x 2 bytes costs
+// ~3 GB of traffic per ResNet-50 step (0.5 ms) and turns those layers into plain TMA-fed GEMMs.
+// One thread per 16-byte chunk (eight weights = one Philox block); blockIdx.y = sample.
+__global__ void __launch_bounds__(256) tc2_presample_kernel(const uint4* __restrict__ mu_p, const uint4* __restrict__ sig_p,
+                                                            uint4* __restrict__ wq, int64_t chunks, uint64_t seed, uint32_t sample_id,
+                                                            uint32_t layer_id) {
+  const int s = blockIdx.y;
+  const BtRngKey rk = bt_rng_key(seed, sample_id + (uint32_t)s, layer_id, BT_KIND_EPS_W);
+  uint4* __restrict__ dst = wq + (int64_t)s * chunks;
+  for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < chunks; c += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 mu = __ldg(mu_p + c), sg = __ldg(sig_p + c);
+    float z[8];
+    bt_normal8((uint64_t)c, rk, z);
+    uint4 w;
+    w.x = fma_bf16x2(sg.x, pack_bf16(z[0], z[1]), mu.x);
+    w.y = fma_bf16x2(sg.y, pack_bf16(z[2], z[3]), mu.y);
+    w.z = fma_bf16x2(sg.z, pack_bf16(z[4], z[5]), mu.z);
+    w.w = fma_bf16x2(sg.w, pack_bf16(z[6], z[7]), mu.w);
+    dst[c] = w;
+  }
+}
+
 // x * s_in as a bf16 tensor with x's strides (patch-matrix Flipout: the RGB stem, odd C_in): one thread per
 // word of the SIGN_IN stream, i.e. 32 consecutive elements of the sample in channels-last order.
 struct FlipGeo {
@@ -609,7 +639,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       mbar_init(smem_u32(&ctrl->a_full[i]), 1); mbar_init(smem_u32(&ctrl->a_empty[i]), 1);
       mbar_init(smem_u32(&ctrl->af_full[i]), N_FLIP_WARPS);
     }
-    for (int i = 0; i < a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), NPW); mbar_init(smem_u32(&ctrl->w_empty[i]), N_MMA_WARPS * CL); }
+    for (int i = 0; i < a.RW; ++i) { mbar_init(smem_u32(&ctrl->w_full[i]), a.w_pre ? 1 : NPW); mbar_init(smem_u32(&ctrl->w_empty[i]), N_MMA_WARPS * CL); }
     mbar_init(smem_u32(&ctrl->w_full[a.RW]), NPW);  // the shift tile stays CTA-local
     mbar_init(smem_u32(&ctrl->w_empty[a.RW]), N_MMA_WARPS);
     for (int i = 0; i < a.NSETS; ++i) mbar_init(smem_u32(&ctrl->acc_full[i]), N_MMA_WARPS);
@@ -622,7 +652,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   if (warp == WARP_TMA && lane == 0) {
     prefetch_tmap(&tm_a); prefetch_tmap(&tm_out);
     if (a.res_bufs) prefetch_tmap(&tm_res);
-    if (FLIP && a.a2_tma) prefetch_tmap(&tm_a2);
+    if ((FLIP && a.a2_tma) || a.w_pre) prefetch_tmap(&tm_a2);
   }
   if (warp == WARP_MMA) tmem_alloc(smem_u32(&ctrl->tmem_base), 512);
   tc_fence_before();
@@ -642,9 +672,14 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   const int vN = a.N * a.spn;  // width of the (virtual) N axis the tiles are cut from
   const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
   const int cid = blockIdx.x / CL, ncl = gridDim.x / CL;
-  const int64_t i0 = a.total_items * cid / ncl;
+  // Items are dealt to the clusters in contiguous ranges, or (a.rr, order 1 only) round-robin: cluster c takes items
+  // c, c + ncl, ...  With the n-block fastest, the NB passes over one group of A tiles then run on NEIGHBOURING
+  // clusters at the same time and all but one are served by the L2, whatever the length of the reduction.  A
+  // contiguous range runs them one after the other on one SM, and the 148 A streams in flight between two passes
+  // (MT x 128 rows x K each: 150-300 MB at K = 1024-2048) evict the tiles before they are read again.
+  const int64_t i0 = a.rr ? (int64_t)cid : a.total_items * cid / ncl;
   const int64_t i1 = a.total_items * (cid + 1) / ncl;
-  const int n_items = (int)(i1 - i0);
+  const int n_items = a.rr ? (int)((a.total_items - cid + ncl - 1) / ncl) : (int)(i1 - i0);
   // first m-tile of this CTA's m-group within cluster step mg (may lie past num_mt for the odd
   // tail of a pair: such an item has no tiles, but its W k-blocks are still produced and consumed)
   auto tile0 = [&](int mg) { return (mg * CL + crank) * a.MT; };
@@ -677,6 +712,16 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
   auto walk = [&](int& ws, int& wnb, int& wmg) -> bool {
     if (a.nb_inner == 2) {
       if (++ws == a.S) { ws = 0; if (++wnb == a.NB) { wnb = 0; ++wmg; } }
+      return false;
+    }
+    if (a.rr) {  // + ncl items in the (s, mg, nb) mixed radix; the digits of ncl come from the host
+      wnb += a.rr_dnb;
+      int c = 0;
+      if (wnb >= a.NB) { wnb -= a.NB; c = 1; }
+      wmg += a.rr_dmg + c;
+      c = 0;
+      if (wmg >= a.num_mg) { wmg -= a.num_mg; c = 1; }
+      ws += a.rr_ds + c;
       return false;
     }
     if (a.nb_inner) {
@@ -1317,6 +1362,22 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           if (lane == 0) mbar_arrive(smem_u32(&ctrl->w_full[a.RW]));
           sphase ^= 1u;
         }
+        if (a.w_pre) {
+          // pre-sampled weights (tc2_presample_kernel): the k-blocks of W[s][nb * BN .. + BN) arrive by TMA with the
+          // 128-byte swizzle the sampling loop below writes; rows past N and columns past K are zero-filled by the map
+          if (p == 0) {
+            for (int kb = 0; kb < a.nkb; ++kb) {
+              PW(0, mbar_wait(smem_u32(&ctrl->w_empty[wslot_r]), wphase ^ 1u));
+              const uint32_t bar = smem_u32(&ctrl->w_full[wslot_r]);
+              mbar_expect_tx(bar, (uint32_t)W_SUB);
+              tma_load_3d(w_base + (uint32_t)(wslot_r * W_SLOT), &tm_a2, bar, kb * BKE, nb * BN, s);
+              if (++wslot_r == a.RW) { wslot_r = 0; wphase ^= 1u; }
+            }
+          }
+          first = false;
+          walk(s, nb, mg);
+          continue;
+        }
         const BtRngKey rk0 = bt_rng_key(a.seed, a.sample_id + (uint32_t)(s * a.spn), a.layer_id, BT_KIND_EPS_W);
         // packed bf16 (mu, sigma) of this thread's chunk of k-block kb2, eight weights per row
         uint4 nmu8[ROWS_PER_THREAD], nsg8[ROWS_PER_THREAD];
@@ -1654,6 +1715,14 @@ static int64_t patch_bytes(const bt_geom* g, int64_t rows_per_s, int64_t Kp) {
   const bool x_shared = g->n_samples > 1 && g->x_sample_stride == 0;
   return ((rows_per_s * (x_shared ? 1 : g->n_samples) * Kp * (g->x_dtype == BT_F32 ? 4 : 2) + 255) / 256) * 256;
 }
+// Pre-sampled weights ([S][N][K] bf16 behind the packed area): geometry-only eligibility, a superset of what the
+// launch finally chooses (it also needs a streamed W, Philox-drawn eps, a forward run), so that the size the
+// caller allocates always covers the launch's carve-up.
+static int64_t wpre_bytes(const bt_geom* g, const Plan& pl, bool flipout) {
+  if (flipout || g->x_dtype != BT_BF16 || pl.mode == A_PATCH || pl.es != 2 || (pl.K & 7)) return 0;
+  const int64_t b = (int64_t)g->n_samples * g->c_out * pl.K * 2;
+  return b <= (1ll << 31) ? ((b + 255) / 256) * 256 : 0;
+}
 int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout) {
   int64_t taps = 1;
   for (int i = 0; i < g->rank; ++i) taps *= g->k_size[i];
@@ -1663,10 +1732,13 @@ int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout) {
   memset(&none, 0, sizeof(none));
   Plan pl;
   const char* why = "";
-  if (tc2_plan(g, &none, flipout, &pl, &why) && pl.mode == A_PATCH) {
-    const int64_t pm = patch_bytes(g, pl.rows_per_s, pl.Kp);
-    bytes += pm;
-    if (flipout) bytes += pm + ((x_span_elems(g) * 2 + 255) / 256) * 256;
+  if (tc2_plan(g, &none, flipout, &pl, &why)) {
+    if (pl.mode == A_PATCH) {
+      const int64_t pm = patch_bytes(g, pl.rows_per_s, pl.Kp);
+      bytes += pm;
+      if (flipout) bytes += pm + ((x_span_elems(g) * 2 + 255) / 256) * 256;
+    }
+    bytes += wpre_bytes(g, pl, flipout);
   }
   return bytes;
 }
@@ -1866,12 +1938,15 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   float* eps_p = (p->eps_w || opt.dgrad) ? (a.tf32 ? (float*)workspace + 2 * wn : (float*)(sig_p + wn)) : nullptr;
   __nv_bfloat16* patches = (__nv_bfloat16*)((char*)workspace + ((3 * wn * 4 + 255) / 256) * 256);
   bool kl_done = false;
+  bool wq_fits = opt.ws_bytes == 0;   // unchecked workspace: sized by bt_workspace_bytes, which counts them
   if (opt.ws_bytes > 0) {  // the carve-up below must fit what the caller allocated (bt_workspace_bytes)
     int64_t need = ((3 * wn * 4 + 255) / 256) * 256;
     if (pl.mode == A_PATCH) {
       const int64_t pm = patch_bytes(g, pl.rows_per_s, pl.Kp);
       need += pm + (flipout ? pm + ((x_span_elems(g) * 2 + 255) / 256) * 256 : 0);
     }
+    // room for the pre-sampled weights is optional: a caller that sized its workspace without them gets the fused sampling
+    wq_fits = need + wpre_bytes(g, pl, flipout) <= opt.ws_bytes;
     BT_REQUIRE(need <= opt.ws_bytes, BT_ERR_INVALID, "tensor-core %s: workspace of %lld bytes, %lld needed (bt_workspace_bytes)",
                opt.dgrad ? "dgrad" : "forward", (long long)opt.ws_bytes, (long long)need);
   }
@@ -2055,6 +2130,22 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   const bool s_inner = x_shared && !flipout && a.nkb <= MAX_NA / 2 && env_int("BT_TC2_SINNER", 0) != 0;
   if (s_inner) a.stationary = 0;
   const int NSLOTS = 512 / (NSUBW * BN);
+  // Streamed W on a layer with many m-tiles per sample: the fused kernel would re-sample every [BN x K] panel once per
+  // m-group (x25 on the 3x3 layers at 14x14) and its producers, not the tensor core, set the pace.  Sample once into the
+  // workspace instead (tc2_presample_kernel) and stream the k-blocks in by TMA; no CTA pairs then (no sampling left to
+  // share).  Measured at 32 samples x 128 images, fused -> pre-sampled (profiles/r2_experiments.txt 7): 3x3 128 @28
+  // 1.11 -> 0.93 ms, 3x3 256 @14 1.03 -> 0.90, 256<-1024 @14 0.69 -> 0.65, 512<-256 /2 1.42 -> 1.25; at 7x7 (49 m-tiles per
+  // sample) the W stream costs more than the sampling it replaces (512<-2048: 0.69 -> 0.80), hence the m-tile floor.
+  {
+    const int64_t wq = wpre_bytes(g, pl, flipout);
+    const bool wpre_ok = wq > 0 && wq_fits && !s_inner && !opt.dgrad && !p->eps_w && a.spn == 1 && a.Kt == a.K && !a.tf32 && !a.epi8 &&
+                         a.num_mt >= env_int("BT_TC2_WPRE_MIN", 128) && env_int("BT_TC2_WPRE", 1) != 0;
+    // a stationary panel walks (sample, n-block, m-group): with two or more n-blocks every A tile comes from HBM once per
+    // n-block.  Streaming pre-sampled W with the n-block innermost reads it once (256<-512 at 28x28: 3.3 GB of A).
+    if (wpre_ok && a.stationary && a.NB >= 2 && a.nkb >= 2 && force_stat != 1) a.stationary = 0;
+    a.w_pre = (wpre_ok && !a.stationary) ? 1 : 0;
+    if (a.w_pre && a.pdl == 2) a.pdl = 1;   // the W loader reads what the kernel just before this one wrote
+  }
   if (a.stationary) {
     a.RW = a.nkb;
     a.MT = a.num_mt >= 2 ? 2 : 1;  // one tile per issuer warp
@@ -2069,6 +2160,9 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
     // overlaps the MMAs of the next.  Without a residual the epilogue is short and four tiles per sampled k-block win
     // (512<-256 /2 at 56x56: 1.63 -> 1.40 ms, 1024<-256 at 14x14: 0.84 -> 0.73 ms; profiles/r2_experiments.txt)
     if (a.nkb <= 8 && a.MT > 2 && (p->residual || env_int("BT_TC2_SHORTK_MT2", 0))) a.MT = 2;
+    // pre-sampled W, 1x1 layers: nothing is saved by sharing a k-block between four tiles, and two sets of two overlap
+    // the epilogue with the next item's MMAs (256<-1024 @14: 0.74 ms with four, 0.65 with two; the 3x3 layers prefer four)
+    if (a.w_pre && pl.T == 1 && a.MT > 2) a.MT = 2;
     if (s_inner) a.MT = a.num_mt >= 2 ? 2 : 1;
     if (force_mt >= 1 && force_mt <= MAX_MT && force_mt <= NSLOTS) a.MT = force_mt;
     a.RW = (ring_bytes(2, res_min) - 4 * A_SLOT_T) / WB;
@@ -2082,9 +2176,9 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   // Streaming layers are bound by the W producers (~30 issue slots and 2 MUFU per sampled weight):
   // a CTA pair walks the same k-block sequence on neighbouring m-groups and each CTA samples half
   // of every k-block, storing it into both rings over DSMEM.
-  a.CL = (!a.stationary && a.num_mg >= 2 && sms % 2 == 0) ? 2 : 1;
+  a.CL = (!a.stationary && !a.w_pre && a.num_mg >= 2 && sms % 2 == 0) ? 2 : 1;
   if (env_int("BT_TC2_CL", 0) == 1) a.CL = 1;
-  if (env_int("BT_TC2_CL", 0) == 2 && a.num_mg >= 2 && sms % 2 == 0) a.CL = 2;
+  if (env_int("BT_TC2_CL", 0) == 2 && a.num_mg >= 2 && sms % 2 == 0 && !a.w_pre) a.CL = 2;
   a.num_mg = (a.num_mg + a.CL - 1) / a.CL;
   a.nb_inner = (!a.stationary && a.NB > 1) ? 1 : 0;
   if (env_int("BT_TC2_NBINNER", -1) == 0) a.nb_inner = 0;
@@ -2125,11 +2219,35 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   a.total_items = (int64_t)a.S * a.NB * a.num_mg;
   const int ncl = sms / a.CL;
   const int grid = (int)(a.total_items < ncl ? a.total_items : ncl) * a.CL;
+  if (a.nb_inner == 1 && grid == ncl * a.CL && env_int("BT_TC2_RR", 1) != 0) {
+    a.rr = 1;
+    a.rr_dnb = ncl % a.NB;
+    a.rr_dmg = (ncl / a.NB) % a.num_mg;
+    a.rr_ds = (ncl / a.NB) / a.num_mg;
+  }
   const int smem_bytes = 1024 + CTRL_BYTES + (flipout ? SHIFT_BYTES : 0) + (a.stage_bufs * SG + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT_T + a.RW * WB;
   BT_REQUIRE(smem_bytes <= SMEM_LIMIT, BT_ERR_UNSUPPORTED, "tensor-core forward: shared memory plan %d exceeds %d", smem_bytes, SMEM_LIMIT);
+  if (a.w_pre) {
+    // behind the packed area (w_pre excludes the patch-matrix mode, whose matrices would sit there)
+    uint4* wq = reinterpret_cast<uint4*>(patches);
+    const int64_t chunks = wn / 8;
+    int64_t bx = (chunks + 255) / 256;
+    const int64_t capx = ((int64_t)sms * 8 + S - 1) / S;
+    if (bx > capx) bx = capx < 1 ? 1 : capx;
+    tc2_presample_kernel<<<dim3((unsigned)bx, (unsigned)S), 256, 0, stream>>>(reinterpret_cast<const uint4*>(mu_p), reinterpret_cast<const uint4*>(sig_p),
+                                                                          wq, chunks, p->seed, p->sample_id, p->layer_id);
+    BT_LAUNCH_OK("tc2_presample_kernel");
+    const cuuint64_t gdim[3] = {(cuuint64_t)a.K, (cuuint64_t)a.N, (cuuint64_t)S};
+    const cuuint64_t gstr[2] = {(cuuint64_t)a.K * 2, (cuuint64_t)a.N * a.K * 2};
+    const cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)BN, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = drv.tiled(&tm_a2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, wq, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                 CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    BT_REQUIRE(r == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeTiled(pre-sampled W) failed with %d", (int)r);
+  }
   if (env_int("BT_TC2_LOG", 0))
-    fprintf(stderr, "tc2: flip=%d mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d order=%d keep=%d spn=%d epi8=%d tf32=%d pdl=%d\n",
-            (int)flipout, (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,
+    fprintf(stderr, "tc2: wpre=%d flip=%d mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d order=%d keep=%d spn=%d epi8=%d tf32=%d pdl=%d\n",
+            a.w_pre, (int)flipout, (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,
             (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs, a.CL, a.nb_inner, a.a_keep, a.spn, a.epi8, a.tf32, a.pdl);
   const bool o32 = g->out_dtype == BT_F32;
   if (BN == 64)

@@ -1,0 +1,7 @@
+#!/bin/bash
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/t_gpu.log 2>&1; echo "gpu suite rc=$?"; tail -3 gpurun_out/t_gpu.log
+bash tools/${1:-exp5}.sh > gpurun_out/${1:-exp5}.txt 2>&1; cat gpurun_out/${1:-exp5}.txt
+python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-eager --no-extras > gpurun_out/bench_new.json 2> gpurun_out/bench_new.err; echo "bench rc=$?"; cut -c1-200 gpurun_out/bench_new.json
+python tools/layer_table.py 32 > gpurun_out/layer_table_mc32.txt 2>&1; tail -32 gpurun_out/layer_table_mc32.txt
