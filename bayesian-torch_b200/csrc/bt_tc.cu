@@ -2109,8 +2109,9 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   // bf16 outputs and ONE k-block (K <= 64: the 256<-64 expansions of layer1, -3 % on the same box).  Longer
   // reductions stream W and need all 16 producer warps: 1024<-256 with 12 producers ran 0.95 -> 1.26 ms
   // (profiles/r2_experiments.txt), so the switch stays where the producers are idle.
-  a.epi8 = (BN == 128 && !flipout && !a.tf32 && g->out_dtype == BT_BF16 && a.spn == 1 && a.N % 128 == 0 && !env_int("BT_TC2_PROF", 0) &&
-            a.nkb <= env_int("BT_TC2_EPI8_NKB", 1) && env_int("BT_TC2_EPI8", 1) != 0) ? 1 : 0;
+  const bool epi8_ok = BN == 128 && !flipout && !a.tf32 && g->out_dtype == BT_BF16 && a.spn == 1 && a.N % 128 == 0 && !env_int("BT_TC2_PROF", 0) &&
+                       env_int("BT_TC2_EPI8", 1) != 0;
+  a.epi8 = (epi8_ok && a.nkb <= env_int("BT_TC2_EPI8_NKB", 1)) ? 1 : 0;
   if (a.epi8) SG = 2;
   const int WB = NSUBW * BN * BK * 2;
   a.NB = (a.N * a.spn + BN - 1) / BN;
@@ -2139,11 +2140,16 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   {
     const int64_t wq = wpre_bytes(g, pl, flipout);
     const bool wpre_ok = wq > 0 && wq_fits && !s_inner && !opt.dgrad && !p->eps_w && a.spn == 1 && a.Kt == a.K && !a.tf32 && !a.epi8 &&
-                         a.num_mt >= env_int("BT_TC2_WPRE_MIN", 128) && env_int("BT_TC2_WPRE", 1) != 0;
+                         a.num_mt >= env_int("BT_TC2_WPRE_MIN", 16) && env_int("BT_TC2_WPRE", 1) != 0;
     // a stationary panel walks (sample, n-block, m-group): with two or more n-blocks every A tile comes from HBM once per
     // n-block.  Streaming pre-sampled W with the n-block innermost reads it once (256<-512 at 28x28: 3.3 GB of A).
     if (wpre_ok && a.stationary && a.NB >= 2 && a.nkb >= 2 && force_stat != 1) a.stationary = 0;
     a.w_pre = (wpre_ok && !a.stationary) ? 1 : 0;
+    // with the weights pre-sampled the producer warps idle: four of them become the second epilogue group on the layers
+    // whose output (+ residual) stream sets the pace (short reductions into wide outputs)
+    // (measured: NOT a win -- 512<-128 0.89 -> 0.95 ms, 1024<-256 0.62 -> 0.67, 256<-512 1.05 -> 1.31; with a residual within
+    // +-5 %; profiles/r2_exp6_epi8_presampled.txt -- the epilogue of these layers is not short of warps.  Off by default.)
+    if (a.w_pre && epi8_ok && a.nkb <= env_int("BT_TC2_EPI8_WPRE_NKB", 0)) { a.epi8 = 1; SG = 2; }
     if (a.w_pre && a.pdl == 2) a.pdl = 1;   // the W loader reads what the kernel just before this one wrote
   }
   if (a.stationary) {
@@ -2161,8 +2167,8 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
     // (512<-256 /2 at 56x56: 1.63 -> 1.40 ms, 1024<-256 at 14x14: 0.84 -> 0.73 ms; profiles/r2_experiments.txt)
     if (a.nkb <= 8 && a.MT > 2 && (p->residual || env_int("BT_TC2_SHORTK_MT2", 0))) a.MT = 2;
     // pre-sampled W, 1x1 layers: nothing is saved by sharing a k-block between four tiles, and two sets of two overlap
-    // the epilogue with the next item's MMAs (256<-1024 @14: 0.74 ms with four, 0.65 with two; the 3x3 layers prefer four)
-    if (a.w_pre && pl.T == 1 && a.MT > 2) a.MT = 2;
+    // the epilogue with the next item's MMAs (256<-1024 @14: 0.74 ms with four, 0.65 with two; the 3x3 layers and the wide 1x1 layers prefer four)
+    if (a.w_pre && pl.T == 1 && a.MT > 2 && a.NB <= 2) a.MT = 2;
     if (s_inner) a.MT = a.num_mt >= 2 ? 2 : 1;
     if (force_mt >= 1 && force_mt <= MAX_MT && force_mt <= NSLOTS) a.MT = force_mt;
     a.RW = (ring_bytes(2, res_min) - 4 * A_SLOT_T) / WB;
