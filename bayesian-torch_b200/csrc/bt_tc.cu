@@ -104,7 +104,8 @@ struct Tc2Args {
   int rr, rr_dnb, rr_dmg, rr_ds;  // round-robin item assignment (order 1) and the (nb, mg, s) digits of the cluster count
   int tf32;          // fp32 activations: fp32 A tiles, tf32 MMAs (k-blocks of 32 elements), fp32 packed parameters
   int debug;         // BT_TC2_DEBUG bits, honoured by the BT_TC2_PROF=1 instantiation only: 1 skip output stores, 4 skip MMAs,
-                     // 8 skip A loads, 16 skip the normal draws, 32 skip the parameter loads
+                     // 8 skip A loads, 16 skip the normal draws, 32 skip the parameter loads, 64 skip the residual loads, 128 skip the
+                     // loads of pre-sampled W
   uint64_t seed;
   uint32_t sample_id, layer_id;
   // Flipout (FLIP instantiation): tensor-fed signs (deterministic mode; fp32 +-1 laid out like x / out) or null
@@ -1176,8 +1177,12 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           mbar_wait(smem_u32(&ctrl->res_empty[slot]), phase ^ 1u);
           if (leader) {
             const uint32_t bar = smem_u32(&ctrl->res_full[slot]);
-            mbar_expect_tx(bar, (uint32_t)STAGE_UNIT);
-            tma_load_3d(res_base + (uint32_t)slot * (uint32_t)STAGE_UNIT, &tm_res, bar, nb * BN + sub * SUBN, (tile0(mg) + t) * BM, s);
+            if (PROF && (a.debug & 64)) {
+              mbar_arrive(bar);
+            } else {
+              mbar_expect_tx(bar, (uint32_t)STAGE_UNIT);
+              tma_load_3d(res_base + (uint32_t)slot * (uint32_t)STAGE_UNIT, &tm_res, bar, nb * BN + sub * SUBN, (tile0(mg) + t) * BM, s);
+            }
           }
           if (++slot == a.res_bufs) { slot = 0; phase ^= 1u; }
         }
@@ -1369,8 +1374,12 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             for (int kb = 0; kb < a.nkb; ++kb) {
               PW(0, mbar_wait(smem_u32(&ctrl->w_empty[wslot_r]), wphase ^ 1u));
               const uint32_t bar = smem_u32(&ctrl->w_full[wslot_r]);
-              mbar_expect_tx(bar, (uint32_t)W_SUB);
-              tma_load_3d(w_base + (uint32_t)(wslot_r * W_SLOT), &tm_a2, bar, kb * BKE, nb * BN, s);
+              if (PROF && (a.debug & 128)) {
+                mbar_arrive(bar);
+              } else {
+                mbar_expect_tx(bar, (uint32_t)W_SUB);
+                tma_load_3d(w_base + (uint32_t)(wslot_r * W_SLOT), &tm_a2, bar, kb * BKE, nb * BN, s);
+              }
               if (++wslot_r == a.RW) { wslot_r = 0; wphase ^= 1u; }
             }
           }

@@ -301,6 +301,45 @@ def test_cluster_pair_matches_single_cta(cin, cout, k, pad, batch, hw, S, cuda_d
     torch.testing.assert_close(outs["2"], outs["1"], rtol=0, atol=0)
 
 
+PRESAMPLE_CASES = [
+    # cin, cout, k, pad, batch, hw, S, residual     streamed layers with >= 16 m-tiles per sample
+    (128, 128, 3, 1, 16, 14, 2, False),   # one n-block: pre-sampled W, contiguous item ranges
+    (256, 256, 3, 1, 16, 14, 2, False),   # two n-blocks: round-robin items
+    (1024, 512, 1, 0, 16, 14, 3, False),  # long 1x1 reduction, four n-blocks, three samples
+    (256, 520, 1, 0, 16, 14, 2, True),    # N tail (520 = 4 x 128 + 8) with a residual input
+    (512, 256, 1, 0, 24, 14, 2, False),   # the panel would fit (stationary): switched to streaming when W is pre-sampled
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,pad,batch,hw,S,res", PRESAMPLE_CASES)
+def test_presampled_weights_and_round_robin_items_match_the_fused_schedule(cin, cout, k, pad, batch, hw, S, res, cuda_device, monkeypatch):
+    """tc2_presample_kernel writes the weights the in-kernel sampling loop would draw (same Philox positions, same
+    bf16 arithmetic) and the round-robin item order changes WHICH SM computes a tile, not how: outputs are
+    bit-identical to the fused, contiguous-range schedule."""
+    torch.manual_seed(cin + cout + k)
+    layer = L.Conv2dReparameterization(cin, cout, k, padding=pad, bias=True, prior_type="normal").to(cuda_device)
+    layer.dnn_to_bnn_flag = True
+    layer.path = "tc"
+    layer._ep_scale = torch.rand(cout, device=cuda_device) + 0.5
+    layer._ep_shift = torch.randn(cout, device=cuda_device)
+    layer._ep_relu = True
+    x = torch.randn(S * batch, cin, hw, hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    r = torch.randn(S * batch, cout, hw, hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last) if res else None
+    outs = {}
+    for wpre, rr in (("0", "0"), ("1", "1"), ("0", "1"), ("1", "0")):
+        monkeypatch.setenv("BT_TC2_WPRE", wpre)
+        monkeypatch.setenv("BT_TC2_RR", rr)
+        n0 = ops.PROFILE.launches
+        with torch.no_grad(), bt.mc_batched(S, 5):
+            outs[wpre + rr] = layer(x, residual=r) if res else layer(x)
+        torch.cuda.synchronize()
+        if wpre == "1":
+            assert ops.PROFILE.launches - n0 >= 2      # the pre-sampling pass ran (and the GEMM)
+    assert float(outs["00"].float().abs().max()) > 0
+    for key in ("11", "01", "10"):
+        torch.testing.assert_close(outs[key], outs["00"], rtol=0, atol=0)
+
+
 def test_tc_forward_kl_is_fused_into_the_packing_pass(cuda_device):
     """forward(return_kl=True) on the tensor-core path: the KL term comes out of the parameter-packing launch (mu / rho
     read once for sampling and KL), with scalar and with tensor-valued priors, bias included; rtol 1e-5 vs the oracle,
