@@ -469,7 +469,13 @@ __global__ void __launch_bounds__(256) tc2_patch_tab_kernel(const TX* __restrict
 // One thread per 16-byte chunk (eight weights = one Philox block); blockIdx.y = sample.
 __global__ void __launch_bounds__(256) tc2_presample_kernel(const uint4* __restrict__ mu_p, const uint4* __restrict__ sig_p,
                                                             uint4* __restrict__ wq, int64_t chunks, uint64_t seed, uint32_t sample_id,
-                                                            uint32_t layer_id) {
+                                                            uint32_t layer_id, int pdl) {
+  // Programmatic dependent launch (pdl != 0): this grid may start while the previous kernel of the stream drains.
+  // pdl = 1: the packed parameters were written by that kernel -- wait first.  pdl = 2 (frozen layer: the packed
+  // parameters are old, nothing here depends on the previous kernel): sample during its tail and wait at the END, so
+  // that this grid -- and with it the GEMM that waits on it -- still completes after everything before it.
+  if (pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (pdl == 1) asm volatile("griddepcontrol.wait;" ::: "memory");
   const int s = blockIdx.y;
   const BtRngKey rk = bt_rng_key(seed, sample_id + (uint32_t)s, layer_id, BT_KIND_EPS_W);
   uint4* __restrict__ dst = wq + (int64_t)s * chunks;
@@ -484,6 +490,7 @@ __global__ void __launch_bounds__(256) tc2_presample_kernel(const uint4* __restr
     w.w = fma_bf16x2(sg.w, pack_bf16(z[6], z[7]), mu.w);
     dst[c] = w;
   }
+  if (pdl == 2) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 // x * s_in as a bf16 tensor with x's strides (patch-matrix Flipout: the RGB stem, odd C_in): one thread per
@@ -1946,7 +1953,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   __nv_bfloat16* sig_p = a.tf32 ? (__nv_bfloat16*)((float*)workspace + wn) : mu_p + wn;
   float* eps_p = (p->eps_w || opt.dgrad) ? (a.tf32 ? (float*)workspace + 2 * wn : (float*)(sig_p + wn)) : nullptr;
   __nv_bfloat16* patches = (__nv_bfloat16*)((char*)workspace + ((3 * wn * 4 + 255) / 256) * 256);
-  bool kl_done = false;
+  bool kl_done = false, packed_frozen = false;
   bool wq_fits = opt.ws_bytes == 0;   // unchecked workspace: sized by bt_workspace_bytes, which counts them
   if (opt.ws_bytes > 0) {  // the carve-up below must fit what the caller allocated (bt_workspace_bytes)
     int64_t need = ((3 * wn * 4 + 255) / 256) * 256;
@@ -1969,6 +1976,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
       BT_LAUNCH_OK("tc2_pack_dgrad_kernel");
     } else if ((p->flags & BT_FLAG_PACKED_VALID) && !p->eps_w) {
       // frozen inference model: the workspace still holds this layer's packed parameters
+      packed_frozen = true;
       if (a.pdl && !p->eps_b && pl.mode != A_PATCH) a.pdl = 2;
     } else if (opt.kl_out) {
       BT_REQUIRE(opt.kl_scratch, BT_ERR_INVALID, "tensor-core forward: kl_out needs the workspace's KL scratch");
@@ -2230,6 +2238,14 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
     a.NA = a.NR * a.NAr;
     a.a_keep = 1;
   }
+  // second pass over what the roundings above left unused (an odd A slot of a two-ring plan, a W slot given up for a
+  // residual ring that still did not fit): 256<-1024-class expansions with a residual ran with 2.5 of 13 units idle
+  if (!flipout && env_int("BT_TC2_SMEM2", 1) != 0) {
+    auto used = [&]() { return 1024 + CTRL_BYTES + (a.stage_bufs * SG + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT_T + a.RW * WB; };
+    if (a.res_bufs == 2 && SMEM_LIMIT - used() >= 2 * STAGE_UNIT) a.res_bufs = 4;
+    if (!a.stationary && a.RW < 4 && SMEM_LIMIT - used() >= WB) a.RW += 1;
+    if (a.stage_bufs == 2 && SMEM_LIMIT - used() >= 2 * SG * STAGE_UNIT) a.stage_bufs = 4;
+  }
   BT_REQUIRE(a.NA >= 2 && a.RW >= 1 && a.RW <= MAX_RW, BT_ERR_UNSUPPORTED, "tensor-core forward: no room for the pipelines");
   a.total_items = (int64_t)a.S * a.NB * a.num_mg;
   const int ncl = sms / a.CL;
@@ -2249,8 +2265,21 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
     int64_t bx = (chunks + 255) / 256;
     const int64_t capx = ((int64_t)sms * 8 + S - 1) / S;
     if (bx > capx) bx = capx < 1 ? 1 : capx;
-    tc2_presample_kernel<<<dim3((unsigned)bx, (unsigned)S), 256, 0, stream>>>(reinterpret_cast<const uint4*>(mu_p), reinterpret_cast<const uint4*>(sig_p),
-                                                                          wq, chunks, p->seed, p->sample_id, p->layer_id);
+    {
+      const int ppdl = !a.pdl ? 0 : (packed_frozen && env_int("BT_TC2_WPRE_PDL", 2) == 2 ? 2 : 1);
+      cudaLaunchConfig_t cfg;
+      memset(&cfg, 0, sizeof(cfg));
+      cfg.gridDim = dim3((unsigned)bx, (unsigned)S);
+      cfg.blockDim = dim3(256);
+      cfg.stream = stream;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[0].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = ppdl ? 1 : 0;
+      BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_presample_kernel, reinterpret_cast<const uint4*>(mu_p), reinterpret_cast<const uint4*>(sig_p), wq, chunks,
+                                    (uint64_t)p->seed, (uint32_t)p->sample_id, (uint32_t)p->layer_id, ppdl));
+    }
     BT_LAUNCH_OK("tc2_presample_kernel");
     const cuuint64_t gdim[3] = {(cuuint64_t)a.K, (cuuint64_t)a.N, (cuuint64_t)S};
     const cuuint64_t gstr[2] = {(cuuint64_t)a.K * 2, (cuuint64_t)a.N * a.K * 2};
