@@ -137,6 +137,43 @@ __global__ void add_relu_kernel(T* __restrict__ y, const T* __restrict__ r, int6
 
 // Channels-last max pooling, 8 channels (16 bytes) per thread: the stem's MaxPool2d(3, 2, 1)
 // sits between two Bayesian layers of every ResNet and torch's NHWC kernel runs it at ~0.7 TB/s.
+// K = 3 (every ResNet): the nine taps are loaded first, all in flight at once, then reduced -- the generic loop below issues
+// load -> max -> load and ran latency-bound at 48 % of the DRAM rate (profiles/r2_maxpool_pool_ncu_metrics.txt).
+template <typename IDX>
+__global__ void __launch_bounds__(256) maxpool2d_k3_nhwc_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                                                     int64_t total64, int C8, int IH, int IW, int OH, int OW, int st, int pd) {
+  const IDX total = (IDX)total64, stride = (IDX)gridDim.x * blockDim.x;
+  const uint32_t ninf = 0xFF80FF80u;   // (-inf, -inf) in bf16
+  for (IDX i = (IDX)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c8 = (int)(i % (IDX)C8);
+    IDX r = i / (IDX)C8;
+    const int ow = (int)(r % (IDX)OW); r /= (IDX)OW;
+    const int oh = (int)(r % (IDX)OH); r /= (IDX)OH;
+    const __nv_bfloat16* xb = x + (int64_t)r * IH * IW * C8 * 8 + c8 * 8;
+    uint4 v[9];
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int ih = oh * st - pd + kh;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int iw = ow * st - pd + kw;
+        const bool ok = (unsigned)ih < (unsigned)IH && (unsigned)iw < (unsigned)IW;
+        v[kh * 3 + kw] = ok ? __ldg(reinterpret_cast<const uint4*>(xb + ((int64_t)ih * IW + iw) * C8 * 8)) : make_uint4(ninf, ninf, ninf, ninf);
+      }
+    }
+    __nv_bfloat162 m[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) m[e] = reinterpret_cast<const __nv_bfloat162*>(&v[0])[e];
+#pragma unroll
+    for (int t = 1; t < 9; ++t) {
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v[t]);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) m[e] = __hmax2_nan(m[e], h[e]);  // NaN propagates like torch's max_pool2d
+    }
+    reinterpret_cast<uint4*>(y)[i] = *reinterpret_cast<const uint4*>(m);
+  }
+}
+
 template <typename IDX>
 __global__ void __launch_bounds__(256) maxpool2d_nhwc_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y,
                                                                   int64_t total64, int C8, int IH, int IW, int OH, int OW, int k,
@@ -216,7 +253,10 @@ extern "C" int bt_maxpool2d_nhwc(const void* x, void* y, int64_t batch, int64_t 
   int64_t blocks = (total + 255) / 256;
   const int64_t cap = (int64_t)bt_num_sms() * 64;
   if (blocks > cap) blocks = cap;
-  if (total + cap * 256 < 0x7fffffffll)
+  if (kernel == 3 && total + cap * 256 < 0x7fffffffll)
+    maxpool2d_k3_nhwc_bf16_kernel<uint32_t><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)x, (__nv_bfloat16*)y, total, (int)(channels / 8), (int)ih, (int)iw, (int)oh, (int)ow, stride, pad);
+  else if (total + cap * 256 < 0x7fffffffll)
     maxpool2d_nhwc_bf16_kernel<uint32_t><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(
         (const __nv_bfloat16*)x, (__nv_bfloat16*)y, total, (int)(channels / 8), (int)ih, (int)iw, (int)oh, (int)ow, kernel, stride, pad);
   else

@@ -23,6 +23,25 @@ import sys
 import threading
 import time
 
+# stdout carries ONE JSON line.  Libraries write there too (NCCL's version banner under NCCL_DEBUG=VERSION / WARN / INFO comes
+# from C code, past sys.stdout): file descriptor 1 is pointed at stderr for the whole run and the line goes to the saved one.
+_STDOUT_FD = None
+
+
+def _claim_stdout():
+    global _STDOUT_FD
+    if _STDOUT_FD is None:
+        sys.stdout.flush()
+        _STDOUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    os.write(_STDOUT_FD if _STDOUT_FD is not None else 1, data)
+
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -181,7 +200,7 @@ def run_reference(args):
             "cpu_baseline": base,
             "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 def eager_on_gpu(dev, batch: int, samples: int, timed_forwards: int = 2):
@@ -508,7 +527,7 @@ def run_b200(args):
                     line["eager_b200"] = {"error": str(e)}
             if not args.no_extras:
                 line["extra"] = extras(dev, model, pk)
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -581,7 +600,7 @@ def run_train(args, dev, rank, world):
     prefetch.take()
     if rank == 0:
         value = B * world * 1e3 / ms_step
-        print(json.dumps({
+        emit({
             "metric": "bayesian_resnet18_flipout_train_images_per_s", "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
@@ -590,7 +609,7 @@ def run_train(args, dev, rank, world):
                        "l2": "activations per step far exceed the 126 MB L2; no flush needed"},
             "clocks": clocks, "loss": float(loss),
             "e2e": {"value": B * world * 1e3 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": x_host.numel() * 4 * world, "d2h_bytes_per_step": 4 * world},
-            "gpu_launches": launches}))
+            "gpu_launches": launches})
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -598,6 +617,7 @@ def run_train(args, dev, rank, world):
 
 if __name__ == "__main__":
     a = parse()
+    _claim_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:

@@ -371,3 +371,4 @@ def test_tc_forward_kl_is_fused_into_the_packing_pass(cuda_device):
     (3.0 * oracle.kl_normal(m, torch.log1p(torch.exp(r)), pm.double(), ps.double())).backward()
     torch.testing.assert_close(layer.mu_kernel.grad.cpu().double(), m.grad, rtol=1e-4, atol=1e-8)
     torch.testing.assert_close(layer.rho_kernel.grad.cpu().double(), r.grad, rtol=1e-4, atol=1e-8)
+
