@@ -44,7 +44,7 @@ constexpr int BK = 64;
 constexpr int A_SLOT = BM * BK * 2;  // 16 KB
 constexpr int BAR_BYTES = 1024;           // mbarriers + TMEM base
 constexpr int ONES_BYTES = BM * 32;       // [128 x 16] bf16 tile of the rank-1 "add shift" MMA (32-byte swizzle)
-constexpr int SHIFT_BYTES = 128 * 32;     // [BN x 16] bf16: per-channel shift split into three bf16 terms
+constexpr int SHIFT_BYTES = 256 * 32;     // [BN x 16] bf16 (BN <= 256): per-channel shift split into three bf16 terms
 constexpr int CTRL_BYTES = BAR_BYTES + ONES_BYTES + SHIFT_BYTES;
 constexpr int STAGE_UNIT = 4 * 4096;  // one staging (or residual) buffer of 32 rows x 128 B for each of the 4 epilogue warps
 constexpr int N_PROD_WARPS = 16;  // warps 0..15: W producers; the Flipout instantiation turns warps 12..15 into A flippers
@@ -101,6 +101,7 @@ struct Tc2Args {
   int epi8;          // eight epilogue warps (EPI8 instantiation): staging holds 2 * stage_bufs buffers per lane quarter
   int w_pre;         // the sampled weights were materialised by tc2_presample_kernel ([S][N][K] bf16 behind tm_a2): one thread of
                      // the producer group streams the W k-blocks in by TMA instead of the 16 warps sampling them per item
+  int pair_launch;   // host-side only: launch the single-CTA kernel with a cluster dimension of two (placement, not cooperation)
   int rr, rr_dnb, rr_dmg, rr_ds;  // round-robin item assignment (order 1) and the (nb, mg, s) digits of the cluster count
   int tf32;          // fp32 activations: fp32 A tiles, tf32 MMAs (k-blocks of 32 elements), fp32 packed parameters
   int debug;         // BT_TC2_DEBUG bits, honoured by the BT_TC2_PROF=1 instantiation only: 1 skip output stores, 4 skip MMAs,
@@ -1771,7 +1772,9 @@ static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CU
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = (unsigned)CL;
+  // a.pair_launch: the CL = 1 kernel launched as clusters of two so that the CTAs with consecutive block ids -- which the
+  // round-robin item order gives consecutive items, i.e. the same A tiles against neighbouring n-blocks -- sit on one TPC
+  attr[0].val.clusterDim.x = (unsigned)(CL == 1 && a.pair_launch && grid % 2 == 0 ? 2 : CL);
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -1786,6 +1789,9 @@ static int tc2_launch_one(const CUtensorMap& ta, const CUtensorMap& to, const CU
 template <int BN, typename TO>
 static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const CUtensorMap& tr, const CUtensorMap& ta2, const Tc2Args& a,
                       int grid, int smem_bytes, bool flip, cudaStream_t stream) {
+  if constexpr (BN == 256) {   // one instantiation: pre-sampled W, single CTA (the plan guarantees both)
+    return tc2_launch_one<BN, TO, false, 1, false>(ta, to, tr, ta2, a, grid, smem_bytes, stream);
+  } else {
   if constexpr (sizeof(TO) == 4) {
     if (a.tf32)
       return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, false, true>(ta, to, tr, ta2, a, grid, smem_bytes, stream)
@@ -1806,6 +1812,7 @@ static int tc2_launch(const CUtensorMap& ta, const CUtensorMap& to, const CUtens
   }
   return a.CL == 2 ? tc2_launch_one<BN, TO, false, 2, false>(ta, to, tr, ta2, a, grid, smem_bytes, stream)
                    : tc2_launch_one<BN, TO, false, 1, false>(ta, to, tr, ta2, a, grid, smem_bytes, stream);
+  }
 }
 
 // Diagnostics: cycle counters of the last BT_TC2_PROF=1 launch, [cta][role][slot] (see bt_b200.h).
@@ -2122,6 +2129,20 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   // (L2 -> shared memory, then shared memory -> tensor core) is the scarcer resource
   // (1024 -> 256 1x1 at 14x14: 0.34 ms stationary/64, 0.23 ms streaming/128).
   if (force_bn == 64 || force_bn == 128) BN = force_bn;
+  // BN = 256 for long reductions into >= 256 channels with pre-sampled W.  The compute-bound layers are bound by the
+  // L2 -> SM fabric (~43 B / cycle / SM: a 16 KB A tile takes ~385 cycles to arrive, as long as its four N = 128 MMAs
+  // run at the sustained rate; 3x3 256 at 14x14 moved 10 TB/s, profiles/r2_conv3x3_fwd_ncu_metrics.txt): twice the
+  // columns per A tile halve the A bytes per FLOP.  Two 256-column accumulators fill the TMEM (MT = 2).  The conditions
+  // repeat those of the pre-sampled mode, which the 256-row panel (never fits for >= 4 k-blocks) then always selects.
+  // Measured (profiles/r2_exp13_bn256.txt, r2_exp14_bn256_short_k.txt): 3x3 256 @14 0.87 -> 0.74 ms (1 275 TFLOP/s; 1 361 inside the
+  // network), 3x3 512 @7 0.94 -> 0.75, 512<-1024 0.90 -> 0.81, 512<-2048 0.47 -> 0.41, 2048<-1024 /2 0.90 -> 0.78.  Short reductions
+  // (4-7 k-blocks) gain without a residual input (512<-256 /2 1.28 -> 1.16) and lose with one (1024<-256 0.73 -> 0.90: the single
+  // accumulator set no longer hides the residual epilogue), hence the two thresholds.
+  if (force_bn != 64 && force_bn != 128 && a.N % 256 == 0 && a.nkb >= env_int("BT_TC2_BN256_NKB", p->residual ? 8 : 4) && g->out_dtype == BT_BF16 && !flipout &&
+      !a.tf32 && a.spn == 1 && a.Kt == a.K && !opt.dgrad && !p->eps_w && wq_fits && wpre_bytes(g, pl, flipout) > 0 &&
+      !(x_shared && env_int("BT_TC2_SINNER", 0) != 0) && a.num_mt >= env_int("BT_TC2_WPRE_MIN", 16) && env_int("BT_TC2_WPRE", 1) != 0 &&
+      !env_int("BT_TC2_PROF", 0) && env_int("BT_TC2_BN256", 1) != 0)
+    BN = 256;
   // Eight epilogue warps (EPI8 instantiation) where the output stream is the bottleneck: full 128-column tiles,
   // bf16 outputs and ONE k-block (K <= 64: the 256<-64 expansions of layer1, -3 % on the same box).  Longer
   // reductions stream W and need all 16 producer warps: 1024<-256 with 12 producers ran 0.95 -> 1.26 ms
@@ -2256,6 +2277,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
     a.rr_dmg = (ncl / a.NB) % a.num_mg;
     a.rr_ds = (ncl / a.NB) / a.num_mg;
   }
+  a.pair_launch = (a.rr && a.CL == 1 && a.NB % 2 == 0 && env_int("BT_TC2_PAIR", 1) != 0) ? 1 : 0;
   const int smem_bytes = 1024 + CTRL_BYTES + (flipout ? SHIFT_BYTES : 0) + (a.stage_bufs * SG + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT_T + a.RW * WB;
   BT_REQUIRE(smem_bytes <= SMEM_LIMIT, BT_ERR_UNSUPPORTED, "tensor-core forward: shared memory plan %d exceeds %d", smem_bytes, SMEM_LIMIT);
   if (a.w_pre) {
@@ -2294,6 +2316,10 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
             a.w_pre, (int)flipout, (int)pl.mode, a.S, a.Ms, a.N, a.K, a.Kt, BN, a.stationary, a.MT, a.NSETS, a.nkb, a.NR, a.NAr, a.RW, a.NB, a.num_mg,
             (long long)a.total_items, grid, smem_bytes, a.stage_bufs, a.res_bufs, a.CL, a.nb_inner, a.a_keep, a.spn, a.epi8, a.tf32, a.pdl);
   const bool o32 = g->out_dtype == BT_F32;
+  if (BN == 256) {
+    BT_REQUIRE(a.w_pre && a.CL == 1 && !o32 && !flipout && !a.tf32 && !a.epi8, BT_ERR_UNSUPPORTED, "tensor-core forward: BN = 256 plan without pre-sampled W");
+    return tc2_launch<256, __nv_bfloat16>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream);
+  }
   if (BN == 64)
     return o32 ? tc2_launch<64, float>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream)
                : tc2_launch<64, __nv_bfloat16>(tm_a, tm_out, tm_res, tm_a2, a, grid, smem_bytes, flipout, stream);

@@ -308,6 +308,7 @@ PRESAMPLE_CASES = [
     (1024, 512, 1, 0, 16, 14, 3, False),  # long 1x1 reduction, four n-blocks, three samples
     (256, 520, 1, 0, 16, 14, 2, True),    # N tail (520 = 4 x 128 + 8) with a residual input
     (512, 256, 1, 0, 24, 14, 2, False),   # the panel would fit (stationary): switched to streaming when W is pre-sampled
+    (512, 512, 1, 0, 16, 14, 2, True),    # BN = 256 tiles (N % 256 == 0, >= 8 k-blocks) with a residual input
 ]
 
 
@@ -326,18 +327,19 @@ def test_presampled_weights_and_round_robin_items_match_the_fused_schedule(cin, 
     x = torch.randn(S * batch, cin, hw, hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
     r = torch.randn(S * batch, cout, hw, hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last) if res else None
     outs = {}
-    for wpre, rr in (("0", "0"), ("1", "1"), ("0", "1"), ("1", "0")):
+    for wpre, rr, bn256 in (("0", "0", "0"), ("1", "1", "1"), ("0", "1", "0"), ("1", "0", "1"), ("1", "1", "0")):
         monkeypatch.setenv("BT_TC2_WPRE", wpre)
         monkeypatch.setenv("BT_TC2_RR", rr)
+        monkeypatch.setenv("BT_TC2_BN256", bn256)   # 256-column tiles where the plan allows them (cases 2, 3, 5, 6)
         n0 = ops.PROFILE.launches
         with torch.no_grad(), bt.mc_batched(S, 5):
-            outs[wpre + rr] = layer(x, residual=r) if res else layer(x)
+            outs[wpre + rr + bn256] = layer(x, residual=r) if res else layer(x)
         torch.cuda.synchronize()
         if wpre == "1":
             assert ops.PROFILE.launches - n0 >= 2      # the pre-sampling pass ran (and the GEMM)
-    assert float(outs["00"].float().abs().max()) > 0
-    for key in ("11", "01", "10"):
-        torch.testing.assert_close(outs[key], outs["00"], rtol=0, atol=0)
+    assert float(outs["000"].float().abs().max()) > 0
+    for key in ("111", "010", "101", "110"):
+        torch.testing.assert_close(outs[key], outs["000"], rtol=0, atol=0)
 
 
 def test_tc_forward_kl_is_fused_into_the_packing_pass(cuda_device):
