@@ -494,6 +494,28 @@ __global__ void __launch_bounds__(256) tc2_presample_kernel(const uint4* __restr
   if (pdl == 2) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
+// Padded reduction (patch-matrix mode: K rounded up to 8, the eps stream keeps the TRUE pitch Kt): element by element.
+// Only tiny weight tensors take this path (the RGB stem: 64 x 147).
+__global__ void __launch_bounds__(256) tc2_presample_padded_kernel(const __nv_bfloat16* __restrict__ mu_p, const __nv_bfloat16* __restrict__ sig_p,
+                                                                   __nv_bfloat16* __restrict__ wq, int N, int K, int Kt, uint64_t seed,
+                                                                   uint32_t sample_id, uint32_t layer_id, int pdl) {
+  if (pdl) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (pdl == 1) asm volatile("griddepcontrol.wait;" ::: "memory");
+  const int s = blockIdx.y;
+  const BtRngKey rk = bt_rng_key(seed, sample_id + (uint32_t)s, layer_id, BT_KIND_EPS_W);
+  const int64_t pairs = (int64_t)N * K / 2;   // K % 8 == 0: a pair never straddles two rows
+  const uint32_t* mu2 = reinterpret_cast<const uint32_t*>(mu_p);
+  const uint32_t* sg2 = reinterpret_cast<const uint32_t*>(sig_p);
+  uint32_t* dst = reinterpret_cast<uint32_t*>(wq) + (int64_t)s * pairs;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < pairs; i += (int64_t)gridDim.x * blockDim.x) {
+    const int n = (int)(2 * i / K), k = (int)(2 * i - (int64_t)n * K);
+    const float z0 = k < Kt ? bt_normal1((uint64_t)n * Kt + k, rk) : 0.f;
+    const float z1 = k + 1 < Kt ? bt_normal1((uint64_t)n * Kt + k + 1, rk) : 0.f;
+    dst[i] = fma_bf16x2(sg2[i], pack_bf16(z0, z1), mu2[i]);   // the instruction of the in-kernel sampling loop
+  }
+  if (pdl == 2) asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // x * s_in as a bf16 tensor with x's strides (patch-matrix Flipout: the RGB stem, odd C_in): one thread per
 // word of the SIGN_IN stream, i.e. 32 consecutive elements of the sample in channels-last order.
 struct FlipGeo {
@@ -1736,8 +1758,9 @@ static int64_t patch_bytes(const bt_geom* g, int64_t rows_per_s, int64_t Kp) {
 // launch finally chooses (it also needs a streamed W, Philox-drawn eps, a forward run), so that the size the
 // caller allocates always covers the launch's carve-up.
 static int64_t wpre_bytes(const bt_geom* g, const Plan& pl, bool flipout) {
-  if (flipout || g->x_dtype != BT_BF16 || pl.mode == A_PATCH || pl.es != 2 || (pl.K & 7)) return 0;
-  const int64_t b = (int64_t)g->n_samples * g->c_out * pl.K * 2;
+  const int64_t K = pl.mode == A_PATCH ? pl.Kp : pl.K;
+  if (flipout || g->x_dtype != BT_BF16 || pl.es != 2 || (K & 7)) return 0;
+  const int64_t b = (int64_t)g->n_samples * g->c_out * K * 2;
   return b <= (1ll << 31) ? ((b + 255) / 256) * 256 : 0;
 }
 int64_t bt_tc_workspace_bytes(const bt_geom* g, bool flipout) {
@@ -2140,7 +2163,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   // accumulator set no longer hides the residual epilogue), hence the two thresholds.
   if (force_bn != 64 && force_bn != 128 && a.N % 256 == 0 && a.nkb >= env_int("BT_TC2_BN256_NKB", p->residual ? 8 : 4) && g->out_dtype == BT_BF16 && !flipout &&
       !a.tf32 && a.spn == 1 && a.Kt == a.K && !opt.dgrad && !p->eps_w && wq_fits && wpre_bytes(g, pl, flipout) > 0 &&
-      !(x_shared && env_int("BT_TC2_SINNER", 0) != 0) && a.num_mt >= env_int("BT_TC2_WPRE_MIN", 16) && env_int("BT_TC2_WPRE", 1) != 0 &&
+      !x_shared && a.num_mt >= env_int("BT_TC2_WPRE_MIN", 16) && env_int("BT_TC2_WPRE", 1) != 0 &&
       !env_int("BT_TC2_PROF", 0) && env_int("BT_TC2_BN256", 1) != 0)
     BN = 256;
   // Eight epilogue warps (EPI8 instantiation) where the output stream is the bottleneck: full 128-column tiles,
@@ -2166,7 +2189,14 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   // memory.  OFF by default: the order re-samples W for every (m-group, sample) item, and on the ResNet stem
   // (3->64 7x7, 32 samples x 128 images) that costs more than the A traffic it saves (7.1 ms against 3.3 ms
   // with one stationary panel per sample; profiles/r1_experiments.txt).
-  const bool s_inner = x_shared && !flipout && a.nkb <= MAX_NA / 2 && env_int("BT_TC2_SINNER", 0) != 0;
+  // With pre-sampled W (below) the order no longer re-samples anything -- the W tiles of an item come from L2 by TMA and the
+  // patch matrix of the stem is read ONCE instead of once per sample pair (7.8 GB -> 0.5 GB) -- and it is still slower:
+  // stem at 32 samples 2.19 -> 2.56 ms, at 4 samples 0.57 -> 0.62 (profiles/r2_exp17_stem_sample_fastest.txt; the 48 KB of W
+  // per two-tile item cost the L2 -> SM fabric what the A tiles did).  BT_TC2_SINNER=1 selects it; bit-identical either way.
+  const bool wpre_static = wpre_bytes(g, pl, flipout) > 0 && wq_fits && !opt.dgrad && !p->eps_w && !a.tf32 &&
+                           a.num_mt >= env_int("BT_TC2_WPRE_MIN", 16) && env_int("BT_TC2_WPRE", 1) != 0;
+  const int sinner_env = env_int("BT_TC2_SINNER", 0);
+  const bool s_inner = x_shared && !flipout && a.nkb <= MAX_NA / 2 && sinner_env == 1;
   if (s_inner) a.stationary = 0;
   const int NSLOTS = 512 / (NSUBW * BN);
   // Streamed W on a layer with many m-tiles per sample: the fused kernel would re-sample every [BN x K] panel once per
@@ -2176,9 +2206,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   // 1.11 -> 0.93 ms, 3x3 256 @14 1.03 -> 0.90, 256<-1024 @14 0.69 -> 0.65, 512<-256 /2 1.42 -> 1.25; at 7x7 (49 m-tiles per
   // sample) the W stream costs more than the sampling it replaces (512<-2048: 0.69 -> 0.80), hence the m-tile floor.
   {
-    const int64_t wq = wpre_bytes(g, pl, flipout);
-    const bool wpre_ok = wq > 0 && wq_fits && !s_inner && !opt.dgrad && !p->eps_w && a.spn == 1 && a.Kt == a.K && !a.tf32 && !a.epi8 &&
-                         a.num_mt >= env_int("BT_TC2_WPRE_MIN", 16) && env_int("BT_TC2_WPRE", 1) != 0;
+    const bool wpre_ok = wpre_static && !a.epi8;
     // a stationary panel walks (sample, n-block, m-group): with two or more n-blocks every A tile comes from HBM once per
     // n-block.  Streaming pre-sampled W with the n-block innermost reads it once (256<-512 at 28x28: 3.3 GB of A).
     if (wpre_ok && a.stationary && a.NB >= 2 && a.nkb >= 2 && force_stat != 1) a.stationary = 0;
@@ -2281,8 +2309,8 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   const int smem_bytes = 1024 + CTRL_BYTES + (flipout ? SHIFT_BYTES : 0) + (a.stage_bufs * SG + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT_T + a.RW * WB;
   BT_REQUIRE(smem_bytes <= SMEM_LIMIT, BT_ERR_UNSUPPORTED, "tensor-core forward: shared memory plan %d exceeds %d", smem_bytes, SMEM_LIMIT);
   if (a.w_pre) {
-    // behind the packed area (w_pre excludes the patch-matrix mode, whose matrices would sit there)
-    uint4* wq = reinterpret_cast<uint4*>(patches);
+    // behind the packed area and, in patch-matrix mode, behind the patch matrix
+    uint4* wq = reinterpret_cast<uint4*>(reinterpret_cast<char*>(patches) + (pl.mode == A_PATCH ? patch_bytes(g, pl.rows_per_s, pl.Kp) : 0));
     const int64_t chunks = wn / 8;
     int64_t bx = (chunks + 255) / 256;
     const int64_t capx = ((int64_t)sms * 8 + S - 1) / S;
@@ -2299,12 +2327,17 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
       attr[0].val.programmaticStreamSerializationAllowed = 1;
       cfg.attrs = attr;
       cfg.numAttrs = ppdl ? 1 : 0;
+      if (a.Kt != a.K)
+        BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_presample_padded_kernel, (const __nv_bfloat16*)mu_p, (const __nv_bfloat16*)sig_p, (__nv_bfloat16*)wq,
+                                      a.N, a.K, a.Kt, (uint64_t)p->seed, (uint32_t)p->sample_id, (uint32_t)p->layer_id, ppdl));
+      else
       BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_presample_kernel, reinterpret_cast<const uint4*>(mu_p), reinterpret_cast<const uint4*>(sig_p), wq, chunks,
                                     (uint64_t)p->seed, (uint32_t)p->sample_id, (uint32_t)p->layer_id, ppdl));
     }
     BT_LAUNCH_OK("tc2_presample_kernel");
-    const cuuint64_t gdim[3] = {(cuuint64_t)a.K, (cuuint64_t)a.N, (cuuint64_t)S};
-    const cuuint64_t gstr[2] = {(cuuint64_t)a.K * 2, (cuuint64_t)a.N * a.K * 2};
+    // a stacked sample pair (spn = 2) reads rows [0, 64) of sample 2 s and of sample 2 s + 1 as ONE 128-row block: the same memory
+    const cuuint64_t gdim[3] = {(cuuint64_t)a.K, (cuuint64_t)a.N * a.spn, (cuuint64_t)(S / a.spn)};
+    const cuuint64_t gstr[2] = {(cuuint64_t)a.K * 2, (cuuint64_t)a.N * a.spn * a.K * 2};
     const cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)BN, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
     const CUresult r = drv.tiled(&tm_a2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, wq, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,

@@ -179,6 +179,8 @@ def test_tc_mc_batched_equals_sample_loop(cuda_device):
     (64, 64, 1, 1, 0, 5, 20, 6),      # 64 output channels: two samples stacked on the N axis of one tile (sampled bias per sample)
     (64, 64, 3, 1, 1, 3, 17, 7),      # odd sample count: no stacking
     (128, 64, 3, 2, 1, 2, 30, 8),     # K = 1152: too long for the kept ring -> the usual order
+    (3, 64, 7, 2, 3, 8, 64, 4),       # the RGB stem (patch matrix, K padded 147 -> 152): 64 m-tiles per sample -> pre-sampled W by default
+    (64, 128, 3, 1, 1, 6, 20, 3),     # 19 m-tiles per sample, odd sample count, N = 128
 ])
 def test_tc_shared_input_sample_fastest_order(cuda_device, cin, cout, k, stride, pad, batch, hw, S, monkeypatch):
     """x shared by all samples: the (m-group, n-block, sample) order with the A tiles kept in shared
@@ -199,9 +201,18 @@ def test_tc_shared_input_sample_fastest_order(cuda_device, cin, cout, k, stride,
         monkeypatch.setenv("BT_TC2_SINNER", "0")
         with bt.mc_batched(S, 11, shared_batch=batch):
             usual = layer(x)
+        monkeypatch.delenv("BT_TC2_SINNER")     # the default order
+        with bt.mc_batched(S, 11, shared_batch=batch):
+            auto = layer(x)
+        monkeypatch.setenv("BT_TC2_SINNER", "1")
+        monkeypatch.setenv("BT_TC2_WPRE", "0")  # sample-fastest order with the fused sampling (the first run pre-samples where it can)
+        with bt.mc_batched(S, 11, shared_batch=batch):
+            fused = layer(x)
     torch.cuda.synchronize()
     assert torch.equal(folded, torch.cat(loop))
     assert torch.equal(folded, usual)
+    assert torch.equal(folded, auto)
+    assert torch.equal(folded, fused)
 
 
 def test_conv3d_tc_matches_oracle(cuda_device):

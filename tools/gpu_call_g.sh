@@ -1,5 +1,5 @@
 #!/bin/bash
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_tc_gpu.py -x -q -m gpu -k "presampled" > gpurun_out/t_pre.log 2>&1; echo "presample tests rc=$?"; tail -5 gpurun_out/t_pre.log
+timeout 900 python -m pytest tests/test_tc_gpu.py -x -q -m gpu > gpurun_out/t_pre.log 2>&1; echo "tc tests rc=$?"; tail -5 gpurun_out/t_pre.log
 bash tools/$1.sh > gpurun_out/$1.txt 2>&1; cat gpurun_out/$1.txt
