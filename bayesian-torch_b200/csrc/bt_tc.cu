@@ -676,7 +676,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     for (int i = 0; i < a.NSETS; ++i) mbar_init(smem_u32(&ctrl->acc_full[i]), N_MMA_WARPS);
     // acc_empty is per accumulator TILE (set * MT + t): the MMAs of the next item restart on tile t as soon as the
     // epilogue has drained it, instead of waiting for the whole set
-    for (int i = 0; i < a.NSETS * a.MT; ++i) mbar_init(smem_u32(&ctrl->acc_empty[i]), EPI8 ? 256 : 128);
+    for (int i = 0; i < a.NSETS * a.MT; ++i) mbar_init(smem_u32(&ctrl->acc_empty[i]), EPI8 ? 8 : 4);   // one arrival per epilogue warp (32 serialized arrivals per warp and tile before)
     for (int i = 0; i < 4; ++i) { mbar_init(smem_u32(&ctrl->res_full[i]), 1); mbar_init(smem_u32(&ctrl->res_empty[i]), 4); }
     mbar_fence_init();
   }
@@ -796,7 +796,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               rslot += 2;
               if (rslot >= a.res_bufs) { rslot -= a.res_bufs; rphase ^= 1u; }
             }
-            mbar_arrive(ebar);
+            if (lane == 0) mbar_arrive(ebar);
             continue;
           }
           const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)((set * a.MT + t) * ACC_COLS + grp * 64);
@@ -819,7 +819,8 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
           tmem_ld32(tacc + 32, va);
           tmem_ld_wait();
           tc_fence_before();
-          mbar_arrive(ebar);        // this thread's reads of its half of tile t are complete
+          __syncwarp();             // every lane's reads of its half of tile t are complete: one arrival for the warp
+          if (lane == 0) mbar_arrive(ebar);
           epi_unit<TO, RELU, RES>(va, rowaddr, resaddr, 4, row_sw);
           fence_proxy_async();
           __syncwarp();
@@ -890,7 +891,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               if (++rslot == a.res_bufs) { rslot = 0; rphase ^= 1u; }
             }
           }
-          mbar_arrive(smem_u32(&ctrl->acc_empty[set * a.MT + t]));
+          if (lane == 0) mbar_arrive(smem_u32(&ctrl->acc_empty[set * a.MT + t]));
           continue;
         }
         const uint32_t tacc = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)((set * a.MT + t) * ACC_COLS);
@@ -1007,9 +1008,10 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             if (++rslot == a.res_bufs) { rslot = 0; rphase ^= 1u; }
           }
         }
-        // this thread's TMEM reads of tile t have completed (tcgen05.wait::ld above): hand the tile back
+        // every lane's TMEM reads of tile t have completed (tcgen05.wait::ld above, then the warp barrier): hand the tile back
         tc_fence_before();
-        mbar_arrive(smem_u32(&ctrl->acc_empty[set * a.MT + t]));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&ctrl->acc_empty[set * a.MT + t]));
       }
       if (++set == a.NSETS) { set = 0; set_phase ^= 1u; }
       walk(s, nb, mg);
