@@ -17,11 +17,14 @@ cap() {  # name kernel-regex skip
 cap kl kl_normal_multi_kernel 2 kl
 cap stem tc2_fwd_kernel 2 fwd
 cap stem tc2_patch 2 patch
-cap maxpool maxpool2d_nhwc 2 pool
+cap maxpool maxpool2d 2 pool
 cap flipout tc2_fwd_kernel 2 flip
 cap tf32 tc2_fwd_kernel 2 tf32
 cap hbm1x1 tc2_fwd_kernel 2 fwd
 cap conv3x3 tc2_fwd_kernel 2 fwd
+cap conv3x3 tc2_presample_kernel 2 presample
+cap conv3x3_128 tc2_fwd_kernel 2 fwd
+cap exp_res tc2_fwd_kernel 2 fwd
 cap pack tc2_pack_kernel 2 pack
 cap wgrad tc_wgrad_kernel 2 wgrad
 cap lstm lstm_step_kernel 4 lstm

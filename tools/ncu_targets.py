@@ -1,5 +1,5 @@
 """Small programs for `ncu --set full` captures of each kernel family (one target per invocation).
-usage: ncu_targets.py {kl|wgrad|flipout|stem|maxpool|tf32|hbm1x1|conv3x3|lstm|pack}"""
+usage: ncu_targets.py {kl|wgrad|flipout|stem|maxpool|tf32|hbm1x1|conv3x3|conv3x3_128|exp_res|lstm|pack}"""
 import os
 import sys
 
@@ -69,12 +69,27 @@ with torch.no_grad():
             with bt.mc_batched(16, 0):
                 lay(x, residual=r)
         run(f)
-    elif what == "conv3x3":   # 256 -> 256 3x3 at 14x14, 32 samples x 128 images: the compute-bound class
+    elif what == "conv3x3":   # 256 -> 256 3x3 at 14x14, 32 samples x 128 images: the compute-bound class (pre-sampled W, BN = 256 tiles)
         lay = conv(256, 256, 3, 1, 1)
         x = torch.randn(32 * 128, 256, 14, 14, device=dev).bfloat16().contiguous(memory_format=cl)
         def f():
             with bt.mc_batched(32, 0):
                 lay(x)
+        run(f)
+    elif what == "conv3x3_128":   # 128 -> 128 3x3 at 28x28, 32 samples x 128 images: pre-sampled W, BN = 128 (one n-block)
+        lay = conv(128, 128, 3, 1, 1)
+        x = torch.randn(32 * 128, 128, 28, 28, device=dev).bfloat16().contiguous(memory_format=cl)
+        def f():
+            with bt.mc_batched(32, 0):
+                lay(x)
+        run(f)
+    elif what == "exp_res":       # 1024 <- 256 1x1 at 14x14 with residual, 32 samples: the residual expansions of layer3
+        lay = conv(256, 1024, 1)
+        x = torch.randn(32 * 128, 256, 14, 14, device=dev).bfloat16().contiguous(memory_format=cl)
+        r = torch.randn(32 * 128, 1024, 14, 14, device=dev).bfloat16().contiguous(memory_format=cl)
+        def f():
+            with bt.mc_batched(32, 0):
+                lay(x, residual=r)
         run(f)
     elif what == "pack":      # parameter packing with the fused KL: Linear 8192 x 8192, forward(return_kl=True)
         lin = L.LinearReparameterization(8192, 8192).to(dev)
