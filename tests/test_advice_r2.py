@@ -195,3 +195,37 @@ def test_raw_pool_and_join_kernels_do_not_cut_autograd(cuda_device):
     with torch.no_grad():   # the raw kernels still serve inference
         y2 = ops.maxpool2d(x.detach(), 3, 2, 1)
     torch.testing.assert_close(y2, torch.nn.functional.max_pool2d(x.detach(), 3, 2, 1))
+
+
+@pytest.mark.gpu
+def test_workspace_without_room_for_presampled_weights_still_computes_the_same(cuda_device):
+    """bt_workspace_bytes counts the pre-sampled weights of a streamed layer; a caller that states only the packed
+    area (what the ABI-4 size function returned) gets the fused-sampling schedule and the same bits."""
+    torch.manual_seed(8)
+    bt.manual_seed(77)
+    layer = L.Conv2dReparameterization(256, 256, 3, padding=1, bias=False, prior_type="normal").to(cuda_device)
+    layer.path = "tc"
+    layer.dnn_to_bnn_flag = True
+    x = torch.randn(16, 256, 14, 14, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    with torch.no_grad(), bt.mc_sample(4):
+        want = layer(x)                                       # 25 m-tiles, K = 2304: pre-sampled W, 256-column tiles
+    call = ops.LayerCall(rank=2, flipout=False, stride=(1, 1), padding=(1, 1), dilation=(1, 1), seed=77, sample_id=4,
+                         layer_id=layer._layer_id)
+    out = torch.empty_like(want)
+    g = ops._build_geom(call, x, layer.mu_kernel.shape, out)
+    p, keep = ops._build_params(call, layer.mu_kernel.detach(), layer.rho_kernel.detach(), None, None)
+    full = int(_lib.lib().bt_workspace_bytes(b"reparam_fwd", C.byref(g), 2))
+    packed = 256 + ((3 * 256 * 2304 * 4 + 255) // 256) * 256  # KL scratch + (mu, sigma, eps) area
+    assert full >= packed + 256 * 2304 * 2                    # the size function counts one sample of bf16 weights
+    ws = torch.empty(full, dtype=torch.uint8, device=cuda_device)
+    outs = []
+    for stated in (full, packed):
+        p.workspace_bytes = stated
+        out = torch.empty_like(want)
+        rc = _lib.lib().bt_conv_reparam_fwd(C.byref(g), C.byref(p), x.data_ptr(), out.data_ptr(), None, ws.data_ptr(), _lib.PATH_TC_BF16,
+                                            torch.cuda.current_stream().cuda_stream)
+        assert rc == 0, _lib.lib().bt_last_error()
+        outs.append(out)
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0], outs[1])
+    assert torch.equal(outs[0], want)
