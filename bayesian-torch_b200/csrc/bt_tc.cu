@@ -101,6 +101,7 @@ struct Tc2Args {
   int epi8;          // eight epilogue warps (EPI8 instantiation): staging holds 2 * stage_bufs buffers per lane quarter
   int w_pre;         // the sampled weights were materialised by tc2_presample_kernel ([S][N][K] bf16 behind tm_a2): one thread of
                      // the producer group streams the W k-blocks in by TMA instead of the 16 warps sampling them per item
+  int two_loaders;   // no residual input, two A rings: the residual-loader warp loads ring 1
   int pair_launch;   // host-side only: launch the single-CTA kernel with a cluster dimension of two (placement, not cooperation)
   int rr, rr_dnb, rr_dmg, rr_ds;  // round-robin item assignment (order 1) and the (nb, mg, s) digits of the cluster count
   int tf32;          // fp32 activations: fp32 A tiles, tf32 MMAs (k-blocks of 32 elements), fp32 packed parameters
@@ -1025,7 +1026,11 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     if (warp == WARP_EPI0) prof_flush(0);
   } else if (warp >= WARP_TMA) {
     reg_dealloc<REGS_CTRL>();
-    if (warp == WARP_TMA) {
+    // a.two_loaders: the residual-loader warp (idle without a residual input) loads ring 1, this warp ring 0 -- the single
+    // loading thread was busy 70-85 % of the time on the layers bound by the A stream
+    constexpr int WARP_RES = WARP_MMA + N_MMA_WARPS;
+    if (warp == WARP_TMA || (a.two_loaders && warp == WARP_RES)) {
+    const int lid = warp == WARP_TMA ? 0 : 1;
     // =========================== A LOADER (TMA) ===========================
     // warp-uniform loop (every lane waits, the elected lane issues): keeps the loop state in
     // uniform registers and off the divergent-code path.
@@ -1062,7 +1067,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       for (int kb = 0; kb < a.nkb; ++kb) {
 #pragma unroll
         for (int t = 0; t < MAX_MT; ++t) {
-          if (t < mtv) {
+          if (t < mtv && (!a.two_loaders || (t % N_MMA_WARPS) == lid)) {
             const int r = t % N_MMA_WARPS;
             const int ring = a.NR == 2 ? r : 0;
             const int slot = ring * a.NAr + (a.NR == 2 ? rslot[r] : rslot[0]);
@@ -1097,7 +1102,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
       walk(s, nb, mg);
     }
     __syncwarp();
-    prof_flush(1);
+    if (lid == 0) prof_flush(1);
     } else if (warp < WARP_MMA + N_MMA_WARPS) {
     // =========================== MMA ISSUERS ===========================
     const int j = warp - WARP_MMA;  // this issuer owns tiles t with t % N_MMA_WARPS == j
@@ -2307,6 +2312,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
     a.rr_dmg = (ncl / a.NB) % a.num_mg;
     a.rr_ds = (ncl / a.NB) / a.num_mg;
   }
+  a.two_loaders = (a.NR == 2 && a.res_bufs == 0 && !a.a_keep && !flipout && env_int("BT_TC2_LOADERS", 2) == 2) ? 1 : 0;
   a.pair_launch = (a.rr && a.CL == 1 && a.NB % 2 == 0 && env_int("BT_TC2_PAIR", 1) != 0) ? 1 : 0;
   const int smem_bytes = 1024 + CTRL_BYTES + (flipout ? SHIFT_BYTES : 0) + (a.stage_bufs * SG + a.res_bufs) * STAGE_UNIT + a.NA * A_SLOT_T + a.RW * WB;
   BT_REQUIRE(smem_bytes <= SMEM_LIMIT, BT_ERR_UNSUPPORTED, "tensor-core forward: shared memory plan %d exceeds %d", smem_bytes, SMEM_LIMIT);
