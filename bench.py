@@ -433,25 +433,49 @@ def run_b200(args):
     # predictive mean / variance back to the host
     prefetch = bt.HostBatchPrefetcher(dev, dtype=torch.bfloat16, memory_format=torch.channels_last, shard=world > 1)
 
+    # results come back the way the batches go in: asynchronously, into two pairs of pinned host buffers, on a side stream
+    # that waits for the step's last kernel -- the host never blocks the next step's launches on a read-back (a blocking
+    # .cpu() per step left the GPUs idle for the host round trip: 8 % of the step at 8 GPUs).  A pair is reused two steps
+    # later, after its event; the timed region ends with a device synchronize, so every read-back has landed inside it.
+    d2h_stream = torch.cuda.Stream(dev)
+    host_out = []
+    turn = [0]
+
     def step_e2e():
         if prefetch._pending is None:          # first step of a timed run: nothing to overlap with, the copy is exposed
             prefetch.submit(x_host)
         xd = prefetch.take()
         res = predictor(xd)
         prefetch.submit(x_host)                # next step's batch (same synthetic images): H2D on the side stream
-        return res.mean.cpu(), res.var.cpu()
+        if not host_out:
+            for _ in range(2):
+                host_out.append((torch.empty(res.mean.shape, dtype=res.mean.dtype).pin_memory(),
+                                 torch.empty(res.var.shape, dtype=res.var.dtype).pin_memory(), torch.cuda.Event()))
+        m, v, ev = host_out[turn[0] & 1]
+        turn[0] += 1
+        ev.synchronize()
+        d2h_stream.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(d2h_stream):
+            m.copy_(res.mean, non_blocking=True)
+            v.copy_(res.var, non_blocking=True)
+            ev.record(d2h_stream)
+        res.mean.record_stream(d2h_stream)
+        res.var.record_stream(d2h_stream)
+        return m, v
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(fn, steps):
+    def timed(fn, steps, tail=None):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         e0.record()
         for _ in range(steps):
             out = fn()
+        if tail is not None:
+            tail()                 # e.g. the last read-back on the side stream joins the timed stream before the closing event
         e1.record()
         barrier()
         ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -495,7 +519,7 @@ def run_b200(args):
     for _ in range(max(args.warmup, 3)):
         step_e2e()
     prefetch.take()
-    ms_e2e, _ = timed(step_e2e, args.steps)
+    ms_e2e, _ = timed(step_e2e, args.steps, tail=lambda: torch.cuda.current_stream(dev).wait_stream(d2h_stream))
     prefetch.take()                            # the batch submitted by the last step (one copy more than steps timed)
 
     if rank == 0:
