@@ -471,7 +471,9 @@ __global__ void __launch_bounds__(256) tc2_patch_tab_kernel(const TX* __restrict
 // One thread per 16-byte chunk (eight weights = one Philox block); blockIdx.y = sample.
 __global__ void __launch_bounds__(256) tc2_presample_kernel(const uint4* __restrict__ mu_p, const uint4* __restrict__ sig_p,
                                                             uint4* __restrict__ wq, int64_t chunks, uint64_t seed, uint32_t sample_id,
-                                                            uint32_t layer_id, int pdl) {
+                                                            uint32_t layer_id, int pdl, const float* __restrict__ eps_p, int flip) {
+  // eps_p: the draws come from a packed fp32 tensor in the weights' order (backward data: tc2_pack_dgrad_kernel regenerated
+  // them at the FORWARD stream positions); flip: Flipout keeps mu apart, only delta = bf16(sigma * eps) is materialised.
   // Programmatic dependent launch (pdl != 0): this grid may start while the previous kernel of the stream drains.
   // pdl = 1: the packed parameters were written by that kernel -- wait first.  pdl = 2 (frozen layer: the packed
   // parameters are old, nothing here depends on the previous kernel): sample during its tail and wait at the END, so
@@ -482,9 +484,16 @@ __global__ void __launch_bounds__(256) tc2_presample_kernel(const uint4* __restr
   const BtRngKey rk = bt_rng_key(seed, sample_id + (uint32_t)s, layer_id, BT_KIND_EPS_W);
   uint4* __restrict__ dst = wq + (int64_t)s * chunks;
   for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < chunks; c += (int64_t)gridDim.x * blockDim.x) {
-    const uint4 mu = __ldg(mu_p + c), sg = __ldg(sig_p + c);
+    const uint4 sg = __ldg(sig_p + c);
+    uint4 mu = make_uint4(0u, 0u, 0u, 0u);
+    if (!flip) mu = __ldg(mu_p + c);
     float z[8];
-    bt_normal8((uint64_t)c, rk, z);
+    if (eps_p) {
+      const float4 e0 = __ldg(reinterpret_cast<const float4*>(eps_p) + 2 * c), e1 = __ldg(reinterpret_cast<const float4*>(eps_p) + 2 * c + 1);
+      z[0] = e0.x; z[1] = e0.y; z[2] = e0.z; z[3] = e0.w; z[4] = e1.x; z[5] = e1.y; z[6] = e1.z; z[7] = e1.w;
+    } else {
+      bt_normal8((uint64_t)c, rk, z);
+    }
     uint4 w;
     w.x = fma_bf16x2(sg.x, pack_bf16(z[0], z[1]), mu.x);
     w.y = fma_bf16x2(sg.y, pack_bf16(z[2], z[3]), mu.y);
@@ -685,6 +694,7 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     prefetch_tmap(&tm_a); prefetch_tmap(&tm_out);
     if (a.res_bufs) prefetch_tmap(&tm_res);
     if ((FLIP && a.a2_tma) || a.w_pre) prefetch_tmap(&tm_a2);
+    if (FLIP && a.w_pre) prefetch_tmap(&tm_res);
   }
   if (warp == WARP_MMA) tmem_alloc(smem_u32(&ctrl->tmem_base), 512);
   tc_fence_before();
@@ -1414,8 +1424,13 @@ tc2_fwd_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
               if (PROF && (a.debug & 128)) {
                 mbar_arrive(bar);
               } else {
-                mbar_expect_tx(bar, (uint32_t)W_SUB);
-                tma_load_3d(w_base + (uint32_t)(wslot_r * W_SLOT), &tm_a2, bar, kb * BKE, nb * BN, s);
+                mbar_expect_tx(bar, (uint32_t)W_SLOT);
+                if constexpr (FLIP) {   // the mu sub-tile straight from the packed parameters (2-d map behind tm_res), then delta
+                  tma_load_2d(w_base + (uint32_t)(wslot_r * W_SLOT), &tm_res, bar, kb * BKE, nb * BN);
+                  tma_load_3d(w_base + (uint32_t)(wslot_r * W_SLOT + W_SUB), &tm_a2, bar, kb * BKE, nb * BN, s);
+                } else {
+                  tma_load_3d(w_base + (uint32_t)(wslot_r * W_SLOT), &tm_a2, bar, kb * BKE, nb * BN, s);
+                }
               }
               if (++wslot_r == a.RW) { wslot_r = 0; wphase ^= 1u; }
             }
@@ -1766,7 +1781,7 @@ static int64_t patch_bytes(const bt_geom* g, int64_t rows_per_s, int64_t Kp) {
 // caller allocates always covers the launch's carve-up.
 static int64_t wpre_bytes(const bt_geom* g, const Plan& pl, bool flipout) {
   const int64_t K = pl.mode == A_PATCH ? pl.Kp : pl.K;
-  if (flipout || g->x_dtype != BT_BF16 || pl.es != 2 || (K & 7)) return 0;
+  if ((flipout && pl.mode == A_PATCH) || g->x_dtype != BT_BF16 || pl.es != 2 || (K & 7)) return 0;
   const int64_t b = (int64_t)g->n_samples * g->c_out * K * 2;
   return b <= (1ll << 31) ? ((b + 255) / 256) * 256 : 0;
 }
@@ -2200,7 +2215,9 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   // patch matrix of the stem is read ONCE instead of once per sample pair (7.8 GB -> 0.5 GB) -- and it is still slower:
   // stem at 32 samples 2.19 -> 2.56 ms, at 4 samples 0.57 -> 0.62 (profiles/r2_exp17_stem_sample_fastest.txt; the 48 KB of W
   // per two-tile item cost the L2 -> SM fabric what the A tiles did).  BT_TC2_SINNER=1 selects it; bit-identical either way.
-  const bool wpre_static = wpre_bytes(g, pl, flipout) > 0 && wq_fits && !opt.dgrad && !p->eps_w && !a.tf32 &&
+  // (backward data draws nothing: its eps come packed from tc2_pack_dgrad_kernel; Flipout materialises delta = sigma * eps only)
+  const bool wpre_static = wpre_bytes(g, pl, flipout) > 0 && wq_fits && (opt.dgrad || !p->eps_w) && !a.tf32 && !(flipout && p->residual) &&
+                           (!(flipout || opt.dgrad) || env_int("BT_TC2_WPRE_TRAIN", 1) != 0) &&
                            a.num_mt >= env_int("BT_TC2_WPRE_MIN", 16) && env_int("BT_TC2_WPRE", 1) != 0;
   const int sinner_env = env_int("BT_TC2_SINNER", 0);
   const bool s_inner = x_shared && !flipout && a.nkb <= MAX_NA / 2 && sinner_env == 1;
@@ -2213,7 +2230,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
   // 1.11 -> 0.93 ms, 3x3 256 @14 1.03 -> 0.90, 256<-1024 @14 0.69 -> 0.65, 512<-256 /2 1.42 -> 1.25; at 7x7 (49 m-tiles per
   // sample) the W stream costs more than the sampling it replaces (512<-2048: 0.69 -> 0.80), hence the m-tile floor.
   {
-    const bool wpre_ok = wpre_static && !a.epi8;
+    const bool wpre_ok = wpre_static && !a.epi8 && (a.Kt == a.K || !(opt.dgrad || flipout));   // (the padded-K pass draws from Philox only)
     // a stationary panel walks (sample, n-block, m-group): with two or more n-blocks every A tile comes from HBM once per
     // n-block.  Streaming pre-sampled W with the n-block innermost reads it once (256<-512 at 28x28: 3.3 GB of A).
     if (wpre_ok && a.stationary && a.NB >= 2 && a.nkb >= 2 && force_stat != 1) a.stationary = 0;
@@ -2340,7 +2357,7 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
                                       a.N, a.K, a.Kt, (uint64_t)p->seed, (uint32_t)p->sample_id, (uint32_t)p->layer_id, ppdl));
       else
       BT_CUDA_OK(cudaLaunchKernelEx(&cfg, tc2_presample_kernel, reinterpret_cast<const uint4*>(mu_p), reinterpret_cast<const uint4*>(sig_p), wq, chunks,
-                                    (uint64_t)p->seed, (uint32_t)p->sample_id, (uint32_t)p->layer_id, ppdl));
+                                    (uint64_t)p->seed, (uint32_t)p->sample_id, (uint32_t)p->layer_id, ppdl, (const float*)eps_p, flipout ? 1 : 0));
     }
     BT_LAUNCH_OK("tc2_presample_kernel");
     // a stacked sample pair (spn = 2) reads rows [0, 64) of sample 2 s and of sample 2 s + 1 as ONE 128-row block: the same memory
@@ -2351,6 +2368,15 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
     const CUresult r = drv.tiled(&tm_a2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, wq, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     BT_REQUIRE(r == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeTiled(pre-sampled W) failed with %d", (int)r);
+    if (flipout) {   // the mu sub-tiles come from the packed parameters themselves ([N][K] bf16); no residual in this mode: tm_res is free
+      const cuuint64_t gdim2[2] = {(cuuint64_t)a.K, (cuuint64_t)a.N};
+      const cuuint64_t gstr2[1] = {(cuuint64_t)a.K * 2};
+      const cuuint32_t box2[2] = {(cuuint32_t)BK, (cuuint32_t)BN};
+      const cuuint32_t estr2[2] = {1, 1};
+      const CUresult r2 = drv.tiled(&tm_res, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, mu_p, gdim2, gstr2, box2, estr2, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      BT_REQUIRE(r2 == CUDA_SUCCESS, BT_ERR_CUDA, "cuTensorMapEncodeTiled(packed mu) failed with %d", (int)r2);
+    }
   }
   if (env_int("BT_TC2_LOG", 0))
     fprintf(stderr, "tc2: wpre=%d flip=%d mode=%d S=%d Ms=%d N=%d K=%d(%d) BN=%d stat=%d MT=%d NSETS=%d nkb=%d NA=%dx%d RW=%d NB=%d num_mg=%d items=%lld grid=%d smem=%d stage=%d res=%d CL=%d order=%d keep=%d spn=%d epi8=%d tf32=%d pdl=%d\n",
