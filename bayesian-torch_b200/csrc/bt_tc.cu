@@ -2341,7 +2341,9 @@ static int tc2_run(const bt_geom* g, const bt_layer_params* p, const void* x, vo
     const int64_t capx = ((int64_t)sms * 8 + S - 1) / S;
     if (bx > capx) bx = capx < 1 ? 1 : capx;
     {
-      const int ppdl = !a.pdl ? 0 : (packed_frozen && env_int("BT_TC2_WPRE_PDL", 2) == 2 ? 2 : 1);
+      // Early start (2) is opt-in: it measured within noise, and it is only safe when the kernel just before this one in the
+      // stream does not read this layer's pre-sampled copy (the same frozen layer called back to back would).
+      const int ppdl = !a.pdl ? 0 : (packed_frozen && env_int("BT_TC2_WPRE_PDL", 1) == 2 ? 2 : 1);
       cudaLaunchConfig_t cfg;
       memset(&cfg, 0, sizeof(cfg));
       cfg.gridDim = dim3((unsigned)bx, (unsigned)S);
