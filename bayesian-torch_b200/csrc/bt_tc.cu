@@ -1,29 +1,32 @@
-// TMA-fed tcgen05 / TMEM implicit GEMM with the weight tile SAMPLED IN SHARED MEMORY (sm_100a).
+// TMA-fed tcgen05 / TMEM implicit GEMM over sampled weights (sm_100a).
 //
-//   out[s][m][n] = sum_k A(x_s)[m][k] * bf16(mu[n][k] + sigma[n][k] * eps_s[n][k]) + (mu_b + sigma_b * eps_b)[n]
+//   out[s][m][n] = act( sum_k A(x_s)[m][k] * bf16(mu'[n][k] + sigma'[n][k] * eps_s[n][k]) + shift_s[n] + residual[s][m][n] )
 //
-// replaces, for bf16 channels-last activations, the reference's per-call sequence
+// replaces, for bf16 channels-last (or fp32: tf32 instantiation) activations, the reference's per-call sequence
 // log1p(exp(rho)) -> normal_() -> sigma*eps -> mu+tmp -> F.linear / F.conv2d
-// (linear_variational.py:163-181, conv_variational.py:366-385).  The sampled weight never
-// exists in global memory.
+// (linear_variational.py:163-181, conv_variational.py:366-385), Flipout's dual contraction
+// (linear_flipout.py:145-197, conv_flipout.py:370-439) and, run on grad_out, their backward data.
 //
-// Persistent warp-specialised CTA, one per SM:
-//   warps 0-3   epilogue : tcgen05.ld -> +sampled bias -> bf16/f32 -> swizzled smem -> TMA store
-//   warp  4     A loader : ONE thread issues TMA loads; convolutions use the im2col tensor-map
-//                          mode (cuTensorMapEncodeIm2col), so the 128-pixel x 64-channel tile of one
-//                          filter tap lands in the 128B-swizzled K-major layout tcgen05.mma reads,
-//                          padding zero-filled by the hardware; Linear uses a tiled 2-d map
-//   warps 5-6   MMA      : two issuer warps (tile t of an m-group -> issuer t % 2), each a
-//                          warp-uniform loop whose elected lane issues tcgen05.mma (M=128, N=BN,
-//                          K=16) into TMEM accumulators.  Measured on B200 (tools/ubench/pipe2.cu):
-//                          one issuing thread costs ~340 cycles per 4-MMA ring slot against 256
-//                          cycles of tensor work at N=128, two issuers overlap completely
-//   warps 8-23  W producers: mu + sigma * eps -> bf16 -> swizzled smem, eps from in-register
-//                          Philox4x32-10 (8 normals per call) or the caller's tensor
-// mbarrier pipelines: A ring (TMA complete_tx / tcgen05.commit), W ring or stationary panel,
-// accumulator sets in TMEM.  The sampling cost is amortised over the batch either by keeping
-// the whole [BN x K] sampled panel in shared memory (stationary) or by keeping MT accumulators
-// resident in TMEM so one generated k-block feeds MT m-tiles (streaming).
+// Where the sampled weight lives:
+//   stationary   the [BN x K] panel of a (sample, n-block) is sampled into shared memory once per CTA and kept while
+//                the CTA walks m-groups: the weight never exists in global memory
+//   streamed     long reductions: the S sampled copies of a call are written once by tc2_presample_kernel (same
+//                Philox positions, same bf16 arithmetic) and their k-blocks arrive by TMA (a.w_pre); the fused variant
+//                (16 producer warps sample every k-block of every item, CTA pairs share the work) stays for tiny calls
+//
+// Persistent warp-specialised CTA of 768 threads, one per SM (warp ids are issue priorities):
+//   warps 0-15   W producers (fused sampling; one thread becomes the W loader when the weights are pre-sampled;
+//                FLIP / EPI8 instantiations: warps 12-15 are A flippers / a second epilogue group)
+//   warps 16-19  epilogue : tcgen05.ld -> (residual) -> ReLU -> bf16/f32 -> swizzled smem -> TMA store
+//   warp  20     A loader : ONE thread issues TMA loads; convolutions use the im2col tensor-map mode
+//                (cuTensorMapEncodeIm2col): the 128-pixel x 64-channel tile of one filter tap lands in the
+//                128B-swizzled K-major layout tcgen05.mma reads, padding zero-filled by the hardware
+//   warps 21-22  MMA      : two issuer warps (tile t of an m-group -> issuer t % 2), each a warp-uniform loop whose
+//                elected lane issues tcgen05.mma (M = 128, N = BN in {64, 128, 256}, K = 16) into TMEM accumulators
+//   warp  23     residual loader, or the second A loader when the call has no residual input
+// mbarrier pipelines: A rings (TMA complete_tx / tcgen05.commit), W ring or stationary panel, accumulator tiles in
+// TMEM (512 columns), residual ring.  Items (sample, n-block, m-group) are dealt round-robin to the CTAs when the
+// n-block is the fastest index, so the passes over one group of A tiles run on neighbouring SMs at the same time.
 #include <cuda.h>
 #include <stdlib.h>
 #include <string.h>
