@@ -144,3 +144,39 @@ def test_linear_backward_tc_matches_simt(kind, k, n, rows, cuda_device):
     dx_o, gp_o = oracle_grads(layer, x, go, kind, 6, 7)
     check_vs_oracle(dx_t, gp_t, dx_o, gp_o, dx_on_tc=n % 64 == 0)
 
+
+
+@pytest.mark.parametrize("kind,cin,cout,k,pad,batch,hw", [
+    ("flipout", 128, 128, 3, 1, 32, 14),    # 49 m-tiles, K = 1152: streamed, Flipout delta pre-sampled forward and backward
+    ("reparam", 256, 256, 3, 1, 16, 14),    # backward data through the pre-sampled pass (eps from the packed tensor)
+    ("flipout", 512, 256, 1, 0, 24, 14),    # 1x1 Flipout, two n-blocks
+])
+def test_training_path_presampled_weights_are_bit_identical(kind, cin, cout, k, pad, batch, hw, cuda_device, monkeypatch):
+    """Flipout forward and the backward-data run take the pre-sampled pass too (Flipout: delta = bf16(sigma * eps) only,
+    mu sub-tiles by TMA from the packed parameters; dgrad: eps from the packed tensor): outputs and the input gradient are
+    the bits of the fused-sampling schedule (BT_TC2_WPRE_TRAIN=0)."""
+    torch.manual_seed(cin + cout + k)
+    bt.manual_seed(9)
+    layer = _layer(kind, cin, cout, k, 1, pad, cuda_device)
+    x = torch.randn(batch, cin, hw, hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    go = torch.randn(batch, cout, hw, hw, device=cuda_device).bfloat16().contiguous(memory_format=torch.channels_last)
+    res = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("BT_TC2_WPRE_TRAIN", flag)
+        monkeypatch.setenv("BT_TC2_WPRE", flag)          # (the Reparameterization forward of the second case as well)
+        layer.path, layer.sample_mode = "tc", "philox"
+        for p in layer.parameters():
+            p.grad = None
+        xi = x.clone().requires_grad_(True)
+        with bt.mc_sample(3):
+            out, kl = layer(xi)
+        (out.float() * go.float()).sum().backward()
+        torch.cuda.synchronize()
+        res[flag] = (out.detach().clone(), xi.grad.clone(), [p.grad.clone() for p in layer.parameters()])
+    assert float(res["0"][0].float().abs().max()) > 0
+    assert torch.equal(res["1"][0], res["0"][0])
+    assert torch.equal(res["1"][1], res["0"][1])
+    # (the weight-gradient kernel is not touched by the switch; its split-pixel fp32 atomics make its sums run-to-run
+    # reproducible to rounding only)
+    for a, b in zip(res["1"][2], res["0"][2]):
+        torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5 * float(b.abs().max()))
