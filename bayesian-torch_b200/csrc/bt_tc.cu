@@ -2984,7 +2984,10 @@ int bt_tc_wgrad(const bt_geom* g, const bt_layer_params* p, const void* x, const
   a.m_tiles = (a.U + 1) / 2;
   const int sms = bt_num_sms();
   const int64_t tiles = (int64_t)a.n_tiles * a.m_tiles;
-  int64_t splits = (2 * sms + tiles - 1) / tiles;   // about two CTAs' worth of work per SM, so the tail is short
+  // About two CTAs' worth of work per SM, and never ONE CTA more than whole waves (one CTA per SM: 133 KB of shared memory):
+  // rounding the split count up gave 9 tiles x 33 = 297 CTAs = two waves and a third with a single CTA
+  // (profiles/r2_wgrad_wgrad_ncu_metrics.txt: SMs active 63 % of the kernel).
+  int64_t splits = env_int("BT_WG_ROUND_UP", 0) ? (2 * sms + tiles - 1) / tiles : (2 * sms) / tiles;
   if (splits > a.steps_total) splits = a.steps_total;
   if (splits < 1) splits = 1;
   if (env_int("BT_WG_SPLITS", 0) > 0) splits = env_int("BT_WG_SPLITS", 0) < a.steps_total ? env_int("BT_WG_SPLITS", 0) : a.steps_total;
