@@ -2984,10 +2984,12 @@ int bt_tc_wgrad(const bt_geom* g, const bt_layer_params* p, const void* x, const
   a.m_tiles = (a.U + 1) / 2;
   const int sms = bt_num_sms();
   const int64_t tiles = (int64_t)a.n_tiles * a.m_tiles;
-  // About two CTAs' worth of work per SM, and never ONE CTA more than whole waves (one CTA per SM: 133 KB of shared memory):
-  // rounding the split count up gave 9 tiles x 33 = 297 CTAs = two waves and a third with a single CTA
-  // (profiles/r2_wgrad_wgrad_ncu_metrics.txt: SMs active 63 % of the kernel).
-  int64_t splits = env_int("BT_WG_ROUND_UP", 0) ? (2 * sms + tiles - 1) / tiles : (2 * sms) / tiles;
+  // ONE wave of CTAs (one CTA per SM: 133 KB of shared memory), never a CTA more: the first version aimed at two CTAs' worth of
+  // work per SM and rounded the split count up -- 9 tiles x 33 = 297 CTAs = two waves and a third with a single CTA (SMs active
+  // 63 % of the kernel).  Whole waves: ResNet-18 Flipout training step 19.23 -> 18.31 ms; one wave instead of two (half the
+  // fp32 atomics into the packed accumulators): 17.93 (profiles/r2_exp28_wgrad_waves.txt).
+  const int waves = env_int("BT_WG_WAVES", 1);
+  int64_t splits = env_int("BT_WG_ROUND_UP", 0) ? (waves * sms + tiles - 1) / tiles : (waves * sms) / tiles;
   if (splits > a.steps_total) splits = a.steps_total;
   if (splits < 1) splits = 1;
   if (env_int("BT_WG_SPLITS", 0) > 0) splits = env_int("BT_WG_SPLITS", 0) < a.steps_total ? env_int("BT_WG_SPLITS", 0) : a.steps_total;
@@ -2995,6 +2997,7 @@ int bt_tc_wgrad(const bt_geom* g, const bt_layer_params* p, const void* x, const
   const int stage_bytes = (2 * WG_UNIT + (a.NT / 64) * WG_UNIT) * (flipout ? 2 : 1);
   a.stages = (SMEM_LIMIT - 2048) / stage_bytes;
   if (a.stages > 4) a.stages = 4;
+  if (env_int("BT_WG_STAGES", 0) >= 2 && env_int("BT_WG_STAGES", 0) < a.stages) a.stages = env_int("BT_WG_STAGES", 0);
   BT_REQUIRE(a.stages >= 2, BT_ERR_UNSUPPORTED, "tensor-core wgrad: no room for two pipeline stages");
   const int smem_bytes = 2048 + a.stages * stage_bytes;
   const int64_t grid = tiles * splits;
